@@ -1,0 +1,228 @@
+/* i64b.h — C ABI of the B200-native token-routed MoE FFN block for vllm-i64.
+ *
+ * Drop-in boundary: every entry point takes plain device pointers, sizes and an
+ * explicit CUDA stream; returns 0 or a negative I64B_ERR_* code (text via
+ * i64b_last_error(), thread-local); never throws, never allocates device memory,
+ * never synchronises, never touches the legacy default stream unless the caller
+ * passes stream 0.  All outputs and workspaces are caller-allocated (query sizes
+ * with the *_bytes functions).  Each function cites the reference interface it
+ * replaces (paths relative to the Complexity-ML/vllm-i64 checkout).
+ *
+ * The reference's own native conventions this improves on: csrc/i64_router.cu:200-268
+ * and csrc/i64_expert_dispatch.cu:144-233 (extern "C" entry points that throw,
+ * cudaMallocAsync temporaries and a D2H sync per call).
+ */
+#ifndef I64B_H_
+#define I64B_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* i64b_stream_t; /* cudaStream_t */
+
+enum {
+    I64B_OK = 0,
+    I64B_ERR_ARG = -1,       /* bad argument / unsupported shape */
+    I64B_ERR_CUDA = -2,      /* CUDA runtime or driver error */
+    I64B_ERR_WORKSPACE = -3, /* workspace too small */
+    I64B_ERR_STATE = -4      /* layer not ready (weights / table not loaded) */
+};
+
+enum { I64B_BF16 = 0, I64B_F32 = 1, I64B_F16 = 2 };
+enum { I64B_MODE_BF16 = 0, I64B_MODE_W8A8 = 1 };
+
+const char* i64b_last_error(void);
+int i64b_version(void);
+/* number of kernels launched by this thread through the library since the last reset */
+int64_t i64b_launch_count(void);
+void i64b_launch_count_reset(void);
+/* host pointer to the 2049-entry Q7 SiLU table (round(silu(i/128)*128), i in [-1024,1024]) used by the W8A8
+ * SwiGLU epilogue; identical to _SILU_LUT of layers/integer_activations.py:28-36. */
+const int16_t* i64b_silu_lut_q7(void);
+
+/* ---------------------------------------------------------------------------
+ * Routing  (a1, a6)
+ * ------------------------------------------------------------------------- */
+
+/* expert = token_id & (E-1), int32.  Replaces route_tokens (csrc/i64_ops_binding.cu:32-65),
+ * i64_route_tokens_kernel (csrc/i64_router.cu:51-70), kernels/i64_ops.py:17-34. */
+int i64b_route_modulo(const int64_t* token_ids, int32_t* expert_ids, int64_t n, int num_experts,
+                      i64b_stream_t stream);
+
+/* Pack the checkpoint's topk_token_to_expert [K,V] int64 table to uint8 (load time).
+ * Source of the table: core/loader.py:374-407. */
+int i64b_pack_table(const int64_t* table_i64, uint8_t* table_u8, int top_k, int vocab, int num_experts,
+                    i64b_stream_t stream);
+
+/* routes[k,t] = table[k, clamp(token_ids[t],0,V-1)]; token_ids == NULL -> (0+k)%E.
+ * Replaces TokenRoutedMLP.route (layers/token_routed_mlp.py:113-130).  routes is int64 [K,N]. */
+int i64b_route_table(const int64_t* token_ids, const uint8_t* table_u8, int64_t* routes, int64_t n, int vocab,
+                     int top_k, int num_experts, i64b_stream_t stream);
+
+/* ---------------------------------------------------------------------------
+ * Dispatch plan / scatter / gather  (a7, a8)
+ * ------------------------------------------------------------------------- */
+
+size_t i64b_plan_workspace_bytes(int64_t n, int top_k, int num_experts);
+
+/* Deterministic (stable-by-token-index) dispatch plan for K routes at once.
+ *   expert_ids      int32 [K,N] (device)
+ *   scatter_indices int32 [K,N] per-route destination row (== stable argsort inverse), nullable
+ *   counts/offsets  int32 [K,E] per-route bincount and exclusive scan, nullable
+ *   dest_row        int32 [K,N] row in the merged expert-major layout, nullable
+ *   group_rows      int32 [E]   rows per expert in the merged layout, nullable
+ * Replaces scatter_by_expert's argsort/bincount/cumsum (csrc/i64_ops_binding.cu:179-204),
+ * i64_prefix_sum_kernel + atomic slot claiming (csrc/i64_router.cu:94-134,171-184). */
+int i64b_dispatch_plan(const int32_t* expert_ids, int top_k, int64_t n, int num_experts,
+                       int32_t* scatter_indices, int32_t* counts, int32_t* offsets, int32_t* dest_row,
+                       int32_t* group_rows, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+
+/* out[dest[t], :] = x[t, :] for row_bytes-wide rows (row_bytes % 16 == 0).
+ * Replaces i64_scatter_kernel (csrc/i64_router.cu:94-134), atomic_scatter / fused_route_scatter row copies. */
+int i64b_scatter_rows(const void* x, const int32_t* dest, void* out, int64_t n, int64_t row_bytes,
+                      i64b_stream_t stream);
+
+/* out[t, :] = src[idx[t], :].  Replaces i64_gather_kernel (csrc/i64_router.cu:150-165),
+ * gather_by_expert (csrc/i64_ops_binding.cu:207-209). */
+int i64b_gather_rows(const void* src, const int32_t* idx, void* out, int64_t n, int64_t row_bytes,
+                     i64b_stream_t stream);
+
+/* ---------------------------------------------------------------------------
+ * Elementwise / quantisation ops  (a9, a12)
+ * ------------------------------------------------------------------------- */
+
+/* out[n,i] = silu(gate_up[n,i]) * gate_up[n,inter+i]; dtype in {BF16,F32,F16}.
+ * Replaces silu_hadamard (csrc/i64_ops_binding.cu:74-172), i64_silu_hadamard_kernel
+ * (csrc/i64_expert_dispatch.cu:100-122), kernels/triton/I64_fused_silu_mul.py. */
+int i64b_silu_hadamard(const void* gate_up, void* out, int64_t n, int inter, int dtype, i64b_stream_t stream);
+
+/* Per-row symmetric INT8: s = max(absmax,1e-8)/127, q = clamp(rint(x/s)).  dtype of x in {BF16,F32,F16};
+ * arithmetic is IEEE fp32 (bit-exact with core/quantization.py:80-116).
+ * Replaces I64_quantize_int8 / I64_quantize_perchannel_int8 (csrc/I64_quantize.cu:41-92,118-166,173-243). */
+int i64b_quantize_rows_int8(const void* x, int dtype, int8_t* q, float* scale, int64_t rows, int64_t cols,
+                            i64b_stream_t stream);
+/* out_f32[r,c] = q[r,c] * scale[r].  Replaces I64_dequantize_int8 (csrc/I64_quantize.cu:99-111). */
+int i64b_dequantize_int8(const int8_t* q, const float* scale, float* out, int64_t rows, int64_t cols,
+                         i64b_stream_t stream);
+
+/* ---------------------------------------------------------------------------
+ * The block as one object  (a2, a3, a4, a5, a12)
+ * ------------------------------------------------------------------------- */
+
+typedef struct {
+    int32_t hidden_size;        /* H, multiple of 64 (128 in W8A8 mode) */
+    int32_t num_experts;        /* E in [1,64] (0 = dense FFN: only the "shared" SwiGLU runs) */
+    int32_t expert_inter;       /* I_e per expert, multiple of 16 */
+    int32_t shared_inter;       /* S, 0 = no shared expert */
+    int32_t vocab_size;         /* V */
+    int32_t top_k;              /* K in [1,4] */
+    int32_t mode;               /* I64B_MODE_BF16 | I64B_MODE_W8A8 */
+    int32_t reserved;
+    float route_weight[4];      /* w0 = primary, others (1-w0)/(K-1)  (layers/token_routed_mlp.py:53-58,158) */
+    float routed_scale;         /* routed_output_scale or routed_output_gate (:174-185) */
+    float shared_scale;         /* shared_output_scale or shared_output_gate */
+} i64b_moe_config;
+
+typedef struct i64b_layer i64b_layer;
+
+int i64b_moe_create(const i64b_moe_config* cfg, i64b_layer** out);
+void i64b_moe_destroy(i64b_layer* layer);
+int i64b_moe_set_scales(i64b_layer* layer, const float* route_weight, int top_k, float routed_scale,
+                        float shared_scale);
+
+/* bytes of device memory the caller must provide for the packed (tcgen05-friendly, K-major) weights */
+size_t i64b_moe_packed_bytes(const i64b_layer* layer);
+
+/* Repack reference-layout bf16 weights (layers/token_routed_mlp.py:66-82): gate,up [E,H,I_e];
+ * down [E,I_e,H]; shared_gate,shared_up [S,H]; shared_down [H,S] (nn.Linear (out,in)), into `packed`.
+ * Replaces load_full_weights / fuse_shared_gate_up / materialize_expert_linears (:189-258).
+ * Shared pointers may be NULL when shared_inter == 0; expert pointers NULL when num_experts == 0. */
+int i64b_moe_load_bf16(i64b_layer* layer, const void* gate, const void* up, const void* down,
+                       const void* shared_gate, const void* shared_up, const void* shared_down, void* packed,
+                       i64b_stream_t stream);
+
+/* W8A8: weights already quantised per out-row (quantize_int8, core/quantization.py:80-91) in the
+ * materialised (out,in) form: w13 [E,2I_e,H] int8 (+[E,2I_e] fp32 scales), w2 [E,H,I_e] (+[E,H]);
+ * shared sh13 [2S,H], sh2 [H,S].  Copied into `packed`. */
+int i64b_moe_load_w8a8(i64b_layer* layer, const int8_t* w13_q, const float* w13_s, const int8_t* w2_q,
+                       const float* w2_s, const int8_t* sh13_q, const float* sh13_s, const int8_t* sh2_q,
+                       const float* sh2_s, void* packed, i64b_stream_t stream);
+
+/* uint8 routing table [K,V] (device, from i64b_pack_table); kept by pointer. */
+int i64b_moe_set_table(i64b_layer* layer, const uint8_t* table_u8);
+
+size_t i64b_moe_workspace_bytes(const i64b_layer* layer, int64_t max_tokens);
+
+/* out[N,H] = routed_scale * sum_k w_k * expert_{route_k(t)}(x[t]) + shared_scale * shared(x[t]).
+ * x: bf16 [N,H] device; token_ids: int64 [N] device or NULL; out: out_dtype in {BF16,F32}.
+ * Replaces TokenRoutedMLP.forward (layers/token_routed_mlp.py:154-187) and, with num_experts == 0,
+ * DenseSwiGLUMLP.forward / DenseMLP.forward (models/complexity_deep/model.py:250-255, layers/dense_mlp.py:46-97). */
+int i64b_moe_forward(i64b_layer* layer, const void* x, const int64_t* token_ids, void* out, int out_dtype,
+                     int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+
+/* Same block with the routes supplied by the caller: routes int32 [K,N] expert ids (device).  This is the
+ * form the reference's kernels package uses — fused_token_routed_forward(x, gate_up, down, expert_ids, ...)
+ * (kernels/fused_experts.py:29-150), i64_expert_forward / i64_full_pipeline (kernels/i64_ops.py:100-193),
+ * i64_expert_dispatch (csrc/i64_expert_dispatch.cu:144-233). */
+int i64b_moe_forward_routed(i64b_layer* layer, const void* x, const int32_t* routes, int top_k,
+                            const float* route_weight, float routed_scale, float shared_scale, int use_shared,
+                            void* out, int out_dtype, int64_t n, void* workspace, size_t workspace_bytes,
+                            i64b_stream_t stream);
+size_t i64b_moe_workspace_bytes_routed(const i64b_layer* layer, int64_t max_tokens, int top_k);
+
+/* stream-ordered device-to-device copy (lets a ctypes host read the debug taps without a torch extension) */
+int i64b_copy_device(void* dst, const void* src, size_t bytes, i64b_stream_t stream);
+
+/* Same call with HOST buffers (pinned or pageable): H2D of x/token_ids, forward, D2H of out, all
+ * enqueued on `stream`; x_dev/ids_dev/out_dev are caller-provided device staging buffers. */
+int i64b_moe_forward_host(i64b_layer* layer, const void* x_host, const int64_t* token_ids_host, void* out_host,
+                          int out_dtype, int64_t n, void* x_dev, int64_t* ids_dev, void* out_dev,
+                          void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+
+/* Debug taps into the workspace of the LAST forward on this layer (device pointers, valid until the
+ * next forward): lets the parity tests compare dispatch plan, INT8 activations and INT32 accumulators
+ * bit-for-bit.  `what` is one of the I64B_TAP_* ids; returns NULL if not applicable. */
+enum {
+    I64B_TAP_ROUTES = 0,      /* int32 [K,N] expert ids */
+    I64B_TAP_DEST_ROW = 1,    /* int32 [K,N] merged-layout row */
+    I64B_TAP_SCATTER_IDX = 2, /* int32 [K,N] per-route row */
+    I64B_TAP_COUNTS = 3,      /* int32 [K,E] */
+    I64B_TAP_OFFSETS = 4,     /* int32 [K,E] */
+    I64B_TAP_XS = 5,          /* dispatched activations [N*K + N, H] (bf16 or int8) */
+    I64B_TAP_XS_SCALE = 6,    /* fp32 [N*K + N] (W8A8) */
+    I64B_TAP_INTER_R = 7,     /* routed intermediate [N*K, I_e] (bf16 or int8) */
+    I64B_TAP_INTER_S = 8,     /* shared intermediate [N, S] */
+    I64B_TAP_INTER_SCALE_R = 9,
+    I64B_TAP_INTER_SCALE_S = 10,
+    I64B_TAP_Q14_R = 11,      /* int32 [N*K, I_e] (W8A8) */
+    I64B_TAP_Q14_S = 12,      /* int32 [N, S] */
+    I64B_TAP_Y = 13,          /* fp32 [N*K + N, H] per-assignment expert outputs */
+    I64B_TAP_GROUP_ROWS = 14  /* int32 [E] */
+};
+void* i64b_moe_tap(i64b_layer* layer, int what);
+
+/* ---------------------------------------------------------------------------
+ * Stand-alone W8A8 / weight-only GEMM ops  (a12, a13)
+ * ------------------------------------------------------------------------- */
+
+/* out_f32[m,n] = (x_q[m,:] . w_q[n,:]) * (x_scale[m] * w_scale[n])  — tcgen05 kind::i8, exact INT32.
+ * Replaces int8_linear_native's torch._int_mm + rescale (core/quantization.py:119-176) and
+ * triton_int8_gemm (kernels/triton/I64_int8_gemm.py:30-156).  acc_out (int32 [m,n]) optional. */
+int i64b_int8_gemm(const int8_t* x_q, const float* x_scale, const int8_t* w_q, const float* w_scale,
+                   float* out, int32_t* acc_out, int64_t m, int64_t n, int64_t k, i64b_stream_t stream);
+
+/* out[m,n] = (sum_k a[m,k] * b[n,k]) * col_scale[n]   (bf16 inputs, fp32 accumulate; col_scale nullable;
+ * out_dtype BF16 or F32).  With b = int8 weights held exactly in bf16 and col_scale = their per-channel scales
+ * this replaces the W8A32 kernels I64_gemm_dequant_int8 / triton_dequant_gemm_int8 (csrc/I64_gemm.cu:40-78,
+ * kernels/triton/I64_fused_dequant_gemm.py:32-146). */
+int i64b_bf16_gemm(const void* a, const void* b, const float* col_scale, void* out, int out_dtype, int64_t m,
+                   int64_t n, int64_t k, i64b_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* I64B_H_ */

@@ -288,6 +288,20 @@ def _mm(a: np.ndarray, b: np.ndarray) -> np.ndarray:
     return np.matmul(a.astype(np.float32), b.astype(np.float32))
 
 
+def round_bf16(a: np.ndarray) -> np.ndarray:
+    """fp32 → nearest bf16 (ties to even) → fp32, in pure numpy."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    r = ((u + np.uint32(0x7FFF) + ((u >> np.uint32(16)) & np.uint32(1))) & np.uint32(0xFFFF0000)).astype(np.uint32)
+    return r.view(np.float32)
+
+
+def _inter(x: np.ndarray, inter_bf16: bool) -> np.ndarray:
+    """The reference's bf16 path materialises the SwiGLU intermediate as a bf16 tensor
+    (layers/token_routed_mlp.py:150 with bf16 operands); ``inter_bf16=True`` reproduces that single rounding
+    so the comparison with a bf16 implementation is not dominated by it."""
+    return round_bf16(x) if inter_bf16 else x
+
+
 @dataclass
 class MoEWeights:
     """Tensors exactly as the reference module holds them
@@ -321,7 +335,8 @@ class MoEConfig:
         return [self.primary_weight] + [sec] * (self.top_k - 1)
 
 
-def expert_forward_fp32(x: np.ndarray, ids: np.ndarray, w: MoEWeights, num_experts: int) -> np.ndarray:
+def expert_forward_fp32(x: np.ndarray, ids: np.ndarray, w: MoEWeights, num_experts: int,
+                        inter_bf16: bool = False) -> np.ndarray:
     """``TokenRoutedMLP.expert_forward`` (layers/token_routed_mlp.py:132-152), tp=1."""
     out = np.zeros_like(x, dtype=np.float32)
     for e in range(num_experts):
@@ -329,15 +344,15 @@ def expert_forward_fp32(x: np.ndarray, ids: np.ndarray, w: MoEWeights, num_exper
         if rows.size == 0:
             continue
         xe = x[rows].astype(np.float32)
-        inter = _silu(_mm(xe, w.gate[e])) * _mm(xe, w.up[e])
+        inter = _inter(_silu(_mm(xe, w.gate[e])) * _mm(xe, w.up[e]), inter_bf16)
         out[rows] = _mm(inter, w.down[e])
     return out
 
 
-def shared_forward_fp32(x: np.ndarray, w: MoEWeights) -> np.ndarray:
+def shared_forward_fp32(x: np.ndarray, w: MoEWeights, inter_bf16: bool = False) -> np.ndarray:
     """Shared SwiGLU (layers/token_routed_mlp.py:165-173); Linear weights are (out, in)."""
     x = x.astype(np.float32)
-    inter = _silu(_mm(x, w.shared_gate.T)) * _mm(x, w.shared_up.T)
+    inter = _inter(_silu(_mm(x, w.shared_gate.T)) * _mm(x, w.shared_up.T), inter_bf16)
     return _mm(inter, w.shared_down.T)
 
 
@@ -355,23 +370,24 @@ def combine_fp32(routed: Sequence[np.ndarray], shared: Optional[np.ndarray], cfg
 
 
 def moe_block_fp32(x: np.ndarray, token_ids: Optional[np.ndarray], table: np.ndarray, w: MoEWeights,
-                   cfg: MoEConfig) -> np.ndarray:
+                   cfg: MoEConfig, inter_bf16: bool = False) -> np.ndarray:
     """``TokenRoutedMLP.forward`` (layers/token_routed_mlp.py:154-187) in fp32."""
     routes = route_table(token_ids, table, x.shape[0], cfg.num_experts)
-    routed = [expert_forward_fp32(x, routes[r], w, cfg.num_experts) for r in range(cfg.top_k)]
-    shared = shared_forward_fp32(x, w) if w.shared_gate is not None else None
+    routed = [expert_forward_fp32(x, routes[r], w, cfg.num_experts, inter_bf16) for r in range(cfg.top_k)]
+    shared = shared_forward_fp32(x, w, inter_bf16) if w.shared_gate is not None else None
     return combine_fp32(routed, shared, cfg)
 
 
-def dense_swiglu_fp32(x: np.ndarray, gate_w: np.ndarray, up_w: np.ndarray, down_w: np.ndarray) -> np.ndarray:
+def dense_swiglu_fp32(x: np.ndarray, gate_w: np.ndarray, up_w: np.ndarray, down_w: np.ndarray,
+                      inter_bf16: bool = False) -> np.ndarray:
     """``DenseSwiGLUMLP.forward`` (models/complexity_deep/model.py:250-255) /
     ``DenseMLP.forward`` float branch (layers/dense_mlp.py:59-73); weights (out, in)."""
     x = x.astype(np.float32)
-    return _mm(_silu(_mm(x, gate_w.T)) * _mm(x, up_w.T), down_w.T)
+    return _mm(_inter(_silu(_mm(x, gate_w.T)) * _mm(x, up_w.T), inter_bf16), down_w.T)
 
 
 def expert_segments_fp32(scattered: np.ndarray, gate_up: np.ndarray, down: np.ndarray,
-                         offsets: np.ndarray, counts: np.ndarray) -> np.ndarray:
+                         offsets: np.ndarray, counts: np.ndarray, inter_bf16: bool = False) -> np.ndarray:
     """``i64_expert_forward`` (kernels/i64_ops.py:100-158; csrc/i64_expert_dispatch.cu:144-233):
     fused ``gate_up [E,H,2I]`` (gate columns first), ``down [E,I,H]``."""
     out = np.zeros((scattered.shape[0], down.shape[2]), dtype=np.float32)
@@ -381,16 +397,16 @@ def expert_segments_fp32(scattered: np.ndarray, gate_up: np.ndarray, down: np.nd
         if c == 0:
             continue
         gu = _mm(scattered[o:o + c], gate_up[e])
-        out[o:o + c] = _mm(_silu(gu[:, :inter]) * gu[:, inter:], down[e])
+        out[o:o + c] = _mm(_inter(_silu(gu[:, :inter]) * gu[:, inter:], inter_bf16), down[e])
     return out
 
 
 def fused_token_routed_fp32(x: np.ndarray, gate_up: np.ndarray, down: np.ndarray, expert_ids: np.ndarray,
-                            num_experts: int) -> np.ndarray:
+                            num_experts: int, inter_bf16: bool = False) -> np.ndarray:
     """``fused_token_routed_forward`` (kernels/fused_experts.py:29-150): sort → per
     expert SwiGLU → unsort.  Both of the reference's modes compute this."""
     plan = dispatch_plan(expert_ids, num_experts)
-    seg = expert_segments_fp32(x[plan.perm], gate_up, down, plan.offsets, plan.counts)
+    seg = expert_segments_fp32(x[plan.perm], gate_up, down, plan.offsets, plan.counts, inter_bf16)
     return seg[plan.scatter_indices]
 
 

@@ -1,0 +1,640 @@
+// C ABI of the block: layer object (packed weights + tensor maps), forward orchestration
+// (plan → fused scatter → grouped GEMM1+SwiGLU → [re-quant] → grouped GEMM2 → combine), stand-alone GEMM ops.
+// No allocation, no synchronisation, no default-stream use; see include/i64b.h for the contract.
+#include <stdarg.h>
+#include <new>
+#include <stdlib.h>
+
+#include "i64b_gemm.cuh"
+#include "i64b_plan.cuh"
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+
+void i64b_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void i64b_count_launch(int n) { g_launches += n; }
+
+static const int16_t kSiluLutQ7[I64B_SILU_LUT_SIZE] = {
+#include "i64b_silu_lut.inc"
+};
+
+static size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// ------------------------------------------------------------------------------------------------ layer
+static const int kNMmaChoices[3] = {64, 128, 256};
+
+struct i64b_layer {
+    i64b_moe_config cfg;
+    int elt;                 // bytes per weight / activation element fed to the tensor cores
+    // packed weights (caller-owned device memory)
+    uint8_t* packed = nullptr;
+    uint8_t* w13 = nullptr;      // [(E*2I + 2S), H]   rows = out-features (gate rows then up rows per expert; shared last)
+    uint8_t* w2r = nullptr;      // [E*H, I]
+    uint8_t* w2s = nullptr;      // [H, S]
+    float* w13_scale = nullptr;  // W8A8 per out-row scales, same row indexing as the tensors above
+    float* w2r_scale = nullptr;
+    float* w2s_scale = nullptr;
+    int16_t* silu_lut = nullptr;
+    const uint8_t* table = nullptr;
+    bool loaded = false;
+    CUtensorMap tm_w13[3], tm_w2r[3], tm_w2s[3];   // per n_mma choice (box rows differ)
+    // activation tensor maps, valid for (ws_base, n)
+    void* cached_ws = nullptr;
+    int64_t cached_n = -1;
+    CUtensorMap tm_xs, tm_inter_r, tm_inter_s;
+    // carve of the last forward (debug taps)
+    struct Carve {
+        I64bPlanWs plan;
+        int32_t *routes, *dest_row, *scatter_idx;
+        uint8_t *xs, *inter_r, *inter_s;
+        float *xs_scale, *inter_scale_r, *inter_scale_s, *y;
+        int32_t *q14_r, *q14_s, *amax_r, *amax_s;
+        int amax_ld_r, amax_ld_s;
+        size_t bytes;
+    } cv;
+};
+
+static int w13_rows(const i64b_moe_config& c) { return c.num_experts * 2 * c.expert_inter + 2 * c.shared_inter; }
+
+static void carve_packed(i64b_layer* L, uint8_t* base, size_t* total) {
+    const i64b_moe_config& c = L->cfg;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        uint8_t* p = base ? base + off : nullptr;
+        off += align256(bytes > 0 ? bytes : 16);
+        return p;
+    };
+    L->w13 = take((size_t)w13_rows(c) * c.hidden_size * L->elt);
+    L->w2r = take((size_t)c.num_experts * c.hidden_size * c.expert_inter * L->elt);
+    L->w2s = take((size_t)c.hidden_size * c.shared_inter * L->elt);
+    L->w13_scale = reinterpret_cast<float*>(take(sizeof(float) * w13_rows(c)));
+    L->w2r_scale = reinterpret_cast<float*>(take(sizeof(float) * c.num_experts * c.hidden_size));
+    L->w2s_scale = reinterpret_cast<float*>(take(sizeof(float) * c.hidden_size));
+    L->silu_lut = reinterpret_cast<int16_t*>(take(sizeof(int16_t) * I64B_SILU_LUT_SIZE));
+    if (total) *total = off;
+}
+
+static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
+    const i64b_moe_config& c = L->cfg;
+    i64b_layer::Carve cv;
+    uint8_t* p = reinterpret_cast<uint8_t*>(base);
+    const int64_t nn = n > 0 ? n : 1;
+    const int64_t R = nn * c.top_k, T = R + nn;
+    const bool q = c.mode == I64B_MODE_W8A8;
+    cv.plan = i64b_plan_ws_carve(p, n, c.top_k, c.num_experts);
+    size_t off = cv.plan.bytes;
+    auto take = [&](size_t bytes) {
+        uint8_t* r = p ? p + off : nullptr;
+        off += align256(bytes > 0 ? bytes : 16);
+        return r;
+    };
+    cv.routes = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
+    cv.dest_row = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
+    cv.scatter_idx = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
+    cv.xs = take((size_t)T * c.hidden_size * L->elt);
+    cv.xs_scale = reinterpret_cast<float*>(take(sizeof(float) * T));
+    cv.inter_r = take((size_t)R * c.expert_inter * L->elt);
+    cv.inter_s = take((size_t)nn * c.shared_inter * L->elt);
+    cv.inter_scale_r = reinterpret_cast<float*>(take(sizeof(float) * R));
+    cv.inter_scale_s = reinterpret_cast<float*>(take(sizeof(float) * nn));
+    cv.amax_ld_r = (c.expert_inter + 31) / 32;      // enough for the narrowest GEMM1 tile (BN = 32)
+    cv.amax_ld_s = (c.shared_inter + 31) / 32;
+    cv.q14_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * c.expert_inter : 0));
+    cv.q14_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * c.shared_inter : 0));
+    cv.amax_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * cv.amax_ld_r : 0));
+    cv.amax_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * cv.amax_ld_s : 0));
+    cv.y = reinterpret_cast<float*>(take(sizeof(float) * T * c.hidden_size));
+    cv.bytes = off;
+    return cv;
+}
+
+// ------------------------------------------------------------------------------------------------ repack kernels
+namespace {
+// dst[(b*cols + c) * dst_ld_rows ... ] — batched transpose of 2-byte elements: src [B, R, C] -> dst rows
+// (dst_row0 + b*dst_batch_rows + c), column r, pitch R.
+__global__ void transpose16_kernel(const uint16_t* __restrict__ src, uint16_t* __restrict__ dst, int R, int C,
+                                   int64_t dst_row0, int64_t dst_batch_rows) {
+    __shared__ uint16_t tile[32][33];
+    const int b = blockIdx.z;
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const uint16_t* s = src + (int64_t)b * R * C;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        if (r < R && c < C) tile[i][threadIdx.x] = s[(int64_t)r * C + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (r < R && c < C) dst[(dst_row0 + (int64_t)b * dst_batch_rows + c) * R + r] = tile[threadIdx.x][i];
+    }
+}
+}  // namespace
+
+static int encode_weight_maps(i64b_layer* L) {
+    const i64b_moe_config& c = L->cfg;
+    const bool q = c.mode == I64B_MODE_W8A8;
+    for (int i = 0; i < 3; ++i) {
+        const int n_mma = kNMmaChoices[i];
+        int rc = i64b_encode_tmap(&L->tm_w13[i], L->w13, q, w13_rows(c), c.hidden_size,
+                                  (int64_t)c.hidden_size * L->elt, n_mma / 2);
+        if (rc) return rc;
+        if (c.num_experts > 0) {
+            rc = i64b_encode_tmap(&L->tm_w2r[i], L->w2r, q, (int64_t)c.num_experts * c.hidden_size, c.expert_inter,
+                                  (int64_t)c.expert_inter * L->elt, n_mma);
+            if (rc) return rc;
+        } else {
+            L->tm_w2r[i] = L->tm_w13[i];
+        }
+        if (c.shared_inter > 0) {
+            rc = i64b_encode_tmap(&L->tm_w2s[i], L->w2s, q, c.hidden_size, c.shared_inter,
+                                  (int64_t)c.shared_inter * L->elt, n_mma);
+            if (rc) return rc;
+        } else {
+            L->tm_w2s[i] = L->tm_w2r[i];
+        }
+    }
+    return I64B_OK;
+}
+
+static int pick_nmma(int64_t m_tiles_r, int n_r, int64_t m_tiles_s, int n_s, bool dual, const char* env) {
+    const int forced = env_int(env, 0);
+    if (forced == 64 || forced == 128 || forced == 256) return forced;
+    const int sms = i64b_num_sms();
+    for (int i = 2; i >= 0; --i) {
+        const int bn = dual ? kNMmaChoices[i] / 2 : kNMmaChoices[i];
+        const int64_t tiles = m_tiles_r * ((n_r + bn - 1) / bn) + m_tiles_s * ((n_s + bn - 1) / bn);
+        if (tiles >= sms) return kNMmaChoices[i];
+    }
+    return 64;
+}
+static int nmma_index(int n_mma) { return n_mma == 64 ? 0 : (n_mma == 128 ? 1 : 2); }
+
+extern "C" {
+
+const char* i64b_last_error(void) { return g_err; }
+int i64b_version(void) { return 100; }
+int64_t i64b_launch_count(void) { return g_launches; }
+void i64b_launch_count_reset(void) { g_launches = 0; }
+const int16_t* i64b_silu_lut_q7(void) { return kSiluLutQ7; }
+
+int i64b_moe_create(const i64b_moe_config* cfg, i64b_layer** out) {
+    I64B_CHECK(cfg && out, I64B_ERR_ARG, "null argument");
+    const i64b_moe_config& c = *cfg;
+    I64B_CHECK(c.mode == I64B_MODE_BF16 || c.mode == I64B_MODE_W8A8, I64B_ERR_ARG, "unknown mode %d", c.mode);
+    const int kalign = c.mode == I64B_MODE_W8A8 ? 16 : 8;   // 16-byte TMA pitch
+    I64B_CHECK(c.hidden_size > 0 && c.hidden_size % 16 == 0, I64B_ERR_ARG, "hidden_size %d must be a multiple of 16",
+               c.hidden_size);
+    I64B_CHECK(c.num_experts >= 0 && c.num_experts <= I64B_MAX_EXPERTS, I64B_ERR_ARG, "num_experts %d not in [0,%d]",
+               c.num_experts, I64B_MAX_EXPERTS);
+    I64B_CHECK(c.num_experts == 0 || (c.top_k >= 1 && c.top_k <= I64B_MAX_TOPK && c.top_k <= c.num_experts),
+               I64B_ERR_ARG, "top_k (%d) cannot exceed num_experts (%d) or %d", c.top_k, c.num_experts, I64B_MAX_TOPK);
+    I64B_CHECK(c.num_experts == 0 || (c.expert_inter > 0 && c.expert_inter % 16 == 0), I64B_ERR_ARG,
+               "expert_inter %d must be a positive multiple of 16", c.expert_inter);
+    I64B_CHECK(c.shared_inter >= 0 && c.shared_inter % 16 == 0, I64B_ERR_ARG, "shared_inter %d must be a multiple of 16",
+               c.shared_inter);
+    I64B_CHECK(c.num_experts > 0 || c.shared_inter > 0, I64B_ERR_ARG, "layer has neither experts nor a dense FFN");
+    I64B_CHECK(c.num_experts == 0 || c.vocab_size > 0, I64B_ERR_ARG, "vocab_size must be positive");
+    (void)kalign;
+    i64b_layer* L = new (std::nothrow) i64b_layer();
+    I64B_CHECK(L != nullptr, I64B_ERR_ARG, "out of host memory");
+    L->cfg = c;
+    if (c.num_experts == 0) L->cfg.top_k = 0;
+    L->elt = c.mode == I64B_MODE_W8A8 ? 1 : 2;
+    *out = L;
+    return I64B_OK;
+}
+
+void i64b_moe_destroy(i64b_layer* layer) { delete layer; }
+
+int i64b_moe_set_scales(i64b_layer* L, const float* route_weight, int top_k, float routed_scale, float shared_scale) {
+    I64B_CHECK(L && route_weight && top_k == L->cfg.top_k, I64B_ERR_ARG, "bad set_scales arguments");
+    for (int k = 0; k < top_k; ++k) L->cfg.route_weight[k] = route_weight[k];
+    L->cfg.routed_scale = routed_scale;
+    L->cfg.shared_scale = shared_scale;
+    return I64B_OK;
+}
+
+size_t i64b_moe_packed_bytes(const i64b_layer* layer) {
+    if (!layer) return 0;
+    i64b_layer tmp = *layer;
+    size_t total = 0;
+    carve_packed(&tmp, nullptr, &total);
+    return total + 256;
+}
+
+int i64b_moe_load_bf16(i64b_layer* L, const void* gate, const void* up, const void* down, const void* shared_gate,
+                       const void* shared_up, const void* shared_down, void* packed, i64b_stream_t stream) {
+    I64B_CHECK(L && packed, I64B_ERR_ARG, "null argument");
+    I64B_CHECK(L->cfg.mode == I64B_MODE_BF16, I64B_ERR_STATE, "layer was created in W8A8 mode");
+    const i64b_moe_config& c = L->cfg;
+    I64B_CHECK(c.num_experts == 0 || (gate && up && down), I64B_ERR_ARG, "expert weights missing");
+    I64B_CHECK(c.shared_inter == 0 || (shared_gate && shared_up && shared_down), I64B_ERR_ARG, "shared weights missing");
+    cudaStream_t s = (cudaStream_t)stream;
+    L->packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(packed) + 255) & ~uintptr_t(255));
+    carve_packed(L, L->packed, nullptr);
+    const int H = c.hidden_size, I = c.expert_inter, S = c.shared_inter, E = c.num_experts;
+    if (E > 0) {
+        dim3 blk(32, 8);
+        // gate/up [E,H,I] -> rows e*2I (+I) + i, pitch H
+        dim3 g1((I + 31) / 32, (H + 31) / 32, E);
+        transpose16_kernel<<<g1, blk, 0, s>>>(reinterpret_cast<const uint16_t*>(gate),
+                                              reinterpret_cast<uint16_t*>(L->w13), H, I, 0, 2 * I);
+        transpose16_kernel<<<g1, blk, 0, s>>>(reinterpret_cast<const uint16_t*>(up),
+                                              reinterpret_cast<uint16_t*>(L->w13), H, I, I, 2 * I);
+        // down [E,I,H] -> rows e*H + h, pitch I
+        dim3 g2((H + 31) / 32, (I + 31) / 32, E);
+        transpose16_kernel<<<g2, blk, 0, s>>>(reinterpret_cast<const uint16_t*>(down),
+                                              reinterpret_cast<uint16_t*>(L->w2r), I, H, 0, H);
+        I64B_LAUNCH_CHECK();
+    }
+    if (S > 0) {   // nn.Linear weights are already (out, in) = K-major
+        uint8_t* sh = L->w13 + (size_t)E * 2 * I * H * 2;
+        I64B_CUDA(cudaMemcpyAsync(sh, shared_gate, (size_t)S * H * 2, cudaMemcpyDeviceToDevice, s));
+        I64B_CUDA(cudaMemcpyAsync(sh + (size_t)S * H * 2, shared_up, (size_t)S * H * 2, cudaMemcpyDeviceToDevice, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w2s, shared_down, (size_t)H * S * 2, cudaMemcpyDeviceToDevice, s));
+    }
+    int rc = encode_weight_maps(L);
+    if (rc) return rc;
+    L->loaded = true;
+    L->cached_ws = nullptr;
+    return I64B_OK;
+}
+
+int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, const int8_t* w2_q, const float* w2_s,
+                       const int8_t* sh13_q, const float* sh13_s, const int8_t* sh2_q, const float* sh2_s, void* packed,
+                       i64b_stream_t stream) {
+    I64B_CHECK(L && packed, I64B_ERR_ARG, "null argument");
+    I64B_CHECK(L->cfg.mode == I64B_MODE_W8A8, I64B_ERR_STATE, "layer was created in bf16 mode");
+    const i64b_moe_config& c = L->cfg;
+    I64B_CHECK(c.num_experts == 0 || (w13_q && w13_s && w2_q && w2_s), I64B_ERR_ARG, "expert weights missing");
+    I64B_CHECK(c.shared_inter == 0 || (sh13_q && sh13_s && sh2_q && sh2_s), I64B_ERR_ARG, "shared weights missing");
+    cudaStream_t s = (cudaStream_t)stream;
+    L->packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(packed) + 255) & ~uintptr_t(255));
+    carve_packed(L, L->packed, nullptr);
+    const size_t H = c.hidden_size, I = c.expert_inter, S = c.shared_inter, E = c.num_experts;
+    const cudaMemcpyKind dd = cudaMemcpyDeviceToDevice;
+    if (E > 0) {
+        I64B_CUDA(cudaMemcpyAsync(L->w13, w13_q, E * 2 * I * H, dd, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w13_scale, w13_s, sizeof(float) * E * 2 * I, dd, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w2r, w2_q, E * H * I, dd, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w2r_scale, w2_s, sizeof(float) * E * H, dd, s));
+    }
+    if (S > 0) {
+        I64B_CUDA(cudaMemcpyAsync(L->w13 + E * 2 * I * H, sh13_q, 2 * S * H, dd, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w13_scale + E * 2 * I, sh13_s, sizeof(float) * 2 * S, dd, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w2s, sh2_q, H * S, dd, s));
+        I64B_CUDA(cudaMemcpyAsync(L->w2s_scale, sh2_s, sizeof(float) * H, dd, s));
+    }
+    I64B_CUDA(cudaMemcpyAsync(L->silu_lut, kSiluLutQ7, sizeof(kSiluLutQ7), cudaMemcpyHostToDevice, s));
+    int rc = encode_weight_maps(L);
+    if (rc) return rc;
+    L->loaded = true;
+    L->cached_ws = nullptr;
+    return I64B_OK;
+}
+
+int i64b_moe_set_table(i64b_layer* L, const uint8_t* table_u8) {
+    I64B_CHECK(L, I64B_ERR_ARG, "null layer");
+    L->table = table_u8;
+    return I64B_OK;
+}
+
+size_t i64b_moe_workspace_bytes(const i64b_layer* L, int64_t max_tokens) {
+    if (!L) return 0;
+    return carve_ws(L, nullptr, max_tokens).bytes + 1024;
+}
+
+struct FwdOpts {
+    const int32_t* given_routes = nullptr;  // int32 [K,N] expert ids supplied by the caller
+    int top_k = -1;                         // override (given routes only)
+    const float* route_weight = nullptr;
+    float routed_scale = 1.0f, shared_scale = 1.0f;
+    bool use_shared = true;
+    bool override_scales = false;
+};
+
+static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_ids, const FwdOpts& o,
+                            void* out, int out_dtype, int64_t n, void* workspace, size_t workspace_bytes,
+                            i64b_stream_t stream) {
+    I64B_CHECK(L, I64B_ERR_ARG, "null layer");
+    const int32_t* given_routes = o.given_routes;
+    I64B_CHECK(L->loaded, I64B_ERR_STATE, "weights not loaded (call i64b_moe_load_bf16 / i64b_moe_load_w8a8)");
+    I64B_CHECK(out_dtype == I64B_BF16 || out_dtype == I64B_F32, I64B_ERR_ARG, "unsupported output dtype %d", out_dtype);
+    I64B_CHECK(n >= 0, I64B_ERR_ARG, "negative token count");
+    if (n == 0) return I64B_OK;
+    I64B_CHECK(x && out && workspace, I64B_ERR_ARG, "null pointer");
+    i64b_moe_config c = L->cfg;
+    if (o.top_k >= 0) {
+        I64B_CHECK(given_routes != nullptr && o.top_k >= 1 && o.top_k <= I64B_MAX_TOPK && c.num_experts > 0,
+                   I64B_ERR_ARG, "top_k override %d needs caller-supplied routes", o.top_k);
+        c.top_k = o.top_k;
+    }
+    if (!o.use_shared) c.shared_inter = 0;
+    if (o.override_scales) {
+        for (int k = 0; k < c.top_k; ++k) c.route_weight[k] = o.route_weight ? o.route_weight[k] : 1.0f;
+        c.routed_scale = o.routed_scale;
+        c.shared_scale = o.shared_scale;
+    }
+    const bool q = c.mode == I64B_MODE_W8A8;
+    const int E = c.num_experts, K = c.top_k, H = c.hidden_size, I = c.expert_inter, S = c.shared_inter;
+    I64B_CHECK(E == 0 || given_routes != nullptr || token_ids == nullptr || L->table != nullptr, I64B_ERR_STATE,
+               "routing table not set (call i64b_moe_set_table)");
+    I64B_CHECK(n * (K + 1) < ((int64_t)1 << 31) / 8, I64B_ERR_ARG, "token count %lld too large", (long long)n);
+    void* base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~uintptr_t(1023));
+    i64b_layer view = *L;     // carve with the effective (possibly overridden) geometry
+    view.cfg = c;
+    const i64b_layer::Carve cv = carve_ws(&view, base, n);
+    I64B_CHECK(workspace_bytes >= cv.bytes + 1024, I64B_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes,
+               cv.bytes + 1024);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t R = n * K, T = R + n;
+
+    const int64_t cache_key = n * 64 + K * 2 + (S > 0 ? 1 : 0);
+    if (L->cached_ws != base || L->cached_n != cache_key) {
+        int rc = i64b_encode_tmap(&L->tm_xs, cv.xs, q, T, H, (int64_t)H * L->elt, 128);
+        if (rc) return rc;
+        if (E > 0) {
+            rc = i64b_encode_tmap(&L->tm_inter_r, cv.inter_r, q, R, I, (int64_t)I * L->elt, 128);
+            if (rc) return rc;
+        } else {
+            L->tm_inter_r = L->tm_xs;
+        }
+        if (S > 0) {
+            rc = i64b_encode_tmap(&L->tm_inter_s, cv.inter_s, q, n, S, (int64_t)S * L->elt, 128);
+            if (rc) return rc;
+        } else {
+            L->tm_inter_s = L->tm_inter_r;
+        }
+        L->cached_ws = base;
+        L->cached_n = cache_key;
+    }
+    L->cv = cv;
+
+    // 1. routing + deterministic dispatch plan + GEMM group tables (device-resident, no host sync)
+    I64bPlanArgs pa = {};
+    pa.mode = given_routes ? I64B_ROUTE_GIVEN : (token_ids ? I64B_ROUTE_TABLE : I64B_ROUTE_NOIDS);
+    pa.token_ids = token_ids;
+    pa.given = given_routes;
+    pa.table = L->table;
+    pa.n = n;
+    pa.vocab = c.vocab_size;
+    pa.top_k = K;
+    pa.num_experts = E;
+    pa.expert_inter = I;
+    pa.shared_inter = S;
+    pa.hidden = H;
+    int rc = i64b_run_plan(pa, cv.plan, s);
+    if (rc) return rc;
+
+    // 2. fused (quantize-and-)scatter
+    I64bDispatchArgs da = {};
+    da.x = x;
+    da.n = n;
+    da.hidden = H;
+    da.top_k = K;
+    da.num_experts = E;
+    da.quantize = q ? 1 : 0;
+    da.shared_copy = S > 0 ? 1 : 0;
+    da.xs = cv.xs;
+    da.xs_scale = cv.xs_scale;
+    da.routes_out = cv.routes;
+    da.scatter_idx_out = cv.scatter_idx;
+    da.dest_row_out = cv.dest_row;
+    rc = i64b_run_dispatch(da, cv.plan, s);
+    if (rc) return rc;
+
+    const int64_t mt_r = E > 0 ? R / 128 + E : 0;     // upper bound on routed m-tiles
+    const int64_t mt_s = S > 0 ? (n + 127) / 128 : 0;
+
+    // 3. GEMM1: gate|up projections + fused SwiGLU epilogue
+    {
+        const int n_mma = pick_nmma(mt_r, I, mt_s, S, true, "I64B_GEMM1_NMMA");
+        const int bn = n_mma / 2;
+        I64bGemmParams gp = {};
+        gp.groups = cv.plan.groups1;
+        gp.num_groups = E + 1;
+        gp.k[0] = gp.k[1] = H;
+        gp.out[0] = q ? (void*)cv.q14_r : (void*)cv.inter_r;
+        gp.out[1] = q ? (void*)cv.q14_s : (void*)cv.inter_s;
+        gp.ld_out[0] = I;
+        gp.ld_out[1] = S;
+        gp.row_scale[0] = gp.row_scale[1] = cv.xs_scale;
+        gp.col_scale[0] = gp.col_scale[1] = L->w13_scale;
+        gp.amax_part[0] = cv.amax_r;
+        gp.amax_part[1] = cv.amax_s;
+        gp.amax_ld[0] = cv.amax_ld_r;
+        gp.amax_ld[1] = cv.amax_ld_s;
+        gp.silu_lut = L->silu_lut;
+        const int wi = nmma_index(n_mma);
+        const int64_t tiles = mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
+        rc = i64b_launch_gemm(q, true, n_mma, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
+        if (rc) return rc;
+        if (q) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
+            if (E > 0) {
+                rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, (I + bn - 1) / bn,
+                                          reinterpret_cast<int8_t*>(cv.inter_r), cv.inter_scale_r, nullptr, R, I, s);
+                if (rc) return rc;
+            }
+            if (S > 0) {
+                rc = i64b_run_requant_q14(cv.q14_s, cv.amax_s, cv.amax_ld_s, (S + bn - 1) / bn,
+                                          reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, nullptr, n, S, s);
+                if (rc) return rc;
+            }
+        }
+    }
+
+    // 4. GEMM2: down projections -> per-assignment fp32 outputs
+    {
+        const int n_mma = pick_nmma(mt_r + mt_s, H, 0, 0, false, "I64B_GEMM2_NMMA");
+        I64bGemmParams gp = {};
+        gp.groups = cv.plan.groups2;
+        gp.num_groups = E + 1;
+        gp.k[0] = E > 0 ? I : S;
+        gp.k[1] = S > 0 ? S : I;
+        gp.out[0] = gp.out[1] = cv.y;
+        gp.ld_out[0] = gp.ld_out[1] = H;
+        gp.out_dtype = I64B_F32;
+        gp.epi = q ? I64B_EPI_DEQUANT : I64B_EPI_F32;
+        gp.row_scale[0] = cv.inter_scale_r;
+        gp.row_scale[1] = cv.inter_scale_s;
+        gp.col_scale[0] = L->w2r_scale;
+        gp.col_scale[1] = L->w2s_scale;
+        const int wi = nmma_index(n_mma);
+        const int64_t tiles = (mt_r + mt_s) * ((H + n_mma - 1) / n_mma);
+        rc = i64b_launch_gemm(q, false, n_mma, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi], L->tm_w2s[wi], gp, tiles, s);
+        if (rc) return rc;
+    }
+
+    // 5. weighted un-permute combine with the shared / routed output scales
+    I64bCombineArgs ca = {};
+    ca.y = cv.y;
+    ca.dest_row = cv.dest_row;
+    ca.n = n;
+    ca.hidden = H;
+    ca.top_k = K;
+    ca.has_shared = S > 0;
+    ca.has_routed = E > 0;
+    for (int k = 0; k < I64B_MAX_TOPK; ++k) ca.w[k] = k < K ? c.route_weight[k] : 0.0f;
+    ca.routed_scale = c.routed_scale;
+    ca.shared_scale = c.shared_scale;
+    ca.out = out;
+    ca.out_dtype = out_dtype;
+    return i64b_run_combine(ca, s);
+}
+
+int i64b_moe_forward(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype, int64_t n,
+                     void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
+    return moe_forward_impl(L, x, token_ids, FwdOpts(), out, out_dtype, n, workspace, workspace_bytes, stream);
+}
+
+int i64b_moe_forward_routed(i64b_layer* L, const void* x, const int32_t* routes, int top_k, const float* route_weight,
+                            float routed_scale, float shared_scale, int use_shared, void* out, int out_dtype,
+                            int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
+    I64B_CHECK(routes != nullptr || n == 0, I64B_ERR_ARG, "null routes");
+    FwdOpts o;
+    o.given_routes = routes;
+    o.top_k = top_k;
+    o.route_weight = route_weight;
+    o.routed_scale = routed_scale;
+    o.shared_scale = shared_scale;
+    o.use_shared = use_shared != 0;
+    o.override_scales = true;
+    return moe_forward_impl(L, x, nullptr, o, out, out_dtype, n, workspace, workspace_bytes, stream);
+}
+
+size_t i64b_moe_workspace_bytes_routed(const i64b_layer* L, int64_t max_tokens, int top_k) {
+    if (!L) return 0;
+    i64b_layer view = *L;
+    if (top_k > view.cfg.top_k) view.cfg.top_k = top_k;
+    return carve_ws(&view, nullptr, max_tokens).bytes + 1024;
+}
+
+int i64b_copy_device(void* dst, const void* src, size_t bytes, i64b_stream_t stream) {
+    if (bytes == 0) return I64B_OK;
+    I64B_CHECK(dst && src, I64B_ERR_ARG, "null pointer");
+    I64B_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return I64B_OK;
+}
+
+int i64b_moe_forward_host(i64b_layer* L, const void* x_host, const int64_t* token_ids_host, void* out_host,
+                          int out_dtype, int64_t n, void* x_dev, int64_t* ids_dev, void* out_dev, void* workspace,
+                          size_t workspace_bytes, i64b_stream_t stream) {
+    I64B_CHECK(L && x_host && out_host && x_dev && out_dev, I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(token_ids_host == nullptr || ids_dev != nullptr, I64B_ERR_ARG, "ids staging buffer missing");
+    if (n == 0) return I64B_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t H = L->cfg.hidden_size;
+    I64B_CUDA(cudaMemcpyAsync(x_dev, x_host, (size_t)n * H * 2, cudaMemcpyHostToDevice, s));
+    if (token_ids_host)
+        I64B_CUDA(cudaMemcpyAsync(ids_dev, token_ids_host, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    int rc = i64b_moe_forward(L, x_dev, token_ids_host ? ids_dev : nullptr, out_dev, out_dtype, n, workspace,
+                              workspace_bytes, stream);
+    if (rc) return rc;
+    I64B_CUDA(cudaMemcpyAsync(out_host, out_dev, (size_t)n * H * (out_dtype == I64B_F32 ? 4 : 2),
+                              cudaMemcpyDeviceToHost, s));
+    return I64B_OK;
+}
+
+void* i64b_moe_tap(i64b_layer* L, int what) {
+    if (!L) return nullptr;
+    const i64b_layer::Carve& cv = L->cv;
+    switch (what) {
+        case I64B_TAP_ROUTES: return cv.routes;
+        case I64B_TAP_DEST_ROW: return cv.dest_row;
+        case I64B_TAP_SCATTER_IDX: return cv.scatter_idx;
+        case I64B_TAP_COUNTS: return cv.plan.counts;
+        case I64B_TAP_OFFSETS: return cv.plan.offsets;
+        case I64B_TAP_XS: return cv.xs;
+        case I64B_TAP_XS_SCALE: return cv.xs_scale;
+        case I64B_TAP_INTER_R: return cv.inter_r;
+        case I64B_TAP_INTER_S: return cv.inter_s;
+        case I64B_TAP_INTER_SCALE_R: return cv.inter_scale_r;
+        case I64B_TAP_INTER_SCALE_S: return cv.inter_scale_s;
+        case I64B_TAP_Q14_R: return cv.q14_r;
+        case I64B_TAP_Q14_S: return cv.q14_s;
+        case I64B_TAP_Y: return cv.y;
+        case I64B_TAP_GROUP_ROWS: return cv.plan.group_start;
+        default: return nullptr;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ stand-alone GEMMs
+static int pick_nmma_single(int64_t m, int64_t n) {
+    const int forced = env_int("I64B_GEMM_NMMA", 0);
+    if (forced == 64 || forced == 128 || forced == 256) return forced;
+    const int sms = i64b_num_sms();
+    const int64_t mt = (m + 127) / 128;
+    for (int i = 2; i >= 0; --i)
+        if (mt * ((n + kNMmaChoices[i] - 1) / kNMmaChoices[i]) >= sms) return kNMmaChoices[i];
+    return 64;
+}
+
+int i64b_int8_gemm(const int8_t* x_q, const float* x_scale, const int8_t* w_q, const float* w_scale, float* out,
+                   int32_t* acc_out, int64_t m, int64_t n, int64_t k, i64b_stream_t stream) {
+    if (m == 0 || n == 0) return I64B_OK;
+    I64B_CHECK(x_q && w_q && (out || acc_out), I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(out == nullptr || (x_scale && w_scale), I64B_ERR_ARG, "scales required for the dequantised output");
+    I64B_CHECK(k > 0 && k % 16 == 0 && n % 16 == 0, I64B_ERR_ARG, "k (%lld) and n (%lld) must be multiples of 16",
+               (long long)k, (long long)n);
+    I64B_CHECK(m < ((int64_t)1 << 31) && n < ((int64_t)1 << 31), I64B_ERR_ARG, "matrix too large");
+    const int n_mma = pick_nmma_single(m, n);
+    CUtensorMap ta, tb;
+    int rc = i64b_encode_tmap(&ta, x_q, true, m, k, k, 128);
+    if (rc) return rc;
+    rc = i64b_encode_tmap(&tb, w_q, true, n, k, k, n_mma);
+    if (rc) return rc;
+    I64bGemmParams gp = {};
+    gp.inline_group = I64bGroup{0, (int32_t)m, 0, (int32_t)n, 0, 0, 0, 0};
+    gp.num_groups = 1;
+    gp.k[0] = gp.k[1] = (int32_t)k;
+    gp.out[0] = gp.out[1] = out;
+    gp.ld_out[0] = gp.ld_out[1] = n;
+    gp.out_dtype = I64B_F32;
+    gp.epi = out ? I64B_EPI_DEQUANT : I64B_EPI_F32;
+    gp.row_scale[0] = gp.row_scale[1] = x_scale;
+    gp.col_scale[0] = gp.col_scale[1] = w_scale;
+    gp.raw_out = acc_out;
+    gp.ld_raw = n;
+    const int64_t tiles = ((m + 127) / 128) * ((n + n_mma - 1) / n_mma);
+    return i64b_launch_gemm(true, false, n_mma, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
+}
+
+int i64b_bf16_gemm(const void* a, const void* b, const float* col_scale, void* out, int out_dtype, int64_t m,
+                   int64_t n, int64_t k, i64b_stream_t stream) {
+    if (m == 0 || n == 0) return I64B_OK;
+    I64B_CHECK(a && b && out, I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(out_dtype == I64B_BF16 || out_dtype == I64B_F32, I64B_ERR_ARG, "unsupported output dtype");
+    I64B_CHECK(k > 0 && k % 8 == 0 && n % 16 == 0, I64B_ERR_ARG, "k (%lld) must be a multiple of 8 and n (%lld) of 16",
+               (long long)k, (long long)n);
+    I64B_CHECK(m < ((int64_t)1 << 31) && n < ((int64_t)1 << 31), I64B_ERR_ARG, "matrix too large");
+    const int n_mma = pick_nmma_single(m, n);
+    CUtensorMap ta, tb;
+    int rc = i64b_encode_tmap(&ta, a, false, m, k, k * 2, 128);
+    if (rc) return rc;
+    rc = i64b_encode_tmap(&tb, b, false, n, k, k * 2, n_mma);
+    if (rc) return rc;
+    I64bGemmParams gp = {};
+    gp.inline_group = I64bGroup{0, (int32_t)m, 0, (int32_t)n, 0, 0, 0, 0};
+    gp.num_groups = 1;
+    gp.k[0] = gp.k[1] = (int32_t)k;
+    gp.out[0] = gp.out[1] = out;
+    gp.ld_out[0] = gp.ld_out[1] = n;
+    gp.out_dtype = out_dtype;
+    gp.epi = col_scale ? I64B_EPI_DEQUANT : I64B_EPI_F32;
+    gp.col_scale[0] = gp.col_scale[1] = col_scale;
+    const int64_t tiles = ((m + 127) / 128) * ((n + n_mma - 1) / n_mma);
+    return i64b_launch_gemm(false, false, n_mma, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,464 @@
+// Grouped expert GEMM for sm_100a: TMA-fed, tcgen05.mma with TMEM accumulators, persistent,
+// warp-specialised (1 TMA thread, 1 MMA-issuing thread, 4 epilogue warps), device-side tile
+// scheduling over the group table produced by the plan kernels (no host synchronisation).
+//
+//   C[rows_g, n_out_g] = A[rows_g, K] · B_g[n_out_g, K]^T          (A, B K-major; bf16→fp32 or int8→int32)
+//
+// Two shapes of the same kernel:
+//   kDual  (GEMM1, gate|up): each stage holds a gate tile and an up tile of the packed weight, one
+//          UMMA of width N = 2·BN writes both accumulators, and the epilogue fuses SiLU(gate)·up:
+//            bf16 : fp32 SiLU, bf16 store           (layers/token_routed_mlp.py:148-150)
+//            int8 : per-row × per-channel dequant, Q7 LUT SiLU × Q7 up → Q14 int32 store + row |max|
+//                   (core/quantization.py:227-286, layers/integer_activations.py:53-66)
+//   !kDual (GEMM2, down; dense linears): plain fp32/bf16 store or W8A8 dequant
+//          `acc.float() * (x_scale ⊗ w_scale)` (core/quantization.py:173).
+//
+// Reference counterparts being replaced: cublasHgemm loop with a D2H sync per call
+// (csrc/i64_expert_dispatch.cu:144-233), the 1-thread-per-output INT8 GEMMs (csrc/I64_gemm.cu:40-126),
+// Triton tl.dot kernels (kernels/triton_fused_expert.py, kernels/triton/I64_int8_gemm.py) and
+// torch._int_mm call sites (core/quantization.py:168-172).
+#include "i64b_gemm.cuh"
+
+namespace {
+
+constexpr int kBlockM = 128;
+constexpr int kRowBytes = 128;                     // one 128B swizzle span of K per stage row
+constexpr int kStageA = kBlockM * kRowBytes;       // 16 KiB
+constexpr int kThreads = 192;                      // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kMiscBytes = 8192;
+
+template <int kNMma> struct StageCfg {
+    static constexpr int kStageB = kNMma * kRowBytes;
+    static constexpr int kStagesRaw = 196608 / (kStageA + kStageB);
+    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+    static constexpr int kSmem = 1024 + kStages * (kStageA + kStageB) + kMiscBytes;
+};
+
+__device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem_ptr) {
+    uint64_t d = (uint64_t)((smem_u32(smem_ptr) >> 4) & 0x3FFFu);   // start address
+    d |= (uint64_t)(1024 >> 4) << 32;                                // SBO: 8 rows x 128 B
+    d |= 1ull << 46;                                                 // descriptor version (sm_100)
+    d |= 2ull << 61;                                                 // SWIZZLE_128B
+    return d;
+}
+
+template <bool kInt8, int kNMma>
+__device__ __forceinline__ constexpr uint32_t make_idesc() {
+    // c_format [4,6): 1=F32, 2=S32; a/b format [7,10)/[10,13): BF16=1 / S8=1; K-major both;
+    // n_dim [17,23) = N>>3; m_dim [24,29) = M>>4
+    return (uint32_t)((kInt8 ? 2u : 1u) << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kNMma >> 3) << 17) |
+           ((uint32_t)(kBlockM >> 4) << 24);
+}
+
+struct TileCoord {
+    int g, m_t, n_t;
+};
+
+template <int kBnOut>
+__device__ __forceinline__ void decode_tile(int tile, int& g, const int* prefix, const I64bGroup* sg,
+                                            TileCoord& tc) {
+    while (tile >= prefix[g + 1]) ++g;
+    const int nt = (sg[g].n_out + kBnOut - 1) / kBnOut;
+    const int local = tile - prefix[g];
+    tc.g = g;
+    tc.m_t = local / nt;
+    tc.n_t = local % nt;
+}
+
+__device__ __forceinline__ float silu_f32(float g) {
+    return g * __frcp_rn(1.0f + __expf(-g));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <bool kInt8, bool kDual, int kNMma>
+__global__ void __launch_bounds__(kThreads, 1)
+i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                 const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmB1,
+                 const __grid_constant__ I64bGemmParams p) {
+    using Cfg = StageCfg<kNMma>;
+    constexpr int kStages = Cfg::kStages;
+    constexpr int kStageB = Cfg::kStageB;
+    constexpr int kBnOut = kDual ? kNMma / 2 : kNMma;
+    constexpr int kBlockK = kInt8 ? 128 : 64;          // elements per 128-byte row
+    constexpr uint32_t kTmemCols = 2 * kNMma;          // two accumulator stages (power of two ≥ 32)
+    static_assert(kTmemCols >= 32 && kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + kStages * kStageA;
+    uint8_t* misc = sB + kStages * kStageB;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tfull_bar = empty_bar + kStages;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    int* prefix = reinterpret_cast<int*>(tmem_ptr + 2);
+    I64bGroup* sg = reinterpret_cast<I64bGroup*>(misc + 512);
+    int16_t* slut = reinterpret_cast<int16_t*>(misc + 512 + sizeof(I64bGroup) * I64B_MAX_GROUPS);
+    static_assert(512 + sizeof(I64bGroup) * I64B_MAX_GROUPS + 2 * I64B_SILU_LUT_SIZE <= kMiscBytes, "misc smem");
+    static_assert((2 * 8 + 2 * 2) * 8 + 8 + 4 * (I64B_MAX_GROUPS + 1) <= 512, "barrier area");
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA0);
+        tma_prefetch_desc(&tmB0);
+        tma_prefetch_desc(&tmA1);
+        tma_prefetch_desc(&tmB1);
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tfull_bar[i], 1);
+            mbar_init(&tempty_bar[i], 4);
+        }
+        fence_barrier_init();
+    } else if (warp == 1) {
+        tmem_alloc<kTmemCols>(tmem_ptr);
+    }
+
+    // everything above overlaps the previous kernel's tail under PDL; below reads its outputs
+    pdl_wait_prior();
+
+    const int ng = p.num_groups;
+    for (int i = threadIdx.x; i < ng; i += kThreads) sg[i] = p.groups ? p.groups[i] : p.inline_group;
+    if constexpr (kInt8 && kDual) {
+        for (int i = threadIdx.x; i < I64B_SILU_LUT_SIZE; i += kThreads) slut[i] = p.silu_lut[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int g = 0; g < ng; ++g) {
+            prefix[g] = acc;
+            const int mt = (sg[g].rows + kBlockM - 1) / kBlockM;
+            const int nt = (sg[g].n_out + kBnOut - 1) / kBnOut;
+            acc += mt * nt;
+        }
+        prefix[ng] = acc;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const int total_tiles = prefix[ng];
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0, g = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                TileCoord tc;
+                decode_tile<kBnOut>(tile, g, prefix, sg, tc);
+                const I64bGroup grp = sg[tc.g];
+                const CUtensorMap* ta = grp.which ? &tmA1 : &tmA0;
+                const CUtensorMap* tb = grp.which ? &tmB1 : &tmB0;
+                const int nkb = (p.k[grp.which] + kBlockK - 1) / kBlockK;
+                const int a_row = grp.row_start + tc.m_t * kBlockM;
+                const int b_row = grp.w_row_base + tc.n_t * kBnOut;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full_bar[stage], kStageA + kStageB);
+                    tma_load_2d(sA + stage * kStageA, ta, &full_bar[stage], kb * kBlockK, a_row,
+                                I64B_L2_EVICT_NORMAL);
+                    if constexpr (kDual) {
+                        tma_load_2d(sB + stage * kStageB, tb, &full_bar[stage], kb * kBlockK, b_row,
+                                    I64B_L2_EVICT_NORMAL);
+                        tma_load_2d(sB + stage * kStageB + kBnOut * kRowBytes, tb, &full_bar[stage],
+                                    kb * kBlockK, b_row + grp.n_out, I64B_L2_EVICT_NORMAL);
+                    } else {
+                        tma_load_2d(sB + stage * kStageB, tb, &full_bar[stage], kb * kBlockK, b_row,
+                                    I64B_L2_EVICT_NORMAL);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (one thread)
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc<kInt8, kNMma>();
+            int stage = 0, g = 0, iter = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++iter) {
+                TileCoord tc;
+                decode_tile<kBnOut>(tile, g, prefix, sg, tc);
+                const int nkb = (p.k[sg[tc.g].which] + kBlockK - 1) / kBlockK;
+                const int as = iter & 1;
+                mbar_wait(&tempty_bar[as], ((iter >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * kNMma;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint64_t a_desc = make_sw128_kmajor_desc(sA + stage * kStageA);
+                    const uint64_t b_desc = make_sw128_kmajor_desc(sB + stage * kStageB);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {   // 4 x 32-byte K slices inside the swizzle span
+                        if constexpr (kInt8)
+                            umma_i8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        else
+                            umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);             // smem slot reusable once these MMAs retire
+                    if (kb == nkb - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue (4 warps = 128 TMEM lanes)
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access
+        const int r = q * 32 + lane;            // tile row owned by this thread
+        int g = 0, iter = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++iter) {
+            TileCoord tc;
+            decode_tile<kBnOut>(tile, g, prefix, sg, tc);
+            const I64bGroup grp = sg[tc.g];
+            const int w = grp.which;
+            const int as = iter & 1;
+            mbar_wait(&tfull_bar[as], (iter >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma;
+            const int row_in_group = tc.m_t * kBlockM + r;
+            const bool valid = row_in_group < grp.rows;
+            const int64_t out_row = (int64_t)grp.out_row_start + row_in_group;
+            const int64_t a_row = (int64_t)grp.row_start + row_in_group;
+            const int n_out = grp.n_out;
+
+            if constexpr (kDual && !kInt8) {
+                __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out[w]) + out_row * p.ld_out[w];
+#pragma unroll 1
+                for (int c = 0; c < kBnOut / 32; ++c) {
+                    const int col0 = tc.n_t * kBnOut + c * 32;
+                    if (col0 >= n_out) break;
+                    uint32_t gr[32], ur[32];
+                    tmem_ld_32x32(taddr + c * 32, gr);
+                    tmem_ld_32x32(taddr + kBnOut + c * 32, ur);
+                    tmem_ld_wait();
+                    uint32_t o[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
+                        const float h1 = silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]);
+                        o[j] = pack_bf16x2(h0, h1);
+                    }
+                    if (valid) {
+#pragma unroll
+                        for (int v = 0; v < 4; ++v)
+                            if (col0 + v * 8 < n_out)
+                                *reinterpret_cast<int4*>(orow + col0 + v * 8) =
+                                    make_int4(o[4 * v], o[4 * v + 1], o[4 * v + 2], o[4 * v + 3]);
+                    }
+                }
+            } else if constexpr (kDual && kInt8) {
+                int32_t* orow = reinterpret_cast<int32_t*>(p.out[w]) + out_row * p.ld_out[w];
+                const float rs = valid ? p.row_scale[w][a_row] : 0.0f;
+                const float* cs_g = p.col_scale[w] + grp.w_row_base;
+                const float* cs_u = cs_g + n_out;
+                int amax = 0;
+#pragma unroll 1
+                for (int c = 0; c < kBnOut / 32; ++c) {
+                    const int col0 = tc.n_t * kBnOut + c * 32;
+                    if (col0 >= n_out) break;
+                    uint32_t gr[32], ur[32];
+                    tmem_ld_32x32(taddr + c * 32, gr);
+                    tmem_ld_32x32(taddr + kBnOut + c * 32, ur);
+                    tmem_ld_wait();
+                    int o[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const bool cv = col0 + j < n_out;
+                        const float sg_ = cv ? __ldg(cs_g + col0 + j) : 0.0f;
+                        const float su_ = cv ? __ldg(cs_u + col0 + j) : 0.0f;
+                        // result_i32.float() * (x_scale * w_scale)           core/quantization.py:278
+                        const float gate = __fmul_rn((float)(int)gr[j], __fmul_rn(rs, sg_));
+                        const float up = __fmul_rn((float)(int)ur[j], __fmul_rn(rs, su_));
+                        // silu_multiply_integer                              layers/integer_activations.py:53-66
+                        const int gq = __float2int_rn(__fmul_rn(gate, 128.0f));
+                        const int uq = __float2int_rn(__fmul_rn(up, 128.0f));
+                        int sq = (int)slut[min(max(gq, -1024), 1024) + 1024];
+                        sq = gq > 1024 ? gq : sq;
+                        sq = gq < -1024 ? 0 : sq;
+                        const int q14 = sq * uq;
+                        o[j] = q14;
+                        if (cv) amax = max(amax, abs(q14));
+                    }
+                    if (valid) {
+#pragma unroll
+                        for (int v = 0; v < 8; ++v)
+                            if (col0 + v * 4 < n_out)
+                                *reinterpret_cast<int4*>(orow + col0 + v * 4) =
+                                    make_int4(o[4 * v], o[4 * v + 1], o[4 * v + 2], o[4 * v + 3]);
+                    }
+                }
+                if (valid) p.amax_part[w][out_row * p.amax_ld[w] + tc.n_t] = amax;
+            } else {
+                const bool dequant = p.epi == I64B_EPI_DEQUANT;
+                const float rs = (dequant && valid && p.row_scale[w] != nullptr) ? p.row_scale[w][a_row] : 1.0f;
+                const float* cs = dequant ? p.col_scale[w] + grp.w_row_base : nullptr;
+#pragma unroll 1
+                for (int c = 0; c < kNMma / 32; ++c) {
+                    const int col0 = tc.n_t * kNMma + c * 32;
+                    if (col0 >= n_out) break;
+                    uint32_t ar[32];
+                    tmem_ld_32x32(taddr + c * 32, ar);
+                    tmem_ld_wait();
+                    if constexpr (kInt8) {
+                        if (p.raw_out != nullptr && valid) {
+                            int32_t* rrow = p.raw_out + out_row * p.ld_raw;
+#pragma unroll
+                            for (int v = 0; v < 8; ++v)
+                                if (col0 + v * 4 < n_out)
+                                    *reinterpret_cast<int4*>(rrow + col0 + v * 4) =
+                                        make_int4(ar[4 * v], ar[4 * v + 1], ar[4 * v + 2], ar[4 * v + 3]);
+                        }
+                        if (dequant) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const float s = (col0 + j < n_out) ? __ldg(cs + col0 + j) : 0.0f;
+                                ar[j] = __float_as_uint(__fmul_rn((float)(int)ar[j], __fmul_rn(rs, s)));
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) ar[j] = __float_as_uint((float)(int)ar[j]);
+                        }
+                    } else if (dequant) {   // bf16 GEMM with a per-column (and optional per-row) fp32 scale
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float s = (col0 + j < n_out) ? __ldg(cs + col0 + j) : 0.0f;
+                            ar[j] = __float_as_uint(__fmul_rn(__uint_as_float(ar[j]), __fmul_rn(rs, s)));
+                        }
+                    }
+                    if (valid && p.out[w] != nullptr) {
+                        if (p.out_dtype == I64B_F32) {
+                            float* orow = reinterpret_cast<float*>(p.out[w]) + out_row * p.ld_out[w];
+#pragma unroll
+                            for (int v = 0; v < 8; ++v)
+                                if (col0 + v * 4 < n_out)
+                                    *reinterpret_cast<int4*>(orow + col0 + v * 4) =
+                                        make_int4(ar[4 * v], ar[4 * v + 1], ar[4 * v + 2], ar[4 * v + 3]);
+                        } else {
+                            __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out[w]) + out_row * p.ld_out[w];
+#pragma unroll
+                            for (int v = 0; v < 4; ++v)
+                                if (col0 + v * 8 < n_out) {
+                                    int4 pk;
+                                    pk.x = pack_bf16x2(__uint_as_float(ar[8 * v]), __uint_as_float(ar[8 * v + 1]));
+                                    pk.y = pack_bf16x2(__uint_as_float(ar[8 * v + 2]), __uint_as_float(ar[8 * v + 3]));
+                                    pk.z = pack_bf16x2(__uint_as_float(ar[8 * v + 4]), __uint_as_float(ar[8 * v + 5]));
+                                    pk.w = pack_bf16x2(__uint_as_float(ar[8 * v + 6]), __uint_as_float(ar[8 * v + 7]));
+                                    *reinterpret_cast<int4*>(orow + col0 + v * 8) = pk;
+                                }
+                        }
+                    }
+                }
+            }
+            // accumulator stage drained: hand it back to the MMA thread
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[as]);
+        }
+    }
+
+    pdl_launch_dependents();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                        CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                        CUtensorMapFloatOOBfill);
+
+PFN_tmapEncodeTiled get_encode_fn() {
+    static PFN_tmapEncodeTiled fn = nullptr;
+    if (fn == nullptr) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_tmapEncodeTiled>(ptr);
+    }
+    return fn;
+}
+
+template <bool kInt8, bool kDual, int kNMma>
+int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b0, const CUtensorMap& b1,
+                const I64bGemmParams& p, int grid, cudaStream_t stream) {
+    auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma>;
+    constexpr int smem = StageCfg<kNMma>::kSmem;
+    static bool configured = false;
+    if (!configured) {
+        I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+    }
+    kern<<<grid, kThreads, smem, stream>>>(a0, a1, b0, b1, p);
+    I64B_LAUNCH_CHECK();
+    i64b_count_launch();
+    return I64B_OK;
+}
+
+}  // namespace
+
+int i64b_num_sms() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+            sms = 148;
+    }
+    return sms;
+}
+
+int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t rows, int64_t cols,
+                     int64_t pitch_bytes, int box_rows) {
+    PFN_tmapEncodeTiled fn = get_encode_fn();
+    I64B_CHECK(fn != nullptr, I64B_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    I64B_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && pitch_bytes % 16 == 0, I64B_ERR_ARG,
+               "TMA operand must be 16-byte aligned (base %p pitch %lld)", base, (long long)pitch_bytes);
+    I64B_CHECK(rows > 0 && cols > 0 && box_rows > 0 && box_rows <= 256, I64B_ERR_ARG, "bad tensor-map shape");
+    const int elt = is_int8 ? 1 : 2;
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch_bytes};
+    cuuint32_t box[2] = {(cuuint32_t)(kRowBytes / elt), (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, is_int8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                    const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    I64B_CHECK(r == CUDA_SUCCESS, I64B_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return I64B_OK;
+}
+
+int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+                     const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
+                     int64_t max_tiles, cudaStream_t stream) {
+    if (max_tiles <= 0) return I64B_OK;
+    I64B_CHECK(p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
+               p.num_groups);
+    I64B_CHECK(p.k[0] > 0 && p.k[1] > 0, I64B_ERR_ARG, "K must be positive");
+    const int sms = i64b_num_sms();
+    const int grid = (int)(max_tiles < sms ? max_tiles : sms);
+#define I64B_DISPATCH(I8, DUAL, N)                                                              \
+    if (is_int8 == I8 && dual == DUAL && n_mma == N)                                            \
+        return launch_inst<I8, DUAL, N>(tmA0, tmA1, tmB0, tmB1, p, grid, stream);
+    I64B_DISPATCH(false, false, 64) I64B_DISPATCH(false, false, 128) I64B_DISPATCH(false, false, 256)
+    I64B_DISPATCH(false, true, 64) I64B_DISPATCH(false, true, 128) I64B_DISPATCH(false, true, 256)
+    I64B_DISPATCH(true, false, 64) I64B_DISPATCH(true, false, 128) I64B_DISPATCH(true, false, 256)
+    I64B_DISPATCH(true, true, 64) I64B_DISPATCH(true, true, 128) I64B_DISPATCH(true, true, 256)
+#undef I64B_DISPATCH
+    i64b_set_error("unsupported GEMM tile configuration n_mma=%d", n_mma);
+    return I64B_ERR_ARG;
+}

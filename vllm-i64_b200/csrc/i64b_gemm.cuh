@@ -1,0 +1,42 @@
+// Grouped GEMM launch interface shared by i64b_gemm.cu (kernels) and i64b_api.cu (the block).
+#pragma once
+#include <cuda.h>
+#include "i64b_common.cuh"
+
+// Epilogue selection (runtime, within a template instantiation)
+enum {
+    I64B_EPI_F32 = 0,       // plain: out = acc (fp32 or bf16 store)
+    I64B_EPI_DEQUANT = 1,   // int8: out = float(acc) * (row_scale * col_scale)
+};
+
+struct I64bGemmParams {
+    const I64bGroup* groups;   // device group table, or nullptr → use `inline_group`
+    I64bGroup inline_group;
+    int32_t num_groups;
+    int32_t k[2];              // reduction length per `which`
+    void* out[2];              // output buffer per `which`
+    int64_t ld_out[2];         // leading dimension of out (elements)
+    int32_t out_dtype;         // I64B_BF16 | I64B_F32 (plain epilogues); SwiGLU-bf16 always bf16; Q14 always int32
+    int32_t epi;               // I64B_EPI_*
+    const float* row_scale[2]; // int8: per A-row scale, indexed by A row of buffer `which`
+    const float* col_scale[2]; // int8: per weight-row (out-feature) scale of packed tensor `which`
+    int32_t* raw_out;          // optional raw int32 accumulator dump (plain int8 epilogue, which==0 layout)
+    int64_t ld_raw;
+    int32_t* amax_part[2];     // Q14 epilogue: per (row, n_tile) max|q14|
+    int32_t amax_ld[2];
+    const int16_t* silu_lut;   // device copy of the Q7 SiLU table (2049 entries)
+};
+
+// Tensor map for a row-major [rows, cols] matrix of 1-byte (int8) or 2-byte (bf16) elements whose
+// tiles are (box_rows x 128 bytes), 128B-swizzled.
+int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t rows, int64_t cols,
+                     int64_t pitch_bytes, int box_rows);
+
+// Launch one grouped GEMM.  n_mma in {64,128,256}; dual = gate|up pair + fused SwiGLU epilogue.
+// max_tiles is an upper bound on the number of (group, m, n) tiles, used only to size the grid.
+int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+                     const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
+                     int64_t max_tiles, cudaStream_t stream);
+
+int i64b_num_sms();
+void i64b_count_launch(int n = 1);

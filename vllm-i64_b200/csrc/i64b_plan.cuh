@@ -1,0 +1,67 @@
+// Integer / bandwidth-bound stages of the block: routing, deterministic dispatch plan,
+// fused (quantize-and-)scatter, re-quantisation of the integer SwiGLU output, weighted combine.
+#pragma once
+#include "i64b_common.cuh"
+
+enum { I64B_ROUTE_TABLE = 0, I64B_ROUTE_MODULO = 1, I64B_ROUTE_GIVEN = 2, I64B_ROUTE_NOIDS = 3 };
+
+// Layout of the plan workspace (all int32 unless noted); sizes depend on (n, K, E) only.
+struct I64bPlanWs {
+    uint32_t* packed;      // [K, N]   expert (8 bits) | rank-in-tile (24 bits)
+    int32_t* tile_counts;  // [tiles, K*E]   per-tile histogram, then in place: exclusive base over tiles
+    int32_t* counts;       // [K, E]
+    int32_t* offsets;      // [K, E]   per-route exclusive scan (reference convention)
+    int32_t* route_base;   // [K, E]   rows of routes < k inside expert e's merged segment
+    int32_t* group_start;  // [E + 1]  merged expert-major segment starts (last = N*K)
+    I64bGroup* groups1;    // [E + 1]  GEMM1 problems (gate|up), shared expert last
+    I64bGroup* groups2;    // [E + 1]  GEMM2 problems (down)
+    size_t bytes;
+};
+I64bPlanWs i64b_plan_ws_carve(void* base, int64_t n, int top_k, int num_experts);
+
+struct I64bPlanArgs {
+    int mode;                    // I64B_ROUTE_*
+    const int64_t* token_ids;    // TABLE / MODULO
+    const uint8_t* table;        // TABLE: [K, V] uint8
+    const int32_t* given;        // GIVEN: [K, N] int32 expert ids
+    int64_t n;
+    int vocab, top_k, num_experts;
+    // geometry for the group tables (0 when only the plan is wanted)
+    int expert_inter, shared_inter, hidden;
+};
+
+// route + per-tile stable ranks + finalisation (counts, offsets, group tables). 1-2 launches.
+int i64b_run_plan(const I64bPlanArgs& a, const I64bPlanWs& ws, cudaStream_t stream);
+
+struct I64bDispatchArgs {
+    const void* x;              // [N, H] bf16 (fused path) or raw rows
+    int64_t n;
+    int hidden;
+    int top_k, num_experts;
+    int quantize;               // 1: per-row int8 quantisation fused into the scatter
+    int shared_copy;            // 1: also write row N*K + t (token order) for the shared expert
+    void* xs;                   // [N*K (+N), H] bf16 or int8
+    float* xs_scale;            // [N*K (+N)] (quantize)
+    // optional reference-convention outputs
+    int32_t* routes_out;        // [K, N]
+    int32_t* scatter_idx_out;   // [K, N]
+    int32_t* dest_row_out;      // [K, N]
+};
+int i64b_run_dispatch(const I64bDispatchArgs& a, const I64bPlanWs& ws, cudaStream_t stream);
+
+// q14 int32 [rows, cols] (+ per-(row, tile) |max| partials) -> int8 rows + fp32 scale (bit-exact re-quantisation
+// of silu_multiply_integer's fp32 output, core/quantization.py:103-116)
+int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_ld, int n_tiles, int8_t* out,
+                         float* scale, const int32_t* rows_dev, int64_t max_rows, int cols, cudaStream_t stream);
+
+struct I64bCombineArgs {
+    const float* y;             // [N*K + N, H] fp32 per-assignment outputs (shared rows last)
+    const int32_t* dest_row;    // [K, N]
+    int64_t n;
+    int hidden, top_k, has_shared, has_routed;
+    float w[I64B_MAX_TOPK];
+    float routed_scale, shared_scale;
+    void* out;
+    int out_dtype;
+};
+int i64b_run_combine(const I64bCombineArgs& a, cudaStream_t stream);

@@ -1,0 +1,150 @@
+"""ctypes binding of ``libi64b.so`` (the C ABI declared in ``include/i64b.h``).
+
+The product path has no fallback: if the shared library is missing or a call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libi64b.so")
+
+BF16, F32, F16 = 0, 1, 2
+MODE_BF16, MODE_W8A8 = 0, 1
+(TAP_ROUTES, TAP_DEST_ROW, TAP_SCATTER_IDX, TAP_COUNTS, TAP_OFFSETS, TAP_XS, TAP_XS_SCALE, TAP_INTER_R, TAP_INTER_S,
+ TAP_INTER_SCALE_R, TAP_INTER_SCALE_S, TAP_Q14_R, TAP_Q14_S, TAP_Y, TAP_GROUP_START) = range(15)
+
+_DTYPES = {torch.bfloat16: BF16, torch.float32: F32, torch.float16: F16}
+
+
+class I64bError(RuntimeError):
+    pass
+
+
+class MoEConfig(C.Structure):
+    _fields_ = [("hidden_size", C.c_int32), ("num_experts", C.c_int32), ("expert_inter", C.c_int32),
+                ("shared_inter", C.c_int32), ("vocab_size", C.c_int32), ("top_k", C.c_int32), ("mode", C.c_int32),
+                ("reserved", C.c_int32), ("route_weight", C.c_float * 4), ("routed_scale", C.c_float),
+                ("shared_scale", C.c_float)]
+
+
+_lib: Optional[C.CDLL] = None
+
+_P, _I, _L, _Z, _F = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
+_SIGNATURES = {
+    "i64b_last_error": (C.c_char_p, []),
+    "i64b_version": (_I, []),
+    "i64b_launch_count": (_L, []),
+    "i64b_launch_count_reset": (None, []),
+    "i64b_silu_lut_q7": (C.POINTER(C.c_int16), []),
+    "i64b_route_modulo": (_I, [_P, _P, _L, _I, _P]),
+    "i64b_pack_table": (_I, [_P, _P, _I, _I, _I, _P]),
+    "i64b_route_table": (_I, [_P, _P, _P, _L, _I, _I, _I, _P]),
+    "i64b_plan_workspace_bytes": (_Z, [_L, _I, _I]),
+    "i64b_dispatch_plan": (_I, [_P, _I, _L, _I, _P, _P, _P, _P, _P, _P, _Z, _P]),
+    "i64b_scatter_rows": (_I, [_P, _P, _P, _L, _L, _P]),
+    "i64b_gather_rows": (_I, [_P, _P, _P, _L, _L, _P]),
+    "i64b_silu_hadamard": (_I, [_P, _P, _L, _I, _I, _P]),
+    "i64b_quantize_rows_int8": (_I, [_P, _I, _P, _P, _L, _L, _P]),
+    "i64b_dequantize_int8": (_I, [_P, _P, _P, _L, _L, _P]),
+    "i64b_moe_create": (_I, [C.POINTER(MoEConfig), C.POINTER(_P)]),
+    "i64b_moe_destroy": (None, [_P]),
+    "i64b_moe_set_scales": (_I, [_P, C.POINTER(_F), _I, _F, _F]),
+    "i64b_moe_packed_bytes": (_Z, [_P]),
+    "i64b_moe_load_bf16": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "i64b_moe_load_w8a8": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "i64b_moe_set_table": (_I, [_P, _P]),
+    "i64b_moe_workspace_bytes": (_Z, [_P, _L]),
+    "i64b_moe_forward": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, _P]),
+    "i64b_moe_forward_routed": (_I, [_P, _P, _P, _I, C.POINTER(_F), _F, _F, _I, _P, _I, _L, _P, _Z, _P]),
+    "i64b_moe_workspace_bytes_routed": (_Z, [_P, _L, _I]),
+    "i64b_copy_device": (_I, [_P, _P, _Z, _P]),
+    "i64b_moe_forward_host": (_I, [_P, _P, _P, _P, _I, _L, _P, _P, _P, _P, _Z, _P]),
+    "i64b_moe_tap": (_P, [_P, _I]),
+    "i64b_int8_gemm": (_I, [_P, _P, _P, _P, _P, _P, _L, _L, _L, _P]),
+    "i64b_bf16_gemm": (_I, [_P, _P, _P, _P, _I, _L, _L, _L, _P]),
+}
+EXPORTED = tuple(sorted(_SIGNATURES))
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the C-ABI library.  Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: build the CUDA library first (python -c 'import __graft_entry__ as g; "
+                "g.build()' or make -C vllm-i64_b200/csrc).  There is no CPU or PyTorch fallback for this path.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise I64bError(f"i64b error {rc}: {lib().i64b_last_error().decode(errors='replace')}")
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}") from None
+
+
+def require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "vllm_i64 (B200 build): this op runs only on CUDA tensors; there is no CPU fallback on this path")
+
+
+def launch_count() -> int:
+    return int(lib().i64b_launch_count())
+
+
+def launch_count_reset() -> None:
+    lib().i64b_launch_count_reset()
+
+
+_workspaces = {}
+
+
+def workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Per-(device, stream) scratch buffer, grown on demand; owned by torch's caching allocator."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+def tap_tensor(layer_handle, what: int, shape, dtype: torch.dtype, device) -> torch.Tensor:
+    """View a debug tap of the last forward as a tensor (copy)."""
+    p = lib().i64b_moe_tap(layer_handle, what)
+    if not p:
+        raise I64bError(f"tap {what} unavailable")
+    n = 1
+    for s in shape:
+        n *= int(s)
+    out = torch.empty(shape, dtype=dtype, device=device)
+    if n:
+        check(lib().i64b_copy_device(out.data_ptr(), p, n * out.element_size(), stream_ptr(out.device)))
+    return out

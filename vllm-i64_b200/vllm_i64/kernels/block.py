@@ -1,0 +1,156 @@
+"""``I64Block`` — Python owner of one ``i64b_layer`` handle (include/i64b.h): packed weights, routing table,
+workspace and the forward calls.  All device memory is torch-owned; the C side never allocates."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from vllm_i64 import _C
+
+
+class I64Block:
+    def __init__(self, hidden_size: int, num_experts: int, expert_inter: int, shared_inter: int, vocab_size: int,
+                 top_k: int, route_weights: Sequence[float], routed_scale: float, shared_scale: float,
+                 mode: int, device: torch.device):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("I64Block needs a CUDA device: this build has no CPU path")
+        cfg = _C.MoEConfig()
+        cfg.hidden_size, cfg.num_experts, cfg.expert_inter = int(hidden_size), int(num_experts), int(expert_inter)
+        cfg.shared_inter, cfg.vocab_size, cfg.top_k, cfg.mode = int(shared_inter), int(vocab_size), int(top_k), int(mode)
+        for i in range(4):
+            cfg.route_weight[i] = float(route_weights[i]) if i < len(route_weights) else 0.0
+        cfg.routed_scale, cfg.shared_scale = float(routed_scale), float(shared_scale)
+        self.cfg = cfg
+        self.mode = int(mode)
+        self.top_k = int(top_k) if num_experts > 0 else 0
+        self._h = C.c_void_p()
+        _C.check(_C.lib().i64b_moe_create(C.byref(cfg), C.byref(self._h)))
+        self._packed: Optional[torch.Tensor] = None
+        self._table_u8: Optional[torch.Tensor] = None
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                _C.lib().i64b_moe_destroy(h)
+            except Exception:
+                pass
+            self._h = C.c_void_p()
+
+    # ---- parameters
+    def _alloc_packed(self):
+        nbytes = _C.lib().i64b_moe_packed_bytes(self._h)
+        self._packed = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+
+    @staticmethod
+    def _bf16(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        return None if t is None else t.detach().to(torch.bfloat16).contiguous()
+
+    def load_bf16(self, gate, up, down, shared_gate=None, shared_up=None, shared_down=None) -> None:
+        """gate/up ``[E,H,I]``, down ``[E,I,H]``, shared nn.Linear weights ``(out,in)`` (reference layouts)."""
+        with torch.cuda.device(self.device):
+            self._alloc_packed()
+            ts = [self._bf16(t) for t in (gate, up, down, shared_gate, shared_up, shared_down)]
+            _C.check(_C.lib().i64b_moe_load_bf16(self._h, *[_C.ptr(t) for t in ts], self._packed.data_ptr(),
+                                                 _C.stream_ptr(self.device)))
+            self._keep = ts    # inputs must outlive the stream-ordered repack
+
+    def load_w8a8(self, w13_q, w13_s, w2_q, w2_s, sh13_q=None, sh13_s=None, sh2_q=None, sh2_s=None) -> None:
+        """Materialised ``(out,in)`` int8 weights + per-out-row fp32 scales (see include/i64b.h)."""
+        with torch.cuda.device(self.device):
+            self._alloc_packed()
+            ts = [None if t is None else t.detach().contiguous() for t in
+                  (w13_q, w13_s, w2_q, w2_s, sh13_q, sh13_s, sh2_q, sh2_s)]
+            _C.check(_C.lib().i64b_moe_load_w8a8(self._h, *[_C.ptr(t) for t in ts], self._packed.data_ptr(),
+                                                 _C.stream_ptr(self.device)))
+            self._keep = ts
+
+    def set_table(self, table_i64: torch.Tensor) -> None:
+        """``topk_token_to_expert [K,V]`` int64 → uint8 device table."""
+        t = table_i64.detach().to(self.device, torch.int64).contiguous()
+        k, v = t.shape
+        out = torch.empty(k, v, dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _C.check(_C.lib().i64b_pack_table(t.data_ptr(), out.data_ptr(), k, v, max(1, self.cfg.num_experts),
+                                              _C.stream_ptr(self.device)))
+        self._table_u8 = out
+        self._table_src = t
+        _C.check(_C.lib().i64b_moe_set_table(self._h, out.data_ptr()))
+
+    def set_scales(self, route_weights: Sequence[float], routed_scale: float, shared_scale: float) -> None:
+        arr = (C.c_float * 4)(*[float(route_weights[i]) if i < len(route_weights) else 0.0 for i in range(4)])
+        _C.check(_C.lib().i64b_moe_set_scales(self._h, arr, self.top_k, float(routed_scale), float(shared_scale)))
+
+    # ---- forward
+    def _out(self, n: int, out_dtype: torch.dtype) -> torch.Tensor:
+        if out_dtype not in (torch.bfloat16, torch.float32):
+            raise TypeError("output dtype must be bfloat16 or float32")
+        return torch.empty(n, self.cfg.hidden_size, dtype=out_dtype, device=self.device)
+
+    def forward(self, x: torch.Tensor, token_ids: Optional[torch.Tensor], out_dtype=torch.bfloat16,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        _C.require_cuda(x, token_ids)
+        if x.dtype != torch.bfloat16 or not x.is_contiguous():
+            x = x.to(torch.bfloat16).contiguous()
+        n = x.shape[0]
+        if token_ids is not None:
+            if token_ids.dtype != torch.int64 or not token_ids.is_contiguous():
+                token_ids = token_ids.to(torch.int64).contiguous()
+            if token_ids.numel() != n:
+                raise RuntimeError("token_ids must have one id per row of x")
+        if out is None:
+            out = self._out(n, out_dtype)
+        lib = _C.lib()
+        with torch.cuda.device(self.device):
+            ws = _C.workspace(self.device, lib.i64b_moe_workspace_bytes(self._h, n))
+            _C.check(lib.i64b_moe_forward(self._h, x.data_ptr(), _C.ptr(token_ids), out.data_ptr(), _C.dtype_code(out),
+                                          n, ws.data_ptr(), ws.numel(), _C.stream_ptr(self.device)))
+        return out
+
+    def forward_routed(self, x: torch.Tensor, routes: torch.Tensor, route_weights: Sequence[float],
+                       routed_scale: float = 1.0, shared_scale: float = 1.0, use_shared: bool = False,
+                       out_dtype=torch.bfloat16) -> torch.Tensor:
+        """Caller-supplied routes ``[K,N]`` (any integer dtype)."""
+        _C.require_cuda(x, routes)
+        if x.dtype != torch.bfloat16 or not x.is_contiguous():
+            x = x.to(torch.bfloat16).contiguous()
+        r = routes.to(torch.int32).contiguous()
+        if r.dim() == 1:
+            r = r.view(1, -1)
+        k, n = r.shape
+        if n != x.shape[0]:
+            raise RuntimeError("routes must be [K, N] with N == x.shape[0]")
+        out = self._out(n, out_dtype)
+        w = (C.c_float * 4)(*[float(route_weights[i]) if i < len(route_weights) else 0.0 for i in range(4)])
+        lib = _C.lib()
+        with torch.cuda.device(self.device):
+            ws = _C.workspace(self.device, lib.i64b_moe_workspace_bytes_routed(self._h, n, k))
+            _C.check(lib.i64b_moe_forward_routed(self._h, x.data_ptr(), r.data_ptr(), k, w, float(routed_scale),
+                                                 float(shared_scale), int(bool(use_shared)), out.data_ptr(),
+                                                 _C.dtype_code(out), n, ws.data_ptr(), ws.numel(),
+                                                 _C.stream_ptr(self.device)))
+        return out
+
+    def forward_host(self, x_host: torch.Tensor, ids_host: Optional[torch.Tensor], out_host: torch.Tensor,
+                     staging: dict) -> None:
+        """Host-buffer call: H2D + forward + D2H enqueued on the current stream (pinned tensors recommended)."""
+        n = x_host.shape[0]
+        lib = _C.lib()
+        with torch.cuda.device(self.device):
+            ws = _C.workspace(self.device, lib.i64b_moe_workspace_bytes(self._h, n))
+            _C.check(lib.i64b_moe_forward_host(
+                self._h, x_host.data_ptr(), _C.ptr(ids_host), out_host.data_ptr(), _C.dtype_code(out_host), n,
+                staging["x"].data_ptr(), staging["ids"].data_ptr(), staging["out"].data_ptr(), ws.data_ptr(),
+                ws.numel(), _C.stream_ptr(self.device)))
+
+    def make_staging(self, n: int, out_dtype=torch.bfloat16) -> dict:
+        return {"x": torch.empty(n, self.cfg.hidden_size, dtype=torch.bfloat16, device=self.device),
+                "ids": torch.empty(n, dtype=torch.int64, device=self.device),
+                "out": torch.empty(n, self.cfg.hidden_size, dtype=out_dtype, device=self.device)}
+
+    def tap(self, what: int, shape, dtype: torch.dtype) -> torch.Tensor:
+        with torch.cuda.device(self.device):
+            return _C.tap_tensor(self._h, what, shape, dtype, self.device)

@@ -1,0 +1,78 @@
+"""``fused_token_routed_forward{,_int8}`` — kernels/fused_experts.py:29-291 on the grouped tcgen05 GEMMs.
+
+The reference switches between a per-token ``bmm`` (N ≤ ``bmm_threshold``, materialising ``[N,H,2I]`` weights)
+and a chunked loop with ``.item()`` syncs; both compute the same function, so this build has one path (sort-free
+deterministic dispatch → grouped GEMM1+SwiGLU → grouped GEMM2 → un-permute) for every N, CUDA-graph safe.
+Packed weights are cached per (tensor storage, version).
+"""
+from __future__ import annotations
+
+from typing import Dict, Tuple
+
+import torch
+
+from vllm_i64 import _C
+from vllm_i64.kernels.block import I64Block
+
+_CACHE: Dict[Tuple, I64Block] = {}
+_CACHE_MAX = 64
+
+
+def _key(*tensors: torch.Tensor) -> Tuple:
+    return tuple((t.data_ptr(), t._version, tuple(t.shape), t.dtype) for t in tensors)
+
+
+def _cached_block(gate_up_proj: torch.Tensor, down_proj: torch.Tensor, num_experts: int) -> I64Block:
+    key = _key(gate_up_proj, down_proj)
+    blk = _CACHE.get(key)
+    if blk is None:
+        e, h, two_i = gate_up_proj.shape
+        inter = two_i // 2
+        if e != num_experts or down_proj.shape != (e, inter, h):
+            raise RuntimeError("gate_up_proj must be [E,H,2I] and down_proj [E,I,H]")
+        if len(_CACHE) >= _CACHE_MAX:
+            _CACHE.clear()
+        blk = I64Block(h, e, inter, 0, 1, 1, [1.0], 1.0, 1.0, _C.MODE_BF16, gate_up_proj.device)
+        blk.load_bf16(gate_up_proj[:, :, :inter], gate_up_proj[:, :, inter:], down_proj)
+        _CACHE[key] = blk
+    return blk
+
+
+def fused_token_routed_forward(x: torch.Tensor, gate_up_proj: torch.Tensor, down_proj: torch.Tensor,
+                               expert_ids: torch.Tensor, num_experts: int, intermediate_per_tp: int,
+                               bmm_threshold: int = 64) -> torch.Tensor:
+    """``(N,H)`` → ``(N,H)``; ``gate_up_proj [E,H,2I]`` (gate columns first), ``down_proj [E,I,H]``."""
+    if x.shape[0] == 0:
+        return x
+    _C.require_cuda(x, gate_up_proj, down_proj, expert_ids)
+    blk = _cached_block(gate_up_proj, down_proj, num_experts)
+    out = blk.forward_routed(x, expert_ids.view(1, -1), [1.0], 1.0, 1.0, False,
+                             torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32)
+    return out if out.dtype == x.dtype else out.to(x.dtype)
+
+
+def fused_token_routed_forward_int8(x: torch.Tensor, gate_up_int8: torch.Tensor, gate_up_scale: torch.Tensor,
+                                    down_int8: torch.Tensor, down_scale: torch.Tensor, expert_ids: torch.Tensor,
+                                    num_experts: int, intermediate_per_tp: int, bmm_threshold: int = 64
+                                    ) -> torch.Tensor:
+    """Weight-only INT8 with per-K-row scales (``gate_up_scale [E,H]``, ``down_scale [E,I]``,
+    kernels/fused_experts.py:153-291, core/quantization.py:424-454): weights are dequantised once to the compute
+    dtype (exactly what the reference's torch path does each call) and cached, then the bf16 grouped path runs."""
+    if x.shape[0] == 0:
+        return x
+    _C.require_cuda(x, gate_up_int8, down_int8, expert_ids)
+    key = _key(gate_up_int8, gate_up_scale, down_int8, down_scale)
+    blk = _CACHE.get(key)
+    if blk is None:
+        gu = (gate_up_int8.float() * gate_up_scale.unsqueeze(-1).float())
+        dn = (down_int8.float() * down_scale.unsqueeze(-1).float())
+        e, h, two_i = gu.shape
+        inter = two_i // 2
+        if len(_CACHE) >= _CACHE_MAX:
+            _CACHE.clear()
+        blk = I64Block(h, e, inter, 0, 1, 1, [1.0], 1.0, 1.0, _C.MODE_BF16, x.device)
+        blk.load_bf16(gu[:, :, :inter], gu[:, :, inter:], dn)
+        _CACHE[key] = blk
+    out = blk.forward_routed(x, expert_ids.view(1, -1), [1.0], 1.0, 1.0, False,
+                             torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32)
+    return out if out.dtype == x.dtype else out.to(x.dtype)

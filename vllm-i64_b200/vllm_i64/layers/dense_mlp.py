@@ -1,0 +1,117 @@
+"""``DenseMLP`` / ``DenseSwiGLUMLP`` — drop-ins for layers/dense_mlp.py:33-138 and
+models/complexity_deep/model.py:243-276 (the FFN ``dense-306`` runs; BASELINE config 4).
+
+``down(silu(gate(x)) * up(x))`` as two grouped-GEMM launches of the same tcgen05 kernels the MoE block uses
+(one "expert" holding every row): GEMM1 with the SwiGLU epilogue, GEMM2.  ``quantize_w8a8()`` selects the
+reference's ``_forward_int8_fused`` semantics (one activation quant → fused gate|up INT8 GEMM → Q7-LUT SiLU·up →
+re-quant → down INT8 GEMM).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from vllm_i64 import _C
+from vllm_i64.kernels.block import I64Block
+from vllm_i64.parallel.tensor_parallel import ColumnParallelLinear, RowParallelLinear, all_reduce, get_tp
+
+
+class _DenseBlockMixin:
+    quantization = "none"
+    _block: Optional[I64Block] = None
+    _block_key = None
+
+    def _weights(self):
+        raise NotImplementedError
+
+    def _ensure_block(self, device: torch.device) -> I64Block:
+        gate, up, down = self._weights()
+        key = (device, self.quantization, tuple((t.data_ptr(), t._version) for t in (gate, up, down)))
+        if self._block is not None and self._block_key == key:
+            return self._block
+        inter, hidden = gate.shape
+        mode = _C.MODE_W8A8 if self.quantization == "int8" else _C.MODE_BF16
+        blk = I64Block(hidden, 0, 0, inter, 1, 0, [], 1.0, 1.0, mode, device)
+        with torch.no_grad():
+            if mode == _C.MODE_BF16:
+                blk.load_bf16(None, None, None, gate, up, down)
+            else:
+                from vllm_i64.core.quantization import quantize_int8
+                q13, s13 = quantize_int8(torch.cat([gate, up], dim=0).float().contiguous())
+                q2, s2 = quantize_int8(down.float().contiguous())
+                blk.load_w8a8(None, None, None, None, q13, s13, q2, s2)
+        self._block, self._block_key = blk, key
+        return blk
+
+    def quantize_w8a8(self):
+        self.quantization = "int8"
+        self._block = None
+        return self
+
+    def _run(self, x: torch.Tensor) -> torch.Tensor:
+        _C.require_cuda(x)
+        blk = self._ensure_block(x.device)
+        x2 = x.reshape(-1, x.shape[-1])
+        tp = get_tp()
+        if tp.tp_size > 1:
+            out = all_reduce(blk.forward(x2, None, torch.float32))
+            return out.to(x.dtype).reshape(x.shape)
+        odt = torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32
+        out = blk.forward(x2, None, odt)
+        return (out if out.dtype == x.dtype else out.to(x.dtype)).reshape(x.shape)
+
+
+class DenseMLP(_DenseBlockMixin, nn.Module):
+    """TP-aware dense SwiGLU (layers/dense_mlp.py:33-138): gate/up column-parallel, down row-parallel."""
+
+    def __init__(self, hidden_size: int, intermediate_size: int):
+        super().__init__()
+        tp = get_tp()
+        self.hidden_size = hidden_size
+        self.intermediate_size = intermediate_size
+        self.inter_per_tp = intermediate_size // tp.tp_size
+        self.gate_proj = ColumnParallelLinear(hidden_size, intermediate_size, bias=False)
+        self.up_proj = ColumnParallelLinear(hidden_size, intermediate_size, bias=False)
+        self.down_proj = RowParallelLinear(intermediate_size, hidden_size, bias=False)
+
+    def _weights(self):
+        return self.gate_proj.linear.weight, self.up_proj.linear.weight, self.down_proj.linear.weight
+
+    def forward(self, x: torch.Tensor, x_preq=None, **kwargs) -> torch.Tensor:
+        """``x_preq`` (int8, scale) from a fused RMSNorm+quant is accepted for signature compatibility; the block
+        re-derives identical values from ``x`` (same quantisation rule), so it is not needed."""
+        return self._run(x)
+
+
+class DenseSwiGLUMLP(_DenseBlockMixin, nn.Module):
+    """models/complexity_deep/model.py:243-276 (what ``dense-306`` instantiates)."""
+
+    def __init__(self, config):
+        super().__init__()
+        self.gate_proj = nn.Linear(config.hidden_size, config.intermediate_size, bias=False)
+        self.up_proj = nn.Linear(config.hidden_size, config.intermediate_size, bias=False)
+        self.down_proj = nn.Linear(config.intermediate_size, config.hidden_size, bias=False)
+
+    def _weights(self):
+        if hasattr(self, "gate_up_proj"):
+            i = self.gate_up_proj.out_features // 2
+            return self.gate_up_proj.weight[:i], self.gate_up_proj.weight[i:], self.down_proj.weight
+        return self.gate_proj.weight, self.up_proj.weight, self.down_proj.weight
+
+    def forward(self, x, token_ids=None, **kwargs):
+        return self._run(x)
+
+    def fuse_gate_up(self) -> bool:
+        if hasattr(self, "gate_up_proj"):
+            return False
+        fused = nn.Linear(self.gate_proj.in_features, self.gate_proj.out_features + self.up_proj.out_features,
+                          bias=False, device=self.gate_proj.weight.device, dtype=self.gate_proj.weight.dtype)
+        with torch.no_grad():
+            fused.weight.copy_(torch.cat([self.gate_proj.weight, self.up_proj.weight], dim=0))
+        self.gate_up_proj = fused
+        del self.gate_proj
+        del self.up_proj
+        self._block = None
+        return True
