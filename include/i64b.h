@@ -164,6 +164,16 @@ size_t i64b_moe_workspace_bytes(const i64b_layer* layer, int64_t max_tokens);
 int i64b_moe_forward(i64b_layer* layer, const void* x, const int64_t* token_ids, void* out, int out_dtype,
                      int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
 
+/* Run only the selected stages of the forward on the workspace contents left by an earlier full forward with the
+ * same (n, workspace): used by bench.py to time each kernel in isolation (roofline per stage). */
+enum {
+    I64B_STAGE_PLAN = 1, I64B_STAGE_DISPATCH = 2, I64B_STAGE_GEMM1 = 4, I64B_STAGE_REQUANT = 8,
+    I64B_STAGE_GEMM2 = 16, I64B_STAGE_COMBINE = 32, I64B_STAGE_ALL = 0xFF
+};
+int i64b_moe_forward_stages(i64b_layer* layer, const void* x, const int64_t* token_ids, void* out, int out_dtype,
+                            int64_t n, void* workspace, size_t workspace_bytes, unsigned stage_mask,
+                            i64b_stream_t stream);
+
 /* Same block with the routes supplied by the caller: routes int32 [K,N] expert ids (device).  This is the
  * form the reference's kernels package uses — fused_token_routed_forward(x, gate_up, down, expert_ids, ...)
  * (kernels/fused_experts.py:29-150), i64_expert_forward / i64_full_pipeline (kernels/i64_ops.py:100-193),

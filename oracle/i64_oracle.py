@@ -77,21 +77,14 @@ def route_modulo(token_ids: np.ndarray, num_experts: int) -> np.ndarray:
 
 
 def synthetic_hash_table(vocab_size: int, num_experts: int, top_k: int, layer: int) -> np.ndarray:
-    """Layer-specific balanced hash table used as the synthetic stand-in for the
-    checkpoint's ``topk_token_to_expert``; not a reference
-    function (the real tables ship in the checkpoint, core/loader.py:374-387).
-    Pure numpy so that tests, bench and oracle build the same table anywhere."""
-    rng = np.random.RandomState(1000 + layer)
-    perm = rng.permutation(vocab_size)
-    t0 = np.empty(vocab_size, dtype=np.int64)
-    t0[perm] = np.arange(vocab_size, dtype=np.int64) % num_experts
-    rows = [t0]
-    v = np.arange(vocab_size, dtype=np.int64)
-    for r in range(1, top_k):
-        h = (v * 2654435761 + (layer + 1) * 40503 + r * 977) % (2 ** 32)
-        step = 1 + (h >> 7) % max(1, num_experts - 1)
-        rows.append((t0 + step) % num_experts if num_experts > 1 else t0.copy())
-    return np.stack(rows)
+    """Synthetic layer-specific balanced hash table (not a reference function): see tools/synth_data.py."""
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    from tools.synth_data import synthetic_hash_table as gen
+    return gen(vocab_size, num_experts, top_k, layer)
 
 
 # --------------------------------------------------------------------------- #

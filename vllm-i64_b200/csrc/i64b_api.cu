@@ -19,6 +19,10 @@ void i64b_set_error(const char* fmt, ...) {
     va_end(ap);
 }
 void i64b_count_launch(int n) { g_launches += n; }
+bool i64b_pdl_enabled() {
+    static const bool on = !(getenv("I64B_PDL") && atoi(getenv("I64B_PDL")) == 0);
+    return on;
+}
 
 static const int16_t kSiluLutQ7[I64B_SILU_LUT_SIZE] = {
 #include "i64b_silu_lut.inc"
@@ -174,7 +178,7 @@ static int pick_nmma(int64_t m_tiles_r, int n_r, int64_t m_tiles_s, int n_s, boo
     for (int i = 2; i >= 0; --i) {
         const int bn = dual ? kNMmaChoices[i] / 2 : kNMmaChoices[i];
         const int64_t tiles = m_tiles_r * ((n_r + bn - 1) / bn) + m_tiles_s * ((n_s + bn - 1) / bn);
-        if (tiles >= sms) return kNMmaChoices[i];
+        if (2 * tiles >= sms) return kNMmaChoices[i];   // wider tiles re-read fewer activation bytes per weight byte
     }
     return 64;
 }
@@ -322,6 +326,7 @@ struct FwdOpts {
     float routed_scale = 1.0f, shared_scale = 1.0f;
     bool use_shared = true;
     bool override_scales = false;
+    unsigned stage_mask = 0xFFu;            // I64B_STAGE_* bits (per-stage timing replays)
 };
 
 static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_ids, const FwdOpts& o,
@@ -394,8 +399,11 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     pa.expert_inter = I;
     pa.shared_inter = S;
     pa.hidden = H;
-    int rc = i64b_run_plan(pa, cv.plan, s);
-    if (rc) return rc;
+    int rc = I64B_OK;
+    if (o.stage_mask & I64B_STAGE_PLAN) {
+        rc = i64b_run_plan(pa, cv.plan, s);
+        if (rc) return rc;
+    }
 
     // 2. fused (quantize-and-)scatter
     I64bDispatchArgs da = {};
@@ -411,8 +419,10 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.routes_out = cv.routes;
     da.scatter_idx_out = cv.scatter_idx;
     da.dest_row_out = cv.dest_row;
-    rc = i64b_run_dispatch(da, cv.plan, s);
-    if (rc) return rc;
+    if (o.stage_mask & I64B_STAGE_DISPATCH) {
+        rc = i64b_run_dispatch(da, cv.plan, s);
+        if (rc) return rc;
+    }
 
     const int64_t mt_r = E > 0 ? R / 128 + E : 0;     // upper bound on routed m-tiles
     const int64_t mt_s = S > 0 ? (n + 127) / 128 : 0;
@@ -438,9 +448,11 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.silu_lut = L->silu_lut;
         const int wi = nmma_index(n_mma);
         const int64_t tiles = mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
-        rc = i64b_launch_gemm(q, true, n_mma, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
-        if (rc) return rc;
-        if (q) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
+        if (o.stage_mask & I64B_STAGE_GEMM1) {
+            rc = i64b_launch_gemm(q, true, n_mma, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
+            if (rc) return rc;
+        }
+        if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
             if (E > 0) {
                 rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, (I + bn - 1) / bn,
                                           reinterpret_cast<int8_t*>(cv.inter_r), cv.inter_scale_r, nullptr, R, I, s);
@@ -472,9 +484,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.col_scale[1] = L->w2s_scale;
         const int wi = nmma_index(n_mma);
         const int64_t tiles = (mt_r + mt_s) * ((H + n_mma - 1) / n_mma);
-        rc = i64b_launch_gemm(q, false, n_mma, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi], L->tm_w2s[wi], gp, tiles, s);
-        if (rc) return rc;
+        if (o.stage_mask & I64B_STAGE_GEMM2) {
+            rc = i64b_launch_gemm(q, false, n_mma, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi], L->tm_w2s[wi], gp, tiles,
+                                  s);
+            if (rc) return rc;
+        }
     }
+    if (!(o.stage_mask & I64B_STAGE_COMBINE)) return I64B_OK;
 
     // 5. weighted un-permute combine with the shared / routed output scales
     I64bCombineArgs ca = {};
@@ -496,6 +512,14 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
 int i64b_moe_forward(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype, int64_t n,
                      void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
     return moe_forward_impl(L, x, token_ids, FwdOpts(), out, out_dtype, n, workspace, workspace_bytes, stream);
+}
+
+int i64b_moe_forward_stages(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype,
+                            int64_t n, void* workspace, size_t workspace_bytes, unsigned stage_mask,
+                            i64b_stream_t stream) {
+    FwdOpts o;
+    o.stage_mask = stage_mask;
+    return moe_forward_impl(L, x, token_ids, o, out, out_dtype, n, workspace, workspace_bytes, stream);
 }
 
 int i64b_moe_forward_routed(i64b_layer* L, const void* x, const int32_t* routes, int top_k, const float* route_weight,
@@ -576,7 +600,7 @@ static int pick_nmma_single(int64_t m, int64_t n) {
     const int sms = i64b_num_sms();
     const int64_t mt = (m + 127) / 128;
     for (int i = 2; i >= 0; --i)
-        if (mt * ((n + kNMmaChoices[i] - 1) / kNMmaChoices[i]) >= sms) return kNMmaChoices[i];
+        if (2 * mt * ((n + kNMmaChoices[i] - 1) / kNMmaChoices[i]) >= sms) return kNMmaChoices[i];
     return 64;
 }
 

@@ -17,6 +17,7 @@
 // (csrc/i64_expert_dispatch.cu:144-233), the 1-thread-per-output INT8 GEMMs (csrc/I64_gemm.cu:40-126),
 // Triton tl.dot kernels (kernels/triton_fused_expert.py, kernels/triton/I64_int8_gemm.py) and
 // torch._int_mm call sites (core/quantization.py:168-172).
+#include <stdlib.h>
 #include "i64b_gemm.cuh"
 
 namespace {
@@ -66,7 +67,9 @@ __device__ __forceinline__ void decode_tile(int tile, int& g, const int* prefix,
 }
 
 __device__ __forceinline__ float silu_f32(float g) {
-    return g * __frcp_rn(1.0f + __expf(-g));
+    // branch-free: ex2.approx + rcp.approx (an IEEE rcp carries a slow-path branch per element, which serialises
+    // the 32-element chunk on the single epilogue warp of each SM sub-partition)
+    return __fdividef(g, 1.0f + __expf(-g));
 }
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -104,6 +107,14 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    pdl_launch_dependents();      // let the next kernel's CTAs start their prologue as SMs free up
+    const long long t0 = clock64();
+    long long* tl = p.debug_timeline ? p.debug_timeline + (size_t)blockIdx.x * 8 : nullptr;
+    if (tl && threadIdx.x == 0) {
+        unsigned long long gt;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        tl[0] = (long long)gt;
+    }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA0);
@@ -147,6 +158,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
     const int total_tiles = prefix[ng];
+    if (tl && threadIdx.x == 0) tl[1] = clock64() - t0;
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -164,6 +176,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 const int b_row = grp.w_row_base + tc.n_t * kBnOut;
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (tl && kb == 0 && tile == (int)blockIdx.x) tl[2] = clock64() - t0;
                     mbar_arrive_expect_tx(&full_bar[stage], kStageA + kStageB);
                     tma_load_2d(sA + stage * kStageA, ta, &full_bar[stage], kb * kBlockK, a_row,
                                 I64B_L2_EVICT_NORMAL);
@@ -197,6 +210,13 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
+                    if (tl && kb == 0 && tile == (int)blockIdx.x) tl[3] = clock64() - t0;
+                    if (p.debug_flags & 1u) {      // pure TMA streaming: release the slot without touching the tensor core
+                        mbar_arrive(&empty_bar[stage]);
+                        if (kb == nkb - 1) { mbar_arrive(&tfull_bar[as]); if (tl) tl[4] = clock64() - t0; }
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     const uint64_t a_desc = make_sw128_kmajor_desc(sA + stage * kStageA);
                     const uint64_t b_desc = make_sw128_kmajor_desc(sB + stage * kStageB);
 #pragma unroll
@@ -207,7 +227,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                             umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);             // smem slot reusable once these MMAs retire
-                    if (kb == nkb - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
+                    if (kb == nkb - 1) { umma_commit(&tfull_bar[as]); if (tl) tl[4] = clock64() - t0; }   // accumulator complete
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -225,6 +245,13 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const int as = iter & 1;
             mbar_wait(&tfull_bar[as], (iter >> 1) & 1);
             tc_fence_after();
+            if (tl && threadIdx.x == 64) tl[5] = clock64() - t0;
+            if (p.debug_flags & 2u) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty_bar[as]);
+                continue;
+            }
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma;
             const int row_in_group = tc.m_t * kBlockM + r;
             const bool valid = row_in_group < grp.rows;
@@ -364,10 +391,11 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            if (tl && threadIdx.x == 64) tl[6] = clock64() - t0;
         }
     }
+    if (tl && threadIdx.x == 0) tl[7] = clock64() - t0;
 
-    pdl_launch_dependents();
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -403,9 +431,38 @@ int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap&
         I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    kern<<<grid, kThreads, smem, stream>>>(a0, a1, b0, b1, p);
+    static const int dbg_flags = getenv("I64B_DEBUG_FLAGS") ? atoi(getenv("I64B_DEBUG_FLAGS")) : 0;
+    static const bool dbg_tl = getenv("I64B_DEBUG_TIMELINE") != nullptr;
+    if (dbg_flags == 0 && !dbg_tl) {
+        I64B_CUDA(i64b_launch(kern, dim3(grid), dim3(kThreads), smem, stream, a0, a1, b0, b1, p));
+        i64b_count_launch();
+        return I64B_OK;
+    }
+    // ---- bring-up instrumentation only (allocates + synchronises; never active unless the env asks for it)
+    I64bGemmParams q = p;
+    q.debug_flags = (uint32_t)dbg_flags;
+    static long long* d_tl = nullptr;
+    if (dbg_tl && d_tl == nullptr) cudaMalloc(&d_tl, 256 * 8 * sizeof(long long));
+    if (dbg_tl) { cudaMemsetAsync(d_tl, 0, 256 * 8 * sizeof(long long), stream); q.debug_timeline = d_tl; }
+    kern<<<grid, kThreads, smem, stream>>>(a0, a1, b0, b1, q);
     I64B_LAUNCH_CHECK();
     i64b_count_launch();
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cs);
+    if (dbg_tl && cs == cudaStreamCaptureStatusNone) {
+        static int printed = 0;
+        long long h[256 * 8];
+        cudaStreamSynchronize(stream);
+        cudaMemcpy(h, d_tl, sizeof(h), cudaMemcpyDeviceToHost);
+        if (printed++ < 12) {
+            long long g0 = h[0];
+            for (int b = 0; b < grid; ++b) if (h[b * 8] && h[b * 8] < g0) g0 = h[b * 8];
+            fprintf(stderr, "[i64b timeline] int8=%d dual=%d nmma=%d grid=%d\n", (int)kInt8, (int)kDual, kNMma, grid);
+            for (int b = 0; b < grid; b += (grid > 16 ? grid / 8 : 1))
+                fprintf(stderr, "  cta %3d start+%lldns prologue=%lld tma0=%lld full0=%lld lastmma=%lld epi0=%lld epiend=%lld end=%lld (cycles)\n",
+                        b, h[b * 8] - g0, h[b * 8 + 1], h[b * 8 + 2], h[b * 8 + 3], h[b * 8 + 4], h[b * 8 + 5], h[b * 8 + 6], h[b * 8 + 7]);
+        }
+    }
     return I64B_OK;
 }
 

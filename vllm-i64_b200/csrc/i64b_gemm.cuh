@@ -25,6 +25,9 @@ struct I64bGemmParams {
     int32_t* amax_part[2];     // Q14 epilogue: per (row, n_tile) max|q14|
     int32_t amax_ld[2];
     const int16_t* silu_lut;   // device copy of the Q7 SiLU table (2049 entries)
+    // bring-up instrumentation (env I64B_DEBUG_FLAGS / I64B_DEBUG_TIMELINE; never set in production)
+    uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores
+    long long* debug_timeline; // [grid, 8] clock64 offsets per CTA
 };
 
 // Tensor map for a row-major [rows, cols] matrix of 1-byte (int8) or 2-byte (bf16) elements whose

@@ -91,7 +91,7 @@ class I64Block:
         return torch.empty(n, self.cfg.hidden_size, dtype=out_dtype, device=self.device)
 
     def forward(self, x: torch.Tensor, token_ids: Optional[torch.Tensor], out_dtype=torch.bfloat16,
-                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, stages: int = _C.STAGE_ALL) -> torch.Tensor:
         _C.require_cuda(x, token_ids)
         if x.dtype != torch.bfloat16 or not x.is_contiguous():
             x = x.to(torch.bfloat16).contiguous()
@@ -106,8 +106,9 @@ class I64Block:
         lib = _C.lib()
         with torch.cuda.device(self.device):
             ws = _C.workspace(self.device, lib.i64b_moe_workspace_bytes(self._h, n))
-            _C.check(lib.i64b_moe_forward(self._h, x.data_ptr(), _C.ptr(token_ids), out.data_ptr(), _C.dtype_code(out),
-                                          n, ws.data_ptr(), ws.numel(), _C.stream_ptr(self.device)))
+            _C.check(lib.i64b_moe_forward_stages(self._h, x.data_ptr(), _C.ptr(token_ids), out.data_ptr(),
+                                                 _C.dtype_code(out), n, ws.data_ptr(), ws.numel(), int(stages),
+                                                 _C.stream_ptr(self.device)))
         return out
 
     def forward_routed(self, x: torch.Tensor, routes: torch.Tensor, route_weights: Sequence[float],
