@@ -259,6 +259,57 @@ def cpu_reference_run(wl, steps, warmup, mode="int8", max_seconds=25.0, layers_c
                        f", {threads} threads")
 
 
+# ------------------------------------------------------------------------------------------------- expert parallel
+def run_ep(wl, device, rank, world, args):
+    """BASELINE config 5: experts sharded over the ranks, 64K tokens per step in total (strong scaling), NCCL
+    all-to-all over NVLink for the token exchange.  Timed on the device, max over ranks."""
+    import torch.distributed as dist
+    from vllm_i64 import _C
+    from vllm_i64.parallel.expert_parallel import EPTokenRoutedBlock, init_expert_parallel
+    from tools.synth_data import synthetic_hash_table
+    ep = init_expert_parallel()
+    H, E, I, S, V, K = (wl[k] for k in "HEISVK")
+    L = 4
+    n = args.ep_tokens // world
+    blocks = []
+    for layer in range(L):
+        g = torch.Generator(device=device).manual_seed(layer)
+
+        def u(shape, fan_in):
+            return (torch.rand(shape, device=device, generator=g) * 2 - 1) / fan_in ** 0.5
+
+        b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep)
+        b.load_bf16(u((E, H, I), H), u((E, H, I), H), u((E, I, H), I), u((S, H), H), u((S, H), H), u((H, S), S))
+        b.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
+        blocks.append(b)
+    x = torch.randn(n, H, device=device, generator=torch.Generator(device=device).manual_seed(100 + rank)).to(torch.bfloat16)
+    ids = torch.randint(0, V, (n,), device=device, generator=torch.Generator(device=device).manual_seed(200 + rank))
+
+    def step():
+        for b in blocks:
+            b.forward(x, ids, torch.bfloat16)
+
+    steps, warm = max(3, min(args.steps, 20)), 3
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    e1.synchronize()
+    dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0]) / steps
+    sent = n * K * (world - 1) / world * H * 2
+    return {"workload": "tr-hash-moe-500m bf16 expert-parallel", "tokens_per_step_total": n * world,
+            "layers_per_step": L, "ms_per_step": ms, "value": n * world * L / (ms * 1e-3), "unit": UNIT,
+            "scaling": "strong", "a2a_bytes_out_per_rank_per_layer": int(sent), "ep_size": world}
+
+
 # ------------------------------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
@@ -270,6 +321,8 @@ def main():
     ap.add_argument("--cpu-mode", default="int8", choices=["int8", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
+    ap.add_argument("--no-ep", action="store_true")
+    ap.add_argument("--ep-tokens", type=int, default=65536, help="tokens per step over ALL ranks (BASELINE config 5)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
@@ -389,6 +442,10 @@ def main():
         stages_json["_block_min_bytes"] = min_bytes
         stages_json["_block_frac_hbm"] = round(min_bytes / (ms * 1e-3 / (args.steps * L)) / 1e9 / pk["hbm"], 4)
 
+    ep_json = None
+    if world > 1 and wl["E"] and wl["E"] % world == 0 and not args.no_ep:
+        ep_json = run_ep(wl, device, rank, world, args)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         r = cpu_reference_run(wl, steps=3, warmup=1, mode=args.cpu_mode, max_seconds=20.0,
@@ -403,7 +460,7 @@ def main():
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                         "h2d_bytes_per_step": N * H * 2 + N * 8, "d2h_bytes_per_step": N * H * 2},
                 "gpu_launches": int(launches_per_step) * args.steps, "gpu_launches_per_step": int(launches_per_step),
-                "roofline": roof, "stages": stages_json, "cpu_baseline": cpu}
+                "roofline": roof, "stages": stages_json, "cpu_baseline": cpu, "expert_parallel": ep_json}
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist

@@ -91,6 +91,13 @@ int i64b_scatter_rows(const void* x, const int32_t* dest, void* out, int64_t n, 
 int i64b_gather_rows(const void* src, const int32_t* idx, void* out, int64_t n, int64_t row_bytes,
                      i64b_stream_t stream);
 
+/* Weighted un-permute combine: out[t,:] = routed_scale * sum_k w[k] * y[dest_row[k,t],:] + shared_scale *
+ * y_shared[t,:] in the reference's fp32 operation order (layers/token_routed_mlp.py:156-185); y fp32 [rows,H],
+ * y_shared nullable.  Used stand-alone by the expert-parallel path (rows come back from the return all-to-all). */
+int i64b_combine(const float* y, const int32_t* dest_row, const float* y_shared, int top_k, const float* route_weight,
+                 float routed_scale, float shared_scale, void* out, int out_dtype, int64_t n, int hidden,
+                 i64b_stream_t stream);
+
 /* ---------------------------------------------------------------------------
  * Elementwise / quantisation ops  (a9, a12)
  * ------------------------------------------------------------------------- */

@@ -1,0 +1,62 @@
+"""Expert-parallel block on GPUs (NCCL): world_size 1 always, 2 when the box has two devices.  Every rank's output
+must match the single-GPU block on the same tokens (same kernels, so the match is tight) and the oracle."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import i64_test_helpers as Hh
+from oracle import i64_oracle as O
+
+pytestmark = pytest.mark.gpu
+if not torch.cuda.is_available():
+    pytest.skip("CUDA device required", allow_module_level=True)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, case, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from vllm_i64 import _C
+        from vllm_i64.parallel.expert_parallel import EPTokenRoutedBlock, init_expert_parallel
+        ep = init_expert_parallel()
+        h, e, ie, s, v, k, n_total = case
+        cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n_total, seed=8)
+        cuts = np.linspace(0, n_total, world + 1).astype(int)
+        lo, hi = cuts[rank], cuts[rank + 1]
+        t = lambda a, dt=None: (torch.from_numpy(np.ascontiguousarray(a)).to(dev) if dt is None
+                                else torch.from_numpy(np.ascontiguousarray(a)).to(dev).to(dt))
+        blk = EPTokenRoutedBlock(h, e, ie, s, v, k, cfg.route_weights(), cfg.routed_output_scale,
+                                 cfg.shared_output_scale, _C.MODE_BF16, dev, ep)
+        blk.load_bf16(t(w.gate), t(w.up), t(w.down), *((t(w.shared_gate), t(w.shared_up), t(w.shared_down)) if s else ()))
+        blk.set_table(torch.from_numpy(table))
+        out = blk.forward(t(x[lo:hi], torch.bfloat16), t(ids[lo:hi]), torch.float32)
+        ref = O.moe_block_fp32(x[lo:hi], ids[lo:hi], table, w, cfg, inter_bf16=True)
+        mx, mean = O.rel_errors(out.cpu().numpy(), ref)
+        ret[rank] = (mx, mean)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_ep_block_matches_oracle(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), (256, 8, 64, 128, 1000, 2, 700), ret), nprocs=world, join=True)
+    for r in range(world):
+        mx, mean = ret[r]
+        assert mx <= Hh.TOL_MAX and mean <= Hh.TOL_MEAN, (r, mx, mean)

@@ -56,6 +56,7 @@ int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_
 
 struct I64bCombineArgs {
     const float* y;             // [N*K + N, H] fp32 per-assignment outputs (shared rows last)
+    const float* y_shared;      // optional separate [N, H] shared-expert outputs (else rows N*K.. of y)
     const int32_t* dest_row;    // [K, N]
     int64_t n;
     int hidden, top_k, has_shared, has_routed;

@@ -49,6 +49,7 @@ _SIGNATURES = {
     "i64b_dispatch_plan": (_I, [_P, _I, _L, _I, _P, _P, _P, _P, _P, _P, _Z, _P]),
     "i64b_scatter_rows": (_I, [_P, _P, _P, _L, _L, _P]),
     "i64b_gather_rows": (_I, [_P, _P, _P, _L, _L, _P]),
+    "i64b_combine": (_I, [_P, _P, _P, _I, C.POINTER(_F), _F, _F, _P, _I, _L, _I, _P]),
     "i64b_silu_hadamard": (_I, [_P, _P, _L, _I, _I, _P]),
     "i64b_quantize_rows_int8": (_I, [_P, _I, _P, _P, _L, _L, _P]),
     "i64b_dequantize_int8": (_I, [_P, _P, _P, _L, _L, _P]),

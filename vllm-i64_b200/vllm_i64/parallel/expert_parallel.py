@@ -1,0 +1,186 @@
+"""Expert parallelism for the token-routed MoE block (BASELINE config 5).
+
+Behavioural spec: ``TokenRoutedMLP._forward_ep`` of the reference's vLLM-fork copy
+(layers/token_routed_i64/layer.py:209-298 — not importable in the reference tree): experts are block-partitioned
+over the EP group (``rank = expert_id // local_E``, :227), tokens stay data-parallel, one all-to-all carries the
+dispatched rows to the owning ranks and one carries the expert outputs back.  Differences from the reference:
+
+  * top-k routes (the reference EP path is top-1 only) — every (route, token) assignment is exchanged;
+  * the deterministic dispatch plan (stable by destination rank, then assignment index) replaces argsort;
+  * expert ids ride along as int32; the shared expert and the weighted combine run on the token's home rank, so the
+    shared expert's GEMMs overlap the dispatch exchange on a side stream;
+  * local expert compute is ONE grouped-GEMM block call (``I64Block.forward_routed``), not a per-expert loop.
+
+The exchange uses ``torch.distributed.all_to_all_single`` (NCCL over NVLink/NVSwitch on GPUs; gloo in the CPU unit
+tests, where the expert compute is injected).  Split sizes are exchanged first, like the reference (:230-247).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass
+class EPState:
+    ep_size: int = 1
+    ep_rank: int = 0
+    group: Optional[dist.ProcessGroup] = None
+
+
+_EP = EPState()
+
+
+def get_ep() -> EPState:
+    return _EP
+
+
+def init_expert_parallel(ep_size: Optional[int] = None, group: Optional[dist.ProcessGroup] = None) -> EPState:
+    """EP group = all ranks of ``group`` (default: the world).  ``dist`` must be initialised."""
+    global _EP
+    if not dist.is_initialized():
+        _EP = EPState()
+        return _EP
+    size = dist.get_world_size(group)
+    if ep_size is not None and ep_size != size:
+        raise ValueError(f"ep_size {ep_size} != group size {size}")
+    _EP = EPState(ep_size=size, ep_rank=dist.get_rank(group), group=group)
+    return _EP
+
+
+def local_expert_range(num_experts: int, ep: Optional[EPState] = None):
+    """Block partition ``e -> rank e // (E / G)`` (layers/token_routed_i64/layer.py:84-88)."""
+    ep = ep or _EP
+    if num_experts % ep.ep_size != 0:
+        raise ValueError(f"num_experts ({num_experts}) must be divisible by ep_size ({ep.ep_size})")
+    local = num_experts // ep.ep_size
+    return ep.ep_rank * local, local
+
+
+@dataclass
+class ExchangePlan:
+    order: torch.Tensor          # [A] assignment index (k*N + t) in send order (stable by destination rank)
+    send_counts: List[int]       # rows to each rank
+    recv_counts: List[int]       # rows from each rank
+
+
+def make_exchange_plan(routes: torch.Tensor, num_experts: int, ep: EPState) -> ExchangePlan:
+    """routes ``[K,N]`` (expert ids) → deterministic send order + split sizes (counts all-to-all, :230-247)."""
+    local = num_experts // ep.ep_size
+    dest = (routes.reshape(-1).to(torch.int64) // local)
+    order = torch.argsort(dest, stable=True)
+    send = torch.bincount(dest, minlength=ep.ep_size).to(torch.int64)
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv, send, group=ep.group)
+    return ExchangePlan(order, send.tolist(), recv.tolist())
+
+
+def ep_moe_forward(x: torch.Tensor, routes: torch.Tensor, num_experts: int,
+                   local_expert_fn: Callable[[torch.Tensor, torch.Tensor], torch.Tensor],
+                   combine_fn: Callable[[torch.Tensor, torch.Tensor], torch.Tensor],
+                   shared_fn: Optional[Callable[[torch.Tensor], torch.Tensor]] = None,
+                   ep: Optional[EPState] = None, return_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """One expert-parallel MoE FFN forward on this rank's tokens.
+
+    ``local_expert_fn(rows [M,H], local_ids [M]) -> [M,H]`` runs this rank's experts on the received rows;
+    ``combine_fn(y [K*N,H] in assignment order (k*N+t), shared [N,H] | None) -> [N,H]`` applies the route weights
+    and output scales; ``shared_fn(x) -> [N,H]`` is the replicated shared expert (overlaps the exchange).
+    """
+    ep = ep or _EP
+    k, n = routes.shape
+    h = x.shape[1]
+    plan = make_exchange_plan(routes, num_experts, ep)
+    local = num_experts // ep.ep_size
+    tok = plan.order % n
+    send_x = x.index_select(0, tok)
+    send_e = routes.reshape(-1).index_select(0, plan.order).to(torch.int32)
+    m = sum(plan.recv_counts)
+    recv_x = torch.empty(m, h, dtype=x.dtype, device=x.device)
+    recv_e = torch.empty(m, dtype=torch.int32, device=x.device)
+
+    side = None
+    shared = None
+    if shared_fn is not None and x.is_cuda:
+        side = torch.cuda.Stream(x.device)
+        side.wait_stream(torch.cuda.current_stream(x.device))
+        with torch.cuda.stream(side):
+            shared = shared_fn(x)
+    dist.all_to_all_single(recv_x, send_x, plan.recv_counts, plan.send_counts, group=ep.group)
+    dist.all_to_all_single(recv_e, send_e, plan.recv_counts, plan.send_counts, group=ep.group)
+    if shared_fn is not None and side is None:
+        shared = shared_fn(x)
+
+    y_recv = local_expert_fn(recv_x, recv_e - ep.ep_rank * local).to(return_dtype)
+    y_back = torch.empty(k * n, h, dtype=return_dtype, device=x.device)
+    dist.all_to_all_single(y_back, y_recv.contiguous(), plan.send_counts, plan.recv_counts, group=ep.group)
+    y = torch.empty_like(y_back)
+    y.index_copy_(0, plan.order, y_back)                    # un-sort to assignment order (layer.py:294-295)
+    if side is not None:
+        torch.cuda.current_stream(x.device).wait_stream(side)
+        shared.record_stream(torch.cuda.current_stream(x.device))
+    return combine_fn(y, shared)
+
+
+class EPTokenRoutedBlock:
+    """The block with its routed experts sharded over the EP group (GPU).  Holds two C-ABI blocks: the local
+    experts (E/G of them, no shared expert) and the replicated dense shared expert."""
+
+    def __init__(self, hidden_size: int, num_experts: int, expert_inter: int, shared_inter: int, vocab_size: int,
+                 top_k: int, route_weights: Sequence[float], routed_scale: float, shared_scale: float, mode: int,
+                 device: torch.device, ep: Optional[EPState] = None):
+        from vllm_i64.kernels.block import I64Block
+        self.ep = ep or _EP
+        self.E, self.K, self.H = num_experts, top_k, hidden_size
+        self.first, self.local_E = local_expert_range(num_experts, self.ep)
+        self.w, self.rs, self.ss = list(route_weights), routed_scale, shared_scale
+        self.device = torch.device(device)
+        self.router = I64Block(hidden_size, num_experts, expert_inter, 0, vocab_size, top_k, route_weights, 1.0, 1.0,
+                               mode, device)               # routing table owner (no weights loaded)
+        self.local = I64Block(hidden_size, self.local_E, expert_inter, 0, 1, 1, [1.0], 1.0, 1.0, mode, device)
+        self.shared = (I64Block(hidden_size, 0, 0, shared_inter, 1, 0, [], 1.0, 1.0, mode, device)
+                       if shared_inter > 0 else None)
+        self._table = None
+
+    def load_bf16(self, gate, up, down, shared_gate=None, shared_up=None, shared_down=None) -> None:
+        """FULL reference-layout weights; this rank keeps experts [first, first + local_E) and the shared expert."""
+        lo, hi = self.first, self.first + self.local_E
+        self.local.load_bf16(gate[lo:hi], up[lo:hi], down[lo:hi])
+        if self.shared is not None:
+            self.shared.load_bf16(None, None, None, shared_gate, shared_up, shared_down)
+
+    def set_table(self, table_i64: torch.Tensor) -> None:
+        self.router.set_table(table_i64)
+        self._table = self.router._table_u8
+
+    def route(self, token_ids: torch.Tensor) -> torch.Tensor:
+        from vllm_i64 import _C
+        n = token_ids.numel()
+        out = torch.empty(self.K, n, dtype=torch.int64, device=self.device)
+        _C.check(_C.lib().i64b_route_table(token_ids.data_ptr(), self._table.data_ptr(), out.data_ptr(), n,
+                                           self.router.cfg.vocab_size, self.K, self.E, _C.stream_ptr(self.device)))
+        return out
+
+    def forward(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16) -> torch.Tensor:
+        from vllm_i64 import _C
+        n = x.shape[0]
+        routes = self.route(token_ids)
+
+        def local_fn(rows, ids):
+            if rows.shape[0] == 0:
+                return torch.empty(0, self.H, dtype=torch.float32, device=self.device)
+            return self.local.forward_routed(rows, ids.view(1, -1), [1.0], 1.0, 1.0, False, torch.float32)
+
+        def shared_fn(xx):
+            return self.shared.forward(xx, None, torch.float32)
+
+        def combine(y, shared):
+            out = torch.empty(n, self.H, dtype=out_dtype, device=self.device)
+            dest = torch.arange(self.K * n, dtype=torch.int32, device=self.device)      # y is in assignment order
+            wts = (_C.C.c_float * 4)(*[self.w[i] if i < len(self.w) else 0.0 for i in range(4)])
+            _C.check(_C.lib().i64b_combine(y.data_ptr(), dest.data_ptr(), _C.ptr(shared), self.K, wts, self.rs, self.ss,
+                                           out.data_ptr(), _C.dtype_code(out), n, self.H, _C.stream_ptr(self.device)))
+            return out
+
+        return ep_moe_forward(x, routes, self.E, local_fn, combine, shared_fn if self.shared else None, self.ep)
