@@ -433,7 +433,18 @@ def main():
             roof = {"kernel": dom, "bound": "tensor", "achieved": d[key], "peak": peak,
                     "unit": "TFLOP/s" if wl["mode"] == "bf16" else "TOP/s", "frac": round(d[key] / peak, 4),
                     "traffic": None, "peak_source": pk["src"] + (" bf16 burst x2 (nominal INT8:bf16 ratio)" if wl["mode"] == "int8" else " bf16 burst")}
-        sum_us = sum(v["us_per_launch"] for v in stages_json.values())
+        if layers[0].uses_fused(N):
+            # the step runs ONE fused kernel per layer; the stage list above is the unfused chain, for comparison
+            us = ms * 1e3 / (args.steps * L)
+            a_ = 1 if wl["mode"] == "int8" else 2
+            fb = ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * H * a_) + N * H * 2 * 2
+            gbs = fb / (us * 1e-6) / 1e9
+            roof = {"kernel": "i64b_fused_layer_kernel", "bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"],
+                    "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4), "traffic": None,
+                    "peak_source": pk["src"] + " (burst copy)", "algorithmic_bytes": fb, "us_per_launch": round(us, 3)}
+            stages_json = {"unfused_chain_for_comparison": stages_json}
+            stages_json["_step_us_per_layer"] = round(us, 2)
+        sum_us = sum(v["us_per_launch"] for v in stages_json.values() if isinstance(v, dict) and "us_per_launch" in v)
         stages_json["_sum_us_per_layer"] = round(sum_us, 2)
         stages_json["_step_us_per_layer"] = round(ms * 1e3 / (args.steps * L), 2)
         # whole-block HBM roofline: algorithmic minimum bytes of the fused block per layer

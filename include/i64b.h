@@ -171,6 +171,10 @@ size_t i64b_moe_workspace_bytes(const i64b_layer* layer, int64_t max_tokens);
 int i64b_moe_forward(i64b_layer* layer, const void* x, const int64_t* token_ids, void* out, int out_dtype,
                      int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
 
+/* 1 if i64b_moe_forward on n tokens takes the single-launch fused decode kernel (bf16, n <= 1024; env
+ * I64B_FUSED=0 disables it), else 0 (plan / dispatch / GEMM1 / GEMM2 / combine as separate launches). */
+int i64b_moe_uses_fused(const i64b_layer* layer, int64_t n);
+
 /* Run only the selected stages of the forward on the workspace contents left by an earlier full forward with the
  * same (n, workspace): used by bench.py to time each kernel in isolation (roofline per stage). */
 enum {

@@ -444,7 +444,8 @@ def test_host_buffer_call_and_launch_count():
     _C.launch_count_reset()
     blk.forward_host(xh, ih, oh, st)
     torch.cuda.synchronize()
-    assert _C.launch_count() == 5                       # plan, dispatch, GEMM1, GEMM2, combine
+    # one fused launch for decode-sized bf16 batches; plan, dispatch, GEMM1, GEMM2, combine otherwise
+    assert _C.launch_count() == (1 if blk.uses_fused(300) else 5)
     dev = blk.forward(xh.cuda(), ih.cuda(), torch.bfloat16)
     assert torch.equal(oh.cuda(), dev)
 

@@ -5,6 +5,7 @@
 #include <new>
 #include <stdlib.h>
 
+#include "i64b_fused.cuh"
 #include "i64b_gemm.cuh"
 #include "i64b_plan.cuh"
 
@@ -50,6 +51,7 @@ struct i64b_layer {
     float* w2r_scale = nullptr;
     float* w2s_scale = nullptr;
     int16_t* silu_lut = nullptr;
+    int* sync = nullptr;         // fused-kernel counters (persistent, zero between launches)
     const uint8_t* table = nullptr;
     bool loaded = false;
     CUtensorMap tm_w13[3], tm_w2r[3], tm_w2s[3];   // per n_mma choice (box rows differ)
@@ -86,6 +88,7 @@ static void carve_packed(i64b_layer* L, uint8_t* base, size_t* total) {
     L->w2r_scale = reinterpret_cast<float*>(take(sizeof(float) * c.num_experts * c.hidden_size));
     L->w2s_scale = reinterpret_cast<float*>(take(sizeof(float) * c.hidden_size));
     L->silu_lut = reinterpret_cast<int16_t*>(take(sizeof(int16_t) * I64B_SILU_LUT_SIZE));
+    L->sync = reinterpret_cast<int*>(take(sizeof(int) * I64B_SYNC_INTS));
     if (total) *total = off;
 }
 
@@ -118,7 +121,8 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
     cv.q14_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * c.shared_inter : 0));
     cv.amax_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * cv.amax_ld_r : 0));
     cv.amax_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * cv.amax_ld_s : 0));
-    cv.y = reinterpret_cast<float*>(take(sizeof(float) * T * c.hidden_size));
+    const int64_t slabs = c.shared_inter > 0 ? (c.shared_inter + 511) / 512 : 1;
+    cv.y = reinterpret_cast<float*>(take(sizeof(float) * (R + slabs * nn) * c.hidden_size));
     cv.bytes = off;
     return cv;
 }
@@ -268,6 +272,7 @@ int i64b_moe_load_bf16(i64b_layer* L, const void* gate, const void* up, const vo
         I64B_CUDA(cudaMemcpyAsync(sh + (size_t)S * H * 2, shared_up, (size_t)S * H * 2, cudaMemcpyDeviceToDevice, s));
         I64B_CUDA(cudaMemcpyAsync(L->w2s, shared_down, (size_t)H * S * 2, cudaMemcpyDeviceToDevice, s));
     }
+    I64B_CUDA(cudaMemsetAsync(L->sync, 0, sizeof(int) * I64B_SYNC_INTS, s));
     int rc = encode_weight_maps(L);
     if (rc) return rc;
     L->loaded = true;
@@ -301,6 +306,7 @@ int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, c
         I64B_CUDA(cudaMemcpyAsync(L->w2s_scale, sh2_s, sizeof(float) * H, dd, s));
     }
     I64B_CUDA(cudaMemcpyAsync(L->silu_lut, kSiluLutQ7, sizeof(kSiluLutQ7), cudaMemcpyHostToDevice, s));
+    I64B_CUDA(cudaMemsetAsync(L->sync, 0, sizeof(int) * I64B_SYNC_INTS, s));
     int rc = encode_weight_maps(L);
     if (rc) return rc;
     L->loaded = true;
@@ -317,6 +323,11 @@ int i64b_moe_set_table(i64b_layer* L, const uint8_t* table_u8) {
 size_t i64b_moe_workspace_bytes(const i64b_layer* L, int64_t max_tokens) {
     if (!L) return 0;
     return carve_ws(L, nullptr, max_tokens).bytes + 1024;
+}
+
+static bool fused_enabled() {
+    static const bool on = !(getenv("I64B_FUSED") && atoi(getenv("I64B_FUSED")) == 0);
+    return on;
 }
 
 struct FwdOpts {
@@ -385,6 +396,24 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         L->cached_n = cache_key;
     }
     L->cv = cv;
+
+    // decode-sized bf16 batches: the whole layer in ONE persistent launch (csrc/i64b_fused.cu)
+    if (fused_enabled() && !q && given_routes == nullptr && o.stage_mask == 0xFFu &&
+        i64b_fused_supported((int)n, H, I, S, E, K)) {
+        I64bFusedParams fp = {};
+        fp.x = x;
+        fp.token_ids = token_ids;
+        fp.table = L->table;
+        fp.n = (int)n; fp.hidden = H; fp.num_experts = E; fp.expert_inter = I; fp.shared_inter = S; fp.top_k = K;
+        fp.vocab = c.vocab_size; fp.out_dtype = out_dtype;
+        for (int k = 0; k < I64B_MAX_TOPK; ++k) fp.w[k] = k < K ? c.route_weight[k] : 0.0f;
+        fp.routed_scale = c.routed_scale; fp.shared_scale = c.shared_scale;
+        fp.xs = cv.xs; fp.inter_r = cv.inter_r; fp.inter_s = cv.inter_s; fp.y = cv.y; fp.out = out;
+        fp.sync = L->sync;
+        fp.tap_routes = cv.routes; fp.tap_dest = cv.dest_row; fp.tap_scatter = cv.scatter_idx;
+        fp.tap_counts = cv.plan.counts; fp.tap_offsets = cv.plan.offsets;
+        return i64b_launch_fused(L->tm_xs, L->tm_w13[1], L->tm_inter_r, L->tm_inter_s, L->tm_w2r[1], L->tm_w2s[1], fp, s);
+    }
 
     // 1. routing + deterministic dispatch plan + GEMM group tables (device-resident, no host sync)
     I64bPlanArgs pa = {};
@@ -512,6 +541,12 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
 int i64b_moe_forward(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype, int64_t n,
                      void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
     return moe_forward_impl(L, x, token_ids, FwdOpts(), out, out_dtype, n, workspace, workspace_bytes, stream);
+}
+
+int i64b_moe_uses_fused(const i64b_layer* L, int64_t n) {
+    if (!L || !L->loaded || L->cfg.mode != I64B_MODE_BF16 || !fused_enabled() || n > (1 << 20)) return 0;
+    const i64b_moe_config& c = L->cfg;
+    return i64b_fused_supported((int)n, c.hidden_size, c.expert_inter, c.shared_inter, c.num_experts, c.top_k);
 }
 
 int i64b_moe_forward_stages(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype,

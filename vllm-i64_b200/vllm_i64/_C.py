@@ -62,6 +62,7 @@ _SIGNATURES = {
     "i64b_moe_set_table": (_I, [_P, _P]),
     "i64b_moe_workspace_bytes": (_Z, [_P, _L]),
     "i64b_moe_forward": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, _P]),
+    "i64b_moe_uses_fused": (_I, [_P, _L]),
     "i64b_moe_forward_stages": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, C.c_uint, _P]),
     "i64b_moe_forward_routed": (_I, [_P, _P, _P, _I, C.POINTER(_F), _F, _F, _I, _P, _I, _L, _P, _Z, _P]),
     "i64b_moe_workspace_bytes_routed": (_Z, [_P, _L, _I]),

@@ -111,6 +111,9 @@ class I64Block:
                                                  _C.stream_ptr(self.device)))
         return out
 
+    def uses_fused(self, n: int) -> bool:
+        return bool(_C.lib().i64b_moe_uses_fused(self._h, int(n)))
+
     def forward_routed(self, x: torch.Tensor, routes: torch.Tensor, route_weights: Sequence[float],
                        routed_scale: float = 1.0, shared_scale: float = 1.0, use_shared: bool = False,
                        out_dtype=torch.bfloat16) -> torch.Tensor:
