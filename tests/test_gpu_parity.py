@@ -195,6 +195,9 @@ BLOCK_CASES = [
     (1024, 4, 768, 1024, 32000, 2, 1500),  # tr-moe-306
     (512, 16, 48, 0, 5000, 1, 777),        # no shared expert, top-1, ragged widths
     (256, 4, 64, 96, 700, 3, 130),         # top-3
+    (1024, 4, 768, 1024, 32000, 2, 256),   # tr-moe-306 decode (fused kernel, I_e > one K slab)
+    (256, 4, 64, 96, 700, 3, 700),         # fused kernel, several 128-row passes per expert
+    (192, 8, 48, 80, 900, 2, 1),           # single token
 ]
 
 
@@ -221,6 +224,11 @@ def test_block_bf16_vs_oracle(case):
     blk = Hh.build_gpu_block(cfg, w, table, "bf16")
     out = blk.forward(cu(x, torch.bfloat16), cu(ids), torch.float32)
     routes, lay = _plan_checks(blk, cfg, table, ids, n)
+    if blk.uses_fused(n):
+        # the fused decode kernel gathers A rows inside the GEMM (no dispatched-row buffer): check the stand-alone
+        # plan + dispatch stages, which the unfused chain and the reference-convention scatter op use
+        blk.forward(cu(x, torch.bfloat16), cu(ids), torch.float32, stages=_C.STAGE_PLAN | _C.STAGE_DISPATCH)
+        _plan_checks(blk, cfg, table, ids, n)
     xs = blk.tap(_C.TAP_XS, (n * k + (n if s else 0), h), torch.bfloat16).float().cpu().numpy()
     for r in range(k):                                          # dispatched rows are exact copies
         np.testing.assert_array_equal(xs[lay.dest_row[r]], x)

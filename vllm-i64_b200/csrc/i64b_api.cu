@@ -59,6 +59,9 @@ struct i64b_layer {
     void* cached_ws = nullptr;
     int64_t cached_n = -1;
     CUtensorMap tm_xs, tm_inter_r, tm_inter_s;
+    const void* cached_x = nullptr;   // fused decode kernel: maps over the caller's x
+    int64_t cached_x_n = -1;
+    CUtensorMap tm_x;
     // carve of the last forward (debug taps)
     struct Carve {
         I64bPlanWs plan;
@@ -408,11 +411,18 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         fp.vocab = c.vocab_size; fp.out_dtype = out_dtype;
         for (int k = 0; k < I64B_MAX_TOPK; ++k) fp.w[k] = k < K ? c.route_weight[k] : 0.0f;
         fp.routed_scale = c.routed_scale; fp.shared_scale = c.shared_scale;
-        fp.xs = cv.xs; fp.inter_r = cv.inter_r; fp.inter_s = cv.inter_s; fp.y = cv.y; fp.out = out;
+        fp.inter_r = cv.inter_r; fp.inter_s = cv.inter_s; fp.y = cv.y; fp.out = out;
         fp.sync = L->sync;
         fp.tap_routes = cv.routes; fp.tap_dest = cv.dest_row; fp.tap_scatter = cv.scatter_idx;
         fp.tap_counts = cv.plan.counts; fp.tap_offsets = cv.plan.offsets;
-        return i64b_launch_fused(L->tm_xs, L->tm_w13[1], L->tm_inter_r, L->tm_inter_s, L->tm_w2r[1], L->tm_w2s[1], fp, s);
+        // tensor map over the caller's x (128-row tiles for the shared expert's GEMM1)
+        if (L->cached_x != x || L->cached_x_n != n) {
+            int rc = i64b_encode_tmap(&L->tm_x, x, false, n, H, (int64_t)H * 2, 128);
+            if (rc) return rc;
+            L->cached_x = x;
+            L->cached_x_n = n;
+        }
+        return i64b_launch_fused(L->tm_x, L->tm_w13[1], L->tm_inter_r, L->tm_inter_s, L->tm_w2r[1], L->tm_w2s[1], fp, s);
     }
 
     // 1. routing + deterministic dispatch plan + GEMM group tables (device-resident, no host sync)

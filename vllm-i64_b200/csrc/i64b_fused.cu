@@ -1,51 +1,116 @@
 // Fused decode-sized MoE FFN layer: ONE persistent launch (one CTA per SM) runs
-//   plan (redundantly per CTA, N ≤ 1024) → row dispatch → grouped GEMM1 + SwiGLU → grouped GEMM2 → weighted combine
-// with device-side dependencies instead of kernel boundaries.  Decode is bound by streaming the layer's weights from
-// HBM; separate kernels pay prologue + first-byte latency + tail five times per layer and stop the stream at every
-// boundary.  Here the TMA producer keeps prefetching WEIGHT tiles (which depend on nothing) across the
-// dispatch→GEMM1 and GEMM1→GEMM2 dependencies; only the activation tiles wait on the global counters.
+//   route + plan (per CTA, in shared memory) → grouped GEMM1 + SwiGLU → grouped GEMM2 → weighted combine
+// with device-side dependencies instead of kernel boundaries.
 //
-// Semantics are identical to the unfused chain (same plan, same tile math, same combine order), so the same parity
-// tests cover both.  Reference functions covered: layers/token_routed_mlp.py:113-187 (route, expert_forward, forward).
+// Decode is bound by streaming the layer's weights from HBM exactly once, so the kernel is organised around the
+// WEIGHT stream:
+//   * the work list is STATIC (independent of the routing): unit = one 128-row weight tile of one expert (or of the
+//     shared expert) over its whole K range.  Every CTA therefore knows at entry which weight bytes it will need and
+//     its TMA thread starts pulling them before the plan exists, before the previous kernel has finished (weights
+//     are constants: the loads sit above griddepcontrol.wait) and across the GEMM1→GEMM2 dependency;
+//   * there is no dispatch pass and no dispatched-row buffer: four gather warps copy the A rows of a routed GEMM1
+//     tile straight from x into the 128B-swizzled stage (cp.async, 16 B per lane, four full 128-byte lines per warp
+//     instruction, completion signalled on the stage's mbarrier by cp.async.mbarrier.arrive) using the plan's
+//     expert-sorted token list, so GEMM1 depends only on the CTA-local plan (TMA tile::gather4 was measured at
+//     1.5x the time per k-block: 512-byte requests are too small for the TMA unit);
+//   * the only grid-wide dependencies left are GEMM1→GEMM2 (per expert / per shared m-tile counters) and
+//     GEMM2→combine (one counter); the last CTA to leave resets them, so back-to-back launches need no memset.
+// An expert that owns more than 128 rows is processed in passes of 128 rows; its weight tile is streamed again for
+// every pass (from L2).  Semantics (plan, tile math, combine order) match the unfused chain; the same parity tests
+// cover both.  Reference functions covered: layers/token_routed_mlp.py:113-187 (route, expert_forward, forward).
 #include <cuda.h>
+#include <stdlib.h>
 #include "i64b_fused.cuh"
 
 namespace {
 
-constexpr int kThreads = 256;          // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue, warps 6-7 helpers
-constexpr int kWarps = kThreads / 32;
+constexpr int kThreads = 352;          // warp 0 weight TMA, 1 MMA, 2-5 epilogue, 6-9 A-row gather, 10 activation TMA
+constexpr int kPlanWarps = 8;          // warps 2-9 build the plan before taking their roles
+constexpr int kGatherThreads = 128;
 constexpr int kBlockM = 128;
 constexpr int kNMma = 128;             // UMMA N for both GEMMs (GEMM1: 64 gate + 64 up)
-constexpr int kBn1 = 64;               // intermediate columns per GEMM1 tile
+constexpr int kBn1 = 64;               // intermediate columns per GEMM1 unit
 constexpr int kBlockK = 64;            // bf16 elements per 128-byte swizzle row
 constexpr int kStageA = kBlockM * 128;
 constexpr int kStageB = kNMma * 128;
-constexpr int kStages = 5;
-constexpr int kSlabK = 512;            // GEMM2 split-K slab (keeps every GEMM2 tile at ≤ 8 k-blocks)
+constexpr int kStages = 6;
+constexpr int kSlabK = 512;            // split-K slab of the shared down-projection
 constexpr uint32_t kTmemCols = 2 * kNMma;
 constexpr int kMaxTok = I64B_FUSED_MAX_TOKENS;
-constexpr int kMaxMTiles = I64B_FUSED_MAX_MTILES;
 
 struct Smem {
     uint64_t full_bar[kStages], empty_bar[kStages], tfull_bar[2], tempty_bar[2];
-    uint32_t tmem_ptr, pad;
-    int group_rows[I64B_MAX_GROUPS];      // rows per group (experts, then shared)
-    int group_start[I64B_MAX_GROUPS + 1]; // first xs / y row of each group
-    int mt_prefix[I64B_MAX_GROUPS + 1];   // m-tiles before each group
-    int t1_prefix[I64B_MAX_GROUPS + 1];   // GEMM1 tiles before each group
-    int t2_prefix[I64B_MAX_GROUPS + 1];   // GEMM2 tiles before each group
+    uint32_t tmem_ptr;
+    uint32_t b_seq;                          // weight stages issued so far (release/acquire, CTA scope)
+    int group_rows[I64B_MAX_EXPERTS];        // routed rows per expert
+    int group_start[I64B_MAX_EXPERTS + 1];   // first inter_r / y row of each expert; [E] = N*K
     int route_base[I64B_MAX_BINS];
     int offsets[I64B_MAX_BINS];
-    int warp_cnt[kWarps][I64B_MAX_BINS];
-    uint16_t dest_row[I64B_MAX_TOPK][kMaxTok];
+    uint16_t warp_cnt[kPlanWarps][I64B_MAX_BINS];
+    uint16_t dest_row[I64B_MAX_TOPK][kMaxTok];          // merged expert-major row of assignment (k, t)
+    uint16_t src_tok[I64B_MAX_TOPK * kMaxTok];          // inverse: token of merged row
     uint8_t expert[I64B_MAX_TOPK][kMaxTok];
 };
 
-struct Tile {
-    int type;      // 1 = GEMM1, 2 = GEMM2
-    int g, m_t, n_t, slab;
-    int nkb;
+// static work list
+struct Geo {
+    int nkb_h;                 // k-blocks over H
+    int nt1r, U1r;             // GEMM1 routed: n-tiles per expert, units
+    int mts, nt1s, U1;         // shared m-tiles, GEMM1 shared n-tiles, total GEMM1 units
+    int nt2, U2r, slabs, U2;   // GEMM2 n-tiles, routed units, shared K slabs, total GEMM2 units
+    int U;
 };
+enum { kG1Routed = 0, kG1Shared = 1, kG2Routed = 2, kG2Shared = 3 };
+struct Unit {
+    int type, g, n_t, m_t, slab, nkb;
+};
+
+__device__ __forceinline__ Geo make_geo(const I64bFusedParams& p) {
+    Geo g;
+    const int E = p.num_experts;
+    g.nkb_h = (p.hidden + kBlockK - 1) / kBlockK;
+    g.nt1r = E > 0 ? (p.expert_inter + kBn1 - 1) / kBn1 : 0;
+    g.U1r = E * g.nt1r;
+    g.mts = p.shared_inter > 0 ? (p.n + kBlockM - 1) / kBlockM : 0;
+    g.nt1s = p.shared_inter > 0 ? (p.shared_inter + kBn1 - 1) / kBn1 : 0;
+    g.U1 = g.U1r + g.mts * g.nt1s;
+    g.nt2 = (p.hidden + kNMma - 1) / kNMma;
+    g.U2r = E * g.nt2;
+    g.slabs = p.shared_inter > 0 ? (p.shared_inter + kSlabK - 1) / kSlabK : 0;
+    g.U2 = g.U2r + g.mts * g.nt2 * g.slabs;
+    g.U = g.U1 + g.U2;
+    return g;
+}
+
+__device__ __noinline__ void decode_unit(const I64bFusedParams& p, const Geo& geo, int v, Unit& u) {
+    u.m_t = 0; u.slab = 0;
+    if (v < geo.U1r) {
+        u.type = kG1Routed; u.g = v / geo.nt1r; u.n_t = v % geo.nt1r; u.nkb = geo.nkb_h;
+    } else if (v < geo.U1) {
+        const int w = v - geo.U1r;
+        u.type = kG1Shared; u.g = p.num_experts; u.m_t = w / geo.nt1s; u.n_t = w % geo.nt1s; u.nkb = geo.nkb_h;
+    } else if (v < geo.U1 + geo.U2r) {
+        const int w = v - geo.U1;
+        u.type = kG2Routed; u.g = w / geo.nt2; u.n_t = w % geo.nt2;
+        u.nkb = (p.expert_inter + kBlockK - 1) / kBlockK;
+    } else {
+        int w = v - geo.U1 - geo.U2r;
+        u.type = kG2Shared; u.g = p.num_experts;
+        u.slab = w % geo.slabs; w /= geo.slabs;
+        u.n_t = w % geo.nt2; u.m_t = w / geo.nt2;
+        const int krem = p.shared_inter - u.slab * kSlabK;
+        u.nkb = ((krem < kSlabK ? krem : kSlabK) + kBlockK - 1) / kBlockK;
+    }
+}
+// 128-row passes over a unit's rows (an expert without tokens still runs one, empty, pass: its weights may
+// already be on their way when the plan completes)
+__device__ __forceinline__ int unit_passes(const Smem& s, const Unit& u) {
+    if (u.type == kG1Routed || u.type == kG2Routed) {
+        const int m = (s.group_rows[u.g] + kBlockM - 1) / kBlockM;
+        return m > 0 ? m : 1;
+    }
+    return 1;
+}
 
 __device__ __forceinline__ uint64_t sw128_desc(const void* p) {
     uint64_t d = (uint64_t)((smem_u32(p) >> 4) & 0x3FFFu);
@@ -64,15 +129,67 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void red_release_add(int* p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
     asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_n(uint64_t* bar, uint32_t n) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+}
+// one arrival on `bar` once every cp.async this thread has issued so far has landed
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void st_release_cta(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" :: "r"(smem_u32(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_cta(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
+// The weight thread is the only one that observes every phase of the empty barriers; the activation roles skip the
+// stages of units that are not theirs, so they may not wait on a parity.  They wait until the weight tile of stage
+// `seq` has been issued instead, which the weight thread does right after the slot was released.
+__device__ __forceinline__ void wait_stage_owned(const uint32_t* b_seq, uint32_t seq) {
+    if (ld_acquire_cta(b_seq) > seq) return;
+    const long long t0 = clock64();
+    while (ld_acquire_cta(b_seq) <= seq)
+        if (clock64() - t0 > 4000000000ll) __trap();
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
+    asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(threads) : "memory");
+}
+// mbarrier wait that traps instead of hanging the GPU when a dependency never arrives
+__device__ __noinline__ void mbar_wait_slow(uint64_t* bar, uint32_t parity) {
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+    if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity);
 }
 __device__ __forceinline__ float4 ld_cg_f4(const float* p) {
     float4 v;
     asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     return v;
 }
+__device__ __forceinline__ long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return (long long)t;
+}
+#define TL(slot) do { if (tl) tl[slot] = gtime(); } while (0)
 // bounded spin on a device counter (a stuck dependency traps instead of hanging the GPU)
 __device__ __forceinline__ void wait_counter(const int* ctr, int target) {
     const long long t0 = clock64();
@@ -81,38 +198,11 @@ __device__ __forceinline__ void wait_counter(const int* ctr, int target) {
     }
 }
 
-__device__ __forceinline__ void decode_tile(const I64bFusedParams& p, const Smem& s, int idx, int T1, Tile& t) {
-    const int ng = p.num_experts + 1;
-    if (idx < T1) {
-        int g = 0;
-        while (idx >= s.t1_prefix[g + 1]) ++g;
-        const int n_out = g < p.num_experts ? p.expert_inter : p.shared_inter;
-        const int nt = (n_out + kBn1 - 1) / kBn1;
-        const int local = idx - s.t1_prefix[g];
-        t.type = 1; t.g = g; t.m_t = local / nt; t.n_t = local % nt; t.slab = 0;
-        t.nkb = (p.hidden + kBlockK - 1) / kBlockK;
-    } else {
-        const int j = idx - T1;
-        int g = 0;
-        while (j >= s.t2_prefix[g + 1]) ++g;
-        const int kk = g < p.num_experts ? p.expert_inter : p.shared_inter;
-        const int slabs = (kk + kSlabK - 1) / kSlabK;
-        const int nt = (p.hidden + kNMma - 1) / kNMma;
-        int local = j - s.t2_prefix[g];
-        t.type = 2; t.g = g;
-        t.slab = local % slabs; local /= slabs;
-        t.n_t = local % nt; t.m_t = local / nt;
-        const int krem = kk - t.slab * kSlabK;
-        t.nkb = ((krem < kSlabK ? krem : kSlabK) + kBlockK - 1) / kBlockK;
-    }
-    (void)ng;
-}
-
 __global__ void __launch_bounds__(kThreads, 1)
-i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_xs, const __grid_constant__ CUtensorMap tm_w13,
-                        const __grid_constant__ CUtensorMap tm_inter_r, const __grid_constant__ CUtensorMap tm_inter_s,
-                        const __grid_constant__ CUtensorMap tm_w2r, const __grid_constant__ CUtensorMap tm_w2s,
-                        const __grid_constant__ I64bFusedParams p) {
+i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
+                        const __grid_constant__ CUtensorMap tm_w13, const __grid_constant__ CUtensorMap tm_inter_r,
+                        const __grid_constant__ CUtensorMap tm_inter_s, const __grid_constant__ CUtensorMap tm_w2r,
+                        const __grid_constant__ CUtensorMap tm_w2s, const __grid_constant__ I64bFusedParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = base;
@@ -121,199 +211,203 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_xs, const __grid_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int E = p.num_experts, K = p.top_k, N = p.n, H = p.hidden, bins = K * E, G = gridDim.x;
+    const Geo geo = make_geo(p);
     pdl_launch_dependents();
+    long long* tl = p.timeline ? p.timeline + (size_t)blockIdx.x * 16 : nullptr;
+    if (threadIdx.x == 0) TL(0);
 
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tm_xs); tma_prefetch_desc(&tm_w13); tma_prefetch_desc(&tm_inter_r);
-        tma_prefetch_desc(&tm_inter_s); tma_prefetch_desc(&tm_w2r); tma_prefetch_desc(&tm_w2s);
-        for (int i = 0; i < kStages; ++i) { mbar_init(&s.full_bar[i], 1); mbar_init(&s.empty_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull_bar[i], 1); mbar_init(&s.tempty_bar[i], 4); }
-        fence_barrier_init();
+    // weight tile of (unit, k-block) → shared-memory stage; tx bytes = kStageB
+    auto issue_b = [&](const Unit& u, int kb, int stage) {
+        uint8_t* dstB = sB + stage * kStageB;
+        mbar_arrive_expect_tx(&s.full_bar[stage], kStageB);
+        if (u.type <= kG1Shared) {
+            const int n_out = u.type == kG1Routed ? p.expert_inter : p.shared_inter;
+            const int wrow = (u.type == kG1Routed ? u.g * 2 * p.expert_inter : E * 2 * p.expert_inter) + u.n_t * kBn1;
+            tma_load_2d(dstB, &tm_w13, &s.full_bar[stage], kb * kBlockK, wrow, I64B_L2_EVICT_FIRST);
+            tma_load_2d(dstB + kBn1 * 128, &tm_w13, &s.full_bar[stage], kb * kBlockK, wrow + n_out, I64B_L2_EVICT_FIRST);
+        } else if (u.type == kG2Routed) {
+            tma_load_2d(dstB, &tm_w2r, &s.full_bar[stage], kb * kBlockK, u.g * H + u.n_t * kNMma, I64B_L2_EVICT_FIRST);
+        } else {
+            tma_load_2d(dstB, &tm_w2s, &s.full_bar[stage], u.slab * kSlabK + kb * kBlockK, u.n_t * kNMma,
+                        I64B_L2_EVICT_FIRST);
+        }
+    };
+
+    int pre_issued = 0;          // weight stages the TMA thread put in flight before the plan (first unit, pass 0)
+    if (warp == 0) {
+        Unit u0;
+        if (lane == 0) {
+            tma_prefetch_desc(&tm_w13); tma_prefetch_desc(&tm_w2r); tma_prefetch_desc(&tm_w2s);
+            tma_prefetch_desc(&tm_inter_r); tma_prefetch_desc(&tm_inter_s);
+            tma_prefetch_desc(&tm_x);
+            for (int i = 0; i < kStages; ++i) { mbar_init(&s.full_bar[i], 1 + kGatherThreads); mbar_init(&s.empty_bar[i], 1); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull_bar[i], 1); mbar_init(&s.tempty_bar[i], 4); }
+            fence_barrier_init();
+            // half a ring of weights goes out at once (also under the previous kernel's tail: weights are constants)
+            if ((int)blockIdx.x < geo.U) {
+                decode_unit(p, geo, blockIdx.x, u0);
+                pre_issued = u0.nkb < kStages ? u0.nkb : kStages;
+                for (int kb = 0; kb < pre_issued && kb < kStages / 2; ++kb) issue_b(u0, kb, kb);
+            }
+        }
+        // ... the other half only once the plan's dependent loads (ids, then table) are in the memory system: queued
+        // behind ~100 KB of weight requests per SM they take microseconds instead of a few hundred nanoseconds
+        named_bar_sync(3, 32 + kPlanWarps * 32);
+        if (lane == 0) {
+            for (int kb = kStages / 2; kb < pre_issued; ++kb) issue_b(u0, kb, kb);
+            s.b_seq = (uint32_t)pre_issued;                       // published by the __syncthreads below
+        }
+        pre_issued = __shfl_sync(0xffffffffu, pre_issued, 0);
     } else if (warp == 1) {
         tmem_alloc<kTmemCols>(&s.tmem_ptr);
-    }
-    for (int i = threadIdx.x; i < kWarps * I64B_MAX_BINS; i += kThreads) (&s.warp_cnt[0][0])[i] = 0;
-    pdl_wait_prior();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = s.tmem_ptr;
-
-    // ------------------------------------------------------------------ phase A: plan (every CTA, into smem)
-    {
-        const int tok_per_warp = ((N + kWarps - 1) / kWarps + 31) / 32 * 32;
-        const int iters = tok_per_warp / 32;                       // ≤ 4 for N ≤ 1024
-        const int tbase = warp * tok_per_warp;
-        int e_reg[4][I64B_MAX_TOPK];
-        uint16_t r_reg[4][I64B_MAX_TOPK];
-        long long id[4];
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            const int t = tbase + it * 32 + lane;
-            id[it] = (p.token_ids != nullptr && it < iters && t < N) ? p.token_ids[t] : 0;
-        }
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            const long long c = id[it] < 0 ? 0 : (id[it] >= p.vocab ? p.vocab - 1 : id[it]);
-#pragma unroll
-            for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-                int e = 0;
-                if (k < K) e = p.token_ids ? (int)__ldg(p.table + (int64_t)k * p.vocab + c) : (k % E);
-                e_reg[it][k] = min(e, E - 1);
-            }
-        }
-        const unsigned lt_mask = (1u << lane) - 1u;
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            if (it < iters) {
-                const int t = tbase + it * 32 + lane;
-                const bool valid = t < N;
+    } else {
+        // ------------------------------------------------------------------ plan (warps 2-9, into shared memory)
+        if (warp < 2 + kPlanWarps) {
+            const int pw = warp - 2;
+            const int pt = threadIdx.x - 64;
+            constexpr int kPT = kPlanWarps * 32;
+            pdl_wait_prior();        // token ids may come from the previous kernel in the stream
+            for (int i = pt; i < kPlanWarps * I64B_MAX_BINS / 2; i += kPT) reinterpret_cast<uint32_t*>(&s.warp_cnt[0][0])[i] = 0;
+            // N <= 256 (the decode sizes this kernel is tuned for) is one trip; larger batches pay one round trip each
+            int ev0[I64B_MAX_TOPK];
+            {
+                const int t = pt;
+                const long long id = (p.token_ids != nullptr && t < N) ? p.token_ids[t] : 0;
+                const long long c = id < 0 ? 0 : (id >= p.vocab ? p.vocab - 1 : id);
+                if (pt == 0 && (c | 1)) TL(3);                     // ids have arrived
 #pragma unroll
                 for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-                    if (k < K) {
-                        const int e = valid ? e_reg[it][k] : 0xFF;
-                        const unsigned peers = __match_any_sync(0xffffffffu, e);
-                        const int leader = __ffs(peers) - 1;
-                        const int prev = valid ? s.warp_cnt[warp][k * E + e] : 0;
-                        __syncwarp();
-                        if (valid && lane == leader) s.warp_cnt[warp][k * E + e] = prev + __popc(peers);
-                        __syncwarp();
-                        r_reg[it][k] = (uint16_t)(prev + __popc(peers & lt_mask));
-                    }
+                    ev0[k] = 0;
+                    if (k < K && t < N) ev0[k] = p.token_ids ? (int)__ldg(p.table + (int64_t)k * p.vocab + c) : (k % E);
                 }
             }
-        }
-        __syncthreads();
-        for (int b = threadIdx.x; b < bins; b += kThreads) {       // exclusive scan over warps → per-bin totals
-            int running = 0;
+            named_bar_arrive(3, 32 + kPT);                         // table loads are on their way: weights may start
 #pragma unroll
-            for (int w = 0; w < kWarps; ++w) {
-                const int c = s.warp_cnt[w][b];
-                s.warp_cnt[w][b] = running;
-                running += c;
+            for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                if (k < K && pt < N) s.expert[k][pt] = (uint8_t)min(ev0[k], E - 1);
+#pragma unroll 1
+            for (int t = pt + kPT; t < N; t += kPT) {
+                const long long id = p.token_ids != nullptr ? p.token_ids[t] : 0;
+                const long long c = id < 0 ? 0 : (id >= p.vocab ? p.vocab - 1 : id);
+#pragma unroll 1
+                for (int k = 0; k < K; ++k)
+                    s.expert[k][t] = (uint8_t)min(p.token_ids ? (int)__ldg(p.table + (int64_t)k * p.vocab + c) : (k % E), E - 1);
             }
-            s.offsets[b] = running;                                // holds counts until thread 0 scans them
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            int gs = 0, mt = 0, t1 = 0, t2 = 0;
-            const int nt2 = (H + kNMma - 1) / kNMma;
-            for (int e = 0; e <= E; ++e) {
-                int rows = 0;
-                if (e < E) {
+            if (pt == 0) TL(2);                                    // table values have arrived
+            named_bar_sync(2, kPT);
+            // stable rank of every assignment inside its (route, expert) bin: warp pw owns a contiguous token range
+            const int tok_per_warp = ((N + kPlanWarps - 1) / kPlanWarps + 31) / 32 * 32;
+            const int tbase = pw * tok_per_warp;
+            const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll 1
+            for (int t0 = tbase; t0 < tbase + tok_per_warp && t0 < N; t0 += 32) {
+                const int t = t0 + lane;
+                const bool valid = t < N;
+#pragma unroll 1
+                for (int k = 0; k < K; ++k) {
+                    const int e = valid ? (int)s.expert[k][t] : 0xFF;
+                    const unsigned peers = __match_any_sync(0xffffffffu, e);
+                    const int leader = __ffs(peers) - 1;
+                    const int prev = valid ? s.warp_cnt[pw][k * E + e] : 0;
+                    __syncwarp();
+                    if (valid && lane == leader) s.warp_cnt[pw][k * E + e] = (uint16_t)(prev + __popc(peers));
+                    __syncwarp();
+                    if (valid) s.dest_row[k][t] = (uint16_t)(prev + __popc(peers & lt_mask));   // rank inside the warp's range
+                }
+            }
+            named_bar_sync(2, kPT);
+#pragma unroll 1
+            for (int b = pt; b < bins; b += kPT) {                  // exclusive scan over warps → per-bin totals
+                int running = 0;
+#pragma unroll
+                for (int w = 0; w < kPlanWarps; ++w) {
+                    const int c = s.warp_cnt[w][b];
+                    s.warp_cnt[w][b] = (uint16_t)running;
+                    running += c;
+                }
+                s.offsets[b] = running;                             // holds counts until the scans below
+            }
+            named_bar_sync(2, kPT);
+            if (pt < 32) {                                          // one warp: the three small scans
+                // rows per expert and the base of route k inside expert e's merged segment
+#pragma unroll 1
+                for (int e = lane; e < E; e += 32) {
+                    int rows = 0;
+#pragma unroll 1
                     for (int k = 0; k < K; ++k) { s.route_base[k * E + e] = rows; rows += s.offsets[k * E + e]; }
-                } else {
-                    rows = p.shared_inter > 0 ? N : 0;
+                    s.group_rows[e] = rows;
                 }
-                const int n_out = e < E ? p.expert_inter : p.shared_inter;
-                const int kk = n_out;
-                s.group_rows[e] = rows; s.group_start[e] = gs; s.mt_prefix[e] = mt; s.t1_prefix[e] = t1; s.t2_prefix[e] = t2;
-                const int m = (rows + kBlockM - 1) / kBlockM;
-                mt += m;
-                t1 += m * ((n_out + kBn1 - 1) / kBn1);
-                t2 += m * nt2 * ((kk + kSlabK - 1) / kSlabK);
-                gs += rows;
-            }
-            s.group_start[E + 1] = gs; s.mt_prefix[E + 1] = mt; s.t1_prefix[E + 1] = t1; s.t2_prefix[E + 1] = t2;
-            if (blockIdx.x == 0 && p.tap_counts) {
-                for (int b = 0; b < bins; ++b) p.tap_counts[b] = s.offsets[b];
-            }
-            for (int k = 0; k < K; ++k) {                          // per-route exclusive offsets (reference convention)
-                int off = 0;
-                for (int e = 0; e < E; ++e) { const int c = s.offsets[k * E + e]; s.offsets[k * E + e] = off; off += c; }
-            }
-            if (blockIdx.x == 0 && p.tap_offsets)
-                for (int b = 0; b < bins; ++b) p.tap_offsets[b] = s.offsets[b];
-        }
-        __syncthreads();
+                __syncwarp();
+                int gs = 0;                                         // exclusive scan of group_rows over experts
+#pragma unroll 1
+                for (int e0 = 0; e0 < E; e0 += 32) {
+                    const int v = e0 + lane < E ? s.group_rows[e0 + lane] : 0;
+                    int inc = v;
 #pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            const int t = tbase + it * 32 + lane;
-            if (it < iters && t < N) {
-#pragma unroll
-                for (int k = 0; k < I64B_MAX_TOPK; ++k)
-                    if (k < K) {
-                        const int e = e_reg[it][k];
+                    for (int o = 1; o < 32; o <<= 1) { const int n_ = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += n_; }
+                    if (e0 + lane < E) s.group_start[e0 + lane] = gs + inc - v;
+                    gs += __shfl_sync(0xffffffffu, inc, 31);
+                }
+                if (lane == 0) s.group_start[E] = gs;
+                if (blockIdx.x == 0 && p.tap_counts)
+                    for (int b = lane; b < bins; b += 32) p.tap_counts[b] = s.offsets[b];
+                __syncwarp();
+                if (lane < K) {                                     // per-route exclusive offsets (reference convention)
+                    int off = 0;
+#pragma unroll 1
+                    for (int e = 0; e < E; ++e) { const int c = s.offsets[lane * E + e]; s.offsets[lane * E + e] = off; off += c; }
+                }
+                __syncwarp();
+                if (blockIdx.x == 0 && p.tap_offsets)
+                    for (int b = lane; b < bins; b += 32) p.tap_offsets[b] = s.offsets[b];
+            }
+            named_bar_sync(2, kPT);
+#pragma unroll 1
+            for (int t0 = tbase; t0 < tbase + tok_per_warp && t0 < N; t0 += 32) {
+                const int t = t0 + lane;
+                if (t < N) {
+#pragma unroll 1
+                    for (int k = 0; k < K; ++k) {
+                        const int e = s.expert[k][t];
                         const int bin = k * E + e;
-                        const int in_exp = s.warp_cnt[warp][bin] + r_reg[it][k];
+                        const int in_exp = s.warp_cnt[pw][bin] + s.dest_row[k][t];
                         const int dest = s.group_start[e] + s.route_base[bin] + in_exp;
                         s.dest_row[k][t] = (uint16_t)dest;
-                        s.expert[k][t] = (uint8_t)e;
+                        s.src_tok[dest] = (uint16_t)t;
                         if (blockIdx.x == 0) {
                             if (p.tap_routes) p.tap_routes[(int64_t)k * N + t] = e;
                             if (p.tap_dest) p.tap_dest[(int64_t)k * N + t] = dest;
                             if (p.tap_scatter) p.tap_scatter[(int64_t)k * N + t] = s.offsets[bin] + in_exp;
                         }
                     }
+                }
             }
         }
-        __syncthreads();
     }
-    const int R = s.group_start[E];                  // routed rows (= N*K)
-    const int T1 = s.t1_prefix[E + 1], T2 = s.t2_prefix[E + 1];
-    const int total_tiles = T1 + T2;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = s.tmem_ptr;
+    const int R = E > 0 ? s.group_start[E] : 0;      // routed rows (= N*K)
+    if (threadIdx.x == 0) TL(1);
 
     if (warp == 0) {
-        // ------------------------------------------------------------------ TMA producer
+        // ------------------------------------------------------------------ weight TMA: runs ahead of everything else
+        // by the depth of the ring (the weights of the next unit stream in while this one waits on a dependency)
         if (lane == 0) {
-            int b_idx = blockIdx.x, a_idx = blockIdx.x;      // tile cursors for the weight and the activation loads
-            int b_kb = 0, a_kb = 0, b_stage = 0, a_stage = 0, issued_ahead = 0;
-            uint32_t b_phase = 0;
-            Tile bt, at;
-            bool bt_valid = false, at_valid = false, at_ready = false;
-            const long long t_begin = clock64();
-            while (a_idx < total_tiles) {
-                // weights: run ahead as far as the ring allows
-                while (b_idx < total_tiles && issued_ahead < kStages) {
-                    if (!bt_valid) { decode_tile(p, s, b_idx, T1, bt); bt_valid = true; }
-                    if (!mbar_try_wait(&s.empty_bar[b_stage], b_phase ^ 1)) break;
-                    mbar_arrive_expect_tx(&s.full_bar[b_stage], kStageA + kStageB);
-                    uint8_t* dstB = sB + b_stage * kStageB;
-                    if (bt.type == 1) {
-                        const int n_out = bt.g < E ? p.expert_inter : p.shared_inter;
-                        const int wrow = (bt.g < E ? bt.g * 2 * p.expert_inter : E * 2 * p.expert_inter) + bt.n_t * kBn1;
-                        tma_load_2d(dstB, &tm_w13, &s.full_bar[b_stage], b_kb * kBlockK, wrow, I64B_L2_EVICT_FIRST);
-                        tma_load_2d(dstB + kBn1 * 128, &tm_w13, &s.full_bar[b_stage], b_kb * kBlockK, wrow + n_out,
-                                    I64B_L2_EVICT_FIRST);
-                    } else {
-                        const CUtensorMap* tb = bt.g < E ? &tm_w2r : &tm_w2s;
-                        const int wrow = (bt.g < E ? bt.g * H : 0) + bt.n_t * kNMma;
-                        tma_load_2d(dstB, tb, &s.full_bar[b_stage], bt.slab * kSlabK + b_kb * kBlockK, wrow,
-                                    I64B_L2_EVICT_FIRST);
+            uint32_t seq = 0;
+            for (int v = blockIdx.x; v < geo.U; v += G) {
+                Unit u;
+                decode_unit(p, geo, v, u);
+                const int np = unit_passes(s, u);
+                for (int pass = 0; pass < np; ++pass)
+                    for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
+                        if (seq < (uint32_t)pre_issued) continue;          // issued before the plan
+                        const int stage = (int)(seq % (uint32_t)kStages);
+                        mbar_wait_bounded(&s.empty_bar[stage], ((seq / (uint32_t)kStages) & 1u) ^ 1u);
+                        issue_b(u, kb, stage);
+                        st_release_cta(&s.b_seq, seq + 1);
                     }
-                    ++issued_ahead;
-                    if (++b_stage == kStages) { b_stage = 0; b_phase ^= 1; }
-                    if (++b_kb == bt.nkb) { b_kb = 0; b_idx += G; bt_valid = false; }
-                }
-                // activations: need the producing phase of other CTAs
-                if (issued_ahead > 0) {
-                    if (!at_valid) { decode_tile(p, s, a_idx, T1, at); at_valid = true; at_ready = false; }
-                    if (!at_ready) {
-                        const int* ctr = at.type == 1 ? p.sync + I64B_SYNC_DISPATCH
-                                                      : p.sync + I64B_SYNC_G1 + s.mt_prefix[at.g] + at.m_t;
-                        const int n_out = at.g < E ? p.expert_inter : p.shared_inter;
-                        const int target = at.type == 1 ? N : (n_out + kBn1 - 1) / kBn1;
-                        if (ld_acquire(ctr) >= target) { fence_proxy_async_global(); at_ready = true; }
-                        else if (clock64() - t_begin > 4000000000ll) __trap();
-                    }
-                    if (at_ready) {
-                        uint8_t* dstA = sA + a_stage * kStageA;
-                        const int arow = at.m_t * kBlockM;
-                        if (at.type == 1) {
-                            tma_load_2d(dstA, &tm_xs, &s.full_bar[a_stage], a_kb * kBlockK, s.group_start[at.g] + arow,
-                                        I64B_L2_EVICT_NORMAL);
-                        } else if (at.g < E) {
-                            tma_load_2d(dstA, &tm_inter_r, &s.full_bar[a_stage], at.slab * kSlabK + a_kb * kBlockK,
-                                        s.group_start[at.g] + arow, I64B_L2_EVICT_NORMAL);
-                        } else {
-                            tma_load_2d(dstA, &tm_inter_s, &s.full_bar[a_stage], at.slab * kSlabK + a_kb * kBlockK, arow,
-                                        I64B_L2_EVICT_NORMAL);
-                        }
-                        --issued_ahead;
-                        if (++a_stage == kStages) a_stage = 0;
-                        if (++a_kb == at.nkb) { a_kb = 0; a_idx += G; at_valid = false; }
-                    }
-                }
             }
         }
     } else if (warp == 1) {
@@ -322,26 +416,29 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_xs, const __grid_
             // c_format F32 (1<<4), A/B bf16 (1<<7, 1<<10), N>>3 at 17, M>>4 at 24
             constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kNMma >> 3) << 17) |
                                        ((uint32_t)(kBlockM >> 4) << 24);
-            int stage = 0, iter = 0;
-            uint32_t phase = 0;
-            for (int idx = blockIdx.x; idx < total_tiles; idx += G, ++iter) {
-                Tile t;
-                decode_tile(p, s, idx, T1, t);
-                const int as = iter & 1;
-                mbar_wait(&s.tempty_bar[as], ((iter >> 1) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + as * kNMma;
-                for (int kb = 0; kb < t.nkb; ++kb) {
-                    mbar_wait(&s.full_bar[stage], phase);
+            uint32_t seq = 0;
+            int iter = 0;
+            for (int v = blockIdx.x; v < geo.U; v += G) {
+                Unit u;
+                decode_unit(p, geo, v, u);
+                const int np = unit_passes(s, u);
+                for (int pass = 0; pass < np; ++pass, ++iter) {
+                    const int as = iter & 1;
+                    mbar_wait_bounded(&s.tempty_bar[as], ((iter >> 1) & 1) ^ 1);
                     tc_fence_after();
-                    const uint64_t a_desc = sw128_desc(sA + stage * kStageA);
-                    const uint64_t b_desc = sw128_desc(sB + stage * kStageB);
+                    const uint32_t d_tmem = tmem_base + as * kNMma;
+                    for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
+                        const int stage = (int)(seq % (uint32_t)kStages);
+                        mbar_wait_bounded(&s.full_bar[stage], (seq / (uint32_t)kStages) & 1u);
+                        tc_fence_after();
+                        const uint64_t a_desc = sw128_desc(sA + stage * kStageA);
+                        const uint64_t b_desc = sw128_desc(sB + stage * kStageB);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
-                    umma_commit(&s.empty_bar[stage]);
-                    if (kb == t.nkb - 1) umma_commit(&s.tfull_bar[as]);
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        umma_commit(&s.empty_bar[stage]);
+                        if (kb == u.nkb - 1) { umma_commit(&s.tfull_bar[as]); TL(iter == 0 ? 6 : 9); }
+                    }
                 }
             }
         }
@@ -350,104 +447,163 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_xs, const __grid_
         const int q = warp & 3;
         const int r = q * 32 + lane;
         int iter = 0;
-        for (int idx = blockIdx.x; idx < total_tiles; idx += G, ++iter) {
-            Tile t;
-            decode_tile(p, s, idx, T1, t);
-            const int as = iter & 1;
-            mbar_wait(&s.tfull_bar[as], (iter >> 1) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma;
-            const int row_in_group = t.m_t * kBlockM + r;
-            const bool valid = row_in_group < s.group_rows[t.g];
-            if (t.type == 1) {
-                const bool shared = t.g >= E;
-                const int n_out = shared ? p.shared_inter : p.expert_inter;
-                __nv_bfloat16* orow = shared
-                    ? reinterpret_cast<__nv_bfloat16*>(p.inter_s) + (int64_t)row_in_group * p.shared_inter
-                    : reinterpret_cast<__nv_bfloat16*>(p.inter_r) + (int64_t)(s.group_start[t.g] + row_in_group) * p.expert_inter;
+        for (int v = blockIdx.x; v < geo.U; v += G) {
+            Unit u;
+            decode_unit(p, geo, v, u);
+            const int np = unit_passes(s, u);
+            for (int pass = 0; pass < np; ++pass, ++iter) {
+                const int as = iter & 1;
+                mbar_wait_bounded(&s.tfull_bar[as], (iter >> 1) & 1);
+                tc_fence_after();
+                if (warp == 2 && lane == 0 && iter == 0) TL(14);
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma;
+                const bool routed = u.type == kG1Routed || u.type == kG2Routed;
+                const int row = (routed ? pass : u.m_t) * kBlockM + r;      // row inside the group
+                const bool valid = row < (routed ? s.group_rows[u.g] : N);
+                if (u.type <= kG1Shared) {
+                    const int n_out = routed ? p.expert_inter : p.shared_inter;
+                    __nv_bfloat16* orow = routed
+                        ? reinterpret_cast<__nv_bfloat16*>(p.inter_r) + (int64_t)(s.group_start[u.g] + row) * p.expert_inter
+                        : reinterpret_cast<__nv_bfloat16*>(p.inter_s) + (int64_t)row * p.shared_inter;
 #pragma unroll 1
-                for (int c = 0; c < kBn1 / 32; ++c) {
-                    const int col0 = t.n_t * kBn1 + c * 32;
-                    if (col0 >= n_out) break;
-                    uint32_t gr[32], ur[32];
-                    tmem_ld_32x32(taddr + c * 32, gr);
-                    tmem_ld_32x32(taddr + kBn1 + c * 32, ur);
-                    tmem_ld_wait();
-                    uint32_t o[16];
+                    for (int c = 0; c < kBn1 / 32; ++c) {
+                        const int col0 = u.n_t * kBn1 + c * 32;
+                        if (col0 >= n_out) break;
+                        uint32_t gr[32], ur[32];
+                        tmem_ld_32x32(taddr + c * 32, gr);
+                        tmem_ld_32x32(taddr + kBn1 + c * 32, ur);
+                        tmem_ld_wait();
+                        uint32_t o[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        o[j] = pack_bf16x2(silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]),
-                                           silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]));
-                    if (valid) {
+                        for (int j = 0; j < 16; ++j)
+                            o[j] = pack_bf16x2(silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]),
+                                               silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]));
+                        if (valid) {
 #pragma unroll
-                        for (int v = 0; v < 4; ++v)
-                            if (col0 + v * 8 < n_out)
-                                *reinterpret_cast<int4*>(orow + col0 + v * 8) =
-                                    make_int4(o[4 * v], o[4 * v + 1], o[4 * v + 2], o[4 * v + 3]);
+                            for (int v4 = 0; v4 < 4; ++v4)
+                                if (col0 + v4 * 8 < n_out)
+                                    *reinterpret_cast<int4*>(orow + col0 + v4 * 8) =
+                                        make_int4(o[4 * v4], o[4 * v4 + 1], o[4 * v4 + 2], o[4 * v4 + 3]);
+                        }
+                    }
+                } else {
+                    const int64_t yrow = routed ? (int64_t)s.group_start[u.g] + row
+                                                : (int64_t)R + (int64_t)u.slab * N + row;
+                    float* orow = p.y + yrow * H;
+#pragma unroll 1
+                    for (int c = 0; c < kNMma / 32; ++c) {
+                        const int col0 = u.n_t * kNMma + c * 32;
+                        if (col0 >= H) break;
+                        uint32_t ar[32];
+                        tmem_ld_32x32(taddr + c * 32, ar);
+                        tmem_ld_wait();
+                        if (valid) {
+#pragma unroll
+                            for (int v4 = 0; v4 < 8; ++v4)
+                                if (col0 + v4 * 4 < H)
+                                    *reinterpret_cast<int4*>(orow + col0 + v4 * 4) =
+                                        make_int4(ar[4 * v4], ar[4 * v4 + 1], ar[4 * v4 + 2], ar[4 * v4 + 3]);
+                        }
                     }
                 }
-            } else {
-                const bool shared = t.g >= E;
-                const int64_t yrow = shared ? (int64_t)R + (int64_t)t.slab * N + row_in_group
-                                            : (int64_t)s.group_start[t.g] + row_in_group;
-                float* orow = p.y + yrow * H;
-#pragma unroll 1
-                for (int c = 0; c < kNMma / 32; ++c) {
-                    const int col0 = t.n_t * kNMma + c * 32;
-                    if (col0 >= H) break;
-                    uint32_t ar[32];
-                    tmem_ld_32x32(taddr + c * 32, ar);
-                    tmem_ld_wait();
-                    if (valid) {
-#pragma unroll
-                        for (int v = 0; v < 8; ++v)
-                            if (col0 + v * 4 < H)
-                                *reinterpret_cast<int4*>(orow + col0 + v * 4) =
-                                    make_int4(ar[4 * v], ar[4 * v + 1], ar[4 * v + 2], ar[4 * v + 3]);
-                    }
-                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s.tempty_bar[as]);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s.tempty_bar[as]);
-            // publish the tile: all four epilogue warps' stores → one release increment
+            // publish the unit: all four epilogue warps' stores → one release increment
+            if (warp == 2 && lane == 0 && iter == np) TL(15);
             __threadfence();
             named_bar_sync(1, 128);
             if (warp == 2 && lane == 0) {
-                if (t.type == 1) atomicAdd(p.sync + I64B_SYNC_G1 + s.mt_prefix[t.g] + t.m_t, 1);
-                else atomicAdd(p.sync + I64B_SYNC_G2, 1);
+                if (u.type == kG1Routed) red_release_add(p.sync + I64B_SYNC_G1 + u.g, 1);
+                else if (u.type == kG1Shared) red_release_add(p.sync + I64B_SYNC_G1 + E + u.m_t, 1);
+                else red_release_add(p.sync + I64B_SYNC_G2, 1);
+                TL(u.type <= kG1Shared ? 7 : 10);
+            }
+        }
+    } else if (warp < 10) {
+        // ------------------------------------------------------------------ gather warps: A rows of the routed GEMM1
+        // units.  Lane l of gather warp w copies 16-byte chunk (l & 7) of tile rows 32w + 4j + (l >> 3), j = 0..7.
+        const int gw = warp - 6;
+        const int chunk = lane & 7;
+        pdl_wait_prior();
+        uint32_t seq = 0;
+        const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(p.x);
+        for (int v = blockIdx.x; v < geo.U; v += G) {
+            Unit u;
+            decode_unit(p, geo, v, u);
+            const int np = unit_passes(s, u);
+            if (u.type != kG1Routed) { seq += (uint32_t)(np * u.nkb); continue; }
+            for (int pass = 0; pass < np; ++pass) {
+                const __nv_bfloat16* src[8];
+                uint32_t dst_off[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int rj = gw * 32 + j * 4 + (lane >> 3);
+                    const int row = pass * kBlockM + rj;
+                    src[j] = row < s.group_rows[u.g] ? xb + (int64_t)s.src_tok[s.group_start[u.g] + row] * H + chunk * 8
+                                                     : nullptr;
+                    dst_off[j] = (uint32_t)(rj * 128 + ((chunk ^ (rj & 7)) << 4));
+                }
+                for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
+                    const int stage = (int)(seq % (uint32_t)kStages);
+                    wait_stage_owned(&s.b_seq, seq);
+                    const uint32_t dst = smem_u32(sA + stage * kStageA);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (src[j] != nullptr) cp_async_16(dst + dst_off[j], src[j] + kb * kBlockK);
+                    cp_async_arrive_noinc(&s.full_bar[stage]);
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ activation TMA (one thread):
+        //   GEMM1 shared : rows of x in token order
+        //   GEMM2        : rows of `inter`, after the GEMM1 units that produce them have published
+        if (lane == 0) {
+            pdl_wait_prior();
+            uint32_t seq = 0;
+            const long long t_begin = clock64();
+            for (int v = blockIdx.x; v < geo.U; v += G) {
+                Unit u;
+                decode_unit(p, geo, v, u);
+                const int np = unit_passes(s, u);
+                if (u.type == kG1Routed) { seq += (uint32_t)(np * u.nkb); continue; }
+                if (u.type >= kG2Routed) {
+                    const int* ctr = p.sync + I64B_SYNC_G1 + (u.type == kG2Routed ? u.g : E + u.m_t);
+                    const int target = u.type == kG2Routed ? geo.nt1r : geo.nt1s;
+                    while (ld_acquire(ctr) < target)
+                        if (clock64() - t_begin > 4000000000ll) __trap();
+                    fence_proxy_async_global();
+                    TL(u.type == kG2Routed ? 4 : 5);
+                }
+                for (int pass = 0; pass < np; ++pass)
+                    for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
+                        const int stage = (int)(seq % (uint32_t)kStages);
+                        uint8_t* dstA = sA + stage * kStageA;
+                        uint64_t* bar = &s.full_bar[stage];
+                        wait_stage_owned(&s.b_seq, seq);
+                        mbar_expect_tx(bar, kStageA);
+                        if (u.type == kG1Shared)
+                            tma_load_2d(dstA, &tm_x, bar, kb * kBlockK, u.m_t * kBlockM, I64B_L2_EVICT_NORMAL);
+                        else if (u.type == kG2Routed)
+                            tma_load_2d(dstA, &tm_inter_r, bar, kb * kBlockK, s.group_start[u.g] + pass * kBlockM,
+                                        I64B_L2_EVICT_NORMAL);
+                        else
+                            tma_load_2d(dstA, &tm_inter_s, bar, u.slab * kSlabK + kb * kBlockK, u.m_t * kBlockM,
+                                        I64B_L2_EVICT_NORMAL);
+                        mbar_arrive_n(bar, kGatherThreads);
+                    }
             }
         }
     }
 
-    // ------------------------------------------------------------------ phase B: dispatch rows (warps 6,7 start at
-    // once; the role warps join when their tile loops are empty — with N ≤ 1024 each CTA copies at most a few rows)
-    if (warp >= 6) {
-        const int nvec = H / 8;
-        int copied = 0;
-        for (int t = blockIdx.x + G * (warp - 6); t < N; t += 2 * G) {
-            const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const __nv_bfloat16*>(p.x) + (int64_t)t * H);
-            for (int i = lane; i < nvec; i += 32) {
-                const int4 v = ld_nc_16(src + i);
-                for (int k = 0; k < K; ++k)
-                    *reinterpret_cast<int4*>(reinterpret_cast<__nv_bfloat16*>(p.xs) + (int64_t)s.dest_row[k][t] * H + i * 8) = v;
-                if (p.shared_inter > 0)
-                    *reinterpret_cast<int4*>(reinterpret_cast<__nv_bfloat16*>(p.xs) + (int64_t)(R + t) * H + i * 8) = v;
-            }
-            ++copied;
-        }
-        __threadfence();
-        __syncwarp();
-        if (lane == 0 && copied) atomicAdd(p.sync + I64B_SYNC_DISPATCH, copied);
-    }
-
-    // ------------------------------------------------------------------ phase E: combine this CTA's tokens
+    // ------------------------------------------------------------------ combine this CTA's tokens
     __syncthreads();
-    if (threadIdx.x == 0) wait_counter(p.sync + I64B_SYNC_G2, T2);
+    if (threadIdx.x == 0) { TL(11); wait_counter(p.sync + I64B_SYNC_G2, geo.U2); TL(12); }
     __syncthreads();
     {
         const int hv = H / 4;
-        const int slabs_s = p.shared_inter > 0 ? (p.shared_inter + kSlabK - 1) / kSlabK : 0;
         for (int t = blockIdx.x; t < N; t += G) {
             for (int c = threadIdx.x; c < hv; c += kThreads) {
                 float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -468,9 +624,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_xs, const __grid_
                     const float rs = p.routed_scale;
                     o = make_float4(__fmul_rn(rs, o.x), __fmul_rn(rs, o.y), __fmul_rn(rs, o.z), __fmul_rn(rs, o.w));
                 }
-                if (slabs_s > 0) {
+                if (geo.slabs > 0) {
                     float4 sh = ld_cg_f4(p.y + ((int64_t)R + t) * H + c * 4);
-                    for (int sl = 1; sl < slabs_s; ++sl) {      // split-K slabs of the shared down-projection, fixed order
+                    for (int sl = 1; sl < geo.slabs; ++sl) {    // split-K slabs of the shared down-projection, fixed order
                         const float4 y = ld_cg_f4(p.y + ((int64_t)R + (int64_t)sl * N + t) * H + c * 4);
                         sh.x = __fadd_rn(sh.x, y.x); sh.y = __fadd_rn(sh.y, y.y);
                         sh.z = __fadd_rn(sh.z, y.z); sh.w = __fadd_rn(sh.w, y.w);
@@ -497,6 +653,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_xs, const __grid_
     // ------------------------------------------------------------------ teardown: last CTA resets the counters
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) TL(13);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<kTmemCols>(tmem_base);
@@ -520,24 +677,60 @@ int i64b_fused_supported(int n, int hidden, int expert_inter, int shared_inter, 
     if (hidden % 64 != 0 || hidden > 8192) return 0;
     if (num_experts > 0 && expert_inter % 16 != 0) return 0;
     if (shared_inter % 16 != 0) return 0;
-    const int64_t mt = (int64_t)n * top_k / kBlockM + num_experts + (n + kBlockM - 1) / kBlockM;
-    if (mt > kMaxMTiles) return 0;
-    if ((int64_t)n * (top_k + 1) >= 65536) return 0;       // uint16 destination rows
+    if (num_experts + (n + kBlockM - 1) / kBlockM > I64B_FUSED_MAX_GROUPS) return 0;
+    if ((int64_t)n * top_k >= 65536) return 0;             // uint16 destination rows
     static_assert(kSmemBytes <= 232448, "shared memory budget");
     return 1;
 }
 
-int i64b_launch_fused(const CUtensorMap& tm_xs, const CUtensorMap& tm_w13, const CUtensorMap& tm_inter_r,
-                      const CUtensorMap& tm_inter_s, const CUtensorMap& tm_w2r, const CUtensorMap& tm_w2s,
-                      const I64bFusedParams& p, cudaStream_t stream) {
+int i64b_launch_fused(const CUtensorMap& tm_x, const CUtensorMap& tm_w13, const CUtensorMap& tm_inter_r, const CUtensorMap& tm_inter_s,
+                      const CUtensorMap& tm_w2r, const CUtensorMap& tm_w2s, const I64bFusedParams& p,
+                      cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
         I64B_CUDA(cudaFuncSetAttribute(i64b_fused_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         configured = true;
     }
     const int grid = i64b_num_sms();
-    I64B_CUDA(i64b_launch(i64b_fused_layer_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_xs, tm_w13,
-                          tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, p));
+    static const bool dbg_tl = getenv("I64B_DEBUG_TIMELINE") != nullptr;
+    if (!dbg_tl) {
+        I64B_CUDA(i64b_launch(i64b_fused_layer_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
+                              tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, p));
+        i64b_count_launch(1);
+        return I64B_OK;
+    }
+    // ---- bring-up instrumentation only (allocates + synchronises; never active unless the env asks for it)
+    I64bFusedParams q = p;
+    static long long* d_tl = nullptr;
+    if (d_tl == nullptr) cudaMalloc(&d_tl, 256 * 16 * sizeof(long long));
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cs);
+    if (cs == cudaStreamCaptureStatusNone) { cudaMemsetAsync(d_tl, 0, 256 * 16 * sizeof(long long), stream); q.timeline = d_tl; }
+    I64B_CUDA(i64b_launch(i64b_fused_layer_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
+                          tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, q));
     i64b_count_launch(1);
+    if (cs == cudaStreamCaptureStatusNone) {
+        static int printed = 0;
+        static long long h[256 * 16];
+        cudaStreamSynchronize(stream);
+        cudaMemcpy(h, d_tl, sizeof(h), cudaMemcpyDeviceToHost);
+        if (printed++ >= 2 && printed <= 6) {
+            long long g0 = h[0];
+            for (int b = 0; b < grid; ++b) if (h[b * 16] && h[b * 16] < g0) g0 = h[b * 16];
+            fprintf(stderr, "[i64b fused timeline] ns since first CTA start:\n  %-8s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s\n", "", "start",
+                    "ids", "table", "plan", "g2rA", "g2sA", "mma0", "epi0", "st0", "pub1", "mma1", "pub2", "cwait", "cgo", "end");
+            static const int order[15] = {0, 3, 2, 1, 4, 5, 6, 14, 15, 7, 9, 10, 11, 12, 13};
+            for (int b = 0; b < grid; b += 9) {
+                fprintf(stderr, "  cta %3d:", b);
+                for (int j = 0; j < 15; ++j) { const long long v = h[b * 16 + order[j]]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
+                fprintf(stderr, "\n");
+            }
+            long long mx[16] = {0};
+            for (int b = 0; b < grid; ++b) for (int j = 0; j < 16; ++j) { const long long v = h[b * 16 + j] ? h[b * 16 + j] - g0 : 0; if (v > mx[j]) mx[j] = v; }
+            fprintf(stderr, "  max    :");
+            for (int j = 0; j < 15; ++j) fprintf(stderr, " %6lld", mx[order[j]]);
+            fprintf(stderr, "\n");
+        }
+    }
     return I64B_OK;
 }

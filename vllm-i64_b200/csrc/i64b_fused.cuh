@@ -4,13 +4,12 @@
 #include "i64b_common.cuh"
 
 #define I64B_FUSED_MAX_TOKENS 1024
-#define I64B_FUSED_MAX_MTILES 128
+#define I64B_FUSED_MAX_GROUPS 128     // experts + shared m-tiles (one GEMM1→GEMM2 counter each)
 // persistent per-layer sync area (ints, zero at load, reset by the last CTA of every launch)
-#define I64B_SYNC_DISPATCH 0
 #define I64B_SYNC_G2 1
 #define I64B_SYNC_FINISH 2
 #define I64B_SYNC_G1 4
-#define I64B_SYNC_INTS (I64B_SYNC_G1 + I64B_FUSED_MAX_MTILES)
+#define I64B_SYNC_INTS (I64B_SYNC_G1 + I64B_FUSED_MAX_GROUPS)
 
 struct I64bFusedParams {
     const void* x;              // [N, H] bf16
@@ -19,18 +18,18 @@ struct I64bFusedParams {
     int32_t n, hidden, num_experts, expert_inter, shared_inter, top_k, vocab, out_dtype;
     float w[I64B_MAX_TOPK];
     float routed_scale, shared_scale;
-    void* xs;                   // [N*K + N, H] bf16 dispatched rows
-    void* inter_r;              // [N*K, I_e] bf16
+    void* inter_r;              // [N*K, I_e] bf16, expert-major rows
     void* inter_s;              // [N, S] bf16
     float* y;                   // [N*K + slabs*N, H] fp32
     void* out;                  // [N, H]
     int* sync;                  // I64B_SYNC_INTS ints
+    long long* timeline;        // bring-up only: [grid, 16] ns stamps (env I64B_DEBUG_TIMELINE)
     int32_t *tap_routes, *tap_dest, *tap_scatter, *tap_counts, *tap_offsets;   // reference-convention plan outputs
 };
 
 int i64b_fused_supported(int n, int hidden, int expert_inter, int shared_inter, int num_experts, int top_k);
-int i64b_launch_fused(const CUtensorMap& tm_xs, const CUtensorMap& tm_w13, const CUtensorMap& tm_inter_r,
-                      const CUtensorMap& tm_inter_s, const CUtensorMap& tm_w2r, const CUtensorMap& tm_w2s,
-                      const I64bFusedParams& p, cudaStream_t stream);
+int i64b_launch_fused(const CUtensorMap& tm_x, const CUtensorMap& tm_w13, const CUtensorMap& tm_inter_r, const CUtensorMap& tm_inter_s,
+                      const CUtensorMap& tm_w2r, const CUtensorMap& tm_w2s, const I64bFusedParams& p,
+                      cudaStream_t stream);
 int i64b_num_sms();
 void i64b_count_launch(int n);
