@@ -46,10 +46,14 @@ struct Smem {
     int group_start[I64B_MAX_EXPERTS + 1];   // first inter_r / y row of each expert; [E] = N*K
     int route_base[I64B_MAX_BINS];
     int offsets[I64B_MAX_BINS];
-    uint16_t warp_cnt[kPlanWarps][I64B_MAX_BINS];
     uint16_t dest_row[I64B_MAX_TOPK][kMaxTok];          // merged expert-major row of assignment (k, t)
     uint16_t src_tok[I64B_MAX_TOPK * kMaxTok];          // inverse: token of merged row
-    uint8_t expert[I64B_MAX_TOPK][kMaxTok];
+    uint8_t expert[I64B_MAX_TOPK][kMaxTok];             // 0xFF past N up to the next multiple of 128
+    // fast path for the CTA's first unit (routed GEMM1): the first 128 tokens of its expert, and the expert's row count
+    uint16_t own_tok[kBlockM];
+    int fast_cnt[kPlanWarps];
+    int rows_first;
+    uint32_t plan_ready;                                // full plan published (release/acquire, CTA scope)
 };
 
 // static work list
@@ -102,16 +106,11 @@ __device__ __noinline__ void decode_unit(const I64bFusedParams& p, const Geo& ge
         u.nkb = ((krem < kSlabK ? krem : kSlabK) + kBlockK - 1) / kBlockK;
     }
 }
-// 128-row passes over a unit's rows (an expert without tokens still runs one, empty, pass: its weights may
-// already be on their way when the plan completes)
-__device__ __forceinline__ int unit_passes(const Smem& s, const Unit& u) {
-    if (u.type == kG1Routed || u.type == kG2Routed) {
-        const int m = (s.group_rows[u.g] + kBlockM - 1) / kBlockM;
-        return m > 0 ? m : 1;
-    }
-    return 1;
+__device__ __forceinline__ int warp_sum(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
 }
-
 __device__ __forceinline__ uint64_t sw128_desc(const void* p) {
     uint64_t d = (uint64_t)((smem_u32(p) >> 4) & 0x3FFFu);
     d |= (uint64_t)(1024 >> 4) << 32;
@@ -166,6 +165,25 @@ __device__ __forceinline__ void wait_stage_owned(const uint32_t* b_seq, uint32_t
     while (ld_acquire_cta(b_seq) <= seq)
         if (clock64() - t0 > 4000000000ll) __trap();
 }
+__device__ __noinline__ void wait_plan_slow(const uint32_t* flag) {
+    const long long t0 = clock64();
+    while (ld_acquire_cta(flag) == 0)
+        if (clock64() - t0 > 4000000000ll) __trap();
+}
+// Rows of a routed unit's expert (-1 for the shared expert).  The CTA's first unit gets its count from the fast path;
+// everything else needs the full plan, which the epilogue warps publish a little later.
+__device__ __forceinline__ int unit_rows(const Smem& s, const Unit& u, bool first, bool& have_plan) {
+    if (u.type == kG1Shared || u.type == kG2Shared) return -1;
+    if (first && u.type == kG1Routed) return s.rows_first;
+    if (!have_plan) {
+        if (ld_acquire_cta(&s.plan_ready) == 0) wait_plan_slow(&s.plan_ready);
+        have_plan = true;
+    }
+    return s.group_rows[u.g];
+}
+// 128-row passes over a unit's rows (an expert without tokens still runs one, empty, pass: its weights are already
+// on their way when the plan completes)
+__device__ __forceinline__ int passes_of(int rows) { return rows <= kBlockM ? 1 : (rows + kBlockM - 1) / kBlockM; }
 __device__ __forceinline__ void named_bar_arrive(int id, int threads) {
     asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(threads) : "memory");
 }
@@ -194,6 +212,7 @@ __device__ __forceinline__ long long gtime() {
 __device__ __forceinline__ void wait_counter(const int* ctr, int target) {
     const long long t0 = clock64();
     while (ld_acquire(ctr) < target) {
+        __nanosleep(64);
         if (clock64() - t0 > 4000000000ll) __trap();
     }
 }
@@ -213,7 +232,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     const int E = p.num_experts, K = p.top_k, N = p.n, H = p.hidden, bins = K * E, G = gridDim.x;
     const Geo geo = make_geo(p);
     pdl_launch_dependents();
-    long long* tl = p.timeline ? p.timeline + (size_t)blockIdx.x * 16 : nullptr;
+    long long* tl = p.timeline ? p.timeline + (size_t)blockIdx.x * 32 : nullptr;
     if (threadIdx.x == 0) TL(0);
 
     // weight tile of (unit, k-block) → shared-memory stage; tx bytes = kStageB
@@ -233,6 +252,12 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         }
     };
 
+    int own_e = -1;              // expert of the CTA's first unit when that is a routed GEMM1 unit
+    if ((int)blockIdx.x < geo.U) {
+        Unit uf;
+        decode_unit(p, geo, blockIdx.x, uf);
+        if (uf.type == kG1Routed) own_e = uf.g;
+    }
     int pre_issued = 0;          // weight stages the TMA thread put in flight before the plan (first unit, pass 0)
     if (warp == 0) {
         Unit u0;
@@ -256,6 +281,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         if (lane == 0) {
             for (int kb = kStages / 2; kb < pre_issued; ++kb) issue_b(u0, kb, kb);
             s.b_seq = (uint32_t)pre_issued;                       // published by the __syncthreads below
+            s.plan_ready = 0;
         }
         pre_issued = __shfl_sync(0xffffffffu, pre_issued, 0);
     } else if (warp == 1) {
@@ -267,7 +293,6 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             const int pt = threadIdx.x - 64;
             constexpr int kPT = kPlanWarps * 32;
             pdl_wait_prior();        // token ids may come from the previous kernel in the stream
-            for (int i = pt; i < kPlanWarps * I64B_MAX_BINS / 2; i += kPT) reinterpret_cast<uint32_t*>(&s.warp_cnt[0][0])[i] = 0;
             // N <= 256 (the decode sizes this kernel is tuned for) is one trip; larger batches pay one round trip each
             int ev0[I64B_MAX_TOPK];
             {
@@ -293,93 +318,46 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                 for (int k = 0; k < K; ++k)
                     s.expert[k][t] = (uint8_t)min(p.token_ids ? (int)__ldg(p.table + (int64_t)k * p.vocab + c) : (k % E), E - 1);
             }
+            for (int t = N + pt; t < ((N + 127) & ~127); t += kPT)         // padding: matches no expert
+                for (int k = 0; k < K; ++k) s.expert[k][t] = 0xFF;
             if (pt == 0) TL(2);                                    // table values have arrived
             named_bar_sync(2, kPT);
-            // stable rank of every assignment inside its (route, expert) bin: warp pw owns a contiguous token range
-            const int tok_per_warp = ((N + kPlanWarps - 1) / kPlanWarps + 31) / 32 * 32;
-            const int tbase = pw * tok_per_warp;
-            const unsigned lt_mask = (1u << lane) - 1u;
+            // ---- fast path: the token list (first 128 rows) and the row count of the expert of the CTA's first unit,
+            // which is all its GEMM1 needs to start.  Chunks of 128 tokens in (route, token) order = merged row order;
+            // warp pw owns a contiguous run of chunks; lane l holds tokens 4l..4l+3 of a chunk (one 32-bit load).
+            if (own_e >= 0) {
+                const uint32_t pat = (uint32_t)own_e * 0x01010101u;
+                const unsigned lt_mask = (1u << lane) - 1u;
+                const int nch = (N + 127) >> 7, ctot = K * nch, cpw = (ctot + kPlanWarps - 1) / kPlanWarps;
+                const int c_begin = pw * cpw, c_end = min(ctot, c_begin + cpw);
+                int cnt = 0;
 #pragma unroll 1
-            for (int t0 = tbase; t0 < tbase + tok_per_warp && t0 < N; t0 += 32) {
-                const int t = t0 + lane;
-                const bool valid = t < N;
-#pragma unroll 1
-                for (int k = 0; k < K; ++k) {
-                    const int e = valid ? (int)s.expert[k][t] : 0xFF;
-                    const unsigned peers = __match_any_sync(0xffffffffu, e);
-                    const int leader = __ffs(peers) - 1;
-                    const int prev = valid ? s.warp_cnt[pw][k * E + e] : 0;
-                    __syncwarp();
-                    if (valid && lane == leader) s.warp_cnt[pw][k * E + e] = (uint16_t)(prev + __popc(peers));
-                    __syncwarp();
-                    if (valid) s.dest_row[k][t] = (uint16_t)(prev + __popc(peers & lt_mask));   // rank inside the warp's range
+                for (int c = c_begin; c < c_end; ++c) {
+                    const uint32_t word = reinterpret_cast<const uint32_t*>(s.expert[c / nch])[(c % nch) * 32 + lane];
+                    cnt += __popc(__vcmpeq4(word, pat)) >> 3;
                 }
-            }
-            named_bar_sync(2, kPT);
-#pragma unroll 1
-            for (int b = pt; b < bins; b += kPT) {                  // exclusive scan over warps → per-bin totals
-                int running = 0;
+                cnt = warp_sum(cnt);
+                if (lane == 0) s.fast_cnt[pw] = cnt;
+                named_bar_sync(2, kPT);
+                int running = 0, total = 0;
 #pragma unroll
                 for (int w = 0; w < kPlanWarps; ++w) {
-                    const int c = s.warp_cnt[w][b];
-                    s.warp_cnt[w][b] = (uint16_t)running;
-                    running += c;
+                    const int cw = s.fast_cnt[w];
+                    if (w < pw) running += cw;
+                    total += cw;
                 }
-                s.offsets[b] = running;                             // holds counts until the scans below
-            }
-            named_bar_sync(2, kPT);
-            if (pt < 32) {                                          // one warp: the three small scans
-                // rows per expert and the base of route k inside expert e's merged segment
+                if (pt == 0) s.rows_first = total;
 #pragma unroll 1
-                for (int e = lane; e < E; e += 32) {
-                    int rows = 0;
-#pragma unroll 1
-                    for (int k = 0; k < K; ++k) { s.route_base[k * E + e] = rows; rows += s.offsets[k * E + e]; }
-                    s.group_rows[e] = rows;
-                }
-                __syncwarp();
-                int gs = 0;                                         // exclusive scan of group_rows over experts
-#pragma unroll 1
-                for (int e0 = 0; e0 < E; e0 += 32) {
-                    const int v = e0 + lane < E ? s.group_rows[e0 + lane] : 0;
-                    int inc = v;
+                for (int c = c_begin; c < c_end && running < kBlockM; ++c) {
+                    const uint32_t eq = __vcmpeq4(reinterpret_cast<const uint32_t*>(s.expert[c / nch])[(c % nch) * 32 + lane], pat);
+                    const unsigned b0 = __ballot_sync(0xffffffffu, eq & 0xFFu), b1 = __ballot_sync(0xffffffffu, eq & 0xFF00u);
+                    const unsigned b2 = __ballot_sync(0xffffffffu, eq & 0xFF0000u), b3 = __ballot_sync(0xffffffffu, eq & 0xFF000000u);
+                    int pos = running + __popc(b0 & lt_mask) + __popc(b1 & lt_mask) + __popc(b2 & lt_mask) + __popc(b3 & lt_mask);
+                    const int t0 = (c % nch) * 128 + lane * 4;
 #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) { const int n_ = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += n_; }
-                    if (e0 + lane < E) s.group_start[e0 + lane] = gs + inc - v;
-                    gs += __shfl_sync(0xffffffffu, inc, 31);
-                }
-                if (lane == 0) s.group_start[E] = gs;
-                if (blockIdx.x == 0 && p.tap_counts)
-                    for (int b = lane; b < bins; b += 32) p.tap_counts[b] = s.offsets[b];
-                __syncwarp();
-                if (lane < K) {                                     // per-route exclusive offsets (reference convention)
-                    int off = 0;
-#pragma unroll 1
-                    for (int e = 0; e < E; ++e) { const int c = s.offsets[lane * E + e]; s.offsets[lane * E + e] = off; off += c; }
-                }
-                __syncwarp();
-                if (blockIdx.x == 0 && p.tap_offsets)
-                    for (int b = lane; b < bins; b += 32) p.tap_offsets[b] = s.offsets[b];
-            }
-            named_bar_sync(2, kPT);
-#pragma unroll 1
-            for (int t0 = tbase; t0 < tbase + tok_per_warp && t0 < N; t0 += 32) {
-                const int t = t0 + lane;
-                if (t < N) {
-#pragma unroll 1
-                    for (int k = 0; k < K; ++k) {
-                        const int e = s.expert[k][t];
-                        const int bin = k * E + e;
-                        const int in_exp = s.warp_cnt[pw][bin] + s.dest_row[k][t];
-                        const int dest = s.group_start[e] + s.route_base[bin] + in_exp;
-                        s.dest_row[k][t] = (uint16_t)dest;
-                        s.src_tok[dest] = (uint16_t)t;
-                        if (blockIdx.x == 0) {
-                            if (p.tap_routes) p.tap_routes[(int64_t)k * N + t] = e;
-                            if (p.tap_dest) p.tap_dest[(int64_t)k * N + t] = dest;
-                            if (p.tap_scatter) p.tap_scatter[(int64_t)k * N + t] = s.offsets[bin] + in_exp;
-                        }
-                    }
+                    for (int j = 0; j < 4; ++j)
+                        if ((eq >> (8 * j)) & 1u) { if (pos < kBlockM) s.own_tok[pos] = (uint16_t)(t0 + j); ++pos; }
+                    running += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
                 }
             }
         }
@@ -388,7 +366,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_ptr;
-    const int R = E > 0 ? s.group_start[E] : 0;      // routed rows (= N*K)
+    bool have_plan = false;
     if (threadIdx.x == 0) TL(1);
 
     if (warp == 0) {
@@ -399,7 +377,8 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             for (int v = blockIdx.x; v < geo.U; v += G) {
                 Unit u;
                 decode_unit(p, geo, v, u);
-                const int np = unit_passes(s, u);
+                const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            const int np = passes_of(rows_u);
                 for (int pass = 0; pass < np; ++pass)
                     for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
                         if (seq < (uint32_t)pre_issued) continue;          // issued before the plan
@@ -421,7 +400,8 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             for (int v = blockIdx.x; v < geo.U; v += G) {
                 Unit u;
                 decode_unit(p, geo, v, u);
-                const int np = unit_passes(s, u);
+                const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            const int np = passes_of(rows_u);
                 for (int pass = 0; pass < np; ++pass, ++iter) {
                     const int as = iter & 1;
                     mbar_wait_bounded(&s.tempty_bar[as], ((iter >> 1) & 1) ^ 1);
@@ -446,11 +426,86 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         // ------------------------------------------------------------------ epilogue warps
         const int q = warp & 3;
         const int r = q * 32 + lane;
+        // ---- full plan (these four warps are idle until the first accumulator is complete): counts, segment starts,
+        // dest_row / src_tok for every assignment.  Warp w owns experts w, w + 4, ...; lane l holds tokens 4l..4l+3 of
+        // a 128-token chunk; one 4-way byte compare + four ballots rank a whole chunk in (route, token) order.
+        {
+            const int pw4 = warp - 2;
+            const unsigned lt_mask = (1u << lane) - 1u;
+            const int nch = (N + 127) >> 7;
+            if (warp == 2 && lane == 0) TL(16);
+#pragma unroll 1
+            for (int e = pw4; e < E; e += 4) {
+                const uint32_t pat = (uint32_t)e * 0x01010101u;
+                int rows = 0;
+#pragma unroll 1
+                for (int k = 0; k < K; ++k) {
+                    int c = 0;
+#pragma unroll 1
+                    for (int ch = 0; ch < nch; ++ch)
+                        c += __popc(__vcmpeq4(reinterpret_cast<const uint32_t*>(s.expert[k])[ch * 32 + lane], pat)) >> 3;
+                    c = warp_sum(c);
+                    if (lane == 0) { s.route_base[k * E + e] = rows; s.offsets[k * E + e] = c; }   // offsets = counts for now
+                    rows += c;
+                }
+                if (lane == 0) s.group_rows[e] = rows;
+            }
+            named_bar_sync(1, 128);
+            if (warp == 2 && lane == 0) TL(17);
+            const bool taps = blockIdx.x == 0 && p.tap_routes != nullptr;
+#pragma unroll 1
+            for (int e = pw4; e < E; e += 4) {
+                const uint32_t pat = (uint32_t)e * 0x01010101u;
+                // first merged row of expert e = rows of the experts before it (E <= 64: two values per lane)
+                const int gs = warp_sum((lane < e ? s.group_rows[lane] : 0) + (lane + 32 < e ? s.group_rows[lane + 32] : 0));
+                if (lane == 0) s.group_start[e] = gs;
+#pragma unroll 1
+                for (int k = 0; k < K; ++k) {
+                    int off_k = 0;                                  // per-route exclusive offset (reference convention)
+                    if (taps) {
+                        off_k = warp_sum((lane < e ? s.offsets[k * E + lane] : 0) + (lane + 32 < e ? s.offsets[k * E + lane + 32] : 0));
+                        if (lane == 0) { p.tap_counts[k * E + e] = s.offsets[k * E + e]; p.tap_offsets[k * E + e] = off_k; }
+                    }
+                    int running = gs + s.route_base[k * E + e];
+#pragma unroll 1
+                    for (int ch = 0; ch < nch; ++ch) {
+                        const uint32_t eq = __vcmpeq4(reinterpret_cast<const uint32_t*>(s.expert[k])[ch * 32 + lane], pat);
+                        const unsigned b0 = __ballot_sync(0xffffffffu, eq & 0xFFu), b1 = __ballot_sync(0xffffffffu, eq & 0xFF00u);
+                        const unsigned b2 = __ballot_sync(0xffffffffu, eq & 0xFF0000u), b3 = __ballot_sync(0xffffffffu, eq & 0xFF000000u);
+                        int dest = running + __popc(b0 & lt_mask) + __popc(b1 & lt_mask) + __popc(b2 & lt_mask) + __popc(b3 & lt_mask);
+                        const int t0 = ch * 128 + lane * 4;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if ((eq >> (8 * j)) & 1u) {
+                                const int t = t0 + j;
+                                s.dest_row[k][t] = (uint16_t)dest;
+                                s.src_tok[dest] = (uint16_t)t;
+                                if (taps) {
+                                    p.tap_routes[(int64_t)k * N + t] = e;
+                                    p.tap_dest[(int64_t)k * N + t] = dest;
+                                    p.tap_scatter[(int64_t)k * N + t] = off_k + dest - gs - s.route_base[k * E + e];
+                                }
+                                ++dest;
+                            }
+                        running += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+                    }
+                }
+            }
+            if (pw4 == 0) {                                         // total routed rows
+                const int tot = warp_sum((lane < E ? s.group_rows[lane] : 0) + (lane + 32 < E ? s.group_rows[lane + 32] : 0));
+                if (lane == 0) s.group_start[E] = tot;
+            }
+            named_bar_sync(1, 128);
+            if (warp == 2 && lane == 0) { st_release_cta(&s.plan_ready, 1u); TL(18); }
+            have_plan = true;
+        }
+        const int R = E > 0 ? s.group_start[E] : 0;      // routed rows (= N*K)
         int iter = 0;
         for (int v = blockIdx.x; v < geo.U; v += G) {
             Unit u;
             decode_unit(p, geo, v, u);
-            const int np = unit_passes(s, u);
+            const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            const int np = passes_of(rows_u);
             for (int pass = 0; pass < np; ++pass, ++iter) {
                 const int as = iter & 1;
                 mbar_wait_bounded(&s.tfull_bar[as], (iter >> 1) & 1);
@@ -510,13 +565,13 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&s.tempty_bar[as]);
             }
-            // publish the unit: all four epilogue warps' stores → one release increment
+            // publish the unit: the barrier orders the four epilogue warps' stores before one thread's gpu-scope
+            // release (cumulative), so a single fence covers them all
             if (warp == 2 && lane == 0 && iter == np) TL(15);
-            __threadfence();
             named_bar_sync(1, 128);
             if (warp == 2 && lane == 0) {
-                if (u.type == kG1Routed) red_release_add(p.sync + I64B_SYNC_G1 + u.g, 1);
-                else if (u.type == kG1Shared) red_release_add(p.sync + I64B_SYNC_G1 + E + u.m_t, 1);
+                if (u.type == kG1Routed) red_release_add(p.sync + I64B_SYNC_G1(u.g), 1);
+                else if (u.type == kG1Shared) red_release_add(p.sync + I64B_SYNC_G1(E + u.m_t), 1);
                 else red_release_add(p.sync + I64B_SYNC_G2, 1);
                 TL(u.type <= kG1Shared ? 7 : 10);
             }
@@ -532,7 +587,8 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         for (int v = blockIdx.x; v < geo.U; v += G) {
             Unit u;
             decode_unit(p, geo, v, u);
-            const int np = unit_passes(s, u);
+            const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            const int np = passes_of(rows_u);
             if (u.type != kG1Routed) { seq += (uint32_t)(np * u.nkb); continue; }
             for (int pass = 0; pass < np; ++pass) {
                 const __nv_bfloat16* src[8];
@@ -541,8 +597,16 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                 for (int j = 0; j < 8; ++j) {
                     const int rj = gw * 32 + j * 4 + (lane >> 3);
                     const int row = pass * kBlockM + rj;
-                    src[j] = row < s.group_rows[u.g] ? xb + (int64_t)s.src_tok[s.group_start[u.g] + row] * H + chunk * 8
-                                                     : nullptr;
+                    int tok = -1;
+                    if (row < rows_u) {
+                        if (v == (int)blockIdx.x && pass == 0) {
+                            tok = s.own_tok[rj];                   // fast path: the full plan may still be in the making
+                        } else {
+                            if (!have_plan) { if (ld_acquire_cta(&s.plan_ready) == 0) wait_plan_slow(&s.plan_ready); have_plan = true; }
+                            tok = s.src_tok[s.group_start[u.g] + row];
+                        }
+                    }
+                    src[j] = tok >= 0 ? xb + (int64_t)tok * H + chunk * 8 : nullptr;
                     dst_off[j] = (uint32_t)(rj * 128 + ((chunk ^ (rj & 7)) << 4));
                 }
                 for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
@@ -567,13 +631,16 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             for (int v = blockIdx.x; v < geo.U; v += G) {
                 Unit u;
                 decode_unit(p, geo, v, u);
-                const int np = unit_passes(s, u);
+                const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            const int np = passes_of(rows_u);
                 if (u.type == kG1Routed) { seq += (uint32_t)(np * u.nkb); continue; }
                 if (u.type >= kG2Routed) {
-                    const int* ctr = p.sync + I64B_SYNC_G1 + (u.type == kG2Routed ? u.g : E + u.m_t);
+                    const int* ctr = p.sync + I64B_SYNC_G1(u.type == kG2Routed ? u.g : E + u.m_t);
                     const int target = u.type == kG2Routed ? geo.nt1r : geo.nt1s;
-                    while (ld_acquire(ctr) < target)
+                    while (ld_acquire(ctr) < target) {
+                        __nanosleep(64);                           // keep the pollers off the publishers' L2 line
                         if (clock64() - t_begin > 4000000000ll) __trap();
+                    }
                     fence_proxy_async_global();
                     TL(u.type == kG2Routed ? 4 : 5);
                 }
@@ -602,51 +669,75 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     __syncthreads();
     if (threadIdx.x == 0) { TL(11); wait_counter(p.sync + I64B_SYNC_G2, geo.U2); TL(12); }
     __syncthreads();
+    const int R = E > 0 ? s.group_start[E] : 0;      // routed rows (= N*K); the full plan is complete by now
     {
+        // one item = four output columns of one of this CTA's tokens (t = blockIdx.x + j*G); two items per trip so
+        // that the loads of both are in flight together (a CTA owns at most two tokens at decode sizes)
         const int hv = H / 4;
-        for (int t = blockIdx.x; t < N; t += G) {
-            for (int c = threadIdx.x; c < hv; c += kThreads) {
-                float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (E > 0) {
+        const int ntok = N > (int)blockIdx.x ? (N - (int)blockIdx.x + G - 1) / G : 0;
+        const int items = ntok * hv;
+        auto combine_item = [&](int item) -> float4 {
+            const int t = blockIdx.x + (item / hv) * G, c = item % hv;
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 yk[I64B_MAX_TOPK];
 #pragma unroll
-                    for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-                        if (k < K) {
-                            const float4 y = ld_cg_f4(p.y + (int64_t)s.dest_row[k][t] * H + c * 4);
-                            const float w = p.w[k];
-                            if (k == 0) {
-                                o = make_float4(__fmul_rn(w, y.x), __fmul_rn(w, y.y), __fmul_rn(w, y.z), __fmul_rn(w, y.w));
-                            } else {
-                                o.x = __fadd_rn(o.x, __fmul_rn(w, y.x)); o.y = __fadd_rn(o.y, __fmul_rn(w, y.y));
-                                o.z = __fadd_rn(o.z, __fmul_rn(w, y.z)); o.w = __fadd_rn(o.w, __fmul_rn(w, y.w));
-                            }
-                        }
-                    }
-                    const float rs = p.routed_scale;
-                    o = make_float4(__fmul_rn(rs, o.x), __fmul_rn(rs, o.y), __fmul_rn(rs, o.z), __fmul_rn(rs, o.w));
-                }
-                if (geo.slabs > 0) {
-                    float4 sh = ld_cg_f4(p.y + ((int64_t)R + t) * H + c * 4);
-                    for (int sl = 1; sl < geo.slabs; ++sl) {    // split-K slabs of the shared down-projection, fixed order
-                        const float4 y = ld_cg_f4(p.y + ((int64_t)R + (int64_t)sl * N + t) * H + c * 4);
-                        sh.x = __fadd_rn(sh.x, y.x); sh.y = __fadd_rn(sh.y, y.y);
-                        sh.z = __fadd_rn(sh.z, y.z); sh.w = __fadd_rn(sh.w, y.w);
-                    }
-                    if (E > 0) {
-                        const float ss = p.shared_scale;
-                        o.x = __fadd_rn(o.x, __fmul_rn(ss, sh.x)); o.y = __fadd_rn(o.y, __fmul_rn(ss, sh.y));
-                        o.z = __fadd_rn(o.z, __fmul_rn(ss, sh.z)); o.w = __fadd_rn(o.w, __fmul_rn(ss, sh.w));
-                    } else {
-                        o = sh;
-                    }
-                }
-                if (p.out_dtype == I64B_F32) {
-                    reinterpret_cast<float4*>(p.out)[(int64_t)t * hv + c] = o;
-                } else {
-                    __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
-                    reinterpret_cast<uint2*>(p.out)[(int64_t)t * hv + c] =
-                        make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+            for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                if (k < K) yk[k] = __ldcg(reinterpret_cast<const float4*>(p.y + (int64_t)s.dest_row[k][t] * H) + c);
+            float4 sh = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (geo.slabs > 0) {
+                sh = __ldcg(reinterpret_cast<const float4*>(p.y + ((int64_t)R + t) * H) + c);
+#pragma unroll 1
+                for (int sl = 1; sl < geo.slabs; ++sl) {    // split-K slabs of the shared down-projection, fixed order
+                    const float4 y = __ldcg(reinterpret_cast<const float4*>(p.y + ((int64_t)R + (int64_t)sl * N + t) * H) + c);
+                    sh.x = __fadd_rn(sh.x, y.x); sh.y = __fadd_rn(sh.y, y.y);
+                    sh.z = __fadd_rn(sh.z, y.z); sh.w = __fadd_rn(sh.w, y.w);
                 }
             }
+            if (E > 0) {
+#pragma unroll
+                for (int k = 0; k < I64B_MAX_TOPK; ++k) {
+                    if (k < K) {
+                        const float4 y = yk[k];
+                        const float w = p.w[k];
+                        if (k == 0) {
+                            o = make_float4(__fmul_rn(w, y.x), __fmul_rn(w, y.y), __fmul_rn(w, y.z), __fmul_rn(w, y.w));
+                        } else {
+                            o.x = __fadd_rn(o.x, __fmul_rn(w, y.x)); o.y = __fadd_rn(o.y, __fmul_rn(w, y.y));
+                            o.z = __fadd_rn(o.z, __fmul_rn(w, y.z)); o.w = __fadd_rn(o.w, __fmul_rn(w, y.w));
+                        }
+                    }
+                }
+                const float rs = p.routed_scale;
+                o = make_float4(__fmul_rn(rs, o.x), __fmul_rn(rs, o.y), __fmul_rn(rs, o.z), __fmul_rn(rs, o.w));
+            }
+            if (geo.slabs > 0) {
+                if (E > 0) {
+                    const float ss = p.shared_scale;
+                    o.x = __fadd_rn(o.x, __fmul_rn(ss, sh.x)); o.y = __fadd_rn(o.y, __fmul_rn(ss, sh.y));
+                    o.z = __fadd_rn(o.z, __fmul_rn(ss, sh.z)); o.w = __fadd_rn(o.w, __fmul_rn(ss, sh.w));
+                } else {
+                    o = sh;
+                }
+            }
+            return o;
+        };
+        auto store_item = [&](int item, const float4& o) {
+            const int t = blockIdx.x + (item / hv) * G, c = item % hv;
+            if (p.out_dtype == I64B_F32) {
+                reinterpret_cast<float4*>(p.out)[(int64_t)t * hv + c] = o;
+            } else {
+                __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+                reinterpret_cast<uint2*>(p.out)[(int64_t)t * hv + c] =
+                    make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+            }
+        };
+#pragma unroll 1
+        for (int i = threadIdx.x; i < items; i += 2 * kThreads) {
+            const int i2 = i + kThreads;
+            const float4 o0 = combine_item(i);
+            const float4 o1 = combine_item(i2 < items ? i2 : i);
+            store_item(i, o0);
+            if (i2 < items) store_item(i2, o1);
         }
     }
 
@@ -662,7 +753,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         __threadfence();
         const int ticket = atomicAdd(p.sync + I64B_SYNC_FINISH, 1);
         if (ticket == G - 1) {
-            for (int i = 0; i < I64B_SYNC_INTS; ++i) p.sync[i] = 0;
+            for (int i = 0; i < I64B_SYNC_INTS; i += I64B_SYNC_STRIDE) p.sync[i] = 0;
             __threadfence();
         }
     }
@@ -702,33 +793,36 @@ int i64b_launch_fused(const CUtensorMap& tm_x, const CUtensorMap& tm_w13, const 
     // ---- bring-up instrumentation only (allocates + synchronises; never active unless the env asks for it)
     I64bFusedParams q = p;
     static long long* d_tl = nullptr;
-    if (d_tl == nullptr) cudaMalloc(&d_tl, 256 * 16 * sizeof(long long));
+    if (d_tl == nullptr) cudaMalloc(&d_tl, 256 * 32 * sizeof(long long));
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(stream, &cs);
-    if (cs == cudaStreamCaptureStatusNone) { cudaMemsetAsync(d_tl, 0, 256 * 16 * sizeof(long long), stream); q.timeline = d_tl; }
+    if (cs == cudaStreamCaptureStatusNone) { cudaMemsetAsync(d_tl, 0, 256 * 32 * sizeof(long long), stream); q.timeline = d_tl; }
     I64B_CUDA(i64b_launch(i64b_fused_layer_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
                           tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, q));
     i64b_count_launch(1);
     if (cs == cudaStreamCaptureStatusNone) {
         static int printed = 0;
-        static long long h[256 * 16];
+        static long long h[256 * 32];
         cudaStreamSynchronize(stream);
         cudaMemcpy(h, d_tl, sizeof(h), cudaMemcpyDeviceToHost);
         if (printed++ >= 2 && printed <= 6) {
             long long g0 = h[0];
-            for (int b = 0; b < grid; ++b) if (h[b * 16] && h[b * 16] < g0) g0 = h[b * 16];
-            fprintf(stderr, "[i64b fused timeline] ns since first CTA start:\n  %-8s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s %6s\n", "", "start",
-                    "ids", "table", "plan", "g2rA", "g2sA", "mma0", "epi0", "st0", "pub1", "mma1", "pub2", "cwait", "cgo", "end");
-            static const int order[15] = {0, 3, 2, 1, 4, 5, 6, 14, 15, 7, 9, 10, 11, 12, 13};
+            for (int b = 0; b < grid; ++b) if (h[b * 32] && h[b * 32] < g0) g0 = h[b * 32];
+            static const char* names[18] = {"start", "ids", "table", "fast", "fp0", "fpA", "fpB", "g2rA", "g2sA", "mma0",
+                                            "epi0", "st0", "pub1", "mma1", "pub2", "cwait", "cgo", "end"};
+            static const int order[18] = {0, 3, 2, 1, 16, 17, 18, 4, 5, 6, 14, 15, 7, 9, 10, 11, 12, 13};
+            fprintf(stderr, "[i64b fused timeline] ns since first CTA start:\n  %-8s", "");
+            for (int j = 0; j < 18; ++j) fprintf(stderr, " %6s", names[j]);
+            fprintf(stderr, "\n");
             for (int b = 0; b < grid; b += 9) {
                 fprintf(stderr, "  cta %3d:", b);
-                for (int j = 0; j < 15; ++j) { const long long v = h[b * 16 + order[j]]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
+                for (int j = 0; j < 18; ++j) { const long long v = h[b * 32 + order[j]]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
                 fprintf(stderr, "\n");
             }
-            long long mx[16] = {0};
-            for (int b = 0; b < grid; ++b) for (int j = 0; j < 16; ++j) { const long long v = h[b * 16 + j] ? h[b * 16 + j] - g0 : 0; if (v > mx[j]) mx[j] = v; }
+            long long mx[32] = {0};
+            for (int b = 0; b < grid; ++b) for (int j = 0; j < 32; ++j) { const long long v = h[b * 32 + j] ? h[b * 32 + j] - g0 : 0; if (v > mx[j]) mx[j] = v; }
             fprintf(stderr, "  max    :");
-            for (int j = 0; j < 15; ++j) fprintf(stderr, " %6lld", mx[order[j]]);
+            for (int j = 0; j < 18; ++j) fprintf(stderr, " %6lld", mx[order[j]]);
             fprintf(stderr, "\n");
         }
     }

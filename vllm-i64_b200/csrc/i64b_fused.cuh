@@ -6,10 +6,12 @@
 #define I64B_FUSED_MAX_TOKENS 1024
 #define I64B_FUSED_MAX_GROUPS 128     // experts + shared m-tiles (one GEMM1→GEMM2 counter each)
 // persistent per-layer sync area (ints, zero at load, reset by the last CTA of every launch)
-#define I64B_SYNC_G2 1
-#define I64B_SYNC_FINISH 2
-#define I64B_SYNC_G1 4
-#define I64B_SYNC_INTS (I64B_SYNC_G1 + I64B_FUSED_MAX_GROUPS)
+// every counter sits on its own 128-byte line: pollers of one dependency do not queue behind another's at L2
+#define I64B_SYNC_STRIDE 32
+#define I64B_SYNC_G2 (1 * I64B_SYNC_STRIDE)
+#define I64B_SYNC_FINISH (2 * I64B_SYNC_STRIDE)
+#define I64B_SYNC_G1(i) ((4 + (i)) * I64B_SYNC_STRIDE)
+#define I64B_SYNC_INTS ((4 + I64B_FUSED_MAX_GROUPS) * I64B_SYNC_STRIDE)
 
 struct I64bFusedParams {
     const void* x;              // [N, H] bf16
