@@ -54,6 +54,7 @@ struct Smem {
     int fast_cnt[kPlanWarps];
     int rows_first;
     uint32_t plan_ready;                                // full plan published (release/acquire, CTA scope)
+    int comb_rank, comb_total;                          // this CTA's index among the combine workers (-1: none) and their number
 };
 
 // static work list
@@ -286,13 +287,16 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         pre_issued = __shfl_sync(0xffffffffu, pre_issued, 0);
     } else if (warp == 1) {
         tmem_alloc<kTmemCols>(&s.tmem_ptr);
+        // Combine: token t belongs to CTA t % G.  (Measured: handing the combine to the ~36 CTAs that finish early, so
+        // that the others can exit and free their SMs for the next kernel, costs 9 us of combine against 3 us when all
+        // 148 SMs share it: the pass is bound by per-SM L2 read latency, not by work.)
+        if (lane == 0) { s.comb_rank = blockIdx.x; s.comb_total = G; }
     } else {
         // ------------------------------------------------------------------ plan (warps 2-9, into shared memory)
         if (warp < 2 + kPlanWarps) {
             const int pw = warp - 2;
             const int pt = threadIdx.x - 64;
             constexpr int kPT = kPlanWarps * 32;
-            pdl_wait_prior();        // token ids may come from the previous kernel in the stream
             // N <= 256 (the decode sizes this kernel is tuned for) is one trip; larger batches pay one round trip each
             int ev0[I64B_MAX_TOPK];
             {
@@ -665,19 +669,21 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         }
     }
 
-    // ------------------------------------------------------------------ combine this CTA's tokens
+    // ------------------------------------------------------------------ combine (workers only)
     __syncthreads();
+    const int crank = s.comb_rank, ctot = s.comb_total;
+    if (crank >= 0) {
     if (threadIdx.x == 0) { TL(11); wait_counter(p.sync + I64B_SYNC_G2, geo.U2); TL(12); }
     __syncthreads();
     const int R = E > 0 ? s.group_start[E] : 0;      // routed rows (= N*K); the full plan is complete by now
     {
-        // one item = four output columns of one of this CTA's tokens (t = blockIdx.x + j*G); two items per trip so
-        // that the loads of both are in flight together (a CTA owns at most two tokens at decode sizes)
+        // one item = four output columns of one of this worker's tokens (t = rank + j * workers); two items per trip
+        // so that the loads of all of them are in flight together
         const int hv = H / 4;
-        const int ntok = N > (int)blockIdx.x ? (N - (int)blockIdx.x + G - 1) / G : 0;
+        const int ntok = N > crank ? (N - crank + ctot - 1) / ctot : 0;
         const int items = ntok * hv;
         auto combine_item = [&](int item) -> float4 {
-            const int t = blockIdx.x + (item / hv) * G, c = item % hv;
+            const int t = crank + (item / hv) * ctot, c = item % hv;
             float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
             float4 yk[I64B_MAX_TOPK];
 #pragma unroll
@@ -722,7 +728,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             return o;
         };
         auto store_item = [&](int item, const float4& o) {
-            const int t = blockIdx.x + (item / hv) * G, c = item % hv;
+            const int t = crank + (item / hv) * ctot, c = item % hv;
             if (p.out_dtype == I64B_F32) {
                 reinterpret_cast<float4*>(p.out)[(int64_t)t * hv + c] = o;
             } else {
@@ -733,12 +739,17 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         };
 #pragma unroll 1
         for (int i = threadIdx.x; i < items; i += 2 * kThreads) {
-            const int i2 = i + kThreads;
-            const float4 o0 = combine_item(i);
-            const float4 o1 = combine_item(i2 < items ? i2 : i);
-            store_item(i, o0);
-            if (i2 < items) store_item(i2, o1);
+            const int i1 = i + kThreads;
+            if (i1 < items) {
+                const float4 o0 = combine_item(i);
+                const float4 o1 = combine_item(i1);
+                store_item(i, o0);
+                store_item(i1, o1);
+            } else {
+                store_item(i, combine_item(i));
+            }
         }
+    }
     }
 
     // ------------------------------------------------------------------ teardown: last CTA resets the counters
