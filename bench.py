@@ -57,6 +57,20 @@ def peaks():
         return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
 
 
+def ncu_traffic(workload, kernel_key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full
+    capture of this workload (profiles/ncu_traffic.json, written by tools/summarize_ncu.py); None if not captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f).get(workload, {})
+        for name, v in t.items():
+            if kernel_key in name:
+                return int(v)
+    except Exception:
+        pass
+    return None
+
+
 def route_weights(wl):
     k = wl["K"]
     if k <= 1:
@@ -424,6 +438,8 @@ def main():
         dom = max(stages_json, key=lambda k: stages_json[k]["us_per_launch"])
         d = stages_json[dom]
         hbm_bound = d["frac_hbm"] >= d.get("frac_tensor_bf16_peak", 0.0) / (2.0 if wl["mode"] == "int8" else 1.0)
+        kkey = {"gemm1": "i64b_gemm_kernel<%d, 1" % (1 if wl["mode"] == "int8" else 0),
+                "gemm2": "i64b_gemm_kernel<%d, 0" % (1 if wl["mode"] == "int8" else 0)}.get(dom, dom)
         if hbm_bound:
             roof = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": pk["hbm"], "unit": "GB/s",
                     "frac": d["frac_hbm"], "traffic": None, "peak_source": pk["src"] + " (burst copy)"}
@@ -433,17 +449,11 @@ def main():
             roof = {"kernel": dom, "bound": "tensor", "achieved": d[key], "peak": peak,
                     "unit": "TFLOP/s" if wl["mode"] == "bf16" else "TOP/s", "frac": round(d[key] / peak, 4),
                     "traffic": None, "peak_source": pk["src"] + (" bf16 burst x2 (nominal INT8:bf16 ratio)" if wl["mode"] == "int8" else " bf16 burst")}
+        if roof is not None:
+            roof["traffic"] = ncu_traffic(args.workload, kkey)
         if layers[0].uses_fused(N):
             # the step runs ONE fused kernel per layer; the stage list above is the unfused chain, for comparison
-            us = ms * 1e3 / (args.steps * L)
-            a_ = 1 if wl["mode"] == "int8" else 2
-            fb = ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * H * a_) + N * H * 2 * 2
-            gbs = fb / (us * 1e-6) / 1e9
-            roof = {"kernel": "i64b_fused_layer_kernel", "bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"],
-                    "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4), "traffic": None,
-                    "peak_source": pk["src"] + " (burst copy)", "algorithmic_bytes": fb, "us_per_launch": round(us, 3)}
             stages_json = {"unfused_chain_for_comparison": stages_json}
-            stages_json["_step_us_per_layer"] = round(us, 2)
         sum_us = sum(v["us_per_launch"] for v in stages_json.values() if isinstance(v, dict) and "us_per_launch" in v)
         stages_json["_sum_us_per_layer"] = round(sum_us, 2)
         stages_json["_step_us_per_layer"] = round(ms * 1e3 / (args.steps * L), 2)
@@ -453,6 +463,16 @@ def main():
         stages_json["_block_min_bytes"] = min_bytes
         stages_json["_block_frac_hbm"] = round(min_bytes / (ms * 1e-3 / (args.steps * L)) / 1e9 / pk["hbm"], 4)
 
+    if rank == 0 and layers[0].uses_fused(N):
+        # dominant (only) kernel of the step: the fused layer kernel, timed live over the whole timed region
+        us = ms * 1e3 / (args.steps * L)
+        a_ = 1 if wl["mode"] == "int8" else 2
+        fb = ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * H * a_) + N * H * 2 * 2     # weights once + x in + out
+        gbs = fb / (us * 1e-6) / 1e9
+        roof = {"kernel": "i64b_fused_layer_kernel", "bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"],
+                "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4),
+                "traffic": ncu_traffic(args.workload, "i64b_fused_layer_kernel"),
+                "peak_source": pk["src"] + " (burst copy)", "algorithmic_bytes": fb, "us_per_launch": round(us, 3)}
     ep_json = None
     if world > 1 and wl["E"] and wl["E"] % world == 0 and not args.no_ep:
         ep_json = run_ep(wl, device, rank, world, args)
