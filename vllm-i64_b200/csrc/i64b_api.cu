@@ -291,6 +291,9 @@ int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, c
     const i64b_moe_config& c = L->cfg;
     I64B_CHECK(c.num_experts == 0 || (w13_q && w13_s && w2_q && w2_s), I64B_ERR_ARG, "expert weights missing");
     I64B_CHECK(c.shared_inter == 0 || (sh13_q && sh13_s && sh2_q && sh2_s), I64B_ERR_ARG, "shared weights missing");
+    // the SwiGLU epilogue folds silu_integer's two out-of-range selects into `lut[clamp(g)] + max(g - 1024, 0)`
+    I64B_CHECK(kSiluLutQ7[0] == 0 && kSiluLutQ7[I64B_SILU_LUT_SIZE - 1] == 1024, I64B_ERR_STATE,
+               "Q7 SiLU table ends must be 0 and 1024");
     cudaStream_t s = (cudaStream_t)stream;
     L->packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(packed) + 255) & ~uintptr_t(255));
     carve_packed(L, L->packed, nullptr);
@@ -470,6 +473,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     {
         const int n_mma = pick_nmma(mt_r, I, mt_s, S, true, "I64B_GEMM1_NMMA");
         const int bn = n_mma / 2;
+        const int nh = bn >= 64 ? 2 : 1;       // |max| partials per GEMM1 tile row: one per epilogue column half
         I64bGemmParams gp = {};
         gp.groups = cv.plan.groups1;
         gp.num_groups = E + 1;
@@ -493,12 +497,12 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         }
         if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
             if (E > 0) {
-                rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, (I + bn - 1) / bn,
+                rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, ((I + bn - 1) / bn) * nh,
                                           reinterpret_cast<int8_t*>(cv.inter_r), cv.inter_scale_r, nullptr, R, I, s);
                 if (rc) return rc;
             }
             if (S > 0) {
-                rc = i64b_run_requant_q14(cv.q14_s, cv.amax_s, cv.amax_ld_s, (S + bn - 1) / bn,
+                rc = i64b_run_requant_q14(cv.q14_s, cv.amax_s, cv.amax_ld_s, ((S + bn - 1) / bn) * nh,
                                           reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, nullptr, n, S, s);
                 if (rc) return rc;
             }

@@ -25,14 +25,20 @@ namespace {
 constexpr int kBlockM = 128;
 constexpr int kRowBytes = 128;                     // one 128B swizzle span of K per stage row
 constexpr int kStageA = kBlockM * kRowBytes;       // 16 KiB
-constexpr int kThreads = 192;                      // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kThreads = 320;                      // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
+constexpr int kEpiWarps = 8;
 constexpr int kMiscBytes = 8192;
+constexpr int kStagePitch = 80;                    // 64-byte row payload + 16: row-per-lane 16 B stores hit 8 distinct bank groups
+constexpr int kStageWarpBytes = 32 * kStagePitch;  // per-warp output staging block (32 rows x 64 B)
+constexpr int kScaleWarpBytes = 512;               // per-warp column scales of the current tile (<= 128 floats)
+constexpr int kEpiWarpBytes = kStageWarpBytes + kScaleWarpBytes;
 
 template <int kNMma> struct StageCfg {
     static constexpr int kStageB = kNMma * kRowBytes;
     static constexpr int kStagesRaw = 196608 / (kStageA + kStageB);
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-    static constexpr int kSmem = 1024 + kStages * (kStageA + kStageB) + kMiscBytes;
+    static constexpr int kSmem = 1024 + kStages * (kStageA + kStageB) + kMiscBytes + kEpiWarps * kEpiWarpBytes;
+    static_assert(kSmem <= 232448, "shared memory budget (227 KB per CTA)");
 };
 
 __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem_ptr) {
@@ -75,6 +81,41 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ int ld_shared_s16(uint32_t addr) {
+    int v;
+    asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+// One [32 rows x 64 bytes] output block of a warp: lane i supplies the 64 bytes of row i (the TMEM read layout);
+// the block is transposed through the warp's staging area and leaves as 64-byte row segments, 8 rows per store
+// instruction (16 full sectors) instead of 32 rows x 16 bytes.  Rows >= rows_valid and bytes >= bytes_valid
+// (a multiple of 16) are not written.
+__device__ __forceinline__ void warp_store_block(uint32_t st_addr, const uint32_t (&v)[16], uint8_t* gbase,
+                                                 int64_t pitch_bytes, int rows_valid, int bytes_valid, int lane) {
+    __syncwarp();                                   // the previous block's reads are done
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};"
+                     :: "r"(st_addr + lane * kStagePitch + j * 16), "r"(v[4 * j]), "r"(v[4 * j + 1]), "r"(v[4 * j + 2]),
+                        "r"(v[4 * j + 3]) : "memory");
+    __syncwarp();
+    const int piece = lane & 3;
+    const int rr = (lane >> 3) + 4 * ((lane >> 2) & 1);   // quarter-warps read rows {k, k+4}: 16 banks apart
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = i * 8 + rr;
+        int4 d;
+        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(d.x), "=r"(d.y), "=r"(d.z), "=r"(d.w) : "r"(st_addr + row * kStagePitch + piece * 16));
+        if (row < rows_valid && piece * 16 < bytes_valid)
+            *reinterpret_cast<int4*>(gbase + row * pitch_bytes + piece * 16) = d;
+    }
+}
 
 template <bool kInt8, bool kDual, int kNMma>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -87,6 +128,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     constexpr int kBnOut = kDual ? kNMma / 2 : kNMma;
     constexpr int kBlockK = kInt8 ? 128 : 64;          // elements per 128-byte row
     constexpr uint32_t kTmemCols = 2 * kNMma;          // two accumulator stages (power of two ≥ 32)
+    static_assert((kDual ? kNMma / 2 : kNMma) >= 32, "a warp drains at least one 32-column TMEM chunk");
     static_assert(kTmemCols >= 32 && kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
 
     extern __shared__ uint8_t smem_raw[];
@@ -103,6 +145,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     I64bGroup* sg = reinterpret_cast<I64bGroup*>(misc + 512);
     int16_t* slut = reinterpret_cast<int16_t*>(misc + 512 + sizeof(I64bGroup) * I64B_MAX_GROUPS);
     static_assert(512 + sizeof(I64bGroup) * I64B_MAX_GROUPS + 2 * I64B_SILU_LUT_SIZE <= kMiscBytes, "misc smem");
+    uint8_t* stage_base = misc + kMiscBytes;
     static_assert((2 * 8 + 2 * 2) * 8 + 8 + 4 * (I64B_MAX_GROUPS + 1) <= 512, "barrier area");
 
     const int warp = threadIdx.x >> 5;
@@ -127,7 +170,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull_bar[i], 1);
-            mbar_init(&tempty_bar[i], 4);
+            mbar_init(&tempty_bar[i], kEpiWarps);
         }
         fence_barrier_init();
     } else if (warp == 1) {
@@ -233,9 +276,20 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             }
         }
     } else {
-        // ------------------------------------------------------------------ epilogue (4 warps = 128 TMEM lanes)
-        const int q = warp & 3;                 // TMEM lane quarter this warp may access
-        const int r = q * 32 + lane;            // tile row owned by this thread
+        // ------------------------------------------------------------------ epilogue (8 warps: 4 TMEM lane quarters x 2 column halves)
+        // Every output block goes registers -> per-warp smem staging (row per lane, conflict-free 80-byte pitch) ->
+        // coalesced 64-byte row segments in global memory (8 rows per warp instruction) instead of one row per lane.
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access (hardware: warp id % 4)
+        const int h = (warp - 2) >> 2;          // column half of the tile this warp drains
+        const int r = q * 32 + lane;            // tile row owned by this thread while reading TMEM
+        constexpr bool kSplit = kBnOut >= 64;   // narrow tiles: only the h == 0 warps work
+        constexpr int kColsW = kSplit ? kBnOut / 2 : kBnOut;    // output columns per warp
+        const bool active = kSplit || h == 0;
+        const int cbase = kSplit ? h * kColsW : 0;
+        const uint32_t st_addr = smem_u32(stage_base + (warp - 2) * kEpiWarpBytes);
+        float* wscale = reinterpret_cast<float*>(stage_base + (warp - 2) * kEpiWarpBytes + kStageWarpBytes);
+        const uint32_t ws_addr = st_addr + kStageWarpBytes;
+        const uint32_t lut_addr = smem_u32(slut);
         int g = 0, iter = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++iter) {
             TileCoord tc;
@@ -243,114 +297,158 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const I64bGroup grp = sg[tc.g];
             const int w = grp.which;
             const int as = iter & 1;
+            const int n_out = grp.n_out;
+            const int row_in_group = tc.m_t * kBlockM + r;
+            const bool valid = row_in_group < grp.rows;
+            const int64_t a_row = (int64_t)grp.row_start + row_in_group;
+            const int64_t out_row0 = (int64_t)grp.out_row_start + tc.m_t * kBlockM + q * 32;   // first row of this warp
+            const int rows_valid = min(32, max(0, grp.rows - (tc.m_t * kBlockM + q * 32)));
+            const int colw0 = tc.n_t * kBnOut + cbase;      // first output column of this warp
+
+            // per-column scales of this warp's slice -> smem (before waiting for the accumulator)
+            if constexpr (kInt8 || !kDual) {
+                const bool need = kInt8 ? (kDual || p.epi == I64B_EPI_DEQUANT) : (p.epi == I64B_EPI_DEQUANT);
+                if (active && need) {
+                    const float* cs = p.col_scale[w] + grp.w_row_base;
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < (kColsW + 31) / 32; ++i) {
+                        const int c = i * 32 + lane;
+                        if (c < kColsW) {
+                            const bool cv = colw0 + c < n_out;
+                            wscale[c] = cv ? __ldg(cs + colw0 + c) : 0.0f;
+                            if constexpr (kDual) wscale[kColsW + c] = cv ? __ldg(cs + n_out + colw0 + c) : 0.0f;
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+
             mbar_wait(&tfull_bar[as], (iter >> 1) & 1);
             tc_fence_after();
             if (tl && threadIdx.x == 64) tl[5] = clock64() - t0;
-            if (p.debug_flags & 2u) {
+            if ((p.debug_flags & 2u) || !active) {
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tempty_bar[as]);
                 continue;
             }
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma;
-            const int row_in_group = tc.m_t * kBlockM + r;
-            const bool valid = row_in_group < grp.rows;
-            const int64_t out_row = (int64_t)grp.out_row_start + row_in_group;
-            const int64_t a_row = (int64_t)grp.row_start + row_in_group;
-            const int n_out = grp.n_out;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma + cbase;
 
             if constexpr (kDual && !kInt8) {
-                __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out[w]) + out_row * p.ld_out[w];
+                uint8_t* obase = reinterpret_cast<uint8_t*>(p.out[w]) + (out_row0 * p.ld_out[w] + colw0) * 2;
+                const int64_t pitch = p.ld_out[w] * 2;
 #pragma unroll 1
-                for (int c = 0; c < kBnOut / 32; ++c) {
-                    const int col0 = tc.n_t * kBnOut + c * 32;
-                    if (col0 >= n_out) break;
-                    uint32_t gr[32], ur[32];
-                    tmem_ld_32x32(taddr + c * 32, gr);
-                    tmem_ld_32x32(taddr + kBnOut + c * 32, ur);
-                    tmem_ld_wait();
+                for (int c = 0; c < kColsW; c += 32) {
+                    if (colw0 + c >= n_out) break;
                     uint32_t o[16];
+                    {
+                        uint32_t gr[32], ur[32];
+                        tmem_ld_32x32(taddr + c, gr);
+                        tmem_ld_32x32(taddr + kBnOut + c, ur);
+                        tmem_ld_wait();
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
-                        const float h1 = silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]);
-                        o[j] = pack_bf16x2(h0, h1);
+                        for (int j = 0; j < 16; ++j) {
+                            const float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
+                            const float h1 = silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]);
+                            o[j] = pack_bf16x2(h0, h1);
+                        }
                     }
-                    if (valid) {
-#pragma unroll
-                        for (int v = 0; v < 4; ++v)
-                            if (col0 + v * 8 < n_out)
-                                *reinterpret_cast<int4*>(orow + col0 + v * 8) =
-                                    make_int4(o[4 * v], o[4 * v + 1], o[4 * v + 2], o[4 * v + 3]);
-                    }
+                    warp_store_block(st_addr, o, obase + c * 2, pitch, rows_valid, min(64, (n_out - colw0 - c) * 2), lane);
                 }
             } else if constexpr (kDual && kInt8) {
-                int32_t* orow = reinterpret_cast<int32_t*>(p.out[w]) + out_row * p.ld_out[w];
-                const float rs = valid ? p.row_scale[w][a_row] : 0.0f;
-                const float* cs_g = p.col_scale[w] + grp.w_row_base;
-                const float* cs_u = cs_g + n_out;
+                uint8_t* obase = reinterpret_cast<uint8_t*>(p.out[w]) + (out_row0 * p.ld_out[w] + colw0) * 4;
+                const int64_t pitch = p.ld_out[w] * 4;
+                // fold the Q7 factor into the row scale: fl(fl(a*fl(rs*s))*128) == fl(a*fl((128*rs)*s)) exactly
+                // (scaling by 2^7 commutes with round-to-nearest; scales are >= 1e-8/127, nothing denormal)
+                const float rs128 = valid ? __fmul_rn(p.row_scale[w][a_row], 128.0f) : 0.0f;
                 int amax = 0;
 #pragma unroll 1
-                for (int c = 0; c < kBnOut / 32; ++c) {
-                    const int col0 = tc.n_t * kBnOut + c * 32;
-                    if (col0 >= n_out) break;
-                    uint32_t gr[32], ur[32];
-                    tmem_ld_32x32(taddr + c * 32, gr);
-                    tmem_ld_32x32(taddr + kBnOut + c * 32, ur);
-                    tmem_ld_wait();
-                    int o[32];
+                for (int c = 0; c < kColsW; c += 32) {
+                    if (colw0 + c >= n_out) break;
+                    {
+                        uint32_t gr[32], ur[32];
+                        tmem_ld_32x32(taddr + c, gr);
+                        tmem_ld_32x32(taddr + kBnOut + c, ur);
+                        tmem_ld_wait();
+                        int o[32];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const bool cv = col0 + j < n_out;
-                        const float sg_ = cv ? __ldg(cs_g + col0 + j) : 0.0f;
-                        const float su_ = cv ? __ldg(cs_u + col0 + j) : 0.0f;
-                        // result_i32.float() * (x_scale * w_scale)           core/quantization.py:278
-                        const float gate = __fmul_rn((float)(int)gr[j], __fmul_rn(rs, sg_));
-                        const float up = __fmul_rn((float)(int)ur[j], __fmul_rn(rs, su_));
-                        // silu_multiply_integer                              layers/integer_activations.py:53-66
-                        const int gq = __float2int_rn(__fmul_rn(gate, 128.0f));
-                        const int uq = __float2int_rn(__fmul_rn(up, 128.0f));
-                        int sq = (int)slut[min(max(gq, -1024), 1024) + 1024];
-                        sq = gq > 1024 ? gq : sq;
-                        sq = gq < -1024 ? 0 : sq;
-                        const int q14 = sq * uq;
-                        o[j] = q14;
-                        if (cv) amax = max(amax, abs(q14));
-                    }
-                    if (valid) {
+                        for (int j4 = 0; j4 < 8; ++j4) {
+                            const float4 sg4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
+                            const float4 su4 = ld_shared_f4(ws_addr + (kColsW + c + j4 * 4) * 4);
+                            const float sgv[4] = {sg4.x, sg4.y, sg4.z, sg4.w};
+                            const float suv[4] = {su4.x, su4.y, su4.z, su4.w};
 #pragma unroll
-                        for (int v = 0; v < 8; ++v)
-                            if (col0 + v * 4 < n_out)
-                                *reinterpret_cast<int4*>(orow + col0 + v * 4) =
-                                    make_int4(o[4 * v], o[4 * v + 1], o[4 * v + 2], o[4 * v + 3]);
+                            for (int jj = 0; jj < 4; ++jj) {
+                                const int j = j4 * 4 + jj;
+                                // result_i32.float() * (x_scale * w_scale), then (.. * 128).round()
+                                //                          core/quantization.py:278, layers/integer_activations.py:60-63
+                                const int gq = __float2int_rn(__fmul_rn((float)(int)gr[j], __fmul_rn(rs128, sgv[jj])));
+                                const int uq = __float2int_rn(__fmul_rn((float)(int)ur[j], __fmul_rn(rs128, suv[jj])));
+                                // silu_integer: LUT on [-1024, 1024], identity above, 0 below (LUT ends are 0 and 1024,
+                                // checked at load time), so the two selects collapse into one add
+                                const int idx = min(max(gq, -1024), 1024);
+                                const int sq = ld_shared_s16(lut_addr + (uint32_t)(idx + 1024) * 2) + max(gq - 1024, 0);
+                                o[j] = sq * uq;
+                            }
+                        }
+                        const bool second = colw0 + c + 16 < n_out;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) amax = max(amax, abs(o[j]));
+                        if (second) {
+#pragma unroll
+                            for (int j = 16; j < 32; ++j) amax = max(amax, abs(o[j]));
+                        }
+                        uint32_t blk[16];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) blk[j] = (uint32_t)o[j];
+                        warp_store_block(st_addr, blk, obase + c * 4, pitch, rows_valid, 64, lane);
+                        if (second) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) blk[j] = (uint32_t)o[16 + j];
+                            warp_store_block(st_addr, blk, obase + (c + 16) * 4, pitch, rows_valid, 64, lane);
+                        }
                     }
                 }
-                if (valid) p.amax_part[w][out_row * p.amax_ld[w] + tc.n_t] = amax;
+                if (valid)
+                    p.amax_part[w][(out_row0 + lane) * p.amax_ld[w] + tc.n_t * (kSplit ? 2 : 1) + (kSplit ? h : 0)] = amax;
             } else {
                 const bool dequant = p.epi == I64B_EPI_DEQUANT;
                 const float rs = (dequant && valid && p.row_scale[w] != nullptr) ? p.row_scale[w][a_row] : 1.0f;
-                const float* cs = dequant ? p.col_scale[w] + grp.w_row_base : nullptr;
+                const bool f32out = p.out_dtype == I64B_F32;
+                const int osz = f32out ? 4 : 2;
+                uint8_t* obase = p.out[w] == nullptr ? nullptr
+                                 : reinterpret_cast<uint8_t*>(p.out[w]) + (out_row0 * p.ld_out[w] + colw0) * osz;
+                const int64_t pitch = p.ld_out[w] * osz;
 #pragma unroll 1
-                for (int c = 0; c < kNMma / 32; ++c) {
-                    const int col0 = tc.n_t * kNMma + c * 32;
-                    if (col0 >= n_out) break;
+                for (int c = 0; c < kColsW; c += 32) {
+                    if (colw0 + c >= n_out) break;
                     uint32_t ar[32];
-                    tmem_ld_32x32(taddr + c * 32, ar);
+                    tmem_ld_32x32(taddr + c, ar);
                     tmem_ld_wait();
+                    const bool second = colw0 + c + 16 < n_out;
                     if constexpr (kInt8) {
-                        if (p.raw_out != nullptr && valid) {
-                            int32_t* rrow = p.raw_out + out_row * p.ld_raw;
+                        if (p.raw_out != nullptr) {
+                            uint8_t* rbase = reinterpret_cast<uint8_t*>(p.raw_out) + (out_row0 * p.ld_raw + colw0 + c) * 4;
+                            uint32_t blk[16];
 #pragma unroll
-                            for (int v = 0; v < 8; ++v)
-                                if (col0 + v * 4 < n_out)
-                                    *reinterpret_cast<int4*>(rrow + col0 + v * 4) =
-                                        make_int4(ar[4 * v], ar[4 * v + 1], ar[4 * v + 2], ar[4 * v + 3]);
+                            for (int j = 0; j < 16; ++j) blk[j] = ar[j];
+                            warp_store_block(st_addr, blk, rbase, p.ld_raw * 4, rows_valid, 64, lane);
+                            if (second) {
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) blk[j] = ar[16 + j];
+                                warp_store_block(st_addr, blk, rbase + 64, p.ld_raw * 4, rows_valid, 64, lane);
+                            }
                         }
                         if (dequant) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                const float s = (col0 + j < n_out) ? __ldg(cs + col0 + j) : 0.0f;
-                                ar[j] = __float_as_uint(__fmul_rn((float)(int)ar[j], __fmul_rn(rs, s)));
+                            for (int j4 = 0; j4 < 8; ++j4) {
+                                const float4 s4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
+                                // result_i32.float() * (x_scale * w_scale)              core/quantization.py:173
+                                ar[4 * j4 + 0] = __float_as_uint(__fmul_rn((float)(int)ar[4 * j4 + 0], __fmul_rn(rs, s4.x)));
+                                ar[4 * j4 + 1] = __float_as_uint(__fmul_rn((float)(int)ar[4 * j4 + 1], __fmul_rn(rs, s4.y)));
+                                ar[4 * j4 + 2] = __float_as_uint(__fmul_rn((float)(int)ar[4 * j4 + 2], __fmul_rn(rs, s4.z)));
+                                ar[4 * j4 + 3] = __float_as_uint(__fmul_rn((float)(int)ar[4 * j4 + 3], __fmul_rn(rs, s4.w)));
                             }
                         } else {
 #pragma unroll
@@ -358,31 +456,30 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         }
                     } else if (dequant) {   // bf16 GEMM with a per-column (and optional per-row) fp32 scale
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float s = (col0 + j < n_out) ? __ldg(cs + col0 + j) : 0.0f;
-                            ar[j] = __float_as_uint(__fmul_rn(__uint_as_float(ar[j]), __fmul_rn(rs, s)));
+                        for (int j4 = 0; j4 < 8; ++j4) {
+                            const float4 s4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
+                            ar[4 * j4 + 0] = __float_as_uint(__fmul_rn(__uint_as_float(ar[4 * j4 + 0]), __fmul_rn(rs, s4.x)));
+                            ar[4 * j4 + 1] = __float_as_uint(__fmul_rn(__uint_as_float(ar[4 * j4 + 1]), __fmul_rn(rs, s4.y)));
+                            ar[4 * j4 + 2] = __float_as_uint(__fmul_rn(__uint_as_float(ar[4 * j4 + 2]), __fmul_rn(rs, s4.z)));
+                            ar[4 * j4 + 3] = __float_as_uint(__fmul_rn(__uint_as_float(ar[4 * j4 + 3]), __fmul_rn(rs, s4.w)));
                         }
                     }
-                    if (valid && p.out[w] != nullptr) {
-                        if (p.out_dtype == I64B_F32) {
-                            float* orow = reinterpret_cast<float*>(p.out[w]) + out_row * p.ld_out[w];
+                    if (obase != nullptr) {
+                        uint32_t blk[16];
+                        if (f32out) {
 #pragma unroll
-                            for (int v = 0; v < 8; ++v)
-                                if (col0 + v * 4 < n_out)
-                                    *reinterpret_cast<int4*>(orow + col0 + v * 4) =
-                                        make_int4(ar[4 * v], ar[4 * v + 1], ar[4 * v + 2], ar[4 * v + 3]);
+                            for (int j = 0; j < 16; ++j) blk[j] = ar[j];
+                            warp_store_block(st_addr, blk, obase + c * 4, pitch, rows_valid, 64, lane);
+                            if (second) {
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) blk[j] = ar[16 + j];
+                                warp_store_block(st_addr, blk, obase + (c + 16) * 4, pitch, rows_valid, 64, lane);
+                            }
                         } else {
-                            __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out[w]) + out_row * p.ld_out[w];
 #pragma unroll
-                            for (int v = 0; v < 4; ++v)
-                                if (col0 + v * 8 < n_out) {
-                                    int4 pk;
-                                    pk.x = pack_bf16x2(__uint_as_float(ar[8 * v]), __uint_as_float(ar[8 * v + 1]));
-                                    pk.y = pack_bf16x2(__uint_as_float(ar[8 * v + 2]), __uint_as_float(ar[8 * v + 3]));
-                                    pk.z = pack_bf16x2(__uint_as_float(ar[8 * v + 4]), __uint_as_float(ar[8 * v + 5]));
-                                    pk.w = pack_bf16x2(__uint_as_float(ar[8 * v + 6]), __uint_as_float(ar[8 * v + 7]));
-                                    *reinterpret_cast<int4*>(orow + col0 + v * 8) = pk;
-                                }
+                            for (int j = 0; j < 16; ++j)
+                                blk[j] = pack_bf16x2(__uint_as_float(ar[2 * j]), __uint_as_float(ar[2 * j + 1]));
+                            warp_store_block(st_addr, blk, obase + c * 2, pitch, rows_valid, second ? 64 : 32, lane);
                         }
                     }
                 }
