@@ -94,8 +94,13 @@ def stage_bytes(wl):
     b["gemm1"] = w13 + rows * H * a + inter_w
     b["requant"] = (R * I + N * S) * 5 if a == 1 else 0
     w2 = (E * H * I + H * S) * a
-    b["gemm2"] = w2 + (R * I + N * S) * a + rows * H * 4
-    b["combine"] = rows * H * 4 + N * H * 2 + R * 4
+    if has_s and E == 0:
+        # fused combine (dense FFN): the shared expert's GEMM2 tiles pull the routed fp32 rows and write the block output
+        b["gemm2"] = w2 + (R * I + N * S) * a + 2 * R * H * 4 + R * 4 + N * H * 2
+        b["combine"] = 0
+    else:
+        b["gemm2"] = w2 + (R * I + N * S) * a + rows * H * 4
+        b["combine"] = rows * H * 4 + N * H * 2 + R * 4
     f = {"gemm1": 2.0 * H * 2 * (R * I + N * S), "gemm2": 2.0 * H * (R * I + N * S)}
     return b, f
 

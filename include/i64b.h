@@ -226,6 +226,12 @@ enum {
 };
 void* i64b_moe_tap(i64b_layer* layer, int what);
 
+/* Debug switches of a layer.  I64B_DEBUG_KEEP_TAPS: the down-projection kernel finishes the block inside the shared
+ * expert's tiles (fused combine) and then has no reason to store the shared expert's own fp32 rows; with this flag it
+ * stores them as well, so I64B_TAP_Y is complete (rows N*K.. = shared expert).  The block output is identical. */
+enum { I64B_DEBUG_KEEP_TAPS = 1, I64B_DEBUG_FUSE_COMBINE = 2 /* force the fused combine (default: dense FFN only) */ };
+int i64b_moe_set_debug(i64b_layer* layer, int flags);
+
 /* ---------------------------------------------------------------------------
  * Stand-alone W8A8 / weight-only GEMM ops  (a12, a13)
  * ------------------------------------------------------------------------- */

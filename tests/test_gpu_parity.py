@@ -295,7 +295,11 @@ def test_block_w8a8_bit_exact(case):
     cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=n + 1)
     wq = O.quantize_moe_weights(w)
     blk = Hh.build_gpu_block(cfg, w, table, "int8", wq)
+    out_plain = blk.forward(cu(x, torch.bfloat16), cu(ids), torch.float32)
+    # fused combine (the shared expert's GEMM2 tiles pull the routed rows): same bits as the separate combine pass
+    blk.set_debug(_C.DEBUG_KEEP_TAPS | _C.DEBUG_FUSE_COMBINE)
     out = blk.forward(cu(x, torch.bfloat16), cu(ids), torch.float32)
+    assert torch.equal(out, out_plain)
     _plan_checks(blk, cfg, table, ids, n)
     tr = {}
     ref = O.moe_block_w8a8(x, ids, table, wq, cfg, trace=tr)

@@ -54,6 +54,7 @@ struct i64b_layer {
     int* sync = nullptr;         // fused-kernel counters (persistent, zero between launches)
     const uint8_t* table = nullptr;
     bool loaded = false;
+    int debug = 0;               // I64B_DEBUG_* bits (i64b_moe_set_debug)
     CUtensorMap tm_w13[3], tm_w2r[3], tm_w2s[3];   // per n_mma choice (box rows differ)
     // activation tensor maps, valid for (ws_base, n)
     void* cached_ws = nullptr;
@@ -320,6 +321,12 @@ int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, c
     return I64B_OK;
 }
 
+int i64b_moe_set_debug(i64b_layer* L, int flags) {
+    I64B_CHECK(L, I64B_ERR_ARG, "null layer");
+    L->debug = flags;
+    return I64B_OK;
+}
+
 int i64b_moe_set_table(i64b_layer* L, const uint8_t* table_u8) {
     I64B_CHECK(L, I64B_ERR_ARG, "null layer");
     L->table = table_u8;
@@ -329,6 +336,14 @@ int i64b_moe_set_table(i64b_layer* L, const uint8_t* table_u8) {
 size_t i64b_moe_workspace_bytes(const i64b_layer* L, int64_t max_tokens) {
     if (!L) return 0;
     return carve_ws(L, nullptr, max_tokens).bytes + 1024;
+}
+
+// Fused combine policy (I64B_FUSE_COMBINE: 0 never, 1 always, unset = auto).  Measured on B200 (N = 16 384): for a dense
+// FFN the fused epilogue replaces a 22 us pass for free; with routed experts the shared tiles' pull of 2 fp32 rows per
+// token is not hidden under the MMAs (133 us fused vs 88 + 42 us), so auto keeps the separate combine pass there.
+static int fuse_combine_mode() {
+    static const int mode = getenv("I64B_FUSE_COMBINE") ? atoi(getenv("I64B_FUSE_COMBINE")) : -1;
+    return mode;
 }
 
 static bool fused_enabled() {
@@ -466,6 +481,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         if (rc) return rc;
     }
 
+    bool combine_fused = false;
     const int64_t mt_r = E > 0 ? R / 128 + E : 0;     // upper bound on routed m-tiles
     const int64_t mt_s = S > 0 ? (n + 127) / 128 : 0;
 
@@ -525,6 +541,24 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.row_scale[1] = cv.inter_scale_s;
         gp.col_scale[0] = L->w2r_scale;
         gp.col_scale[1] = L->w2s_scale;
+        // with a shared expert (or a dense FFN) its GEMM2 tiles finish the block: they pull the routed rows of
+        // their tokens and write the combined output, so there is no separate combine pass
+        const int fmode = (L->debug & I64B_DEBUG_FUSE_COMBINE) ? 1 : fuse_combine_mode();
+        combine_fused = S > 0 && fmode != 0 && (E == 0 || (fmode == 1 && K <= 2));
+        if (combine_fused) {
+            gp.fuse_combine = 1;
+            gp.keep_shared_y = (L->debug & I64B_DEBUG_KEEP_TAPS) ? 1 : 0;
+            gp.dest_row = cv.dest_row;
+            gp.n_tokens = (int32_t)n;
+            gp.top_k = E > 0 ? K : 0;
+            for (int k = 0; k < I64B_MAX_TOPK; ++k) gp.w[k] = k < K ? c.route_weight[k] : 0.0f;
+            gp.routed_scale = c.routed_scale;
+            gp.shared_scale = c.shared_scale;
+            gp.final_out = out;
+            gp.final_dtype = out_dtype;
+            gp.ld_final = H;
+            gp.tile_done = cv.plan.sync;
+        }
         const int wi = nmma_index(n_mma);
         const int64_t tiles = (mt_r + mt_s) * ((H + n_mma - 1) / n_mma);
         if (o.stage_mask & I64B_STAGE_GEMM2) {
@@ -533,7 +567,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
             if (rc) return rc;
         }
     }
-    if (!(o.stage_mask & I64B_STAGE_COMBINE)) return I64B_OK;
+    if (!(o.stage_mask & I64B_STAGE_COMBINE) || combine_fused) return I64B_OK;
 
     // 5. weighted un-permute combine with the shared / routed output scales
     I64bCombineArgs ca = {};

@@ -106,14 +106,109 @@ __device__ __forceinline__ void warp_store_block(uint32_t st_addr, const uint32_
     __syncwarp();
     const int piece = lane & 3;
     const int rr = (lane >> 3) + 4 * ((lane >> 2) & 1);   // quarter-warps read rows {k, k+4}: 16 banks apart
+    int4 d[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)         // all four reads first: one shared-memory latency per block, not four
+        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(d[i].x), "=r"(d[i].y), "=r"(d[i].z), "=r"(d[i].w)
+                     : "r"(st_addr + (i * 8 + rr) * kStagePitch + piece * 16));
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int row = i * 8 + rr;
-        int4 d;
-        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(d.x), "=r"(d.y), "=r"(d.z), "=r"(d.w) : "r"(st_addr + row * kStagePitch + piece * 16));
         if (row < rows_valid && piece * 16 < bytes_valid)
-            *reinterpret_cast<int4*>(gbase + row * pitch_bytes + piece * 16) = d;
+            *reinterpret_cast<int4*>(gbase + row * pitch_bytes + piece * 16) = d[i];
+    }
+}
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(int* p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float4 ld_cg_f4(const float* p) {      // L2-coherent load (rows written by other CTAs)
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
+// Fused combine for one [32 tokens x 16 columns] block of a shared-expert GEMM2 tile.  Lane i supplies the shared
+// expert's fp32 outputs of token row i; after the transpose through the staging area each lane owns 4 consecutive
+// columns of 4 token rows, adds the K routed rows of those tokens (loaded by the caller, a whole 32-column chunk in
+// flight before the accumulator is read) and writes the finished block output in the reference's operation order
+// (no FMA contraction):   o = w0*y0; o = o + wk*yk; o = rs*o; o = o + ss*shared     layers/token_routed_mlp.py:156-185
+constexpr int kFuseMaxK = 2;     // the fused combine covers top_k <= 2 (the named models); wider routing takes combine_kernel
+struct CombineCtx {
+    const float* y;          // routed per-assignment rows
+    int64_t ldy;
+    int top_k;
+    float w[kFuseMaxK];
+    float rs, ss;
+    int prk[4][kFuseMaxK];   // routed row of (token row i*8+rr, route k)
+};
+// issue the loads of the routed rows for one 16-column block (4 token rows x K routes per lane)
+__device__ __forceinline__ void combine_issue_loads(const CombineCtx& cx, int col, int rows_valid, int lane,
+                                                    float4 (&yk)[4][kFuseMaxK]) {
+    const int piece = lane & 3;
+    const int rr = (lane >> 3) + 4 * ((lane >> 2) & 1);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const bool rv = i * 8 + rr < rows_valid;
+#pragma unroll
+        for (int k = 0; k < kFuseMaxK; ++k)
+            yk[i][k] = (rv && k < cx.top_k) ? ld_cg_f4(cx.y + (int64_t)cx.prk[i][k] * cx.ldy + col + piece * 4)
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+__device__ __forceinline__ void warp_combine_block(uint32_t st_addr, const uint32_t (&v)[16], const CombineCtx& cx,
+                                                   const float4 (&yk)[4][kFuseMaxK], uint8_t* obase, int64_t opitch,
+                                                   bool f32out, uint8_t* ykeep, int64_t ykeep_pitch, int rows_valid,
+                                                   int lane) {
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};"
+                     :: "r"(st_addr + lane * kStagePitch + j * 16), "r"(v[4 * j]), "r"(v[4 * j + 1]), "r"(v[4 * j + 2]),
+                        "r"(v[4 * j + 3]) : "memory");
+    __syncwarp();
+    const int piece = lane & 3;
+    const int rr = (lane >> 3) + 4 * ((lane >> 2) & 1);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = i * 8 + rr;
+        float4 a;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(st_addr + row * kStagePitch + piece * 16));
+        float4 o = a;                    // dense FFN (no routed experts): the SwiGLU output itself
+        if (cx.top_k > 0) {
+            const float4 y0 = yk[i][0];
+            o = make_float4(__fmul_rn(cx.w[0], y0.x), __fmul_rn(cx.w[0], y0.y), __fmul_rn(cx.w[0], y0.z),
+                            __fmul_rn(cx.w[0], y0.w));
+            if (cx.top_k > 1) {
+                const float4 y1 = yk[i][1];
+                o.x = __fadd_rn(o.x, __fmul_rn(cx.w[1], y1.x));
+                o.y = __fadd_rn(o.y, __fmul_rn(cx.w[1], y1.y));
+                o.z = __fadd_rn(o.z, __fmul_rn(cx.w[1], y1.z));
+                o.w = __fadd_rn(o.w, __fmul_rn(cx.w[1], y1.w));
+            }
+            o = make_float4(__fmul_rn(cx.rs, o.x), __fmul_rn(cx.rs, o.y), __fmul_rn(cx.rs, o.z), __fmul_rn(cx.rs, o.w));
+            o.x = __fadd_rn(o.x, __fmul_rn(cx.ss, a.x));
+            o.y = __fadd_rn(o.y, __fmul_rn(cx.ss, a.y));
+            o.z = __fadd_rn(o.z, __fmul_rn(cx.ss, a.z));
+            o.w = __fadd_rn(o.w, __fmul_rn(cx.ss, a.w));
+        }
+        if (row < rows_valid) {
+            if (f32out) {
+                *reinterpret_cast<float4*>(obase + row * opitch + piece * 16) = o;
+            } else {
+                *reinterpret_cast<uint2*>(obase + row * opitch + piece * 8) =
+                    make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+            }
+            if (ykeep != nullptr) *reinterpret_cast<float4*>(ykeep + row * ykeep_pitch + piece * 16) = a;
+        }
     }
 }
 
@@ -291,6 +386,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         const uint32_t ws_addr = st_addr + kStageWarpBytes;
         const uint32_t lut_addr = smem_u32(slut);
         int g = 0, iter = 0;
+        [[maybe_unused]] bool routed_ready = false;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++iter) {
             TileCoord tc;
             decode_tile<kBnOut>(tile, g, prefix, sg, tc);
@@ -301,7 +397,8 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const int row_in_group = tc.m_t * kBlockM + r;
             const bool valid = row_in_group < grp.rows;
             const int64_t a_row = (int64_t)grp.row_start + row_in_group;
-            const int64_t out_row0 = (int64_t)grp.out_row_start + tc.m_t * kBlockM + q * 32;   // first row of this warp
+            int64_t out_row0 = (int64_t)grp.out_row_start + tc.m_t * kBlockM + q * 32;   // first row of this warp
+            if (p.debug_flags & 32u) out_row0 &= 127;       // bring-up: bit5 = all stores land in the first 128 rows (L2-resident)
             const int rows_valid = min(32, max(0, grp.rows - (tc.m_t * kBlockM + q * 32)));
             const int colw0 = tc.n_t * kBnOut + cbase;      // first output column of this warp
 
@@ -324,13 +421,83 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 }
             }
 
+            [[maybe_unused]] CombineCtx cx;
+            bool combine_tile = false;
+            if constexpr (!kDual) {
+                combine_tile = p.fuse_combine != 0 && w == 1 && active;
+                if (combine_tile) {
+                    cx.y = reinterpret_cast<const float*>(p.out[0]);
+                    cx.ldy = p.ld_out[0];
+                    cx.top_k = p.top_k;
+#pragma unroll
+                    for (int k = 0; k < kFuseMaxK; ++k) cx.w[k] = p.w[k];
+                    cx.rs = p.routed_scale;
+                    cx.ss = p.shared_scale;
+                    if (p.top_k > 0) {
+                        // every routed tile (all groups before the shared one) must have left its epilogue
+                        if (!routed_ready) {
+                            if (lane == 0) {
+                                const int target = prefix[ng - 1] * kEpiWarps;
+                                unsigned spins = 0;
+                                while (ld_acquire_gpu(p.tile_done) < target) {
+                                    __nanosleep(64);
+                                    if (++spins > (1u << 26)) __trap();
+                                }
+                            }
+                            __syncwarp();
+                        }
+                        const int tok = row_in_group;           // shared group rows are tokens, in order
+                        int rk[kFuseMaxK];
+#pragma unroll
+                        for (int k = 0; k < kFuseMaxK; ++k) {
+                            rk[k] = (k < p.top_k && valid) ? __ldg(p.dest_row + (int64_t)k * p.n_tokens + tok) : 0;
+                            if (!routed_ready && k < p.top_k && valid) {      // first shared tile: nobody prefetched for it
+                                const float* seg = cx.y + (int64_t)rk[k] * cx.ldy + colw0;
+#pragma unroll
+                                for (int j = 0; j < kColsW / 32; ++j) prefetch_l2(seg + j * 32);
+                            }
+                        }
+                        routed_ready = true;
+                        const int rr = (lane >> 3) + 4 * ((lane >> 2) & 1);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int k = 0; k < kFuseMaxK; ++k)
+                                cx.prk[i][k] = __shfl_sync(0xffffffffu, rk[k], i * 8 + rr);
+                        // pull the routed rows of this CTA's NEXT tile into L2 now: a whole tile of MMAs ahead of their use
+                        const int nxt = tile + (int)gridDim.x;
+                        if (nxt < total_tiles && !(p.debug_flags & 16u)) {                  // bring-up: bit4 = no prefetch-ahead
+                            int g2 = g;
+                            TileCoord tn;
+                            decode_tile<kBnOut>(nxt, g2, prefix, sg, tn);
+                            const int tok2 = tn.m_t * kBlockM + r;
+                            if (sg[tn.g].which == 1 && tok2 < sg[tn.g].rows) {
+#pragma unroll
+                                for (int k = 0; k < kFuseMaxK; ++k) {
+                                    if (k < p.top_k) {
+                                        const int row2 = __ldg(p.dest_row + (int64_t)k * p.n_tokens + tok2);
+                                        const float* seg = cx.y + (int64_t)row2 * cx.ldy + tn.n_t * kBnOut + cbase;
+#pragma unroll
+                                        for (int j = 0; j < kColsW / 32; ++j) prefetch_l2(seg + j * 32);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+
             mbar_wait(&tfull_bar[as], (iter >> 1) & 1);
             tc_fence_after();
             if (tl && threadIdx.x == 64) tl[5] = clock64() - t0;
             if ((p.debug_flags & 2u) || !active) {
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tempty_bar[as]);
+                if (lane == 0) {
+                    mbar_arrive(&tempty_bar[as]);
+                    if constexpr (!kDual)
+                        if (p.fuse_combine && w == 0) red_release_gpu_add(p.tile_done, 1);   // keep the count uniform
+                }
                 continue;
             }
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * kNMma + cbase;
@@ -423,10 +590,16 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll 1
                 for (int c = 0; c < kColsW; c += 32) {
                     if (colw0 + c >= n_out) break;
+                    const bool second = colw0 + c + 16 < n_out;
+                    float4 yk0[4][kFuseMaxK], yk1[4][kFuseMaxK];       // routed rows of the chunk's two 16-column blocks
+                    if (combine_tile && p.top_k > 0) {
+                        const int rvl = (p.debug_flags & 4u) ? 0 : rows_valid;      // bring-up: bit2 = skip the routed-row loads
+                        combine_issue_loads(cx, colw0 + c, rvl, lane, yk0);
+                        combine_issue_loads(cx, colw0 + c + 16, second ? rvl : 0, lane, yk1);
+                    }
                     uint32_t ar[32];
                     tmem_ld_32x32(taddr + c, ar);
                     tmem_ld_wait();
-                    const bool second = colw0 + c + 16 < n_out;
                     if constexpr (kInt8) {
                         if (p.raw_out != nullptr) {
                             uint8_t* rbase = reinterpret_cast<uint8_t*>(p.raw_out) + (out_row0 * p.ld_raw + colw0 + c) * 4;
@@ -464,7 +637,24 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                             ar[4 * j4 + 3] = __float_as_uint(__fmul_rn(__uint_as_float(ar[4 * j4 + 3]), __fmul_rn(rs, s4.w)));
                         }
                     }
-                    if (obase != nullptr) {
+                    if (combine_tile) {
+                        const bool fo = p.final_dtype == I64B_F32;
+                        const int fsz = fo ? 4 : 2;
+                        const int64_t tok0 = (int64_t)tc.m_t * kBlockM + q * 32;
+                        uint8_t* fbase = reinterpret_cast<uint8_t*>(p.final_out) + (tok0 * p.ld_final + colw0 + c) * fsz;
+                        uint8_t* ykeep = (p.keep_shared_y && obase != nullptr) ? obase + c * 4 : nullptr;
+                        uint32_t blk[16];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) blk[j] = ar[j];
+                        warp_combine_block(st_addr, blk, cx, yk0, fbase, p.ld_final * fsz, fo, ykeep, pitch, rows_valid,
+                                           lane);
+                        if (second) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) blk[j] = ar[16 + j];
+                            warp_combine_block(st_addr, blk, cx, yk1, fbase + 16 * fsz, p.ld_final * fsz, fo,
+                                               ykeep ? ykeep + 64 : nullptr, pitch, rows_valid, lane);
+                        }
+                    } else if (obase != nullptr) {
                         uint32_t blk[16];
                         if (f32out) {
 #pragma unroll
@@ -488,6 +678,13 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            if constexpr (!kDual) {
+                if (p.fuse_combine && w == 0) {     // publish this warp's routed rows to the shared-expert tiles
+                    if (!(p.debug_flags & 8u)) __threadfence();                     // bring-up: bit3 = no fence
+                    __syncwarp();
+                    if (lane == 0) red_release_gpu_add(p.tile_done, 1);
+                }
+            }
             if (tl && threadIdx.x == 64) tl[6] = clock64() - t0;
         }
     }

@@ -25,6 +25,18 @@ struct I64bGemmParams {
     int32_t* amax_part[2];     // Q14 epilogue: per (row, n_tile) max|q14|
     int32_t amax_ld[2];
     const int16_t* silu_lut;   // device copy of the Q7 SiLU table (2049 entries)
+    // fused combine (GEMM2 only): the shared-expert tiles (last group, token order) pull the routed rows of their
+    // tokens and write the finished block output  rs*(sum_k w_k*y_k) + ss*y_shared  (token_routed_mlp.py:156-185)
+    int32_t fuse_combine;
+    int32_t keep_shared_y;     // debug taps: also store the shared expert's own rows to out[1]
+    const int32_t* dest_row;   // [K, N] row of assignment (k, t) in out[0]
+    int32_t n_tokens, top_k;
+    float w[I64B_MAX_TOPK];    // fused combine supports top_k <= 2
+    float routed_scale, shared_scale;
+    void* final_out;           // [N, ld_final] bf16 or fp32
+    int32_t final_dtype;
+    int64_t ld_final;
+    int32_t* tile_done;        // counter of drained routed (tile, epilogue-warp) pairs, zero at launch
     // bring-up instrumentation (env I64B_DEBUG_FLAGS / I64B_DEBUG_TIMELINE; never set in production)
     uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores
     long long* debug_timeline; // [grid, 8] clock64 offsets per CTA

@@ -15,6 +15,7 @@ struct I64bPlanWs {
     int32_t* group_start;  // [E + 1]  merged expert-major segment starts (last = N*K)
     I64bGroup* groups1;    // [E + 1]  GEMM1 problems (gate|up), shared expert last
     I64bGroup* groups2;    // [E + 1]  GEMM2 problems (down)
+    int32_t* sync;         // [64]     device-side counters, zeroed by the plan ([0]: routed GEMM2 tiles drained)
     size_t bytes;
 };
 I64bPlanWs i64b_plan_ws_carve(void* base, int64_t n, int top_k, int num_experts);

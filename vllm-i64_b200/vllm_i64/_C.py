@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libi64b.so")
 BF16, F32, F16 = 0, 1, 2
 STAGE_PLAN, STAGE_DISPATCH, STAGE_GEMM1, STAGE_REQUANT, STAGE_GEMM2, STAGE_COMBINE, STAGE_ALL = 1, 2, 4, 8, 16, 32, 0xFF
 MODE_BF16, MODE_W8A8 = 0, 1
+DEBUG_KEEP_TAPS, DEBUG_FUSE_COMBINE = 1, 2
 (TAP_ROUTES, TAP_DEST_ROW, TAP_SCATTER_IDX, TAP_COUNTS, TAP_OFFSETS, TAP_XS, TAP_XS_SCALE, TAP_INTER_R, TAP_INTER_S,
  TAP_INTER_SCALE_R, TAP_INTER_SCALE_S, TAP_Q14_R, TAP_Q14_S, TAP_Y, TAP_GROUP_START) = range(15)
 
@@ -69,6 +70,7 @@ _SIGNATURES = {
     "i64b_copy_device": (_I, [_P, _P, _Z, _P]),
     "i64b_moe_forward_host": (_I, [_P, _P, _P, _P, _I, _L, _P, _P, _P, _P, _Z, _P]),
     "i64b_moe_tap": (_P, [_P, _I]),
+    "i64b_moe_set_debug": (_I, [_P, _I]),
     "i64b_int8_gemm": (_I, [_P, _P, _P, _P, _P, _P, _L, _L, _L, _P]),
     "i64b_bf16_gemm": (_I, [_P, _P, _P, _P, _I, _L, _L, _L, _P]),
 }

@@ -155,6 +155,10 @@ class I64Block:
                 "ids": torch.empty(n, dtype=torch.int64, device=self.device),
                 "out": torch.empty(n, self.cfg.hidden_size, dtype=out_dtype, device=self.device)}
 
+    def set_debug(self, flags: int) -> None:
+        """``_C.DEBUG_KEEP_TAPS``: keep the shared expert's own rows in TAP_Y (the fused combine does not need them)."""
+        _C.check(_C.lib().i64b_moe_set_debug(self._h, int(flags)))
+
     def tap(self, what: int, shape, dtype: torch.dtype) -> torch.Tensor:
         with torch.cuda.device(self.device):
             return _C.tap_tensor(self._h, what, shape, dtype, self.device)
