@@ -119,8 +119,10 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
     cv.inter_s = take((size_t)nn * c.shared_inter * L->elt);
     cv.inter_scale_r = reinterpret_cast<float*>(take(sizeof(float) * R));
     cv.inter_scale_s = reinterpret_cast<float*>(take(sizeof(float) * nn));
-    cv.amax_ld_r = (c.expert_inter + 31) / 32;      // enough for the narrowest GEMM1 tile (BN = 32)
-    cv.amax_ld_s = (c.shared_inter + 31) / 32;
+    // one |max| partial per (GEMM1 tile, epilogue column half): at most ceil(I/32) for BN = 32 and 64, and
+    // 2*ceil(I/128) for BN = 128, which exceeds ceil(I/32) only for I <= 32
+    cv.amax_ld_r = (c.expert_inter + 31) / 32 + 1;
+    cv.amax_ld_s = (c.shared_inter + 31) / 32 + 1;
     cv.q14_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * c.expert_inter : 0));
     cv.q14_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * c.shared_inter : 0));
     cv.amax_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * cv.amax_ld_r : 0));
@@ -191,6 +193,14 @@ static int pick_nmma(int64_t m_tiles_r, int n_r, int64_t m_tiles_s, int n_s, boo
     return 64;
 }
 static int nmma_index(int n_mma) { return n_mma == 64 ? 0 : (n_mma == 128 ? 1 : 2); }
+// CTA pairs (cta_group::2) for prefill-sized problems: the 256-wide tile was picked and the groups are tall enough
+// that padding every group to 256 rows wastes little.  I64B_CTA2=0 disables, =1 forces (when n_mma == 256).
+static bool use_cta_pairs(int n_mma, int64_t rows_total, int groups) {
+    static const int mode = env_int("I64B_CTA2", -1);
+    if (n_mma != 256 || mode == 0) return false;
+    if (mode == 1) return true;
+    return rows_total >= (int64_t)groups * 1024;
+}
 
 extern "C" {
 
@@ -484,6 +494,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     bool combine_fused = false;
     const int64_t mt_r = E > 0 ? R / 128 + E : 0;     // upper bound on routed m-tiles
     const int64_t mt_s = S > 0 ? (n + 127) / 128 : 0;
+    const int64_t pt_r = E > 0 ? R / 256 + E : 0;     // the same in 256-row units (CTA pairs)
+    const int64_t pt_s = S > 0 ? (n + 255) / 256 : 0;
 
     // 3. GEMM1: gate|up projections + fused SwiGLU epilogue
     {
@@ -506,9 +518,12 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.amax_ld[1] = cv.amax_ld_s;
         gp.silu_lut = L->silu_lut;
         const int wi = nmma_index(n_mma);
-        const int64_t tiles = mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
+        const bool pairs = use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0));
+        const int64_t tiles = pairs ? pt_r * ((I + bn - 1) / bn) + pt_s * ((S + bn - 1) / bn)
+                                    : mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
         if (o.stage_mask & I64B_STAGE_GEMM1) {
-            rc = i64b_launch_gemm(q, true, n_mma, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
+            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp,
+                                  tiles, s);
             if (rc) return rc;
         }
         if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
@@ -559,11 +574,12 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
             gp.ld_final = H;
             gp.tile_done = cv.plan.sync;
         }
-        const int wi = nmma_index(n_mma);
-        const int64_t tiles = (mt_r + mt_s) * ((H + n_mma - 1) / n_mma);
+        const bool pairs = use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0));
+        const int wi = pairs ? 1 : nmma_index(n_mma);       // pairs: each CTA stages a 128-row half of the B tile
+        const int64_t tiles = (pairs ? pt_r + pt_s : mt_r + mt_s) * ((H + n_mma - 1) / n_mma);
         if (o.stage_mask & I64B_STAGE_GEMM2) {
-            rc = i64b_launch_gemm(q, false, n_mma, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi], L->tm_w2s[wi], gp, tiles,
-                                  s);
+            rc = i64b_launch_gemm(q, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi],
+                                  L->tm_w2s[wi], gp, tiles, s);
             if (rc) return rc;
         }
     }
@@ -714,7 +730,7 @@ int i64b_int8_gemm(const int8_t* x_q, const float* x_scale, const int8_t* w_q, c
     gp.raw_out = acc_out;
     gp.ld_raw = n;
     const int64_t tiles = ((m + 127) / 128) * ((n + n_mma - 1) / n_mma);
-    return i64b_launch_gemm(true, false, n_mma, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
+    return i64b_launch_gemm(true, false, n_mma, 1, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
 }
 
 int i64b_bf16_gemm(const void* a, const void* b, const float* col_scale, void* out, int out_dtype, int64_t m,
@@ -741,7 +757,7 @@ int i64b_bf16_gemm(const void* a, const void* b, const float* col_scale, void* o
     gp.epi = col_scale ? I64B_EPI_DEQUANT : I64B_EPI_F32;
     gp.col_scale[0] = gp.col_scale[1] = col_scale;
     const int64_t tiles = ((m + 127) / 128) * ((n + n_mma - 1) / n_mma);
-    return i64b_launch_gemm(false, false, n_mma, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
+    return i64b_launch_gemm(false, false, n_mma, 1, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -33,8 +33,8 @@ constexpr int kStageWarpBytes = 32 * kStagePitch;  // per-warp output staging bl
 constexpr int kScaleWarpBytes = 512;               // per-warp column scales of the current tile (<= 128 floats)
 constexpr int kEpiWarpBytes = kStageWarpBytes + kScaleWarpBytes;
 
-template <int kNMma> struct StageCfg {
-    static constexpr int kStageB = kNMma * kRowBytes;
+template <int kNMma, int kCtas> struct StageCfg {
+    static constexpr int kStageB = kNMma / kCtas * kRowBytes;     // a CTA pair splits the B tile
     static constexpr int kStagesRaw = 196608 / (kStageA + kStageB);
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kSmem = 1024 + kStages * (kStageA + kStageB) + kMiscBytes + kEpiWarps * kEpiWarpBytes;
@@ -49,26 +49,27 @@ __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem_ptr)
     return d;
 }
 
-template <bool kInt8, int kNMma>
+template <bool kInt8, int kNMma, int kCtas>
 __device__ __forceinline__ constexpr uint32_t make_idesc() {
     // c_format [4,6): 1=F32, 2=S32; a/b format [7,10)/[10,13): BF16=1 / S8=1; K-major both;
     // n_dim [17,23) = N>>3; m_dim [24,29) = M>>4
     return (uint32_t)((kInt8 ? 2u : 1u) << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kNMma >> 3) << 17) |
-           ((uint32_t)(kBlockM >> 4) << 24);
+           ((uint32_t)((kBlockM * kCtas) >> 4) << 24);
 }
 
 struct TileCoord {
     int g, m_t, n_t;
 };
 
-template <int kBnOut>
+// `tile` counts (m-tile x kCtas, n-tile) units; CTA `rank` of a pair takes the rank-th 128-row tile of the unit
+template <int kBnOut, int kCtas>
 __device__ __forceinline__ void decode_tile(int tile, int& g, const int* prefix, const I64bGroup* sg,
-                                            TileCoord& tc) {
+                                            TileCoord& tc, int rank) {
     while (tile >= prefix[g + 1]) ++g;
     const int nt = (sg[g].n_out + kBnOut - 1) / kBnOut;
     const int local = tile - prefix[g];
     tc.g = g;
-    tc.m_t = local / nt;
+    tc.m_t = (local / nt) * kCtas + rank;
     tc.n_t = local % nt;
 }
 
@@ -212,12 +213,14 @@ __device__ __forceinline__ void warp_combine_block(uint32_t st_addr, const uint3
     }
 }
 
-template <bool kInt8, bool kDual, int kNMma>
+template <bool kInt8, bool kDual, int kNMma, int kCtas>
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ I64bGemmParams p) {
-    using Cfg = StageCfg<kNMma>;
+    using Cfg = StageCfg<kNMma, kCtas>;
+    static_assert(kCtas == 1 || kCtas == 2, "single CTA or a CTA pair");
+    static_assert(kCtas == 1 || kNMma == 256, "the pair kernel is built for the widest tile only");
     constexpr int kStages = Cfg::kStages;
     constexpr int kStageB = Cfg::kStageB;
     constexpr int kBnOut = kDual ? kNMma / 2 : kNMma;
@@ -245,6 +248,9 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const int rank = kCtas == 2 ? (int)cluster_ctarank() : 0;     // 0 = leader of the pair (issues the MMAs)
+    const int unit0 = (int)blockIdx.x / kCtas;                    // first tile unit of this CTA (pair)
+    const int unit_step = (int)gridDim.x / kCtas;
     pdl_launch_dependents();      // let the next kernel's CTAs start their prologue as SMs free up
     const long long t0 = clock64();
     long long* tl = p.debug_timeline ? p.debug_timeline + (size_t)blockIdx.x * 8 : nullptr;
@@ -265,12 +271,14 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull_bar[i], 1);
-            mbar_init(&tempty_bar[i], kEpiWarps);
+            mbar_init(&tempty_bar[i], kEpiWarps * kCtas);     // the leader's copy collects both CTAs' epilogue warps
         }
         fence_barrier_init();
     } else if (warp == 1) {
-        tmem_alloc<kTmemCols>(tmem_ptr);
+        if constexpr (kCtas == 2) tmem_alloc_cta2<kTmemCols>(tmem_ptr);
+        else tmem_alloc<kTmemCols>(tmem_ptr);
     }
+    if constexpr (kCtas == 2) cluster_sync_all();     // the peer's barriers exist before anything signals them
 
     // everything above overlaps the previous kernel's tail under PDL; below reads its outputs
     pdl_wait_prior();
@@ -285,7 +293,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         int acc = 0;
         for (int g = 0; g < ng; ++g) {
             prefix[g] = acc;
-            const int mt = (sg[g].rows + kBlockM - 1) / kBlockM;
+            const int mt = (sg[g].rows + kBlockM * kCtas - 1) / (kBlockM * kCtas);
             const int nt = (sg[g].n_out + kBnOut - 1) / kBnOut;
             acc += mt * nt;
         }
@@ -303,9 +311,9 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         if (lane == 0) {
             int stage = 0, g = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            for (int tile = unit0; tile < total_tiles; tile += unit_step) {
                 TileCoord tc;
-                decode_tile<kBnOut>(tile, g, prefix, sg, tc);
+                decode_tile<kBnOut, kCtas>(tile, g, prefix, sg, tc, rank);
                 const I64bGroup grp = sg[tc.g];
                 const CUtensorMap* ta = grp.which ? &tmA1 : &tmA0;
                 const CUtensorMap* tb = grp.which ? &tmB1 : &tmB0;
@@ -314,7 +322,19 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 const int b_row = grp.w_row_base + tc.n_t * kBnOut;
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    if (tl && kb == 0 && tile == (int)blockIdx.x) tl[2] = clock64() - t0;
+                    if (tl && kb == 0 && tile == unit0) tl[2] = clock64() - t0;
+                    if constexpr (kCtas == 2) {
+                        // both CTAs load their own A rows and their half of the B tile (dual: leader = gate rows,
+                        // peer = up rows); all bytes are credited to the leader's barrier
+                        if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (kStageA + kStageB));
+                        tma_load_2d_cta2(sA + stage * kStageA, ta, &full_bar[stage], kb * kBlockK, a_row,
+                                         I64B_L2_EVICT_NORMAL);
+                        const int bh = kDual ? b_row + rank * grp.n_out : b_row + rank * (kNMma / 2);
+                        tma_load_2d_cta2(sB + stage * kStageB, tb, &full_bar[stage], kb * kBlockK, bh,
+                                         I64B_L2_EVICT_NORMAL);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     mbar_arrive_expect_tx(&full_bar[stage], kStageA + kStageB);
                     tma_load_2d(sA + stage * kStageA, ta, &full_bar[stage], kb * kBlockK, a_row,
                                 I64B_L2_EVICT_NORMAL);
@@ -333,13 +353,13 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (one thread)
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc<kInt8, kNMma>();
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = make_idesc<kInt8, kNMma, kCtas>();
             int stage = 0, g = 0, iter = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++iter) {
+            for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
                 TileCoord tc;
-                decode_tile<kBnOut>(tile, g, prefix, sg, tc);
+                decode_tile<kBnOut, kCtas>(tile, g, prefix, sg, tc, rank);
                 const int nkb = (p.k[sg[tc.g].which] + kBlockK - 1) / kBlockK;
                 const int as = iter & 1;
                 mbar_wait(&tempty_bar[as], ((iter >> 1) & 1) ^ 1);
@@ -348,8 +368,8 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    if (tl && kb == 0 && tile == (int)blockIdx.x) tl[3] = clock64() - t0;
-                    if (p.debug_flags & 1u) {      // pure TMA streaming: release the slot without touching the tensor core
+                    if (tl && kb == 0 && tile == unit0) tl[3] = clock64() - t0;
+                    if ((p.debug_flags & 1u) && kCtas == 1) {      // pure TMA streaming: release the slot without touching the tensor core
                         mbar_arrive(&empty_bar[stage]);
                         if (kb == nkb - 1) { mbar_arrive(&tfull_bar[as]); if (tl) tl[4] = clock64() - t0; }
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -359,13 +379,24 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const uint64_t b_desc = make_sw128_kmajor_desc(sB + stage * kStageB);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {   // 4 x 32-byte K slices inside the swizzle span
-                        if constexpr (kInt8)
+                        if constexpr (kCtas == 2) {
+                            if constexpr (kInt8)
+                                umma_i8_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                            else
+                                umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        } else if constexpr (kInt8) {
                             umma_i8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
-                        else
+                        } else {
                             umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        }
                     }
-                    umma_commit(&empty_bar[stage]);             // smem slot reusable once these MMAs retire
-                    if (kb == nkb - 1) { umma_commit(&tfull_bar[as]); if (tl) tl[4] = clock64() - t0; }   // accumulator complete
+                    if constexpr (kCtas == 2) {     // the commits arrive on both CTAs' barriers
+                        umma_commit_cta2(&empty_bar[stage]);
+                        if (kb == nkb - 1) umma_commit_cta2(&tfull_bar[as]);
+                    } else {
+                        umma_commit(&empty_bar[stage]);             // smem slot reusable once these MMAs retire
+                        if (kb == nkb - 1) { umma_commit(&tfull_bar[as]); if (tl) tl[4] = clock64() - t0; }   // accumulator complete
+                    }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -387,9 +418,9 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         const uint32_t lut_addr = smem_u32(slut);
         int g = 0, iter = 0;
         [[maybe_unused]] bool routed_ready = false;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++iter) {
+        for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
             TileCoord tc;
-            decode_tile<kBnOut>(tile, g, prefix, sg, tc);
+            decode_tile<kBnOut, kCtas>(tile, g, prefix, sg, tc, rank);
             const I64bGroup grp = sg[tc.g];
             const int w = grp.which;
             const int as = iter & 1;
@@ -437,7 +468,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         // every routed tile (all groups before the shared one) must have left its epilogue
                         if (!routed_ready) {
                             if (lane == 0) {
-                                const int target = prefix[ng - 1] * kEpiWarps;
+                                const int target = prefix[ng - 1] * kEpiWarps * kCtas;
                                 unsigned spins = 0;
                                 while (ld_acquire_gpu(p.tile_done) < target) {
                                     __nanosleep(64);
@@ -465,11 +496,11 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                             for (int k = 0; k < kFuseMaxK; ++k)
                                 cx.prk[i][k] = __shfl_sync(0xffffffffu, rk[k], i * 8 + rr);
                         // pull the routed rows of this CTA's NEXT tile into L2 now: a whole tile of MMAs ahead of their use
-                        const int nxt = tile + (int)gridDim.x;
+                        const int nxt = tile + unit_step;
                         if (nxt < total_tiles && !(p.debug_flags & 16u)) {                  // bring-up: bit4 = no prefetch-ahead
                             int g2 = g;
                             TileCoord tn;
-                            decode_tile<kBnOut>(nxt, g2, prefix, sg, tn);
+                            decode_tile<kBnOut, kCtas>(nxt, g2, prefix, sg, tn, rank);
                             const int tok2 = tn.m_t * kBlockM + r;
                             if (sg[tn.g].which == 1 && tok2 < sg[tn.g].rows) {
 #pragma unroll
@@ -494,7 +525,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    mbar_arrive(&tempty_bar[as]);
+                    if constexpr (kCtas == 2) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
                     if constexpr (!kDual)
                         if (p.fuse_combine && w == 0) red_release_gpu_add(p.tile_done, 1);   // keep the count uniform
                 }
@@ -677,7 +708,9 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             // accumulator stage drained: hand it back to the MMA thread
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            if (lane == 0) {
+                if constexpr (kCtas == 2) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
+            }
             if constexpr (!kDual) {
                 if (p.fuse_combine && w == 0) {     // publish this warp's routed rows to the shared-expert tiles
                     if (!(p.debug_flags & 8u)) __threadfence();                     // bring-up: bit3 = no fence
@@ -691,10 +724,11 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     if (tl && threadIdx.x == 0) tl[7] = clock64() - t0;
 
     tc_fence_before();
-    __syncthreads();
+    if constexpr (kCtas == 2) cluster_sync_all(); else __syncthreads();    // nobody leaves while the peer still signals it
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<kTmemCols>(tmem_base);
+        if constexpr (kCtas == 2) tmem_dealloc_cta2<kTmemCols>(tmem_base);
+        else tmem_dealloc<kTmemCols>(tmem_base);
     }
 }
 
@@ -715,11 +749,11 @@ PFN_tmapEncodeTiled get_encode_fn() {
     return fn;
 }
 
-template <bool kInt8, bool kDual, int kNMma>
+template <bool kInt8, bool kDual, int kNMma, int kCtas>
 int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b0, const CUtensorMap& b1,
                 const I64bGemmParams& p, int grid, cudaStream_t stream) {
-    auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma>;
-    constexpr int smem = StageCfg<kNMma>::kSmem;
+    auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma, kCtas>;
+    constexpr int smem = StageCfg<kNMma, kCtas>::kSmem;
     static bool configured = false;
     if (!configured) {
         I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -727,6 +761,13 @@ int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap&
     }
     static const int dbg_flags = getenv("I64B_DEBUG_FLAGS") ? atoi(getenv("I64B_DEBUG_FLAGS")) : 0;
     static const bool dbg_tl = getenv("I64B_DEBUG_TIMELINE") != nullptr;
+    if (kCtas == 2) {       // CTA pairs: cluster launch; the bring-up flags below are single-CTA only
+        I64bGemmParams q = p;
+        q.debug_flags = (uint32_t)dbg_flags & ~1u;
+        I64B_CUDA(i64b_launch_cluster(kern, dim3(grid), dim3(kThreads), smem, stream, 2, a0, a1, b0, b1, q));
+        i64b_count_launch();
+        return I64B_OK;
+    }
     if (dbg_flags == 0 && !dbg_tl) {
         I64B_CUDA(i64b_launch(kern, dim3(grid), dim3(kThreads), smem, stream, a0, a1, b0, b1, p));
         i64b_count_launch();
@@ -793,18 +834,27 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
     return I64B_OK;
 }
 
-int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream) {
     if (max_tiles <= 0) return I64B_OK;
+    I64B_CHECK(ctas == 1 || (ctas == 2 && n_mma == 256), I64B_ERR_ARG, "CTA pairs need the 256-wide tile");
     I64B_CHECK(p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
                p.num_groups);
     I64B_CHECK(p.k[0] > 0 && p.k[1] > 0, I64B_ERR_ARG, "K must be positive");
     const int sms = i64b_num_sms();
+    if (ctas == 2) {        // max_tiles counts pair units here
+        const int pairs = sms / 2;
+        const int grid2 = 2 * (int)(max_tiles < pairs ? max_tiles : pairs);
+        if (is_int8 && dual) return launch_inst<true, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+        if (is_int8) return launch_inst<true, false, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+        if (dual) return launch_inst<false, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+        return launch_inst<false, false, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+    }
     const int grid = (int)(max_tiles < sms ? max_tiles : sms);
 #define I64B_DISPATCH(I8, DUAL, N)                                                              \
     if (is_int8 == I8 && dual == DUAL && n_mma == N)                                            \
-        return launch_inst<I8, DUAL, N>(tmA0, tmA1, tmB0, tmB1, p, grid, stream);
+        return launch_inst<I8, DUAL, N, 1>(tmA0, tmA1, tmB0, tmB1, p, grid, stream);
     I64B_DISPATCH(false, false, 64) I64B_DISPATCH(false, false, 128) I64B_DISPATCH(false, false, 256)
     I64B_DISPATCH(false, true, 64) I64B_DISPATCH(false, true, 128) I64B_DISPATCH(false, true, 256)
     I64B_DISPATCH(true, false, 64) I64B_DISPATCH(true, false, 128) I64B_DISPATCH(true, false, 256)

@@ -49,7 +49,9 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
 
 // Launch one grouped GEMM.  n_mma in {64,128,256}; dual = gate|up pair + fused SwiGLU epilogue.
 // max_tiles is an upper bound on the number of (group, m, n) tiles, used only to size the grid.
-int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+// ctas = 2 runs CTA pairs (cta_group::2, M = 256 per MMA; n_mma must be 256): the B tensor maps must then have
+// 128-row boxes (each CTA stages half of the B tile) and max_tiles counts (256-row, n) units.
+int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream);
 
