@@ -88,7 +88,8 @@ def stage_bytes(wl):
     rows = R + N * has_s
     b = {}
     b["plan"] = N * 8 + R * 4
-    b["dispatch"] = N * H * 2 + rows * (H * a + (4 if a == 1 else 0)) + R * 4 * 3
+    drows = rows if a == 1 else R          # bf16: the shared expert reads x in place (no token-order copy)
+    b["dispatch"] = (N * H * 2 + drows * (H * a + (4 if a == 1 else 0)) + R * 4 * 3) if drows else 0
     w13 = (E * 2 * I + 2 * S) * H * a
     inter_w = (R * I + N * S) * (4 if a == 1 else 2)   # W8A8: Q14 int32 out; bf16: bf16 out
     b["gemm1"] = w13 + rows * H * a + inter_w

@@ -213,7 +213,7 @@ enum {
     I64B_TAP_SCATTER_IDX = 2, /* int32 [K,N] per-route row */
     I64B_TAP_COUNTS = 3,      /* int32 [K,E] */
     I64B_TAP_OFFSETS = 4,     /* int32 [K,E] */
-    I64B_TAP_XS = 5,          /* dispatched activations [N*K + N, H] (bf16 or int8) */
+    I64B_TAP_XS = 5,          /* dispatched activations [N*K (+ N in W8A8: quantised token-order copy), H] (bf16 or int8) */
     I64B_TAP_XS_SCALE = 6,    /* fp32 [N*K + N] (W8A8) */
     I64B_TAP_INTER_R = 7,     /* routed intermediate [N*K, I_e] (bf16 or int8) */
     I64B_TAP_INTER_S = 8,     /* shared intermediate [N, S] */

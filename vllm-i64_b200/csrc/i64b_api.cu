@@ -466,6 +466,16 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     pa.expert_inter = I;
     pa.shared_inter = S;
     pa.hidden = H;
+    // bf16: the shared expert (and a dense FFN) multiplies the caller's x in place; W8A8 needs the quantised copy
+    const bool shared_from_x = !q && S > 0;
+    pa.shared_from_x = shared_from_x ? 1 : 0;
+    pa.ticket = L->sync + 3 * I64B_SYNC_STRIDE;     // free slot of the layer's persistent counter area
+    if (shared_from_x && (L->cached_x != x || L->cached_x_n != n)) {
+        int rcx = i64b_encode_tmap(&L->tm_x, x, false, n, H, (int64_t)H * 2, 128);
+        if (rcx) return rcx;
+        L->cached_x = x;
+        L->cached_x_n = n;
+    }
     int rc = I64B_OK;
     if (o.stage_mask & I64B_STAGE_PLAN) {
         rc = i64b_run_plan(pa, cv.plan, s);
@@ -480,7 +490,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.top_k = K;
     da.num_experts = E;
     da.quantize = q ? 1 : 0;
-    da.shared_copy = S > 0 ? 1 : 0;
+    da.shared_copy = (S > 0 && !shared_from_x) ? 1 : 0;
     da.xs = cv.xs;
     da.xs_scale = cv.xs_scale;
     da.routes_out = cv.routes;
@@ -522,21 +532,16 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         const int64_t tiles = pairs ? pt_r * ((I + bn - 1) / bn) + pt_s * ((S + bn - 1) / bn)
                                     : mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
         if (o.stage_mask & I64B_STAGE_GEMM1) {
-            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp,
-                                  tiles, s);
+            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, shared_from_x ? L->tm_x : L->tm_xs,
+                                  L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
             if (rc) return rc;
         }
         if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
-            if (E > 0) {
-                rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, ((I + bn - 1) / bn) * nh,
-                                          reinterpret_cast<int8_t*>(cv.inter_r), cv.inter_scale_r, nullptr, R, I, s);
-                if (rc) return rc;
-            }
-            if (S > 0) {
-                rc = i64b_run_requant_q14(cv.q14_s, cv.amax_s, cv.amax_ld_s, ((S + bn - 1) / bn) * nh,
-                                          reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, nullptr, n, S, s);
-                if (rc) return rc;
-            }
+            rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, ((I + bn - 1) / bn) * nh,
+                                      reinterpret_cast<int8_t*>(cv.inter_r), cv.inter_scale_r, E > 0 ? R : 0, I,
+                                      cv.q14_s, cv.amax_s, cv.amax_ld_s, ((S + bn - 1) / bn) * nh,
+                                      reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, S > 0 ? n : 0, S, s);
+            if (rc) return rc;
         }
     }
 

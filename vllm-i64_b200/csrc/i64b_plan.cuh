@@ -29,6 +29,9 @@ struct I64bPlanArgs {
     int vocab, top_k, num_experts;
     // geometry for the group tables (0 when only the plan is wanted)
     int expert_inter, shared_inter, hidden;
+    int* ticket;                 // optional persistent zero-initialised counter: the last rank CTA finalises the plan
+                                 // in the same launch (self-resetting); nullptr -> separate one-CTA finalise launch
+    int shared_from_x;           // 1: the shared expert's GEMM1 reads the caller's x (token order) — no dispatched copy
 };
 
 // route + per-tile stable ranks + finalisation (counts, offsets, group tables). 1-2 launches.
@@ -52,8 +55,11 @@ int i64b_run_dispatch(const I64bDispatchArgs& a, const I64bPlanWs& ws, cudaStrea
 
 // q14 int32 [rows, cols] (+ per-(row, tile) |max| partials) -> int8 rows + fp32 scale (bit-exact re-quantisation
 // of silu_multiply_integer's fp32 output, core/quantization.py:103-116)
+// (two row sets per launch: routed assignments and the shared expert's rows; either may be empty)
 int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_ld, int n_tiles, int8_t* out,
-                         float* scale, const int32_t* rows_dev, int64_t max_rows, int cols, cudaStream_t stream);
+                         float* scale, int64_t rows, int cols, const int32_t* q14_b, const int32_t* amax_part_b,
+                         int amax_ld_b, int n_tiles_b, int8_t* out_b, float* scale_b, int64_t rows_b, int cols_b,
+                         cudaStream_t stream);
 
 struct I64bCombineArgs {
     const float* y;             // [N*K + N, H] fp32 per-assignment outputs (shared rows last)
