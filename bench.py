@@ -45,6 +45,18 @@ WORKLOADS = {
                           pw=1.0, rs=1.0, ss=1.0, L=4, N=16384, mode="bf16"),
 }
 METRIC, UNIT = "moe_ffn_tokens_per_s", "tokens/s"
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract, on the real stdout."""
+    text = json.dumps(line) + "\n"
+    if _JSON_FD is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, text.encode())
 
 
 def peaks():
@@ -305,29 +317,37 @@ def run_ep(wl, device, rank, world, args):
     x = torch.randn(n, H, device=device, generator=torch.Generator(device=device).manual_seed(100 + rank)).to(torch.bfloat16)
     ids = torch.randint(0, V, (n,), device=device, generator=torch.Generator(device=device).manual_seed(200 + rank))
 
-    def step():
-        for b in blocks:
-            b.forward(x, ids, torch.bfloat16)
+    outs = [torch.empty(n, H, dtype=torch.bfloat16, device=device) for _ in range(2)]
 
-    steps, warm = max(3, min(args.steps, 20)), 3
-    for _ in range(warm):
-        step()
-    torch.cuda.synchronize()
-    dist.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        step()
-    e1.record()
-    e1.synchronize()
-    dist.barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t[0]) / steps
+    def timed(exchange, steps, warm):
+        def step():
+            for i, b in enumerate(blocks):
+                b.forward(x, ids, torch.bfloat16, exchange=exchange, out=outs[i & 1])
+        for _ in range(warm):
+            step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        e1.synchronize()
+        dist.barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]) / steps
+
+    steps = max(3, min(args.steps, 20))
+    ms = timed("peer", steps, 3)                 # product path: NVLink peer-memory exchange fused into the kernels
+    ms_nccl = timed("nccl", max(3, steps // 4), 2)   # reference-style all_to_all_single exchange (baseline)
     sent = n * K * (world - 1) / world * H * 2
     return {"workload": "tr-hash-moe-500m bf16 expert-parallel", "tokens_per_step_total": n * world,
             "layers_per_step": L, "ms_per_step": ms, "value": n * world * L / (ms * 1e-3), "unit": UNIT,
-            "scaling": "strong", "a2a_bytes_out_per_rank_per_layer": int(sent), "ep_size": world}
+            "scaling": "strong", "a2a_bytes_out_per_rank_per_layer": int(sent), "ep_size": world,
+            "exchange": "NVLink peer memory (dispatch kernel writes into the owners' buffers; GEMM2 epilogue writes "
+                        "outputs home); NCCL only all-gathers the token ids",
+            "nccl_all_to_all_baseline": {"ms_per_step": ms_nccl, "value": n * world * L / (ms_nccl * 1e-3)}}
 
 
 # ------------------------------------------------------------------------------------------------- main
@@ -364,7 +384,7 @@ def main():
                 "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["threads"], "kind": "port",
                                  "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (use --impl reference for the CPU arm)"
@@ -373,6 +393,14 @@ def main():
     barrier = None
     if world > 1:
         import torch.distributed as dist
+        # NCCL prints its version banner to stdout when NCCL_DEBUG is set by the environment: keep stdout to the ONE
+        # JSON line of the contract
+        # (the banner is written to file descriptor 1 directly, so fd 1 is pointed at stderr for the whole run and the
+        # JSON line goes to the saved descriptor)
+        global _JSON_FD
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=device)
         barrier = lambda: dist.barrier()            # noqa: E731
     from vllm_i64 import _C
@@ -498,7 +526,7 @@ def main():
                         "h2d_bytes_per_step": N * H * 2 + N * 8, "d2h_bytes_per_step": N * H * 2},
                 "gpu_launches": int(launches_per_step) * args.steps, "gpu_launches_per_step": int(launches_per_step),
                 "roofline": roof, "stages": stages_json, "cpu_baseline": cpu, "expert_parallel": ep_json}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()

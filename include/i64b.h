@@ -233,6 +233,56 @@ enum { I64B_DEBUG_KEEP_TAPS = 1, I64B_DEBUG_FUSE_COMBINE = 2 /* force the fused 
 int i64b_moe_set_debug(i64b_layer* layer, int flags);
 
 /* ---------------------------------------------------------------------------
+ * Expert parallelism over NVLink peer memory  (a14)
+ * Replaces TokenRoutedMLP._forward_ep (layers/token_routed_i64/layer.py:209-298): counts all-to-all + .tolist() +
+ * argsort + 2 x all_to_all_single each way.  One process per GPU; every rank allocates its buffers with
+ * i64b_ep_alloc, exports them with i64b_ipc_export, exchanges the 64-byte handles through its own control plane
+ * (torch.distributed.all_gather_object in the Python host) and maps the peers' with i64b_ipc_import.
+ * Per forward (all on one stream, no host synchronisation):
+ *   ids_all = all-gather of the token ids                     (host side: torch.distributed / NCCL)
+ *   i64b_ep_dispatch      global plan on every rank + rows written into the owners' receive buffers
+ *   i64b_ep_signal        "my rows have left"   (the replicated shared expert runs here, hiding the wait)
+ *   i64b_ep_wait          every peer's rows have arrived
+ *   i64b_moe_forward_dispatched   local experts on the receive buffer -> fp32 rows in this rank's y buffer
+ *   i64b_ep_signal / i64b_ep_wait
+ *   i64b_ep_combine       the home rank's weighted combine, reading the K rows of every token straight from the
+ *                         owners' y buffers over NVLink (the return exchange is fused into the combine)
+ * ------------------------------------------------------------------------- */
+#define I64B_EP_MAX_RANKS 8
+typedef struct i64b_ep_ctx {
+    int32_t rank, size;            /* EP rank / group size */
+    int32_t n_local;               /* tokens per rank (equal on all ranks) */
+    int32_t hidden, top_k, num_experts, vocab;
+    int32_t reserved;
+    int64_t cap_rows;              /* rows of every receive buffer (>= size * n_local * top_k: nothing is dropped) */
+    void* peer_xs[I64B_EP_MAX_RANKS];          /* [cap_rows, H] bf16 receive buffer of rank d, mapped here */
+    float* peer_y[I64B_EP_MAX_RANKS];          /* [cap_rows, H] fp32 per-assignment outputs of rank d's experts */
+    int32_t* peer_flags[I64B_EP_MAX_RANKS];    /* [I64B_EP_MAX_RANKS] barrier flags of rank d (zero-initialised) */
+    int32_t* state;                /* local, zero-initialised: [0] barrier epoch */
+} i64b_ep_ctx;
+
+int i64b_ep_alloc(size_t bytes, void** out);               /* cudaMalloc + zero fill (setup only) */
+int i64b_ep_free(void* p);
+int i64b_ipc_export(void* p, unsigned char* handle64);     /* cudaIpcGetMemHandle */
+int i64b_ipc_import(const unsigned char* handle64, void** out);
+int i64b_ipc_close(void* p);
+size_t i64b_ep_workspace_bytes(const i64b_ep_ctx* ctx);
+/* x: [n_local, H] bf16 (this rank's tokens); ids_all: int64 [size * n_local], rank-major; table_u8: [K, V] */
+int i64b_ep_dispatch(const i64b_ep_ctx* ctx, const void* x, const int64_t* ids_all, const uint8_t* table_u8,
+                     int expert_inter, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+/* out[n_local, H] = routed_scale * sum_k w_k * y[owner(k,t)][row(k,t)] + shared_scale * y_shared[t] (y_shared: fp32
+ * [n_local, H] or NULL); same operation order as i64b_combine */
+int i64b_ep_combine(const i64b_ep_ctx* ctx, void* ep_workspace, const float* y_shared, const float* route_weight,
+                    float routed_scale, float shared_scale, void* out, int out_dtype, i64b_stream_t stream);
+int i64b_ep_signal(const i64b_ep_ctx* ctx, i64b_stream_t stream);
+int i64b_ep_wait(const i64b_ep_ctx* ctx, i64b_stream_t stream);
+/* `layer` holds THIS rank's experts (num_experts / size of them, no shared expert, bf16); ep_workspace is the
+ * buffer i64b_ep_dispatch filled.  Runs gate|up + SwiGLU + down on the receive buffer into ctx->peer_y[rank]. */
+size_t i64b_moe_dispatched_workspace_bytes(const i64b_layer* layer, const i64b_ep_ctx* ctx);
+int i64b_moe_forward_dispatched(i64b_layer* layer, const i64b_ep_ctx* ctx, void* ep_workspace, void* workspace,
+                                size_t workspace_bytes, i64b_stream_t stream);
+
+/* ---------------------------------------------------------------------------
  * Stand-alone W8A8 / weight-only GEMM ops  (a12, a13)
  * ------------------------------------------------------------------------- */
 

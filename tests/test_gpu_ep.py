@@ -42,7 +42,13 @@ def _worker(rank, world, port, case, ret):
                                  cfg.shared_output_scale, _C.MODE_BF16, dev, ep)
         blk.load_bf16(t(w.gate), t(w.up), t(w.down), *((t(w.shared_gate), t(w.shared_up), t(w.shared_down)) if s else ()))
         blk.set_table(torch.from_numpy(table))
-        out = blk.forward(t(x[lo:hi], torch.bfloat16), t(ids[lo:hi]), torch.float32)
+        xl, il = t(x[lo:hi], torch.bfloat16), t(ids[lo:hi])
+        out = blk.forward(xl, il, torch.float32)                        # NVLink peer-memory exchange (product path)
+        out_again = blk.forward(xl, il, torch.float32)                  # barrier epochs / buffer reuse
+        out_nccl = blk.forward(xl, il, torch.float32, exchange="nccl")  # reference-style all_to_all_single exchange
+        torch.cuda.synchronize(dev)
+        assert torch.equal(out, out_again), "peer path is not run-to-run identical"
+        assert torch.equal(out, out_nccl), "peer-memory and NCCL exchanges disagree"
         ref = O.moe_block_fp32(x[lo:hi], ids[lo:hi], table, w, cfg, inter_bf16=True)
         mx, mean = O.rel_errors(out.cpu().numpy(), ref)
         ret[rank] = (mx, mean)

@@ -648,6 +648,78 @@ size_t i64b_moe_workspace_bytes_routed(const i64b_layer* L, int64_t max_tokens, 
     return carve_ws(&view, nullptr, max_tokens).bytes + 1024;
 }
 
+// ---- expert-parallel local compute (csrc/i64b_ep.cu holds the exchange)
+void i64b_ep_group_tables(const i64b_ep_ctx* c, void* workspace, const I64bGroup** g1, const I64bGroup** g2);
+
+size_t i64b_moe_dispatched_workspace_bytes(const i64b_layer* L, const i64b_ep_ctx* c) {
+    if (!L || !c) return 0;
+    return align256((size_t)c->cap_rows * L->cfg.expert_inter * 2) + 2048;
+}
+
+int i64b_moe_forward_dispatched(i64b_layer* L, const i64b_ep_ctx* c, void* ep_workspace, void* workspace,
+                                size_t workspace_bytes, i64b_stream_t stream) {
+    I64B_CHECK(L && c && ep_workspace && workspace, I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(L->loaded && L->cfg.mode == I64B_MODE_BF16, I64B_ERR_STATE, "expert-parallel path: bf16 layer with loaded weights");
+    const i64b_moe_config& cfg = L->cfg;
+    I64B_CHECK(cfg.num_experts * c->size == c->num_experts && cfg.hidden_size == c->hidden, I64B_ERR_ARG,
+               "layer holds %d experts, EP context expects %d / %d", cfg.num_experts, c->num_experts, c->size);
+    I64B_CHECK(c->size <= 8, I64B_ERR_ARG, "at most 8 EP ranks");
+    I64B_CHECK(workspace_bytes >= i64b_moe_dispatched_workspace_bytes(L, c), I64B_ERR_WORKSPACE, "workspace too small");
+    if (c->n_local == 0) return I64B_OK;
+    const int E = cfg.num_experts, H = cfg.hidden_size, I = cfg.expert_inter;
+    uint8_t* inter = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~uintptr_t(1023));
+    void* xs = c->peer_xs[c->rank];
+    const int64_t key = -(c->cap_rows + 7);
+    if (L->cached_ws != xs || L->cached_n != key || L->cached_x != inter) {
+        int rc = i64b_encode_tmap(&L->tm_xs, xs, false, c->cap_rows, H, (int64_t)H * 2, 128);
+        if (rc) return rc;
+        rc = i64b_encode_tmap(&L->tm_inter_r, inter, false, c->cap_rows, I, (int64_t)I * 2, 128);
+        if (rc) return rc;
+        L->cached_ws = xs;
+        L->cached_n = key;
+        L->cached_x = inter;
+        L->cached_x_n = -1;
+    }
+    const I64bGroup *g1 = nullptr, *g2 = nullptr;
+    i64b_ep_group_tables(c, ep_workspace, &g1, &g2);
+    cudaStream_t s = (cudaStream_t)stream;
+    // expected load (balanced routing): the real row counts live on the device only
+    const int64_t rows_exp = (int64_t)c->n_local * c->top_k;
+    const int64_t mt = rows_exp / 128 + E, pt = rows_exp / 256 + E;
+    {
+        const int n_mma = pick_nmma(mt, I, 0, 0, true, "I64B_GEMM1_NMMA");
+        const bool pairs = use_cta_pairs(n_mma, rows_exp, E);
+        I64bGemmParams gp = {};
+        gp.groups = g1;
+        gp.num_groups = E + 1;
+        gp.k[0] = gp.k[1] = H;
+        gp.out[0] = gp.out[1] = inter;
+        gp.ld_out[0] = gp.ld_out[1] = I;
+        const int wi = nmma_index(n_mma);
+        // the grid is persistent: any upper bound >= the SM count gives the full machine
+        int rc = i64b_launch_gemm(false, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp,
+                                  (pairs ? pt : mt) * ((I + n_mma / 2 - 1) / (n_mma / 2)) * c->size, s);
+        if (rc) return rc;
+    }
+    {
+        const int n_mma = pick_nmma(mt, H, 0, 0, false, "I64B_GEMM2_NMMA");
+        const bool pairs = use_cta_pairs(n_mma, rows_exp, E);
+        I64bGemmParams gp = {};
+        gp.groups = g2;
+        gp.num_groups = E + 1;
+        gp.k[0] = gp.k[1] = I;
+        gp.out[0] = gp.out[1] = c->peer_y[c->rank];
+        gp.ld_out[0] = gp.ld_out[1] = H;
+        gp.out_dtype = I64B_F32;
+        gp.epi = I64B_EPI_F32;
+        const int wi = pairs ? 1 : nmma_index(n_mma);
+        int rc = i64b_launch_gemm(false, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_r, L->tm_w2r[wi],
+                                  L->tm_w2r[wi], gp, (pairs ? pt : mt) * ((H + n_mma - 1) / n_mma) * c->size, s);
+        if (rc) return rc;
+    }
+    return I64B_OK;
+}
+
 int i64b_copy_device(void* dst, const void* src, size_t bytes, i64b_stream_t stream) {
     if (bytes == 0) return I64B_OK;
     I64B_CHECK(dst && src, I64B_ERR_ARG, "null pointer");

@@ -34,6 +34,18 @@ class MoEConfig(C.Structure):
                 ("shared_scale", C.c_float)]
 
 
+EP_MAX_RANKS = 8
+
+
+class EPCtx(C.Structure):
+    """``i64b_ep_ctx`` (include/i64b.h): peer-mapped buffers of every rank of the expert-parallel group."""
+    _fields_ = [("rank", C.c_int32), ("size", C.c_int32), ("n_local", C.c_int32), ("hidden", C.c_int32),
+                ("top_k", C.c_int32), ("num_experts", C.c_int32), ("vocab", C.c_int32), ("reserved", C.c_int32),
+                ("cap_rows", C.c_int64), ("peer_xs", C.c_void_p * EP_MAX_RANKS),
+                ("peer_y", C.c_void_p * EP_MAX_RANKS),
+                ("peer_flags", C.c_void_p * EP_MAX_RANKS), ("state", C.c_void_p)]
+
+
 _lib: Optional[C.CDLL] = None
 
 _P, _I, _L, _Z, _F = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
@@ -71,6 +83,18 @@ _SIGNATURES = {
     "i64b_moe_forward_host": (_I, [_P, _P, _P, _P, _I, _L, _P, _P, _P, _P, _Z, _P]),
     "i64b_moe_tap": (_P, [_P, _I]),
     "i64b_moe_set_debug": (_I, [_P, _I]),
+    "i64b_ep_alloc": (_I, [_Z, C.POINTER(_P)]),
+    "i64b_ep_free": (_I, [_P]),
+    "i64b_ipc_export": (_I, [_P, C.c_char_p]),
+    "i64b_ipc_import": (_I, [C.c_char_p, C.POINTER(_P)]),
+    "i64b_ipc_close": (_I, [_P]),
+    "i64b_ep_workspace_bytes": (_Z, [C.POINTER(EPCtx)]),
+    "i64b_ep_dispatch": (_I, [C.POINTER(EPCtx), _P, _P, _P, _I, _P, _Z, _P]),
+    "i64b_ep_combine": (_I, [C.POINTER(EPCtx), _P, _P, C.POINTER(_F), _F, _F, _P, _I, _P]),
+    "i64b_ep_signal": (_I, [C.POINTER(EPCtx), _P]),
+    "i64b_ep_wait": (_I, [C.POINTER(EPCtx), _P]),
+    "i64b_moe_dispatched_workspace_bytes": (_Z, [_P, C.POINTER(EPCtx)]),
+    "i64b_moe_forward_dispatched": (_I, [_P, C.POINTER(EPCtx), _P, _P, _Z, _P]),
     "i64b_int8_gemm": (_I, [_P, _P, _P, _P, _P, _P, _L, _L, _L, _P]),
     "i64b_bf16_gemm": (_I, [_P, _P, _P, _P, _I, _L, _L, _L, _P]),
 }

@@ -162,7 +162,128 @@ class EPTokenRoutedBlock:
                                            self.router.cfg.vocab_size, self.K, self.E, _C.stream_ptr(self.device)))
         return out
 
-    def forward(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16) -> torch.Tensor:
+    # ------------------------------------------------------------------ NVLink peer-memory path (the product path)
+    def _setup_peers(self, n: int) -> None:
+        """Allocate this rank's receive / home buffers for ``n`` local tokens, exchange the CUDA IPC handles and map
+        every peer's buffers.  Setup only (allocates and synchronises); ``n`` must be the same on all ranks."""
+        import ctypes as C
+        from vllm_i64 import _C
+        lib = _C.lib()
+        G, K, H = self.ep.ep_size, self.K, self.H
+        if G > _C.EP_MAX_RANKS:
+            raise ValueError(f"at most {_C.EP_MAX_RANKS} expert-parallel ranks")
+        cap = G * n * K                                        # worst case: every assignment lands here (nothing dropped)
+
+        def up(v):
+            return (v + 1023) & ~1023
+        off_xs, off_y = 0, up(cap * H * 2)
+        off_flags = off_y + up(cap * H * 4)
+        total = off_flags + 1024
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize(self.device)
+            self._release_peers()
+            base = C.c_void_p()
+            _C.check(lib.i64b_ep_alloc(total, C.byref(base)))
+            handle = C.create_string_buffer(64)
+            _C.check(lib.i64b_ipc_export(base, handle))
+            handles = [None] * G
+            if G > 1:
+                dist.all_gather_object(handles, bytes(handle.raw), group=self.ep.group)
+            bases = []
+            for d in range(G):
+                if d == self.ep.ep_rank:
+                    bases.append(base.value)
+                else:
+                    p = C.c_void_p()
+                    _C.check(lib.i64b_ipc_import(handles[d], C.byref(p)))
+                    bases.append(p.value)
+        ctx = _C.EPCtx()
+        ctx.rank, ctx.size, ctx.n_local, ctx.hidden = self.ep.ep_rank, G, n, H
+        ctx.top_k, ctx.num_experts, ctx.vocab, ctx.cap_rows = K, self.E, self.router.cfg.vocab_size, cap
+        for d in range(G):
+            ctx.peer_xs[d] = bases[d] + off_xs
+            ctx.peer_y[d] = bases[d] + off_y
+            ctx.peer_flags[d] = bases[d] + off_flags
+        ctx.state = base.value + off_flags + 512
+        self._ctx, self._bases, self._n_setup = ctx, bases, n
+        self._ws_plan = torch.empty(lib.i64b_ep_workspace_bytes(C.byref(ctx)) + 256, dtype=torch.uint8, device=self.device)
+        self._ws_gemm = torch.empty(lib.i64b_moe_dispatched_workspace_bytes(self.local._h, C.byref(ctx)) + 256,
+                                    dtype=torch.uint8, device=self.device)
+        self._ids_all = torch.empty(G * n, dtype=torch.int64, device=self.device)
+        # persistent fp32 output of the replicated shared expert (a fresh 100+ MB torch allocation per call was
+        # measured at ~350 us of allocator time per layer)
+        self._shared_out = (torch.empty(n, H, dtype=torch.float32, device=self.device)
+                            if self.shared is not None else None)
+        if G > 1:
+            dist.barrier(group=self.ep.group)                  # every rank has mapped every buffer
+
+    def _release_peers(self) -> None:
+        from vllm_i64 import _C
+        bases = getattr(self, "_bases", None)
+        if not bases:
+            return
+        lib = _C.lib()
+        for d, b in enumerate(bases):
+            if d == self.ep.ep_rank:
+                lib.i64b_ep_free(b)
+            else:
+                lib.i64b_ipc_close(b)
+        self._bases = None
+
+    def forward_peer(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One expert-parallel forward over NVLink peer memory: no host synchronisation, no NCCL on the data path
+        (NCCL carries only the all-gather of the token ids).  See include/i64b.h (expert parallelism)."""
+        import ctypes as C
+        from vllm_i64 import _C
+        _C.require_cuda(x, token_ids)
+        lib = _C.lib()
+        n = x.shape[0]
+        if x.dtype != torch.bfloat16 or not x.is_contiguous():
+            x = x.to(torch.bfloat16).contiguous()
+        token_ids = token_ids.to(torch.int64).contiguous()
+        if getattr(self, "_n_setup", -1) != n:
+            self._setup_peers(n)
+        ctx = C.byref(self._ctx)
+        with torch.cuda.device(self.device):
+            cur = torch.cuda.current_stream(self.device)
+            shared = None
+            if self.shared is not None:
+                # the replicated shared expert runs on a side stream: its GEMMs fill the SMs while the dispatch kernel
+                # (NVLink-bound, a few warps per SM) and the barrier wait occupy the main stream
+                if getattr(self, "_side", None) is None:
+                    self._side = torch.cuda.Stream(self.device)
+                self._side.wait_stream(cur)
+                with torch.cuda.stream(self._side):
+                    shared = self.shared.forward(x, None, torch.float32, out=self._shared_out)
+            st = _C.stream_ptr(self.device)
+            if self.ep.ep_size > 1:
+                dist.all_gather_into_tensor(self._ids_all, token_ids, group=self.ep.group)
+            else:
+                self._ids_all.copy_(token_ids)
+            _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), self._ids_all.data_ptr(), self._table.data_ptr(),
+                                          self.local.cfg.expert_inter, self._ws_plan.data_ptr(), self._ws_plan.numel(), st))
+            _C.check(lib.i64b_ep_signal(ctx, st))
+            _C.check(lib.i64b_ep_wait(ctx, st))
+            _C.check(lib.i64b_moe_forward_dispatched(self.local._h, ctx, self._ws_plan.data_ptr(), self._ws_gemm.data_ptr(),
+                                                     self._ws_gemm.numel(), st))
+            _C.check(lib.i64b_ep_signal(ctx, st))
+            _C.check(lib.i64b_ep_wait(ctx, st))
+            if out is None:
+                out = torch.empty(n, self.H, dtype=out_dtype, device=self.device)
+            if shared is not None:
+                cur.wait_stream(self._side)
+            wts = (C.c_float * 4)(*[self.w[i] if i < len(self.w) else 0.0 for i in range(4)])
+            _C.check(lib.i64b_ep_combine(ctx, self._ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
+                                         out.data_ptr(), _C.dtype_code(out), st))
+        return out
+
+    def forward(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
+                exchange: str = "peer", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``exchange="peer"``: NVLink peer-memory path (default).  ``"nccl"``: all_to_all_single exchange with
+        host-side split sizes, the reference's scheme — kept as the comparison baseline (bench.py reports both)."""
+        if exchange == "peer":
+            return self.forward_peer(x, token_ids, out_dtype, out)
         from vllm_i64 import _C
         n = x.shape[0]
         routes = self.route(token_ids)
