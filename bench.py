@@ -304,13 +304,15 @@ def run_ep(wl, device, rank, world, args):
     L = 4
     n = args.ep_tokens // world
     blocks = []
+    tdt = torch.bfloat16 if args.ep_transport == "bf16" else torch.float32
     for layer in range(L):
         g = torch.Generator(device=device).manual_seed(layer)
 
         def u(shape, fan_in):
             return (torch.rand(shape, device=device, generator=g) * 2 - 1) / fan_in ** 0.5
 
-        b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep)
+        b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep,
+                               transport_dtype=tdt)
         b.load_bf16(u((E, H, I), H), u((E, H, I), H), u((E, I, H), I), u((S, H), H), u((S, H), H), u((H, S), S))
         b.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
         blocks.append(b)
@@ -345,6 +347,7 @@ def run_ep(wl, device, rank, world, args):
     return {"workload": "tr-hash-moe-500m bf16 expert-parallel", "tokens_per_step_total": n * world,
             "layers_per_step": L, "ms_per_step": ms, "value": n * world * L / (ms * 1e-3), "unit": UNIT,
             "scaling": "strong", "a2a_bytes_out_per_rank_per_layer": int(sent), "ep_size": world,
+            "transport_dtype": args.ep_transport,
             "exchange": "NVLink peer memory (dispatch kernel writes into the owners' buffers; GEMM2 epilogue writes "
                         "outputs home); NCCL only all-gathers the token ids",
             "nccl_all_to_all_baseline": {"ms_per_step": ms_nccl, "value": n * world * L / (ms_nccl * 1e-3)}}
@@ -363,6 +366,8 @@ def main():
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-ep", action="store_true")
     ap.add_argument("--ep-tokens", type=int, default=65536, help="tokens per step over ALL ranks (BASELINE config 5)")
+    ap.add_argument("--ep-transport", default="f32", choices=["f32", "bf16"],
+                    help="dtype the expert outputs travel back in (f32: bit-identical to one GPU; bf16: the reference's)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))

@@ -253,10 +253,12 @@ typedef struct i64b_ep_ctx {
     int32_t rank, size;            /* EP rank / group size */
     int32_t n_local;               /* tokens per rank (equal on all ranks) */
     int32_t hidden, top_k, num_experts, vocab;
-    int32_t reserved;
+    int32_t y_dtype;               /* dtype the expert outputs travel in: I64B_F32 (default; the EP result is then
+                                      bit-identical to the single-GPU block) or I64B_BF16 (the reference's EP path
+                                      returns expert outputs in the model dtype; halves the return traffic) */
     int64_t cap_rows;              /* rows of every receive buffer (>= size * n_local * top_k: nothing is dropped) */
     void* peer_xs[I64B_EP_MAX_RANKS];          /* [cap_rows, H] bf16 receive buffer of rank d, mapped here */
-    float* peer_y[I64B_EP_MAX_RANKS];          /* [cap_rows, H] fp32 per-assignment outputs of rank d's experts */
+    void* peer_y[I64B_EP_MAX_RANKS];           /* [cap_rows, H] y_dtype per-assignment outputs of rank d's experts */
     int32_t* peer_flags[I64B_EP_MAX_RANKS];    /* [I64B_EP_MAX_RANKS] barrier flags of rank d (zero-initialised) */
     int32_t* state;                /* local, zero-initialised: [0] barrier epoch */
 } i64b_ep_ctx;

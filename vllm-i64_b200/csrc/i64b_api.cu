@@ -710,7 +710,7 @@ int i64b_moe_forward_dispatched(i64b_layer* L, const i64b_ep_ctx* c, void* ep_wo
         gp.k[0] = gp.k[1] = I;
         gp.out[0] = gp.out[1] = c->peer_y[c->rank];
         gp.ld_out[0] = gp.ld_out[1] = H;
-        gp.out_dtype = I64B_F32;
+        gp.out_dtype = c->y_dtype;
         gp.epi = I64B_EPI_F32;
         const int wi = pairs ? 1 : nmma_index(n_mma);
         int rc = i64b_launch_gemm(false, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_r, L->tm_w2r[wi],

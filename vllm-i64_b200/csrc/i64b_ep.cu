@@ -111,9 +111,16 @@ __global__ void __launch_bounds__(256) ep_combine_kernel(const i64b_ep_ctx c, co
         for (int k = 0; k < I64B_MAX_TOPK; ++k) {
             if (k < c.top_k) {
                 const int64_t l = __ldg(a.loc + (int64_t)k * c.n_local + t);
-                const float* row = c.peer_y[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)] + (l & 0xffffffffll) * c.hidden;
-                const int4 v = ld_nc_16(reinterpret_cast<const int4*>(row) + col);
-                yk[k] = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w));
+                const void* base = c.peer_y[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)];
+                const int64_t row = l & 0xffffffffll;
+                if (c.y_dtype == I64B_F32) {
+                    const int4 v = ld_nc_16(reinterpret_cast<const int4*>(reinterpret_cast<const float*>(base) + row * c.hidden) + col);
+                    yk[k] = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w));
+                } else {
+                    const uint2 v = *(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(base) + row * c.hidden) + col);
+                    yk[k] = make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xffff0000u),
+                                        __uint_as_float(v.y << 16), __uint_as_float(v.y & 0xffff0000u));
+                }
             }
         }
         float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -192,6 +199,7 @@ static int ep_check(const i64b_ep_ctx* c) {
         I64B_CHECK(c->peer_xs[d] && c->peer_y[d] && c->peer_flags[d], I64B_ERR_ARG,
                    "peer buffers of rank %d not mapped", d);
     I64B_CHECK(c->state != nullptr, I64B_ERR_ARG, "EP state missing");
+    I64B_CHECK(c->y_dtype == I64B_F32 || c->y_dtype == I64B_BF16, I64B_ERR_ARG, "y_dtype must be F32 or BF16");
     return I64B_OK;
 }
 

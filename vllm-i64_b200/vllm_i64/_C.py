@@ -40,7 +40,7 @@ EP_MAX_RANKS = 8
 class EPCtx(C.Structure):
     """``i64b_ep_ctx`` (include/i64b.h): peer-mapped buffers of every rank of the expert-parallel group."""
     _fields_ = [("rank", C.c_int32), ("size", C.c_int32), ("n_local", C.c_int32), ("hidden", C.c_int32),
-                ("top_k", C.c_int32), ("num_experts", C.c_int32), ("vocab", C.c_int32), ("reserved", C.c_int32),
+                ("top_k", C.c_int32), ("num_experts", C.c_int32), ("vocab", C.c_int32), ("y_dtype", C.c_int32),
                 ("cap_rows", C.c_int64), ("peer_xs", C.c_void_p * EP_MAX_RANKS),
                 ("peer_y", C.c_void_p * EP_MAX_RANKS),
                 ("peer_flags", C.c_void_p * EP_MAX_RANKS), ("state", C.c_void_p)]

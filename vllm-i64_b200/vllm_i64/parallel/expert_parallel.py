@@ -129,8 +129,14 @@ class EPTokenRoutedBlock:
 
     def __init__(self, hidden_size: int, num_experts: int, expert_inter: int, shared_inter: int, vocab_size: int,
                  top_k: int, route_weights: Sequence[float], routed_scale: float, shared_scale: float, mode: int,
-                 device: torch.device, ep: Optional[EPState] = None):
+                 device: torch.device, ep: Optional[EPState] = None, transport_dtype: torch.dtype = torch.float32):
+        """``transport_dtype``: dtype the expert outputs travel back in.  float32 (default) makes the EP result
+        bit-identical to the single-GPU block; bfloat16 is the reference's choice (its EP path returns expert outputs
+        in the model dtype, layers/token_routed_i64/layer.py:283-292) and halves the return traffic."""
         from vllm_i64.kernels.block import I64Block
+        if transport_dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError("transport_dtype must be float32 or bfloat16")
+        self.transport_dtype = transport_dtype
         self.ep = ep or _EP
         self.E, self.K, self.H = num_experts, top_k, hidden_size
         self.first, self.local_E = local_expert_range(num_experts, self.ep)
@@ -200,6 +206,7 @@ class EPTokenRoutedBlock:
         ctx = _C.EPCtx()
         ctx.rank, ctx.size, ctx.n_local, ctx.hidden = self.ep.ep_rank, G, n, H
         ctx.top_k, ctx.num_experts, ctx.vocab, ctx.cap_rows = K, self.E, self.router.cfg.vocab_size, cap
+        ctx.y_dtype = _C.F32 if self.transport_dtype == torch.float32 else _C.BF16
         for d in range(G):
             ctx.peer_xs[d] = bases[d] + off_xs
             ctx.peer_y[d] = bases[d] + off_y
