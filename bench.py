@@ -209,6 +209,11 @@ def build_layers(wl, device):
     torch.cuda.synchronize(device)
     for b in layers:
         b._keep = None
+    # decoder order: layer l is followed by l+1 (the step loop wraps around), so each block may prefetch the next one's
+    # weights into L2 (i64b_moe_set_next; a no-op outside the fused decode kernel)
+    if len(layers) > 1 and os.environ.get("I64B_PREFETCH", "1") != "0":
+        for i, b in enumerate(layers):
+            b.set_next(layers[(i + 1) % len(layers)])
     return layers
 
 

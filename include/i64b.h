@@ -232,6 +232,13 @@ void* i64b_moe_tap(i64b_layer* layer, int what);
 enum { I64B_DEBUG_KEEP_TAPS = 1, I64B_DEBUG_FUSE_COMBINE = 2 /* force the fused combine (default: dense FFN only) */ };
 int i64b_moe_set_debug(i64b_layer* layer, int flags);
 
+/* Cross-layer weight prefetch (decode).  `next` is the layer the engine runs after `layer` (the decoder stack calls
+ * its MLPs in a fixed order: models/complexity_deep/model.py:478-486); the fused decode kernel of `layer` then pulls
+ * next's packed weights into L2 while it waits on its own dependencies.  Results are unaffected.  next == NULL turns
+ * it off; `next` must outlive `layer` or be cleared first.  Env I64B_PREFETCH=0 disables, =2 issues the prefetch
+ * after the layer's own weight stream instead of at kernel entry. */
+int i64b_moe_set_next(i64b_layer* layer, const i64b_layer* next);
+
 /* ---------------------------------------------------------------------------
  * Expert parallelism over NVLink peer memory  (a14)
  * Replaces TokenRoutedMLP._forward_ep (layers/token_routed_i64/layer.py:209-298): counts all-to-all + .tolist() +

@@ -55,6 +55,7 @@ struct i64b_layer {
     const uint8_t* table = nullptr;
     bool loaded = false;
     int debug = 0;               // I64B_DEBUG_* bits (i64b_moe_set_debug)
+    const i64b_layer* next = nullptr;   // layer whose weights the fused decode kernel prefetches into L2
     CUtensorMap tm_w13[3], tm_w2r[3], tm_w2s[3];   // per n_mma choice (box rows differ)
     // activation tensor maps, valid for (ws_base, n)
     void* cached_ws = nullptr;
@@ -337,6 +338,13 @@ int i64b_moe_set_debug(i64b_layer* L, int flags) {
     return I64B_OK;
 }
 
+int i64b_moe_set_next(i64b_layer* L, const i64b_layer* next) {
+    I64B_CHECK(L, I64B_ERR_ARG, "null layer");
+    I64B_CHECK(next == nullptr || next->loaded, I64B_ERR_STATE, "next layer has no weights yet");
+    L->next = next;
+    return I64B_OK;
+}
+
 int i64b_moe_set_table(i64b_layer* L, const uint8_t* table_u8) {
     I64B_CHECK(L, I64B_ERR_ARG, "null layer");
     L->table = table_u8;
@@ -441,6 +449,12 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         fp.routed_scale = c.routed_scale; fp.shared_scale = c.shared_scale;
         fp.inter_r = cv.inter_r; fp.inter_s = cv.inter_s; fp.y = cv.y; fp.out = out;
         fp.sync = L->sync;
+        static const int prefetch_mode = env_int("I64B_PREFETCH", 1);
+        if (L->next != nullptr && L->next != L && prefetch_mode > 0) {
+            fp.next_w = L->next->w13;                              // w13 | w2r | w2s are contiguous in the pack
+            fp.next_w_bytes = (uint64_t)(reinterpret_cast<const uint8_t*>(L->next->w13_scale) - L->next->w13);
+            fp.prefetch_mode = prefetch_mode;
+        }
         fp.tap_routes = cv.routes; fp.tap_dest = cv.dest_row; fp.tap_scatter = cv.scatter_idx;
         fp.tap_counts = cv.plan.counts; fp.tap_offsets = cv.plan.offsets;
         // tensor map over the caller's x (128-row tiles for the shared expert's GEMM1)

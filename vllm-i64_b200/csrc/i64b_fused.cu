@@ -208,6 +208,18 @@ __device__ __forceinline__ long long gtime() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return (long long)t;
 }
+// Cross-layer weight prefetch: HBM is idle for most of a decode layer (the time goes to dependency latency), so each
+// launch pulls its share of the NEXT layer's weights (constants) into the 126 MB L2; that layer's TMA stream then
+// hits L2 instead of paying loaded-DRAM latency per ring refill.
+__device__ __forceinline__ void prefetch_next_weights(const I64bFusedParams& p, int cta, int ctas) {
+    constexpr uint64_t kChunk = 16384;
+    const uint64_t chunks = (p.next_w_bytes + kChunk - 1) / kChunk;
+    for (uint64_t c = (uint64_t)cta; c < chunks; c += (uint64_t)ctas) {
+        const uint64_t off = c * kChunk;
+        const uint32_t bytes = (uint32_t)((p.next_w_bytes - off < kChunk ? p.next_w_bytes - off : kChunk) & ~uint64_t(15));
+        if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p.next_w + off), "r"(bytes) : "memory");
+    }
+}
 #define TL(slot) do { if (tl) tl[slot] = gtime(); } while (0)
 // bounded spin on a device counter (a stuck dependency traps instead of hanging the GPU)
 __device__ __forceinline__ void wait_counter(const int* ctr, int target) {
@@ -374,6 +386,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     if (threadIdx.x == 0) TL(1);
 
     if (warp == 0) {
+        if (lane == 1 && p.next_w != nullptr && p.prefetch_mode == 1) prefetch_next_weights(p, blockIdx.x, G);
         // ------------------------------------------------------------------ weight TMA: runs ahead of everything else
         // by the depth of the ring (the weights of the next unit stream in while this one waits on a dependency)
         if (lane == 0) {
@@ -392,6 +405,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                         st_release_cta(&s.b_seq, seq + 1);
                     }
             }
+            if (p.next_w != nullptr && p.prefetch_mode == 2) prefetch_next_weights(p, blockIdx.x, G);
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer

@@ -25,6 +25,9 @@ struct I64bFusedParams {
     float* y;                   // [N*K + slabs*N, H] fp32
     void* out;                  // [N, H]
     int* sync;                  // I64B_SYNC_INTS ints
+    const uint8_t* next_w;      // next layer's packed weights (constants) to pull into L2 while this layer runs, or nullptr
+    uint64_t next_w_bytes;
+    int32_t prefetch_mode;      // 1: a spare thread at kernel entry; 2: the weight thread once its own stream is issued
     long long* timeline;        // bring-up only: [grid, 16] ns stamps (env I64B_DEBUG_TIMELINE)
     int32_t *tap_routes, *tap_dest, *tap_scatter, *tap_counts, *tap_offsets;   // reference-convention plan outputs
 };

@@ -155,6 +155,12 @@ class I64Block:
                 "ids": torch.empty(n, dtype=torch.int64, device=self.device),
                 "out": torch.empty(n, self.cfg.hidden_size, dtype=out_dtype, device=self.device)}
 
+    def set_next(self, nxt: Optional["I64Block"]) -> None:
+        """Name the block the engine runs after this one (decoder order, reference models/complexity_deep/model.py:478-486):
+        the fused decode kernel prefetches its weights into L2.  ``None`` turns the prefetch off."""
+        _C.check(_C.lib().i64b_moe_set_next(self._h, nxt._h if nxt is not None else None))
+        self._next = nxt          # keeps the packed weights alive while they can be prefetched
+
     def set_debug(self, flags: int) -> None:
         """``_C.DEBUG_KEEP_TAPS``: keep the shared expert's own rows in TAP_Y (the fused combine does not need them)."""
         _C.check(_C.lib().i64b_moe_set_debug(self._h, int(flags)))
