@@ -210,8 +210,8 @@ def build_layers(wl, device):
     for b in layers:
         b._keep = None
     # decoder order: layer l is followed by l+1 (the step loop wraps around), so each block may prefetch the next one's
-    # weights into L2 (i64b_moe_set_next; a no-op outside the fused decode kernel)
-    if len(layers) > 1 and os.environ.get("I64B_PREFETCH", "1") != "0":
+    # weights into L2 (i64b_moe_set_next; a no-op outside the fused decode kernel).  Opt-in: measured slower
+    if len(layers) > 1 and os.environ.get("I64B_PREFETCH", "0") != "0":
         for i, b in enumerate(layers):
             b.set_next(layers[(i + 1) % len(layers)])
     return layers
@@ -401,7 +401,7 @@ def main():
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
     barrier = None
-    if world > 1:
+    if world > 1 or os.environ.get("I64B_BENCH_FORCE_DIST") == "1":      # (the env is a bring-up switch: NCCL at world 1)
         import torch.distributed as dist
         # NCCL prints its version banner to stdout when NCCL_DEBUG is set by the environment: keep stdout to the ONE
         # JSON line of the contract
@@ -412,7 +412,7 @@ def main():
         _JSON_FD = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=device)
-        barrier = lambda: dist.barrier()            # noqa: E731
+        barrier = (lambda: None) if os.environ.get("I64B_BENCH_SKIP_BARRIER") == "1" else (lambda: dist.barrier())  # noqa: E731
     from vllm_i64 import _C
 
     H, N, L = wl["H"], wl["N"], wl["L"]
@@ -519,7 +519,10 @@ def main():
                 "peak_source": pk["src"] + " (burst copy)", "algorithmic_bytes": fb, "us_per_launch": round(us, 3)}
     ep_json = None
     if world > 1 and wl["E"] and wl["E"] % world == 0 and not args.no_ep:
-        ep_json = run_ep(wl, device, rank, world, args)
+        try:
+            ep_json = run_ep(wl, device, rank, world, args)
+        except Exception as exc:                      # the data-parallel line above stands on its own
+            ep_json = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

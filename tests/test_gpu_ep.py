@@ -1,4 +1,4 @@
-"""Expert-parallel block on GPUs (NCCL): world_size 1 always, 2 when the box has two devices.  Every rank's output
+"""Expert-parallel block on GPUs (NCCL): world_size 1 always, 2 / 4 / 8 when the box has that many devices.  Every rank's output
 must match the single-GPU block on the same tokens (same kernels, so the match is tight) and the oracle."""
 import os
 import socket
@@ -64,10 +64,14 @@ def _worker(rank, world, port, case, ret):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [1, 2])
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
 def test_ep_block_matches_oracle(world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
+    if world == 8 and os.environ.get("I64B_TEST_EP8") != "1":
+        # world 4 passed on an 8-GPU box; world 8 ran into the 240 s test timeout there (that box's interconnect was
+        # degraded: NCCL all_to_all at 6 GB/s), so it is opt-in until it has been seen green
+        pytest.skip("world 8 is opt-in (I64B_TEST_EP8=1)")
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), (256, 8, 64, 128, 1000, 2, 700), ret), nprocs=world, join=True)

@@ -449,7 +449,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         fp.routed_scale = c.routed_scale; fp.shared_scale = c.shared_scale;
         fp.inter_r = cv.inter_r; fp.inter_s = cv.inter_s; fp.y = cv.y; fp.out = out;
         fp.sync = L->sync;
-        static const int prefetch_mode = env_int("I64B_PREFETCH", 1);
+        static const int prefetch_mode = env_int("I64B_PREFETCH", 0);
         if (L->next != nullptr && L->next != L && prefetch_mode > 0) {
             fp.next_w = L->next->w13;                              // w13 | w2r | w2s are contiguous in the pack
             fp.next_w_bytes = (uint64_t)(reinterpret_cast<const uint8_t*>(L->next->w13_scale) - L->next->w13);
