@@ -240,6 +240,10 @@ int i64b_moe_set_debug(i64b_layer* layer, int flags);
  * 26.2 / 25.3 us with — the layer is bound by its dependency chain, not by where the weights come from). */
 int i64b_moe_set_next(i64b_layer* layer, const i64b_layer* next);
 
+/* Bring-up only (env I64B_DEBUG_TIMELINE=1): after replaying a CUDA graph of fused decode layers, print the per-CTA
+ * globaltimer stamps of the last two layers to stderr.  Synchronises the device.  Returns 0 when no timeline exists. */
+int i64b_debug_timeline_dump(void);
+
 /* ---------------------------------------------------------------------------
  * Expert parallelism over NVLink peer memory  (a14)
  * Replaces TokenRoutedMLP._forward_ep (layers/token_routed_i64/layer.py:209-298): counts all-to-all + .tolist() +

@@ -1,25 +1,20 @@
 #!/bin/bash
-# One GPU iteration: parity tests, then short benches of the named workloads (each under its own timeout).
-#   tools/gpu_iter.sh [workload ...]      default: prefill_bf16 prefill_w8a8 dense_prefill decode_bf16
+# quick iteration: decode parity (fused-kernel tests) + decode bench (+ optional graph timeline)
 mkdir -p gpurun_out
 export PYTHONDONTWRITEBYTECODE=1
-TAG=${TAG:-it}
-if [ -z "$SKIP_TESTS" ]; then
-  timeout 1200 python -m pytest -x -q -p no:cacheprovider --timeout 240 --timeout-method=thread tests/test_gpu_parity.py ${PYTEST_ARGS} > gpurun_out/${TAG}_pytest.log 2>&1
-  echo "pytest rc=$?"; tail -n 8 gpurun_out/${TAG}_pytest.log
-fi
-show() { python - <<PY
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -3
+timeout 300 python bench.py --no-cpu-baseline --no-stages > gpurun_out/it_decode.json 2> gpurun_out/it_decode.err; echo "bench rc=$?"
+python - <<'PY'
 import json
-try:
-    d=json.load(open("$1")); s=d["stages"]
-    inner = s.get("unfused_chain_for_comparison", s)
-    print("$2 value=%.4g e2e=%.4g step_us/layer=%.2f | " % (d["value"], d["e2e"]["value"], s["_step_us_per_layer"]) + " ".join("%s=%.1f" % (k, v["us_per_launch"]) for k, v in inner.items() if isinstance(v, dict)) + " | roof %s %.3f" % (d["roofline"]["kernel"], d["roofline"]["frac"]))
-except Exception as e:
-    print("$2 FAILED", e); print(open("gpurun_out/${TAG}.err").read()[-1500:])
+d=json.loads(open("gpurun_out/it_decode.json").read().strip().splitlines()[-1])
+print("decode", round(d["value"]/1e6,2), "Mtok/s", d["roofline"]["us_per_launch"], "us/layer frac", d["roofline"]["frac"], "e2e", round(d["e2e"]["value"]/1e6,2))
 PY
-}
-WLS=${@:-prefill_bf16 prefill_w8a8 dense_prefill decode_bf16}
-for wl in $WLS; do
-  steps=30; [ "$wl" = decode_bf16 ] && steps=200
-  timeout 300 python bench.py --workload $wl --steps $steps --warmup 10 --no-cpu-baseline > gpurun_out/${TAG}_$wl.json 2>gpurun_out/${TAG}.err; show gpurun_out/${TAG}_$wl.json $wl
+for wl in dense_decode tr_moe_306_decode; do
+  timeout 300 python bench.py --workload $wl --no-cpu-baseline --no-stages > gpurun_out/it_$wl.json 2> gpurun_out/it_$wl.err
+  python - <<PY
+import json
+d=json.loads(open("gpurun_out/it_$wl.json").read().strip().splitlines()[-1])
+print("$wl", round(d["value"]/1e6,2), "Mtok/s", round(d["ms_per_step"]*1000/d["config"]["layers_per_step"],2), "us/layer")
+PY
 done
+if [ "$1" = "tl" ]; then I64B_DEBUG_TIMELINE=1 timeout 300 python tools/probe_graph_tl.py 2>&1 | grep -v eager | tail -34; fi

@@ -38,6 +38,12 @@ constexpr int kSlabK = 512;            // split-K slab of the shared down-projec
 constexpr uint32_t kTmemCols = 2 * kNMma;
 constexpr int kMaxTok = I64B_FUSED_MAX_TOKENS;
 
+constexpr int kMaxUnitsPerCta = 8;
+enum { kG1Routed = 0, kG1Shared = 1, kG2Routed = 2, kG2Shared = 3 };
+struct Unit {
+    int type, g, n_t, m_t, slab, nkb;
+};
+
 struct Smem {
     uint64_t full_bar[kStages], empty_bar[kStages], tfull_bar[2], tempty_bar[2];
     uint32_t tmem_ptr;
@@ -54,23 +60,15 @@ struct Smem {
     int fast_cnt[kPlanWarps];
     int rows_first;
     uint32_t plan_ready;                                // full plan published (release/acquire, CTA scope)
+    Unit units[kMaxUnitsPerCta];                        // this CTA's units (static work list), decoded once by warp 1
+    int n_units;
     int comb_rank, comb_total;                          // this CTA's index among the combine workers (-1: none) and their number
 };
 
 // static work list
-struct Geo {
-    int nkb_h;                 // k-blocks over H
-    int nt1r, U1r;             // GEMM1 routed: n-tiles per expert, units
-    int mts, nt1s, U1;         // shared m-tiles, GEMM1 shared n-tiles, total GEMM1 units
-    int nt2, U2r, slabs, U2;   // GEMM2 n-tiles, routed units, shared K slabs, total GEMM2 units
-    int U;
-};
-enum { kG1Routed = 0, kG1Shared = 1, kG2Routed = 2, kG2Shared = 3 };
-struct Unit {
-    int type, g, n_t, m_t, slab, nkb;
-};
+using Geo = I64bFusedGeo;
 
-__device__ __forceinline__ Geo make_geo(const I64bFusedParams& p) {
+static Geo make_geo(const I64bFusedParams& p) {
     Geo g;
     const int E = p.num_experts;
     g.nkb_h = (p.hidden + kBlockK - 1) / kBlockK;
@@ -211,7 +209,7 @@ __device__ __forceinline__ long long gtime() {
 // Cross-layer weight prefetch: HBM is idle for most of a decode layer (the time goes to dependency latency), so each
 // launch pulls its share of the NEXT layer's weights (constants) into the 126 MB L2; that layer's TMA stream then
 // hits L2 instead of paying loaded-DRAM latency per ring refill.
-__device__ __forceinline__ void prefetch_next_weights(const I64bFusedParams& p, int cta, int ctas) {
+__device__ __noinline__ void prefetch_next_weights(const I64bFusedParams& p, int cta, int ctas) {
     constexpr uint64_t kChunk = 16384;
     const uint64_t chunks = (p.next_w_bytes + kChunk - 1) / kChunk;
     for (uint64_t c = (uint64_t)cta; c < chunks; c += (uint64_t)ctas) {
@@ -220,7 +218,7 @@ __device__ __forceinline__ void prefetch_next_weights(const I64bFusedParams& p, 
         if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p.next_w + off), "r"(bytes) : "memory");
     }
 }
-#define TL(slot) do { if (tl) tl[slot] = gtime(); } while (0)
+#define TL(slot) do { if (kTL && tl) tl[slot] = gtime(); } while (0)
 // bounded spin on a device counter (a stuck dependency traps instead of hanging the GPU)
 __device__ __forceinline__ void wait_counter(const int* ctr, int target) {
     const long long t0 = clock64();
@@ -230,6 +228,23 @@ __device__ __forceinline__ void wait_counter(const int* ctr, int target) {
     }
 }
 
+__device__ __noinline__ void issue_weights(const I64bFusedParams& p, const CUtensorMap* tm_w13, const CUtensorMap* tm_w2r,
+                                           const CUtensorMap* tm_w2s, uint8_t* dstB, uint64_t* bar, int type, int g, int n_t,
+                                           int slab, int kb) {
+    mbar_arrive_expect_tx(bar, kStageB);
+    if (type <= kG1Shared) {
+        const int n_out = type == kG1Routed ? p.expert_inter : p.shared_inter;
+        const int wrow = (type == kG1Routed ? g * 2 * p.expert_inter : p.num_experts * 2 * p.expert_inter) + n_t * kBn1;
+        tma_load_2d(dstB, tm_w13, bar, kb * kBlockK, wrow, I64B_L2_EVICT_FIRST);
+        tma_load_2d(dstB + kBn1 * 128, tm_w13, bar, kb * kBlockK, wrow + n_out, I64B_L2_EVICT_FIRST);
+    } else if (type == kG2Routed) {
+        tma_load_2d(dstB, tm_w2r, bar, kb * kBlockK, g * p.hidden + n_t * kNMma, I64B_L2_EVICT_FIRST);
+    } else {
+        tma_load_2d(dstB, tm_w2s, bar, slab * kSlabK + kb * kBlockK, n_t * kNMma, I64B_L2_EVICT_FIRST);
+    }
+}
+
+template <bool kTL>      // kTL: bring-up time stamps compiled in (a separate instantiation: the product kernel stays small)
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                         const __grid_constant__ CUtensorMap tm_w13, const __grid_constant__ CUtensorMap tm_inter_r,
@@ -243,34 +258,19 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int E = p.num_experts, K = p.top_k, N = p.n, H = p.hidden, bins = K * E, G = gridDim.x;
-    const Geo geo = make_geo(p);
+    const Geo& geo = p.geo;
     pdl_launch_dependents();
-    long long* tl = p.timeline ? p.timeline + (size_t)blockIdx.x * 32 : nullptr;
+    long long* tl = (kTL && p.timeline) ? p.timeline + (size_t)blockIdx.x * 32 : nullptr;
     if (threadIdx.x == 0) TL(0);
 
-    // weight tile of (unit, k-block) → shared-memory stage; tx bytes = kStageB
+    // weight tile of (unit, k-block) → shared-memory stage; tx bytes = kStageB (one out-of-line copy: every TMA call
+    // site costs ~17 instructions of uniform-register plumbing, and this kernel runs its code cold)
     auto issue_b = [&](const Unit& u, int kb, int stage) {
-        uint8_t* dstB = sB + stage * kStageB;
-        mbar_arrive_expect_tx(&s.full_bar[stage], kStageB);
-        if (u.type <= kG1Shared) {
-            const int n_out = u.type == kG1Routed ? p.expert_inter : p.shared_inter;
-            const int wrow = (u.type == kG1Routed ? u.g * 2 * p.expert_inter : E * 2 * p.expert_inter) + u.n_t * kBn1;
-            tma_load_2d(dstB, &tm_w13, &s.full_bar[stage], kb * kBlockK, wrow, I64B_L2_EVICT_FIRST);
-            tma_load_2d(dstB + kBn1 * 128, &tm_w13, &s.full_bar[stage], kb * kBlockK, wrow + n_out, I64B_L2_EVICT_FIRST);
-        } else if (u.type == kG2Routed) {
-            tma_load_2d(dstB, &tm_w2r, &s.full_bar[stage], kb * kBlockK, u.g * H + u.n_t * kNMma, I64B_L2_EVICT_FIRST);
-        } else {
-            tma_load_2d(dstB, &tm_w2s, &s.full_bar[stage], u.slab * kSlabK + kb * kBlockK, u.n_t * kNMma,
-                        I64B_L2_EVICT_FIRST);
-        }
+        issue_weights(p, &tm_w13, &tm_w2r, &tm_w2s, sB + stage * kStageB, &s.full_bar[stage], u.type, u.g, u.n_t, u.slab, kb);
     };
 
     int own_e = -1;              // expert of the CTA's first unit when that is a routed GEMM1 unit
-    if ((int)blockIdx.x < geo.U) {
-        Unit uf;
-        decode_unit(p, geo, blockIdx.x, uf);
-        if (uf.type == kG1Routed) own_e = uf.g;
-    }
+    if ((int)blockIdx.x < geo.U1r) own_e = (int)blockIdx.x / geo.nt1r;
     int pre_issued = 0;          // weight stages the TMA thread put in flight before the plan (first unit, pass 0)
     if (warp == 0) {
         Unit u0;
@@ -299,6 +299,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         pre_issued = __shfl_sync(0xffffffffu, pre_issued, 0);
     } else if (warp == 1) {
         tmem_alloc<kTmemCols>(&s.tmem_ptr);
+        // this CTA's units, decoded once (the role loops below read them from shared memory)
+        if (lane < kMaxUnitsPerCta && (int)blockIdx.x + lane * G < geo.U) decode_unit(p, geo, blockIdx.x + lane * G, s.units[lane]);
+        if (lane == 0) s.n_units = (int)blockIdx.x < geo.U ? (geo.U - (int)blockIdx.x + G - 1) / G : 0;
         // Combine: token t belongs to CTA t % G.  (Measured: handing the combine to the ~36 CTAs that finish early, so
         // that the others can exit and free their SMs for the next kernel, costs 9 us of combine against 3 us when all
         // 148 SMs share it: the pass is bound by per-SM L2 read latency, not by work.)
@@ -382,6 +385,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_ptr;
+    const int n_units = s.n_units;
     bool have_plan = false;
     if (threadIdx.x == 0) TL(1);
 
@@ -391,10 +395,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         // by the depth of the ring (the weights of the next unit stream in while this one waits on a dependency)
         if (lane == 0) {
             uint32_t seq = 0;
-            for (int v = blockIdx.x; v < geo.U; v += G) {
-                Unit u;
-                decode_unit(p, geo, v, u);
-                const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            for (int ui = 0; ui < n_units; ++ui) {
+                const Unit u = s.units[ui];
+                const int rows_u = unit_rows(s, u, ui == 0, have_plan);
             const int np = passes_of(rows_u);
                 for (int pass = 0; pass < np; ++pass)
                     for (int kb = 0; kb < u.nkb; ++kb, ++seq) {
@@ -415,10 +418,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                                        ((uint32_t)(kBlockM >> 4) << 24);
             uint32_t seq = 0;
             int iter = 0;
-            for (int v = blockIdx.x; v < geo.U; v += G) {
-                Unit u;
-                decode_unit(p, geo, v, u);
-                const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            for (int ui = 0; ui < n_units; ++ui) {
+                const Unit u = s.units[ui];
+                const int rows_u = unit_rows(s, u, ui == 0, have_plan);
             const int np = passes_of(rows_u);
                 for (int pass = 0; pass < np; ++pass, ++iter) {
                     const int as = iter & 1;
@@ -429,6 +431,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                         const int stage = (int)(seq % (uint32_t)kStages);
                         mbar_wait_bounded(&s.full_bar[stage], (seq / (uint32_t)kStages) & 1u);
                         tc_fence_after();
+                        if (kTL && tl && iter == 0 && kb < 10) tl[19 + kb] = gtime();      // bring-up: stage arrival times, first unit
                         const uint64_t a_desc = sw128_desc(sA + stage * kStageA);
                         const uint64_t b_desc = sw128_desc(sB + stage * kStageB);
 #pragma unroll
@@ -519,10 +522,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         }
         const int R = E > 0 ? s.group_start[E] : 0;      // routed rows (= N*K)
         int iter = 0;
-        for (int v = blockIdx.x; v < geo.U; v += G) {
-            Unit u;
-            decode_unit(p, geo, v, u);
-            const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+        for (int ui = 0; ui < n_units; ++ui) {
+            const Unit u = s.units[ui];
+            const int rows_u = unit_rows(s, u, ui == 0, have_plan);
             const int np = passes_of(rows_u);
             for (int pass = 0; pass < np; ++pass, ++iter) {
                 const int as = iter & 1;
@@ -599,31 +601,30 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         // units.  Lane l of gather warp w copies 16-byte chunk (l & 7) of tile rows 32w + 4j + (l >> 3), j = 0..7.
         const int gw = warp - 6;
         const int chunk = lane & 7;
+        if (kTL && tl && gw == 0 && lane == 0) tl[29] = gtime();
         pdl_wait_prior();
+        if (kTL && tl && gw == 0 && lane == 0) tl[30] = gtime();
         uint32_t seq = 0;
         const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(p.x);
-        for (int v = blockIdx.x; v < geo.U; v += G) {
-            Unit u;
-            decode_unit(p, geo, v, u);
-            const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+        for (int ui = 0; ui < n_units; ++ui) {
+            const Unit u = s.units[ui];
+            const int rows_u = unit_rows(s, u, ui == 0, have_plan);
             const int np = passes_of(rows_u);
             if (u.type != kG1Routed) { seq += (uint32_t)(np * u.nkb); continue; }
             for (int pass = 0; pass < np; ++pass) {
                 const __nv_bfloat16* src[8];
                 uint32_t dst_off[8];
+                // the CTA's first 128 rows come from the fast path (the full plan may still be in the making)
+                const bool fast = ui == 0 && pass == 0;
+                if (!fast && !have_plan) {
+                    if (ld_acquire_cta(&s.plan_ready) == 0) wait_plan_slow(&s.plan_ready);
+                    have_plan = true;
+                }
+                const uint16_t* toks = fast ? s.own_tok : s.src_tok + s.group_start[u.g] + pass * kBlockM;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int rj = gw * 32 + j * 4 + (lane >> 3);
-                    const int row = pass * kBlockM + rj;
-                    int tok = -1;
-                    if (row < rows_u) {
-                        if (v == (int)blockIdx.x && pass == 0) {
-                            tok = s.own_tok[rj];                   // fast path: the full plan may still be in the making
-                        } else {
-                            if (!have_plan) { if (ld_acquire_cta(&s.plan_ready) == 0) wait_plan_slow(&s.plan_ready); have_plan = true; }
-                            tok = s.src_tok[s.group_start[u.g] + row];
-                        }
-                    }
+                    const int tok = pass * kBlockM + rj < rows_u ? (int)toks[rj] : -1;
                     src[j] = tok >= 0 ? xb + (int64_t)tok * H + chunk * 8 : nullptr;
                     dst_off[j] = (uint32_t)(rj * 128 + ((chunk ^ (rj & 7)) << 4));
                 }
@@ -635,6 +636,11 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                     for (int j = 0; j < 8; ++j)
                         if (src[j] != nullptr) cp_async_16(dst + dst_off[j], src[j] + kb * kBlockK);
                     cp_async_arrive_noinc(&s.full_bar[stage]);
+                    if (kTL && tl && gw == 0 && lane == 0 && seq == 0) {          // bring-up: A-row gather latency of the first k-block
+                        tl[8] = gtime();
+                        asm volatile("cp.async.wait_all;" ::: "memory");
+                        tl[31] = gtime();
+                    }
                 }
             }
         }
@@ -646,10 +652,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             pdl_wait_prior();
             uint32_t seq = 0;
             const long long t_begin = clock64();
-            for (int v = blockIdx.x; v < geo.U; v += G) {
-                Unit u;
-                decode_unit(p, geo, v, u);
-                const int rows_u = unit_rows(s, u, v == (int)blockIdx.x, have_plan);
+            for (int ui = 0; ui < n_units; ++ui) {
+                const Unit u = s.units[ui];
+                const int rows_u = unit_rows(s, u, ui == 0, have_plan);
             const int np = passes_of(rows_u);
                 if (u.type == kG1Routed) { seq += (uint32_t)(np * u.nkb); continue; }
                 if (u.type >= kG2Routed) {
@@ -784,6 +789,42 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     }
 }
 
+
+// ---- bring-up timeline (env I64B_DEBUG_TIMELINE): two halves of [256 CTAs][32 slots] globaltimer stamps
+constexpr int kTlInts = 256 * 32;
+long long* g_tl = nullptr;
+int g_tl_launch = 0;
+void tl_print(const long long* d_half, int grid, long long g0_in, const char* what) {
+    static long long h[kTlInts];
+    cudaMemcpy(h, d_half, sizeof(h), cudaMemcpyDeviceToHost);
+    long long g0 = g0_in;
+    if (g0 == 0) { g0 = h[0]; for (int b = 0; b < grid; ++b) if (h[b * 32] && h[b * 32] < g0) g0 = h[b * 32]; }
+    static const char* names[18] = {"start", "ids", "table", "fast", "fp0", "fpA", "fpB", "g2rA", "g2sA", "mma0",
+                                    "epi0", "st0", "pub1", "mma1", "pub2", "cwait", "cgo", "end"};
+    static const int order[18] = {0, 3, 2, 1, 16, 17, 18, 4, 5, 6, 14, 15, 7, 9, 10, 11, 12, 13};
+    fprintf(stderr, "[i64b fused timeline: %s] ns since t0:\n  %-8s", what, "");
+    for (int j = 0; j < 18; ++j) fprintf(stderr, " %6s", names[j]);
+    fprintf(stderr, "\n");
+    for (int b = 0; b < grid; b += 9) {
+        fprintf(stderr, "  cta %3d:", b);
+        for (int j = 0; j < 18; ++j) { const long long v = h[b * 32 + order[j]]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
+        fprintf(stderr, "\n");
+    }
+    long long mx[32], mn[32];
+    for (int j = 0; j < 32; ++j) { mx[j] = -(1ll << 60); mn[j] = 1ll << 60; }
+    for (int b = 0; b < grid; ++b) for (int j = 0; j < 32; ++j) if (h[b * 32 + j]) { const long long v = h[b * 32 + j] - g0; if (v > mx[j]) mx[j] = v; if (v < mn[j]) mn[j] = v; }
+    fprintf(stderr, "  min    :");
+    for (int j = 0; j < 18; ++j) fprintf(stderr, " %6lld", mn[order[j]]);
+    fprintf(stderr, "\n  max    :");
+    for (int j = 0; j < 18; ++j) fprintf(stderr, " %6lld", mx[order[j]]);
+    fprintf(stderr, "\n  first unit: gather kb0 issued, landed | k-block arrival (full barrier passed) kb = 0..9, before / after griddepcontrol.wait (gather warp 0):\n");
+    for (int b = 0; b < grid; b += 18) {
+        fprintf(stderr, "  cta %3d: %6lld %6lld |", b, h[b * 32 + 8] ? h[b * 32 + 8] - g0 : -1, h[b * 32 + 31] ? h[b * 32 + 31] - g0 : -1);
+        for (int j = 19; j < 31; ++j) { const long long v = h[b * 32 + j]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
+        fprintf(stderr, "\n");
+    }
+}
+
 constexpr int kSmemBytes = 1024 + kStages * (kStageA + kStageB) + (int)sizeof(Smem) + 256;
 
 }  // namespace
@@ -804,52 +845,55 @@ int i64b_launch_fused(const CUtensorMap& tm_x, const CUtensorMap& tm_w13, const 
                       cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
-        I64B_CUDA(cudaFuncSetAttribute(i64b_fused_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        I64B_CUDA(cudaFuncSetAttribute(i64b_fused_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        I64B_CUDA(cudaFuncSetAttribute(i64b_fused_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         configured = true;
     }
     const int grid = i64b_num_sms();
     static const bool dbg_tl = getenv("I64B_DEBUG_TIMELINE") != nullptr;
+    I64bFusedParams q = p;
+    q.geo = make_geo(p);
     if (!dbg_tl) {
-        I64B_CUDA(i64b_launch(i64b_fused_layer_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
-                              tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, p));
+        I64B_CUDA(i64b_launch(i64b_fused_layer_kernel<false>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
+                              tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, q));
         i64b_count_launch(1);
         return I64B_OK;
     }
     // ---- bring-up instrumentation only (allocates + synchronises; never active unless the env asks for it)
-    I64bFusedParams q = p;
-    static long long* d_tl = nullptr;
-    if (d_tl == nullptr) cudaMalloc(&d_tl, 256 * 32 * sizeof(long long));
+    if (g_tl == nullptr) { cudaMalloc(&g_tl, 2 * kTlInts * sizeof(long long)); cudaMemset(g_tl, 0, 2 * kTlInts * sizeof(long long)); }
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(stream, &cs);
-    if (cs == cudaStreamCaptureStatusNone) { cudaMemsetAsync(d_tl, 0, 256 * 32 * sizeof(long long), stream); q.timeline = d_tl; }
-    I64B_CUDA(i64b_launch(i64b_fused_layer_kernel, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
+    if (cs == cudaStreamCaptureStatusNone) {
+        cudaMemsetAsync(g_tl, 0, kTlInts * sizeof(long long), stream);
+        q.timeline = g_tl;
+    } else {
+        // inside a graph: consecutive launches alternate between the two halves, so after a replay the halves hold the
+        // last two layers of the step (i64b_debug_timeline_dump prints them on one time axis)
+        q.timeline = g_tl + (size_t)(g_tl_launch++ & 1) * kTlInts;
+    }
+    I64B_CUDA(i64b_launch(i64b_fused_layer_kernel<true>, dim3(grid), dim3(kThreads), kSmemBytes, stream, tm_x, tm_w13,
                           tm_inter_r, tm_inter_s, tm_w2r, tm_w2s, q));
     i64b_count_launch(1);
     if (cs == cudaStreamCaptureStatusNone) {
         static int printed = 0;
-        static long long h[256 * 32];
         cudaStreamSynchronize(stream);
-        cudaMemcpy(h, d_tl, sizeof(h), cudaMemcpyDeviceToHost);
-        if (printed++ >= 2 && printed <= 6) {
-            long long g0 = h[0];
-            for (int b = 0; b < grid; ++b) if (h[b * 32] && h[b * 32] < g0) g0 = h[b * 32];
-            static const char* names[18] = {"start", "ids", "table", "fast", "fp0", "fpA", "fpB", "g2rA", "g2sA", "mma0",
-                                            "epi0", "st0", "pub1", "mma1", "pub2", "cwait", "cgo", "end"};
-            static const int order[18] = {0, 3, 2, 1, 16, 17, 18, 4, 5, 6, 14, 15, 7, 9, 10, 11, 12, 13};
-            fprintf(stderr, "[i64b fused timeline] ns since first CTA start:\n  %-8s", "");
-            for (int j = 0; j < 18; ++j) fprintf(stderr, " %6s", names[j]);
-            fprintf(stderr, "\n");
-            for (int b = 0; b < grid; b += 9) {
-                fprintf(stderr, "  cta %3d:", b);
-                for (int j = 0; j < 18; ++j) { const long long v = h[b * 32 + order[j]]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
-                fprintf(stderr, "\n");
-            }
-            long long mx[32] = {0};
-            for (int b = 0; b < grid; ++b) for (int j = 0; j < 32; ++j) { const long long v = h[b * 32 + j] ? h[b * 32 + j] - g0 : 0; if (v > mx[j]) mx[j] = v; }
-            fprintf(stderr, "  max    :");
-            for (int j = 0; j < 18; ++j) fprintf(stderr, " %6lld", mx[order[j]]);
-            fprintf(stderr, "\n");
-        }
+        if (printed++ >= 2 && printed <= 6) tl_print(g_tl, grid, 0, "eager launch");
     }
     return I64B_OK;
+}
+
+// Bring-up only: after a graph replay under I64B_DEBUG_TIMELINE, print the last two layers of the step on one time axis.
+extern "C" int i64b_debug_timeline_dump(void) {
+    if (g_tl == nullptr) return 0;
+    cudaDeviceSynchronize();
+    static long long h[2 * kTlInts];
+    cudaMemcpy(h, g_tl, sizeof(h), cudaMemcpyDeviceToHost);
+    const int grid = i64b_num_sms();
+    long long m[2] = {1ll << 62, 1ll << 62};
+    for (int half = 0; half < 2; ++half)
+        for (int b = 0; b < grid; ++b) { const long long v = h[half * kTlInts + b * 32]; if (v && v < m[half]) m[half] = v; }
+    const int first = m[0] <= m[1] ? 0 : 1;
+    tl_print(g_tl + (size_t)first * kTlInts, grid, m[first], "graph: second-to-last layer");
+    tl_print(g_tl + (size_t)(1 - first) * kTlInts, grid, m[first], "graph: last layer (same t0)");
+    return 1;
 }

@@ -13,6 +13,15 @@
 #define I64B_SYNC_G1(i) ((4 + (i)) * I64B_SYNC_STRIDE)
 #define I64B_SYNC_INTS ((4 + I64B_FUSED_MAX_GROUPS) * I64B_SYNC_STRIDE)
 
+// static work list of a launch (a pure function of the shapes; computed on the host)
+struct I64bFusedGeo {
+    int nkb_h;                 // k-blocks over H
+    int nt1r, U1r;             // GEMM1 routed: n-tiles per expert, units
+    int mts, nt1s, U1;         // shared m-tiles, GEMM1 shared n-tiles, total GEMM1 units
+    int nt2, U2r, slabs, U2;   // GEMM2 n-tiles, routed units, shared K slabs, total GEMM2 units
+    int U;
+};
+
 struct I64bFusedParams {
     const void* x;              // [N, H] bf16
     const int64_t* token_ids;   // [N] or nullptr
@@ -27,7 +36,8 @@ struct I64bFusedParams {
     int* sync;                  // I64B_SYNC_INTS ints
     const uint8_t* next_w;      // next layer's packed weights (constants) to pull into L2 while this layer runs, or nullptr
     uint64_t next_w_bytes;
-    int32_t prefetch_mode;      // 1: a spare thread at kernel entry; 2: the weight thread once its own stream is issued
+    int32_t prefetch_mode;
+    I64bFusedGeo geo;           // filled by i64b_launch_fused      // 1: a spare thread at kernel entry; 2: the weight thread once its own stream is issued
     long long* timeline;        // bring-up only: [grid, 16] ns stamps (env I64B_DEBUG_TIMELINE)
     int32_t *tap_routes, *tap_dest, *tap_scatter, *tap_counts, *tap_offsets;   // reference-convention plan outputs
 };
