@@ -33,7 +33,7 @@ constexpr int kBn1 = 64;               // intermediate columns per GEMM1 unit
 constexpr int kBlockK = 64;            // bf16 elements per 128-byte swizzle row
 constexpr int kStageA = kBlockM * 128;
 constexpr int kStageB = kNMma * 128;
-constexpr int kStages = 6;
+constexpr int kStages = 5;
 constexpr int kSlabK = 512;            // split-K slab of the shared down-projection
 constexpr uint32_t kTmemCols = 2 * kNMma;
 constexpr int kMaxTok = I64B_FUSED_MAX_TOKENS;
