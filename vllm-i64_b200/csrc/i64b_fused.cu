@@ -34,6 +34,8 @@ constexpr int kBlockK = 64;            // bf16 elements per 128-byte swizzle row
 constexpr int kStageA = kBlockM * 128;
 constexpr int kStageB = kNMma * 128;
 constexpr int kStages = 5;
+constexpr int kStgPitch = 144;       // bytes per staged row: 128 + 16 (conflict-free 16-byte writes by row, reads by line)
+constexpr int kStgBytes = 4 * 32 * kStgPitch;   // one 32-row x 128-byte staging tile per epilogue warp
 constexpr int kSlabK = 512;            // split-K slab of the shared down-projection
 constexpr uint32_t kTmemCols = 2 * kNMma;
 constexpr int kMaxTok = I64B_FUSED_MAX_TOKENS;
@@ -254,7 +256,8 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = base;
     uint8_t* sB = base + kStages * kStageA;
-    Smem& s = *reinterpret_cast<Smem*>(sB + kStages * kStageB);
+    uint8_t* sStg = sB + kStages * kStageB;
+    Smem& s = *reinterpret_cast<Smem*>(sStg + kStgBytes);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int E = p.num_experts, K = p.top_k, N = p.n, H = p.hidden, bins = K * E, G = gridDim.x;
@@ -535,36 +538,49 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                 const bool routed = u.type == kG1Routed || u.type == kG2Routed;
                 const int row = (routed ? pass : u.m_t) * kBlockM + r;      // row inside the group
                 const bool valid = row < (routed ? s.group_rows[u.g] : N);
+                // Output rows leave through a per-warp staging tile: a thread holds one ROW of the accumulator, so direct
+                // stores would touch 32 different lines per instruction; staged, every quarter warp writes one full
+                // 128-byte line (4 lines per instruction).
+                uint8_t* stg = sStg + q * (32 * kStgPitch);
+                const int rows_lim = (routed ? s.group_rows[u.g] : N) - ((routed ? pass : u.m_t) * kBlockM + q * 32);   // valid rows of this warp
+                const int seg = lane & 7, rsub = lane >> 3;
+                (void)valid;
                 if (u.type <= kG1Shared) {
                     const int n_out = routed ? p.expert_inter : p.shared_inter;
-                    __nv_bfloat16* orow = routed
-                        ? reinterpret_cast<__nv_bfloat16*>(p.inter_r) + (int64_t)(s.group_start[u.g] + row) * p.expert_inter
-                        : reinterpret_cast<__nv_bfloat16*>(p.inter_s) + (int64_t)row * p.shared_inter;
+                    const int col_t = u.n_t * kBn1;                         // first intermediate column of the tile
 #pragma unroll 1
                     for (int c = 0; c < kBn1 / 32; ++c) {
-                        const int col0 = u.n_t * kBn1 + c * 32;
-                        if (col0 >= n_out) break;
+                        if (col_t + c * 32 >= n_out) break;
                         uint32_t gr[32], ur[32];
                         tmem_ld_32x32(taddr + c * 32, gr);
                         tmem_ld_32x32(taddr + kBn1 + c * 32, ur);
                         tmem_ld_wait();
-                        uint32_t o[16];
 #pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            o[j] = pack_bf16x2(silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]),
-                                               silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]));
-                        if (valid) {
+                        for (int v4 = 0; v4 < 4; ++v4) {
+                            uint32_t o[4];
 #pragma unroll
-                            for (int v4 = 0; v4 < 4; ++v4)
-                                if (col0 + v4 * 8 < n_out)
-                                    *reinterpret_cast<int4*>(orow + col0 + v4 * 8) =
-                                        make_int4(o[4 * v4], o[4 * v4 + 1], o[4 * v4 + 2], o[4 * v4 + 3]);
+                            for (int j = 0; j < 4; ++j)
+                                o[j] = pack_bf16x2(silu_f32(__uint_as_float(gr[8 * v4 + 2 * j])) * __uint_as_float(ur[8 * v4 + 2 * j]),
+                                                   silu_f32(__uint_as_float(gr[8 * v4 + 2 * j + 1])) * __uint_as_float(ur[8 * v4 + 2 * j + 1]));
+                            *reinterpret_cast<int4*>(stg + lane * kStgPitch + c * 64 + v4 * 16) = make_int4(o[0], o[1], o[2], o[3]);
                         }
                     }
+                    __syncwarp();
+                    // row pitch and first byte of the tile's columns in the intermediate buffer
+                    const int64_t pitch = (int64_t)n_out * 2;
+                    uint8_t* gbase = (routed ? reinterpret_cast<uint8_t*>(p.inter_r) + (int64_t)(s.group_start[u.g] + pass * kBlockM + q * 32) * pitch
+                                             : reinterpret_cast<uint8_t*>(p.inter_s) + (int64_t)(u.m_t * kBlockM + q * 32) * pitch) + (int64_t)col_t * 2;
+                    const bool seg_ok = col_t + seg * 8 < n_out;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int rl = rsub + 4 * i;
+                        if (rl < rows_lim && seg_ok)
+                            *reinterpret_cast<int4*>(gbase + rl * pitch + seg * 16) = *reinterpret_cast<const int4*>(stg + rl * kStgPitch + seg * 16);
+                    }
+                    __syncwarp();
                 } else {
-                    const int64_t yrow = routed ? (int64_t)s.group_start[u.g] + row
-                                                : (int64_t)R + (int64_t)u.slab * N + row;
-                    float* orow = p.y + yrow * H;
+                    const int64_t yrow0 = (routed ? (int64_t)s.group_start[u.g] + pass * kBlockM
+                                                  : (int64_t)R + (int64_t)u.slab * N + u.m_t * kBlockM) + q * 32;
 #pragma unroll 1
                     for (int c = 0; c < kNMma / 32; ++c) {
                         const int col0 = u.n_t * kNMma + c * 32;
@@ -572,13 +588,20 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                         uint32_t ar[32];
                         tmem_ld_32x32(taddr + c * 32, ar);
                         tmem_ld_wait();
-                        if (valid) {
 #pragma unroll
-                            for (int v4 = 0; v4 < 8; ++v4)
-                                if (col0 + v4 * 4 < H)
-                                    *reinterpret_cast<int4*>(orow + col0 + v4 * 4) =
-                                        make_int4(ar[4 * v4], ar[4 * v4 + 1], ar[4 * v4 + 2], ar[4 * v4 + 3]);
+                        for (int v4 = 0; v4 < 8; ++v4)
+                            *reinterpret_cast<int4*>(stg + lane * kStgPitch + v4 * 16) =
+                                make_int4(ar[4 * v4], ar[4 * v4 + 1], ar[4 * v4 + 2], ar[4 * v4 + 3]);
+                        __syncwarp();
+                        float* gbase = p.y + yrow0 * H + col0;
+                        const bool seg_ok = col0 + seg * 4 < H;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int rl = rsub + 4 * i;
+                            if (rl < rows_lim && seg_ok)
+                                *reinterpret_cast<int4*>(gbase + (int64_t)rl * H + seg * 4) = *reinterpret_cast<const int4*>(stg + rl * kStgPitch + seg * 16);
                         }
+                        __syncwarp();
                     }
                 }
                 tc_fence_before();
@@ -825,7 +848,7 @@ void tl_print(const long long* d_half, int grid, long long g0_in, const char* wh
     }
 }
 
-constexpr int kSmemBytes = 1024 + kStages * (kStageA + kStageB) + (int)sizeof(Smem) + 256;
+constexpr int kSmemBytes = 1024 + kStages * (kStageA + kStageB) + kStgBytes + (int)sizeof(Smem) + 256;
 
 }  // namespace
 
