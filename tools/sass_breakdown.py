@@ -7,7 +7,15 @@ subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=d, check
 cub = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
 txt = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cub)], capture_output=True, text=True).stdout
 cur, cnt = None, collections.Counter()
+only = sys.argv[4] if len(sys.argv) > 4 else None      # substring of the function (section) name to keep
+keep = True
 for line in txt.splitlines():
+    ms = re.match(r"\s*\.section\s+\.text\.(\S+?),", line)
+    if ms:
+        keep = only is None or only in ms.group(1)
+        continue
+    if not keep:
+        continue
     m = re.search(r'//## File "([^"]+)", line (\d+)', line)
     if m:
         cur = (m.group(1).split("/")[-1], int(m.group(2)))

@@ -163,8 +163,10 @@ __device__ __forceinline__ uint32_t ld_acquire_cta(const uint32_t* p) {
 __device__ __forceinline__ void wait_stage_owned(const uint32_t* b_seq, uint32_t seq) {
     if (ld_acquire_cta(b_seq) > seq) return;
     const long long t0 = clock64();
-    while (ld_acquire_cta(b_seq) <= seq)
+    while (ld_acquire_cta(b_seq) <= seq) {
+        __nanosleep(40);                  // four gather warps spin here: keep them off the issue slots of the epilogue warps
         if (clock64() - t0 > 4000000000ll) __trap();
+    }
 }
 __device__ __noinline__ void wait_plan_slow(const uint32_t* flag) {
     const long long t0 = clock64();
