@@ -36,6 +36,7 @@ constexpr int kStageB = kNMma * 128;
 constexpr int kStages = 5;
 constexpr int kStgPitch = 144;       // bytes per staged row: 128 + 16 (conflict-free 16-byte writes by row, reads by line)
 constexpr int kStgBytes = 4 * 32 * kStgPitch;   // one 32-row x 128-byte staging tile per epilogue warp
+constexpr int kMaxSlabs = 8;          // split-K slabs of the shared down-projection (shared_inter <= 4096)
 constexpr int kSlabK = 512;            // split-K slab of the shared down-projection
 constexpr uint32_t kTmemCols = 2 * kNMma;
 constexpr int kMaxTok = I64B_FUSED_MAX_TOKENS;
@@ -733,15 +734,23 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
 #pragma unroll
             for (int k = 0; k < I64B_MAX_TOPK; ++k)
                 if (k < K) yk[k] = __ldcg(reinterpret_cast<const float4*>(p.y + (int64_t)s.dest_row[k][t] * H) + c);
+            // the slab rows are loaded four at a time before they are added (a load-add loop would serialise one L2
+            // round trip per slab; a full unroll costs cold code); the sum keeps the slab order
             float4 sh = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (geo.slabs > 0) {
-                sh = __ldcg(reinterpret_cast<const float4*>(p.y + ((int64_t)R + t) * H) + c);
 #pragma unroll 1
-                for (int sl = 1; sl < geo.slabs; ++sl) {    // split-K slabs of the shared down-projection, fixed order
-                    const float4 y = __ldcg(reinterpret_cast<const float4*>(p.y + ((int64_t)R + (int64_t)sl * N + t) * H) + c);
-                    sh.x = __fadd_rn(sh.x, y.x); sh.y = __fadd_rn(sh.y, y.y);
-                    sh.z = __fadd_rn(sh.z, y.z); sh.w = __fadd_rn(sh.w, y.w);
-                }
+            for (int s0 = 0; s0 < geo.slabs; s0 += 4) {
+                float4 ys[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (s0 + j < geo.slabs)
+                        ys[j] = __ldcg(reinterpret_cast<const float4*>(p.y + ((int64_t)R + (int64_t)(s0 + j) * N + t) * H) + c);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (s0 + j < geo.slabs) {
+                        if (s0 + j == 0) { sh = ys[0]; continue; }
+                        sh.x = __fadd_rn(sh.x, ys[j].x); sh.y = __fadd_rn(sh.y, ys[j].y);
+                        sh.z = __fadd_rn(sh.z, ys[j].z); sh.w = __fadd_rn(sh.w, ys[j].w);
+                    }
             }
             if (E > 0) {
 #pragma unroll
@@ -784,14 +793,11 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
 #pragma unroll 1
         for (int i = threadIdx.x; i < items; i += 2 * kThreads) {
             const int i1 = i + kThreads;
-            if (i1 < items) {
-                const float4 o0 = combine_item(i);
-                const float4 o1 = combine_item(i1);
-                store_item(i, o0);
-                store_item(i1, o1);
-            } else {
-                store_item(i, combine_item(i));
-            }
+            const bool two = i1 < items;
+            const float4 o0 = combine_item(i);
+            const float4 o1 = combine_item(two ? i1 : i);
+            store_item(i, o0);
+            if (two) store_item(i1, o1);
         }
     }
     }
@@ -861,6 +867,7 @@ int i64b_fused_supported(int n, int hidden, int expert_inter, int shared_inter, 
     if (shared_inter % 16 != 0) return 0;
     if (num_experts + (n + kBlockM - 1) / kBlockM > I64B_FUSED_MAX_GROUPS) return 0;
     if ((int64_t)n * top_k >= 65536) return 0;             // uint16 destination rows
+    if (shared_inter > kMaxSlabs * kSlabK) return 0;
     static_assert(kSmemBytes <= 232448, "shared memory budget");
     return 1;
 }
