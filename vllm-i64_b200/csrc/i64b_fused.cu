@@ -85,25 +85,30 @@ static Geo make_geo(const I64bFusedParams& p) {
     g.slabs = p.shared_inter > 0 ? (p.shared_inter + kSlabK - 1) / kSlabK : 0;
     g.U2 = g.U2r + g.mts * g.nt2 * g.slabs;
     g.U = g.U1 + g.U2;
+    auto magic = [](int d) { return d <= 1 ? 0u : (unsigned)((0x100000000ull + (unsigned)d - 1) / (unsigned)d); };
+    g.m_nt1r = magic(g.nt1r); g.m_nt1s = magic(g.nt1s); g.m_nt2 = magic(g.nt2); g.m_slabs = magic(g.slabs);
     return g;
 }
 
+// v / d for v * d < 2^32 with m = ceil(2^32 / d) (exact: the unit indices are small); d <= 1 has m == 0
+__device__ __forceinline__ int fast_div(int v, unsigned m) { return m == 0 ? v : (int)__umulhi((unsigned)v, m); }
 __device__ __noinline__ void decode_unit(const I64bFusedParams& p, const Geo& geo, int v, Unit& u) {
     u.m_t = 0; u.slab = 0;
     if (v < geo.U1r) {
-        u.type = kG1Routed; u.g = v / geo.nt1r; u.n_t = v % geo.nt1r; u.nkb = geo.nkb_h;
+        u.type = kG1Routed; u.g = fast_div(v, geo.m_nt1r); u.n_t = v - u.g * geo.nt1r; u.nkb = geo.nkb_h;
     } else if (v < geo.U1) {
         const int w = v - geo.U1r;
-        u.type = kG1Shared; u.g = p.num_experts; u.m_t = w / geo.nt1s; u.n_t = w % geo.nt1s; u.nkb = geo.nkb_h;
+        u.type = kG1Shared; u.g = p.num_experts; u.m_t = fast_div(w, geo.m_nt1s); u.n_t = w - u.m_t * geo.nt1s; u.nkb = geo.nkb_h;
     } else if (v < geo.U1 + geo.U2r) {
         const int w = v - geo.U1;
-        u.type = kG2Routed; u.g = w / geo.nt2; u.n_t = w % geo.nt2;
+        u.type = kG2Routed; u.g = fast_div(w, geo.m_nt2); u.n_t = w - u.g * geo.nt2;
         u.nkb = (p.expert_inter + kBlockK - 1) / kBlockK;
     } else {
         int w = v - geo.U1 - geo.U2r;
         u.type = kG2Shared; u.g = p.num_experts;
-        u.slab = w % geo.slabs; w /= geo.slabs;
-        u.n_t = w % geo.nt2; u.m_t = w / geo.nt2;
+        const int q = fast_div(w, geo.m_slabs);
+        u.slab = w - q * geo.slabs;
+        u.m_t = fast_div(q, geo.m_nt2); u.n_t = q - u.m_t * geo.nt2;
         const int krem = p.shared_inter - u.slab * kSlabK;
         u.nkb = ((krem < kSlabK ? krem : kSlabK) + kBlockK - 1) / kBlockK;
     }
@@ -276,7 +281,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
     };
 
     int own_e = -1;              // expert of the CTA's first unit when that is a routed GEMM1 unit
-    if ((int)blockIdx.x < geo.U1r) own_e = (int)blockIdx.x / geo.nt1r;
+    if ((int)blockIdx.x < geo.U1r) own_e = fast_div((int)blockIdx.x, geo.m_nt1r);
     int pre_issued = 0;          // weight stages the TMA thread put in flight before the plan (first unit, pass 0)
     if (warp == 0) {
         Unit u0;
@@ -287,18 +292,14 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             for (int i = 0; i < kStages; ++i) { mbar_init(&s.full_bar[i], 1 + kGatherThreads); mbar_init(&s.empty_bar[i], 1); }
             for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull_bar[i], 1); mbar_init(&s.tempty_bar[i], 4); }
             fence_barrier_init();
-            // half a ring of weights goes out at once (also under the previous kernel's tail: weights are constants)
+            // half a ring of weights goes out at once (also under the previous kernel's tail: weights are constants);
+            // the rest follows from the role loop, AFTER the role barrier: this thread used to be the last one there
+            // (0.25-0.5 us per stage issued), holding back the activation rows of the first k-block by ~0.8 us
             if ((int)blockIdx.x < geo.U) {
                 decode_unit(p, geo, blockIdx.x, u0);
-                pre_issued = u0.nkb < kStages ? u0.nkb : kStages;
-                for (int kb = 0; kb < pre_issued && kb < kStages / 2; ++kb) issue_b(u0, kb, kb);
+                pre_issued = u0.nkb < kStages / 2 ? u0.nkb : kStages / 2;
+                for (int kb = 0; kb < pre_issued; ++kb) issue_b(u0, kb, kb);
             }
-        }
-        // ... the other half only once the plan's dependent loads (ids, then table) are in the memory system: queued
-        // behind ~100 KB of weight requests per SM they take microseconds instead of a few hundred nanoseconds
-        named_bar_sync(3, 32 + kPlanWarps * 32);
-        if (lane == 0) {
-            for (int kb = kStages / 2; kb < pre_issued; ++kb) issue_b(u0, kb, kb);
             s.b_seq = (uint32_t)pre_issued;                       // published by the __syncthreads below
             s.plan_ready = 0;
         }
@@ -331,7 +332,6 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                     if (k < K && t < N) ev0[k] = p.token_ids ? (int)__ldg(p.table + (int64_t)k * p.vocab + c) : (k % E);
                 }
             }
-            named_bar_arrive(3, 32 + kPT);                         // table loads are on their way: weights may start
 #pragma unroll
             for (int k = 0; k < I64B_MAX_TOPK; ++k)
                 if (k < K && pt < N) s.expert[k][pt] = (uint8_t)min(ev0[k], E - 1);
@@ -386,6 +386,11 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                 }
             }
         }
+    }
+    if (kTL && tl) {                     // bring-up: who is last at the role barrier
+        if (threadIdx.x == 0) tl[29] = gtime();
+        if (threadIdx.x == 32) tl[30] = gtime();
+        if (threadIdx.x == 64) tl[31] = gtime();
     }
     tc_fence_before();
     __syncthreads();
@@ -627,9 +632,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
         // units.  Lane l of gather warp w copies 16-byte chunk (l & 7) of tile rows 32w + 4j + (l >> 3), j = 0..7.
         const int gw = warp - 6;
         const int chunk = lane & 7;
-        if (kTL && tl && gw == 0 && lane == 0) tl[29] = gtime();
         pdl_wait_prior();
-        if (kTL && tl && gw == 0 && lane == 0) tl[30] = gtime();
         uint32_t seq = 0;
         const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(p.x);
         for (int ui = 0; ui < n_units; ++ui) {
@@ -665,7 +668,6 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
                     if (kTL && tl && gw == 0 && lane == 0 && seq == 0) {          // bring-up: A-row gather latency of the first k-block
                         tl[8] = gtime();
                         asm volatile("cp.async.wait_all;" ::: "memory");
-                        tl[31] = gtime();
                     }
                 }
             }
@@ -848,10 +850,10 @@ void tl_print(const long long* d_half, int grid, long long g0_in, const char* wh
     for (int j = 0; j < 18; ++j) fprintf(stderr, " %6lld", mn[order[j]]);
     fprintf(stderr, "\n  max    :");
     for (int j = 0; j < 18; ++j) fprintf(stderr, " %6lld", mx[order[j]]);
-    fprintf(stderr, "\n  first unit: gather kb0 issued, landed | k-block arrival (full barrier passed) kb = 0..9, before / after griddepcontrol.wait (gather warp 0):\n");
+    fprintf(stderr, "\n  first unit: gather kb0 issued | k-block arrival (full barrier passed) kb = 0..9 | at the role barrier: weight warp, MMA warp, plan warps:\n");
     for (int b = 0; b < grid; b += 18) {
-        fprintf(stderr, "  cta %3d: %6lld %6lld |", b, h[b * 32 + 8] ? h[b * 32 + 8] - g0 : -1, h[b * 32 + 31] ? h[b * 32 + 31] - g0 : -1);
-        for (int j = 19; j < 31; ++j) { const long long v = h[b * 32 + j]; fprintf(stderr, " %6lld", v ? v - g0 : -1); }
+        fprintf(stderr, "  cta %3d: %6lld |", b, h[b * 32 + 8] ? h[b * 32 + 8] - g0 : -1);
+        for (int j = 19; j < 32; ++j) { const long long v = h[b * 32 + j]; fprintf(stderr, "%s %6lld", j == 29 ? " |" : "", v ? v - g0 : -1); }
         fprintf(stderr, "\n");
     }
 }

@@ -20,6 +20,7 @@ struct I64bFusedGeo {
     int mts, nt1s, U1;         // shared m-tiles, GEMM1 shared n-tiles, total GEMM1 units
     int nt2, U2r, slabs, U2;   // GEMM2 n-tiles, routed units, shared K slabs, total GEMM2 units
     int U;
+    unsigned m_nt1r, m_nt1s, m_nt2, m_slabs;   // ceil(2^32 / d) of the four divisors of the unit decode (0 for d <= 1)
 };
 
 struct I64bFusedParams {
