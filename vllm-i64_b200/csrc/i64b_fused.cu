@@ -62,6 +62,7 @@ struct Smem {
     uint16_t own_tok[kBlockM];
     int fast_cnt[kPlanWarps];
     int rows_first;
+    uint32_t roles_go;                                  // everybody but the weight warp is past the role barrier
     uint32_t plan_ready;                                // full plan published (release/acquire, CTA scope)
     Unit units[kMaxUnitsPerCta];                        // this CTA's units (static work list), decoded once by warp 1
     int n_units;
@@ -282,9 +283,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
 
     int own_e = -1;              // expert of the CTA's first unit when that is a routed GEMM1 unit
     if ((int)blockIdx.x < geo.U1r) own_e = fast_div((int)blockIdx.x, geo.m_nt1r);
-    int pre_issued = 0;          // weight stages the TMA thread put in flight before the plan (first unit, pass 0)
     if (warp == 0) {
-        Unit u0;
         if (lane == 0) {
             tma_prefetch_desc(&tm_w13); tma_prefetch_desc(&tm_w2r); tma_prefetch_desc(&tm_w2s);
             tma_prefetch_desc(&tm_inter_r); tma_prefetch_desc(&tm_inter_s);
@@ -292,18 +291,15 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             for (int i = 0; i < kStages; ++i) { mbar_init(&s.full_bar[i], 1 + kGatherThreads); mbar_init(&s.empty_bar[i], 1); }
             for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull_bar[i], 1); mbar_init(&s.tempty_bar[i], 4); }
             fence_barrier_init();
-            // half a ring of weights goes out at once (also under the previous kernel's tail: weights are constants);
-            // the rest follows from the role loop, AFTER the role barrier: this thread used to be the last one there
-            // (0.25-0.5 us per stage issued), holding back the activation rows of the first k-block by ~0.8 us
-            if ((int)blockIdx.x < geo.U) {
-                decode_unit(p, geo, blockIdx.x, u0);
-                pre_issued = u0.nkb < kStages / 2 ? u0.nkb : kStages / 2;
-                for (int kb = 0; kb < pre_issued; ++kb) issue_b(u0, kb, kb);
-            }
-            s.b_seq = (uint32_t)pre_issued;                       // published by the __syncthreads below
+            s.b_seq = 0;
             s.plan_ready = 0;
+            s.roles_go = 0;
+            __threadfence_block();
         }
-        pre_issued = __shfl_sync(0xffffffffu, pre_issued, 0);
+        __syncwarp();
+        // The weight warp only ARRIVES at the role barrier (its barriers and counters are ready) and goes on issuing:
+        // it used to be the last one there (0.25-0.5 us per stage issued), holding back everybody else's start.
+        named_bar_arrive(3, kThreads);
     } else if (warp == 1) {
         tmem_alloc<kTmemCols>(&s.tmem_ptr);
         // this CTA's units, decoded once (the role loops below read them from shared memory)
@@ -387,24 +383,39 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             }
         }
     }
-    if (kTL && tl) {                     // bring-up: who is last at the role barrier
+    if (kTL && tl) {                     // bring-up: arrival times at the role barrier
         if (threadIdx.x == 0) tl[29] = gtime();
         if (threadIdx.x == 32) tl[30] = gtime();
         if (threadIdx.x == 64) tl[31] = gtime();
     }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = s.tmem_ptr;
-    const int n_units = s.n_units;
+    uint32_t tmem_base = 0;
+    int n_units = 0;
+    if (warp != 0) {
+        tc_fence_before();
+        named_bar_sync(3, kThreads);
+        tc_fence_after();
+        tmem_base = s.tmem_ptr;
+        n_units = s.n_units;
+        if (threadIdx.x == 32) { st_release_cta(&s.roles_go, 1u); TL(1); }
+    }
     bool have_plan = false;
-    if (threadIdx.x == 0) TL(1);
 
     if (warp == 0) {
         if (lane == 1 && p.next_w != nullptr && p.prefetch_mode == 1) prefetch_next_weights(p, blockIdx.x, G);
         // ------------------------------------------------------------------ weight TMA: runs ahead of everything else
         // by the depth of the ring (the weights of the next unit stream in while this one waits on a dependency)
         if (lane == 0) {
+            // a ring of weights goes out at once (also under the previous kernel's tail: weights are constants) ...
+            int pre_issued = 0;
+            if ((int)blockIdx.x < geo.U) {
+                Unit u0;
+                decode_unit(p, geo, blockIdx.x, u0);
+                pre_issued = u0.nkb < kStages ? u0.nkb : kStages;
+                for (int kb = 0; kb < pre_issued; ++kb) { issue_b(u0, kb, kb); st_release_cta(&s.b_seq, (uint32_t)kb + 1); }
+            }
+            // ... then the unit table and the fast-path row count exist once the others are past the role barrier
+            if (ld_acquire_cta(&s.roles_go) == 0) wait_plan_slow(&s.roles_go);
+            n_units = s.n_units;
             uint32_t seq = 0;
             for (int ui = 0; ui < n_units; ++ui) {
                 const Unit u = s.units[ui];
