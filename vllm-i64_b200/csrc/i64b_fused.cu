@@ -495,7 +495,7 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             }
             named_bar_sync(1, 128);
             if (warp == 2 && lane == 0) TL(17);
-            const bool taps = blockIdx.x == 0 && p.tap_routes != nullptr;
+            const bool taps = (int)blockIdx.x == G - 1 && p.tap_routes != nullptr;   // a CTA whose epilogue warps have slack (last CTA: one late unit at most)
 #pragma unroll 1
             for (int e = pw4; e < E; e += 4) {
                 const uint32_t pat = (uint32_t)e * 0x01010101u;
