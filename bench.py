@@ -412,7 +412,7 @@ def main():
         _JSON_FD = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=device)
-        barrier = (lambda: None) if os.environ.get("I64B_BENCH_SKIP_BARRIER") == "1" else (lambda: dist.barrier())  # noqa: E731
+        barrier = lambda: dist.barrier()            # noqa: E731
     from vllm_i64 import _C
 
     H, N, L = wl["H"], wl["N"], wl["L"]

@@ -18,5 +18,4 @@ CUDA_VISIBLE_DEVICES=1 timeout 200 python bench.py $A > gpurun_out/d2_dev1.json 
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
 timeout 200 $TR --master-port 29541 bench.py --gpus 2 $A --no-ep > gpurun_out/d2_t2.json 2> gpurun_out/d2_t2.err; show gpurun_out/d2_t2.json
 NCCL_P2P_DISABLE=1 timeout 200 $TR --master-port 29542 bench.py --gpus 2 $A --no-ep > gpurun_out/d2_t2nop2p.json 2> gpurun_out/d2_t2nop2p.err; show gpurun_out/d2_t2nop2p.json
-I64B_BENCH_SKIP_BARRIER=1 timeout 200 $TR --master-port 29543 bench.py --gpus 2 $A --no-ep > gpurun_out/d2_t2nobar.json 2> gpurun_out/d2_t2nobar.err; show gpurun_out/d2_t2nobar.json
 timeout 300 $TR --master-port 29544 bench.py --gpus 2 $A > gpurun_out/d2_t2ep.json 2> gpurun_out/d2_t2ep.err; show gpurun_out/d2_t2ep.json
