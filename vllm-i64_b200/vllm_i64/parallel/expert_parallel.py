@@ -178,6 +178,16 @@ class EPTokenRoutedBlock:
         G, K, H = self.ep.ep_size, self.K, self.H
         if G > _C.EP_MAX_RANKS:
             raise ValueError(f"at most {_C.EP_MAX_RANKS} expert-parallel ranks")
+        if G > 1:
+            # The global plan indexes token t of rank r as r*n + t, and the id all-gather needs equal contributions:
+            # unequal batches would hang in the collective.  Setup is collective and synchronising anyway, so check
+            # here and fail on every rank with the same message (the engine pads decode batches to a common size).
+            nn = torch.tensor([n, -n], dtype=torch.int64, device=self.device)
+            dist.all_reduce(nn, op=dist.ReduceOp.MAX, group=self.ep.group)
+            n_max, n_min = int(nn[0]), -int(nn[1])
+            if n_max != n_min:
+                raise ValueError(f"expert-parallel ranks must bring the same number of tokens per step "
+                                 f"(min {n_min}, max {n_max}): pad the local batch to a common size")
         cap = G * n * K                                        # worst case: every assignment lands here (nothing dropped)
 
         def up(v):
