@@ -1,5 +1,6 @@
 """Expert-parallel block on GPUs (NCCL): world_size 1 always, 2 / 4 / 8 when the box has that many devices.  Every rank's output
 must match the single-GPU block on the same tokens (same kernels, so the match is tight) and the oracle."""
+import datetime
 import os
 import socket
 
@@ -17,6 +18,11 @@ if not torch.cuda.is_available():
     pytest.skip("CUDA device required", allow_module_level=True)
 
 
+# a collective that cannot complete aborts the worker after this long (NCCL watchdog) instead of leaving it on the GPU:
+# orphaned workers of a timed-out test once time-sliced every GPU of the box under the benches that followed
+_PG_TIMEOUT = datetime.timedelta(seconds=120)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
@@ -27,7 +33,7 @@ def _worker(rank, world, port, case, ret):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dev = torch.device("cuda", rank)
     torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=_PG_TIMEOUT)
     try:
         from vllm_i64 import _C
         from vllm_i64.parallel.expert_parallel import EPTokenRoutedBlock, init_expert_parallel
@@ -87,7 +93,7 @@ def _worker_unequal(rank, world, port, ret):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dev = torch.device("cuda", rank)
     torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=_PG_TIMEOUT)
     try:
         from vllm_i64 import _C
         from vllm_i64.parallel.expert_parallel import EPTokenRoutedBlock, init_expert_parallel
