@@ -79,3 +79,33 @@ def test_exchange_plan_is_stable_by_rank():
     t = torch.argsort(torch.from_numpy(dest), stable=True).numpy()
     np.testing.assert_array_equal(order, t)
     assert (np.diff(dest[order]) >= 0).all()
+
+
+def _worker_batches(rank, world, port, equal, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from vllm_i64.parallel.expert_parallel import check_equal_local_batches, init_expert_parallel
+        ep = init_expert_parallel()
+        try:
+            check_equal_local_batches(90 if equal else 87 + rank, ep, torch.device("cpu"))
+            ret[rank] = "ok"
+        except ValueError as exc:
+            ret[rank] = str(exc)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("equal", [True, False])
+def test_equal_local_batches_contract(equal):
+    """The peer-memory exchange needs the same token count on every rank; a mismatch must raise on EVERY rank (a rank
+    that alone walked into the id all-gather would hang: that is what a 700-token test split over 8 ranks once did)."""
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker_batches, args=(world, _free_port(), equal, ret), nprocs=world, join=True)
+    for r in range(world):
+        if equal:
+            assert ret[r] == "ok"
+        else:
+            assert "same number of tokens" in ret[r] and "min 87, max 88" in ret[r], ret[r]

@@ -50,6 +50,23 @@ def init_expert_parallel(ep_size: Optional[int] = None, group: Optional[dist.Pro
     return _EP
 
 
+def check_equal_local_batches(n: int, ep: Optional[EPState] = None, device=None) -> None:
+    """The peer-memory exchange indexes token t of rank r as ``r*n + t`` in the global plan and all-gathers the ids with
+    equal contributions, so unequal local batches would hang in the collective.  Collective call (one small
+    all-reduce): raises the same ``ValueError`` on every rank when the ranks disagree on ``n``.  The engine pads decode
+    batches to a common size; the reference's own EP path exchanges split sizes through the host instead
+    (layers/token_routed_i64/layer.py:230-247)."""
+    ep = ep or _EP
+    if ep.ep_size <= 1:
+        return
+    nn = torch.tensor([n, -n], dtype=torch.int64, device=device)
+    dist.all_reduce(nn, op=dist.ReduceOp.MAX, group=ep.group)
+    n_max, n_min = int(nn[0]), -int(nn[1])
+    if n_max != n_min:
+        raise ValueError(f"expert-parallel ranks must bring the same number of tokens per step "
+                         f"(min {n_min}, max {n_max}): pad the local batch to a common size")
+
+
 def local_expert_range(num_experts: int, ep: Optional[EPState] = None):
     """Block partition ``e -> rank e // (E / G)`` (layers/token_routed_i64/layer.py:84-88)."""
     ep = ep or _EP
@@ -178,16 +195,7 @@ class EPTokenRoutedBlock:
         G, K, H = self.ep.ep_size, self.K, self.H
         if G > _C.EP_MAX_RANKS:
             raise ValueError(f"at most {_C.EP_MAX_RANKS} expert-parallel ranks")
-        if G > 1:
-            # The global plan indexes token t of rank r as r*n + t, and the id all-gather needs equal contributions:
-            # unequal batches would hang in the collective.  Setup is collective and synchronising anyway, so check
-            # here and fail on every rank with the same message (the engine pads decode batches to a common size).
-            nn = torch.tensor([n, -n], dtype=torch.int64, device=self.device)
-            dist.all_reduce(nn, op=dist.ReduceOp.MAX, group=self.ep.group)
-            n_max, n_min = int(nn[0]), -int(nn[1])
-            if n_max != n_min:
-                raise ValueError(f"expert-parallel ranks must bring the same number of tokens per step "
-                                 f"(min {n_min}, max {n_max}): pad the local batch to a common size")
+        check_equal_local_batches(n, self.ep, self.device)
         cap = G * n * K                                        # worst case: every assignment lands here (nothing dropped)
 
         def up(v):
