@@ -174,6 +174,10 @@ int i64b_moe_forward(i64b_layer* layer, const void* x, const int64_t* token_ids,
 /* 1 if i64b_moe_forward on n tokens takes the single-launch fused decode kernel (bf16, n <= 1024; env
  * I64B_FUSED=0 disables it), else 0 (plan / dispatch / GEMM1 / GEMM2 / combine as separate launches). */
 int i64b_moe_uses_fused(const i64b_layer* layer, int64_t n);
+/* The same question for a shape alone (pure host arithmetic, no device needed): bf16 block of `n` tokens with these
+ * widths.  0 when the single-launch kernel's limits are exceeded (n <= 1024, widths <= 4096, hidden % 64 == 0, at most
+ * 8 work units per SM in its static work list, ...): such shapes take the kernel chain. */
+int i64b_fused_decode_supported(int n, int hidden, int expert_inter, int shared_inter, int num_experts, int top_k);
 
 /* Run only the selected stages of the forward on the workspace contents left by an earlier full forward with the
  * same (n, workspace): used by bench.py to time each kernel in isolation (roofline per stage). */

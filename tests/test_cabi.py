@@ -116,3 +116,19 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in text.replace("i64b_", ""), f"{f} references the oracle"
+
+
+def test_fused_decode_shape_limits():
+    """Host arithmetic of the single-launch decode kernel's shape check (no device needed): the named decode shapes
+    qualify; shapes whose static work list would overflow the per-CTA unit table (8 units per SM), or that exceed the
+    width / batch limits, must take the kernel chain."""
+    from vllm_i64 import _C
+    ok = _C.lib().i64b_fused_decode_supported
+    assert ok(256, 1024, 512, 1280, 8, 2) == 1          # tr-hash-moe-500m decode (config 2)
+    assert ok(256, 1024, 768, 1024, 4, 2) == 1          # tr-moe-306
+    assert ok(256, 1024, 0, 4096, 0, 0) == 1            # dense-306 (8 slabs, 64 GEMM1 tiles per m-tile)
+    assert ok(1024, 256, 0, 1536, 0, 0) == 1            # largest batch
+    assert ok(1025, 1024, 512, 1280, 8, 2) == 0         # batch too large
+    assert ok(100, 256, 0, 4096 + 64, 0, 0) == 0        # more than 8 split-K slabs
+    assert ok(256, 4096, 2048, 0, 64, 2) == 0           # 2048 + 2048 units: more than 8 per SM
+    assert ok(256, 1000, 512, 1280, 8, 2) == 0          # hidden not a multiple of 64

@@ -626,6 +626,10 @@ int i64b_moe_forward(i64b_layer* L, const void* x, const int64_t* token_ids, voi
     return moe_forward_impl(L, x, token_ids, FwdOpts(), out, out_dtype, n, workspace, workspace_bytes, stream);
 }
 
+int i64b_fused_decode_supported(int n, int hidden, int expert_inter, int shared_inter, int num_experts, int top_k) {
+    return i64b_fused_supported(n, hidden, expert_inter, shared_inter, num_experts, top_k);
+}
+
 int i64b_moe_uses_fused(const i64b_layer* L, int64_t n) {
     if (!L || !L->loaded || L->cfg.mode != I64B_MODE_BF16 || !fused_enabled() || n > (1 << 20)) return 0;
     const i64b_moe_config& c = L->cfg;

@@ -881,6 +881,12 @@ int i64b_fused_supported(int n, int hidden, int expert_inter, int shared_inter, 
     if (num_experts + (n + kBlockM - 1) / kBlockM > I64B_FUSED_MAX_GROUPS) return 0;
     if ((int64_t)n * top_k >= 65536) return 0;             // uint16 destination rows
     if (shared_inter > kMaxSlabs * kSlabK) return 0;
+    {   // the per-CTA unit table holds kMaxUnitsPerCta units (the role loops read it; larger work lists take the chain)
+        I64bFusedParams q = {};
+        q.n = n; q.hidden = hidden; q.expert_inter = expert_inter; q.shared_inter = shared_inter;
+        q.num_experts = num_experts; q.top_k = top_k;
+        if (make_geo(q).U > kMaxUnitsPerCta * i64b_num_sms()) return 0;
+    }
     static_assert(kSmemBytes <= 232448, "shared memory budget");
     return 1;
 }

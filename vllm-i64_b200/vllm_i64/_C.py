@@ -85,6 +85,7 @@ _SIGNATURES = {
     "i64b_moe_set_debug": (_I, [_P, _I]),
     "i64b_moe_set_next": (_I, [_P, _P]),
     "i64b_debug_timeline_dump": (_I, []),
+    "i64b_fused_decode_supported": (_I, [_I, _I, _I, _I, _I, _I]),
     "i64b_ep_alloc": (_I, [_Z, C.POINTER(_P)]),
     "i64b_ep_free": (_I, [_P]),
     "i64b_ipc_export": (_I, [_P, C.c_char_p]),
