@@ -1,50 +1,67 @@
 #!/usr/bin/env python
 """MoE-FFN throughput benchmark (BASELINE.json metric: MoE-FFN tokens/s at 1/2/4/8 B200 + % of roofline).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload decode_bf16|prefill_w8a8|dense_decode|dense_prefill]
+    python bench.py [--gpus N] [--steps K] [--warmup W]
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
-    python bench.py --impl reference ...        # the reference's CPU path (oracle port) on the host cores
+    python bench.py --impl reference ...        # the reference's own CPU path on the host cores
+    python bench.py --workload decode_bf16 ...  # one single-GPU workload as the line (profiling runs)
 
-One "token" = one row of x through one full MoE FFN block of one layer.  One "step" = one pass of the block over
-one batch of N tokens for each of the model's L layers (L distinct weight sets and routing tables, so decode is an
-HBM number and not an L2 number).  Default workload = BASELINE.json configs[1]: tr-hash-moe-500m, bf16 decode,
-256 concurrent sequences, 1 GPU.  Prints ONE JSON line (rank 0).
+One "token" = one row of x through one full MoE FFN block of one layer.  One "step" = one pass of the block over one
+batch for each of L layers (L distinct weight sets and routing tables, so nothing is an L2 number).
+
+The LINE is BASELINE.json config 5 — tr-hash-moe-500m, 64K tokens per step IN TOTAL, bf16 — at every N, so the driver's
+1 -> 8 curve is the STRONG scaling of the expert-parallel path: at N = 1 the whole step runs on one GPU (all experts local,
+the single-GPU kernel chain), at N > 1 tokens and experts are sharded over the ranks and the rows cross NVLink
+(csrc/i64b_ep.cu; no collective library call on the data path).  At N = 1 the line also carries every other single-GPU
+configuration of BASELINE.json under `workloads` (config 2 decode, config 3 W8A8 prefill, config 4 dense, tr-moe-306),
+each with its own roofline, the measured INT8 peak, the reference's CPU path timed beside it (`cpu_baseline`) and the
+reference's own module on this GPU (`reference_gpu`, the "before" number).  Prints ONE JSON line (rank 0).
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for _p in (ROOT, os.path.join(ROOT, "vllm-i64_b200"), os.path.join(ROOT, "tests")):
-    if _p not in sys.path:
-        sys.path.insert(0, _p)
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+
+def _product_paths():
+    for _p in (ROOT, os.path.join(ROOT, "vllm-i64_b200"), os.path.join(ROOT, "tests")):
+        if _p not in sys.path:
+            sys.path.insert(0, _p)
+
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 # INFERRED architecture shapes: the checkpoint config is not in the reference repo.
+_M500 = dict(H=1024, E=8, I=512, S=1280, V=32000, K=2, pw=0.5, rs=2.0, ss=1.0)
 WORKLOADS = {
-    "decode_bf16": dict(desc="tr-hash-moe-500m bf16 decode, 256 concurrent sequences", H=1024, E=8, I=512, S=1280,
-                        V=32000, K=2, pw=0.5, rs=2.0, ss=1.0, L=24, N=256, mode="bf16"),
-    "prefill_w8a8": dict(desc="tr-hash-moe-500m INT8 W8A8 prefill, 16K-token batch", H=1024, E=8, I=512, S=1280,
-                         V=32000, K=2, pw=0.5, rs=2.0, ss=1.0, L=4, N=16384, mode="int8"),
-    "prefill_bf16": dict(desc="tr-hash-moe-500m bf16 prefill, 16K-token batch", H=1024, E=8, I=512, S=1280,
-                         V=32000, K=2, pw=0.5, rs=2.0, ss=1.0, L=4, N=16384, mode="bf16"),
-    "decode_w8a8": dict(desc="tr-hash-moe-500m INT8 W8A8 decode, 256 concurrent sequences", H=1024, E=8, I=512,
-                        S=1280, V=32000, K=2, pw=0.5, rs=2.0, ss=1.0, L=24, N=256, mode="int8"),
+    "ep64k_bf16": dict(desc="tr-hash-moe-500m bf16, 64K tokens/step in total (BASELINE config 5)", **_M500, L=4, N=65536,
+                       mode="bf16", reps=0),
+    "decode_bf16": dict(desc="tr-hash-moe-500m bf16 decode, 256 concurrent sequences (config 2)", **_M500, L=24, N=256,
+                        mode="bf16", reps=200),
+    "prefill_w8a8": dict(desc="tr-hash-moe-500m INT8 W8A8 prefill, 16K-token batch (config 3)", **_M500, L=4, N=16384,
+                         mode="int8", reps=40),
+    "prefill_bf16": dict(desc="tr-hash-moe-500m bf16 prefill, 16K-token batch", **_M500, L=4, N=16384, mode="bf16", reps=40),
+    "decode_w8a8": dict(desc="tr-hash-moe-500m INT8 W8A8 decode, 256 concurrent sequences", **_M500, L=24, N=256,
+                        mode="int8", reps=200),
     "tr_moe_306_decode": dict(desc="tr-moe-306 bf16 decode, 256 concurrent sequences", H=1024, E=4, I=768, S=1024,
-                              V=32000, K=2, pw=0.5, rs=1.0, ss=1.0, L=18, N=256, mode="bf16"),
-    "dense_decode": dict(desc="dense-306 matched dense FFN, 256 tokens", H=1024, E=0, I=0, S=4096, V=32000, K=0,
-                         pw=1.0, rs=1.0, ss=1.0, L=18, N=256, mode="bf16"),
-    "dense_prefill": dict(desc="dense-306 matched dense FFN, 16K tokens", H=1024, E=0, I=0, S=4096, V=32000, K=0,
-                          pw=1.0, rs=1.0, ss=1.0, L=4, N=16384, mode="bf16"),
+                              V=32000, K=2, pw=0.5, rs=1.0, ss=1.0, L=18, N=256, mode="bf16", reps=200),
+    "dense_decode": dict(desc="dense-306 matched dense FFN, 256 tokens (config 4)", H=1024, E=0, I=0, S=4096, V=32000, K=0,
+                         pw=1.0, rs=1.0, ss=1.0, L=18, N=256, mode="bf16", reps=200),
+    "dense_prefill": dict(desc="dense-306 matched dense FFN, 16K tokens (config 4)", H=1024, E=0, I=0, S=4096, V=32000, K=0,
+                          pw=1.0, rs=1.0, ss=1.0, L=4, N=16384, mode="bf16", reps=40),
 }
+HEADLINE = "ep64k_bf16"
 METRIC, UNIT = "moe_ffn_tokens_per_s", "tokens/s"
+NVLINK_GBS = 770.0          # measured peer copy per direction per GPU on this pool (B200_PROFILING.md)
 _JSON_FD = None
 
 
@@ -90,8 +107,23 @@ def route_weights(wl):
     return [wl["pw"]] + [(1.0 - wl["pw"]) / (k - 1)] * (k - 1)
 
 
+def parallelism_text(world):
+    if world <= 1:
+        return "1 GPU: all experts local (the same step the N > 1 lines shard expert-parallel)"
+    return (f"ep{world}: experts block-partitioned over {world} GPUs, tokens data-parallel, rows exchanged over NVLink peer "
+            "memory (no collective call on the data path)")
+
+
+def cfg_json(wl, world, parallelism=None):
+    parallelism = parallelism or parallelism_text(world)
+    return {"workload": wl["desc"], "hidden": wl["H"], "num_experts": wl["E"], "expert_inter": wl["I"],
+            "shared_inter": wl["S"], "top_k": wl["K"], "layers_per_step": wl["L"], "tokens_per_step_total": wl["N"],
+            "tokens_per_gpu": wl["N"] // world, "shapes": "INFERRED (SURVEY.md §8)", "parallelism": parallelism,
+            "l2_policy": "L distinct layer weight sets per step; activations + weights per step exceed the 126 MB L2"}
+
+
 # ------------------------------------------------------------------------------------------------- algorithmic work
-def stage_bytes(wl):
+def stage_bytes(wl, fused_combine=False):
     """ALGORITHMIC HBM bytes per launch of each stage for one layer, and flops of the GEMMs."""
     H, E, I, S, K, N = (wl[k] for k in "HEISKN")
     a = 1 if wl["mode"] == "int8" else 2               # bytes per operand element fed to the tensor cores
@@ -107,8 +139,8 @@ def stage_bytes(wl):
     b["gemm1"] = w13 + rows * H * a + inter_w
     b["requant"] = (R * I + N * S) * 5 if a == 1 else 0
     w2 = (E * H * I + H * S) * a
-    if has_s and E == 0:
-        # fused combine (dense FFN): the shared expert's GEMM2 tiles pull the routed fp32 rows and write the block output
+    if has_s and (E == 0 or fused_combine):
+        # fused combine: the shared expert's GEMM2 tiles pull the routed fp32 rows and write the block output
         b["gemm2"] = w2 + (R * I + N * S) * a + 2 * R * H * 4 + R * 4 + N * H * 2
         b["combine"] = 0
     else:
@@ -116,6 +148,15 @@ def stage_bytes(wl):
         b["combine"] = rows * H * 4 + N * H * 2 + R * 4
     f = {"gemm1": 2.0 * H * 2 * (R * I + N * S), "gemm2": 2.0 * H * (R * I + N * S)}
     return b, f
+
+
+def block_min_bytes(wl):
+    a = 1 if wl["mode"] == "int8" else 2
+    return ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * wl["H"] * a) + wl["N"] * wl["H"] * 2 * 2     # weights once + x in + out
+
+
+def block_flops(wl):
+    return 6.0 * wl["H"] * (wl["N"] * wl["K"] * wl["I"] + wl["N"] * wl["S"])
 
 
 # ------------------------------------------------------------------------------------------------- clocks sampling
@@ -167,53 +208,67 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+class _Null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
 # ------------------------------------------------------------------------------------------------- model build
+def synth_weights(wl, layer, device):
+    """Random-init weights in the reference's init range (kaiming-uniform bound 1/sqrt(fan_in)), seeded per layer."""
+    H, E, I, S = (wl[k] for k in "HEIS")
+    g = torch.Generator(device=device).manual_seed(layer)
+
+    def u(shape, fan_in):
+        b = 1.0 / fan_in ** 0.5
+        return (torch.rand(shape, device=device, generator=g) * 2 - 1) * b
+
+    gate = u((E, H, I), H) if E else None
+    up = u((E, H, I), H) if E else None
+    down = u((E, I, H), I) if E else None
+    sg, su, sd = (u((S, H), H), u((S, H), H), u((H, S), S)) if S else (None, None, None)
+    return gate, up, down, sg, su, sd
+
+
+def quantize_weights(gate, up, down, sg, su, sd):
+    from vllm_i64.core.quantization import quantize_int8
+    ex = [None] * 4
+    if gate is not None:
+        q13, s13 = quantize_int8(torch.cat([gate.transpose(1, 2), up.transpose(1, 2)], 1).contiguous())
+        q2, s2 = quantize_int8(down.transpose(1, 2).contiguous())
+        ex = [q13, s13, q2, s2]
+    sh = [None] * 4
+    if sg is not None:
+        q, s_ = quantize_int8(torch.cat([sg, su], 0).contiguous())
+        q2s, s2s = quantize_int8(sd.contiguous())
+        sh = [q, s_, q2s, s2s]
+    return ex + sh
+
+
 def build_layers(wl, device):
     """L blocks with distinct random-init weights (reference init range) and layer-specific hash tables."""
     from vllm_i64 import _C
     from vllm_i64.kernels.block import I64Block
-    from vllm_i64.core.quantization import quantize_int8
     from tools.synth_data import synthetic_hash_table
     H, E, I, S, V, K = (wl[k] for k in "HEISVK")
     mode = _C.MODE_W8A8 if wl["mode"] == "int8" else _C.MODE_BF16
     layers = []
     for layer in range(wl["L"]):
-        g = torch.Generator(device=device).manual_seed(layer)
-
-        def u(shape, fan_in):
-            b = 1.0 / fan_in ** 0.5
-            return (torch.rand(shape, device=device, generator=g) * 2 - 1) * b
-
         blk = I64Block(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], mode, device)
-        gate = u((E, H, I), H) if E else None
-        up = u((E, H, I), H) if E else None
-        down = u((E, I, H), I) if E else None
-        sg, su, sd = (u((S, H), H), u((S, H), H), u((H, S), S)) if S else (None, None, None)
+        ws = synth_weights(wl, layer, device)
         if mode == _C.MODE_BF16:
-            blk.load_bf16(gate, up, down, sg, su, sd)
+            blk.load_bf16(*ws)
         else:
-            ex = [None] * 4
-            if E:
-                q13, s13 = quantize_int8(torch.cat([gate.transpose(1, 2), up.transpose(1, 2)], 1).contiguous())
-                q2, s2 = quantize_int8(down.transpose(1, 2).contiguous())
-                ex = [q13, s13, q2, s2]
-            sh = [None] * 4
-            if S:
-                q, s_ = quantize_int8(torch.cat([sg, su], 0).contiguous())
-                q2s, s2s = quantize_int8(sd.contiguous())
-                sh = [q, s_, q2s, s2s]
-            blk.load_w8a8(*ex, *sh)
+            blk.load_w8a8(*quantize_weights(*ws))
         if E:
             blk.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
         layers.append(blk)
     torch.cuda.synchronize(device)
     for b in layers:
         b._keep = None
-    # decoder order: layer l is followed by l+1 (the step loop wraps around), so each block may prefetch the next one's
-    # weights into L2 (i64b_moe_set_next; a no-op outside the fused decode kernel).  Opt-in: measured slower (DESIGN 4b)
-    if len(layers) > 1 and os.environ.get("I64B_PREFETCH", "0") != "0":
-        for i, b in enumerate(layers):
-            b.set_next(layers[(i + 1) % len(layers)])
     return layers
 
 
@@ -243,38 +298,209 @@ def time_graph(run, steps, warmup, stream, barrier=None, sampler=None):
         torch.cuda.synchronize()
         if barrier:
             barrier()
+    del g
     return e0.elapsed_time(e1)
 
 
-class _Null:
-    def __enter__(self):
-        return self
+def measure_int8_peak(device):
+    """Dense INT8 tensor peak as this pool delivers it through cuBLASLt (torch._int_mm 8192^3): best of 10 (burst) and back
+    to back for ~1.5 s (sustained) — the same recipe MEASURED_PEAKS.json uses for bf16 (BASELINE.md §4 asks for it)."""
+    try:
+        n = 8192
+        a = torch.randint(-127, 127, (n, n), device=device, dtype=torch.int8)
+        b = torch.randint(-127, 127, (n, n), device=device, dtype=torch.int8)
+        for _ in range(3):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize(device)
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._int_mm(a, b)
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        ops = 2.0 * n ** 3
+        reps = max(10, int(1500.0 / best))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            torch._int_mm(a, b)
+        e1.record()
+        e1.synchronize()
+        return {"int8_tops": round(ops / (best * 1e-3) / 1e12, 1),
+                "int8_tops_sustained": round(ops * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12, 1),
+                "how": "torch._int_mm 8192^3 (cuBLASLt), best of 10 and back to back for ~1.5 s", "src": "measured in this run"}
+    except Exception as exc:       # no int8 path in this torch build: fall back to the nominal 2x ratio, say so
+        return {"int8_tops": None, "error": f"{type(exc).__name__}: {exc}"[:200]}
 
-    def __exit__(self, *a):
-        return False
+
+# ------------------------------------------------------------------------------------------------- one workload
+def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, rank=0, barrier=None, sampler=None,
+                     with_stages=True):
+    """Device-timed value, e2e (host buffers, copies inside the timed region), per-stage roofline (kernel chain) or the
+    fused kernel's roofline (decode), for one single-GPU workload."""
+    from vllm_i64 import _C
+    H, N, L = wl["H"], wl["N"], wl["L"]
+    layers = build_layers(wl, device)
+    g = torch.Generator().manual_seed(1234 + rank)
+    ids_host = torch.randint(0, wl["V"], (N,), generator=g).pin_memory()
+    x_host = torch.randn(N, H, generator=torch.Generator().manual_seed(rank)).to(torch.bfloat16).pin_memory()
+    out_host = torch.empty(N, H, dtype=torch.bfloat16).pin_memory()
+    x_dev, ids_dev = x_host.to(device), ids_host.to(device)
+    outs = [torch.empty(N, H, dtype=torch.bfloat16, device=device) for _ in range(2)]
+    ids_arg = ids_dev if wl["E"] else None
+
+    def step_device(stages=_C.STAGE_ALL):
+        for i, blk in enumerate(layers):
+            blk.forward(x_dev, ids_arg, torch.bfloat16, out=outs[i & 1], stages=stages)
+
+    def step_e2e():
+        x_dev.copy_(x_host, non_blocking=True)
+        ids_dev.copy_(ids_host, non_blocking=True)
+        step_device()
+        out_host.copy_(outs[(L - 1) & 1], non_blocking=True)
+
+    # the per-layer plugin call with HOST buffers (i64b_moe_forward_host: H2D + forward + D2H inside the C ABI call)
+    staging = layers[0].make_staging(N)
+
+    def step_host_call():
+        for blk in layers:
+            blk.forward_host(x_host, ids_host if wl["E"] else None, out_host, staging)
+
+    with torch.cuda.stream(stream):
+        step_device()
+        stream.synchronize()
+        _C.launch_count_reset()
+        step_device()
+        stream.synchronize()
+    launches_per_step = _C.launch_count()
+
+    ms = time_graph(step_device, steps, warmup, stream, barrier, sampler)
+    e2e_steps = max(3, min(steps, 50))
+    ms_e2e = time_graph(step_e2e, e2e_steps, 3, stream, barrier)
+    ms_host = time_graph(step_host_call, max(3, min(steps, 20)), 3, stream, barrier)
+    us_layer = ms * 1e3 / (steps * L)
+    res = {"desc": wl["desc"], "value": N * L * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+           "us_per_layer": round(us_layer, 3), "steps": steps, "dtype": "bf16" if wl["mode"] == "bf16" else "int8",
+           "gpu_launches_per_step": int(launches_per_step),
+           "e2e": {"value": N * L * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / e2e_steps,
+                   "h2d_bytes_per_step": N * H * 2 + N * 8, "d2h_bytes_per_step": N * H * 2, "copies_per_step": 1,
+                   "via": "engine step: one pinned H2D of x + ids, L block forwards, one D2H of the last output"},
+           "e2e_per_layer_host_call": {
+               "value": N * L * max(3, min(steps, 20)) / (ms_host * 1e-3), "unit": UNIT, "copies_per_step": L,
+               "h2d_bytes_per_step": L * (N * H * 2 + N * 8), "d2h_bytes_per_step": L * N * H * 2,
+               "via": "i64b_moe_forward_host per layer (the plugin call with HOST buffers: H2D + forward + D2H inside the C ABI)"}}
+    i8 = wl["mode"] == "int8"
+    tensor_peak = (int8_peak.get("int8_tops") or 2.0 * pk["tf_burst"]) if i8 else pk["tf_burst"]
+    tensor_src = ("INT8 burst measured in this run (torch._int_mm)" if (i8 and int8_peak.get("int8_tops"))
+                  else ("2x bf16 burst (nominal ratio; int8 peak unmeasured)" if i8 else pk["src"] + " bf16 burst"))
+    fused = layers[0].uses_fused(N)
+    mb = block_min_bytes(wl)
+    res["block"] = {"min_bytes": mb, "frac_hbm": round(mb / (us_layer * 1e-6) / 1e9 / pk["hbm"], 4),
+                    "flops": block_flops(wl),
+                    "frac_tensor": round(block_flops(wl) / (us_layer * 1e-6) / 1e12 / tensor_peak, 4),
+                    "tensor_peak": tensor_peak, "tensor_peak_source": tensor_src}
+    if fused:
+        gbs = mb / (us_layer * 1e-6) / 1e9
+        res["roofline"] = {"kernel": "i64b_fused_layer_kernel", "bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"],
+                           "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4), "traffic": ncu_traffic(name, "i64b_fused_layer_kernel"),
+                           "peak_source": pk["src"] + " (burst copy)", "algorithmic_bytes": mb, "us_per_launch": round(us_layer, 3)}
+    elif with_stages and rank == 0:
+        fc = layers[0].fuses_combine(N)
+        sb, sf = stage_bytes(wl, fc)
+        names = [("plan", _C.STAGE_PLAN), ("dispatch", _C.STAGE_DISPATCH), ("gemm1", _C.STAGE_GEMM1),
+                 ("requant", _C.STAGE_REQUANT), ("gemm2", _C.STAGE_GEMM2), ("combine", _C.STAGE_COMBINE)]
+        reps = 20
+        st = {}
+        for sname, bit in names:
+            if sb[sname] == 0:
+                continue
+            t_ms = time_graph(lambda b=bit: step_device(b), reps, 3, stream)
+            us = t_ms * 1e3 / (reps * L)
+            gbs = sb[sname] / (us * 1e-6) / 1e9
+            ent = {"us_per_launch": round(us, 3), "algorithmic_bytes": sb[sname], "GBps": round(gbs, 1),
+                   "frac_hbm": round(gbs / pk["hbm"], 4)}
+            if sname in sf:
+                tf = sf[sname] / (us * 1e-6) / 1e12
+                ent["TOPs" if i8 else "TFLOPs"] = round(tf, 1)
+                ent["frac_tensor"] = round(tf / tensor_peak, 4)
+            st[sname] = ent
+        dom = max(st, key=lambda k: st[k]["us_per_launch"])
+        d = st[dom]
+        kkey = {"gemm1": "i64b_gemm_kernel<%d, 1" % (1 if i8 else 0), "gemm2": "i64b_gemm_kernel<%d, 0" % (1 if i8 else 0)}.get(dom, dom)
+        if d["frac_hbm"] >= d.get("frac_tensor", 0.0):
+            res["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": pk["hbm"], "unit": "GB/s",
+                               "frac": d["frac_hbm"], "traffic": ncu_traffic(name, kkey), "peak_source": pk["src"] + " (burst copy)"}
+        else:
+            key = "TOPs" if i8 else "TFLOPs"
+            res["roofline"] = {"kernel": dom, "bound": "tensor", "achieved": d[key], "peak": tensor_peak,
+                               "unit": "TOP/s" if i8 else "TFLOP/s", "frac": d["frac_tensor"], "traffic": ncu_traffic(name, kkey),
+                               "peak_source": tensor_src}
+        st["_sum_us_per_layer"] = round(sum(v["us_per_launch"] for v in st.values() if isinstance(v, dict)), 2)
+        st["_combine_fused_into_gemm2"] = bool(fc)
+        res["stages"] = st
+    del layers, staging
+    torch.cuda.empty_cache()
+    return res
 
 
-# ------------------------------------------------------------------------------------------------- CPU arm
-def cpu_reference_run(wl, steps, warmup, mode="int8", max_seconds=25.0, layers_cap=None):
-    """Reference CPU path (oracle port, oracle/cpu_reference.py) on the host cores: tokens/s over bounded steps."""
-    from oracle.cpu_reference import CpuTokenRoutedMLP, quantize_cpu_dynamic, set_cpu_threads
+# ------------------------------------------------------------------------------------------------- CPU / reference arms
+def have_ref():
+    return os.path.isdir(os.path.join(REF_DIR, "vllm_i64"))
+
+
+def cpu_reference_run(wl, steps, warmup, mode="int8", max_seconds=25.0, sample_tokens=2048, layers_cap=2):
+    """The reference's CPU recipe on the host cores, on a bounded sample of the workload: `sample_tokens` tokens x
+    `layers_cap` layers per step.  kind "reference": the reference's OWN TokenRoutedMLP -> _fuse_cpu_projection_layers ->
+    _quantize_cpu_dynamic (core/loader.py:57-94) imported from oracle/_ref (tools/install_ref.py); kind "port": the torch-CPU
+    restatement oracle/cpu_reference.py when the reference copy is absent."""
     from tools.synth_data import synthetic_hash_table
-    threads = set_cpu_threads()
-    H, E, I, S, V, K, N = (wl[k] for k in "HEISVKN")
+    H, E, I, S, V, K = (wl[k] for k in "HEISVK")
+    n = min(wl["N"], sample_tokens)
+    L = min(wl["L"], layers_cap)
     if E == 0:      # dense FFN: one "expert" that every token uses
         E_, I_, S_, K_ = 1, S, 0, 1
     else:
         E_, I_, S_, K_ = E, I, S, K
-    L = min(wl["L"], layers_cap or wl["L"])
-    mods = []
     g = torch.Generator().manual_seed(0)
-    ids = torch.randint(0, V, (N,), generator=g)
-    x = torch.randn(N, H, generator=g)
-    for layer in range(L):
-        torch.manual_seed(layer)
-        table = torch.from_numpy(synthetic_hash_table(V, E_, K_, layer)) if E_ > 1 else torch.zeros(K_, V, dtype=torch.long)
-        m = CpuTokenRoutedMLP(H, E_, I_, S_, K_, wl["pw"], wl["rs"], wl["ss"], table)
-        mods.append(quantize_cpu_dynamic(m) if mode == "int8" else m.eval())
+    ids = torch.randint(0, V, (n,), generator=g)
+    x = torch.randn(n, H, generator=g)
+    kind = "reference" if have_ref() else "port"
+    mods = []
+    if kind == "reference":
+        sys.path.insert(0, REF_DIR)
+        # cli.py:116-134: threads = min(VLLM_I64_CPU_THREADS, affinity), inter-op 1
+        avail = len(os.sched_getaffinity(0))
+        threads = max(1, min(int(os.environ.get("VLLM_I64_CPU_THREADS", avail)), avail))
+        torch.set_num_threads(threads)
+        try:
+            torch.set_num_interop_threads(1)
+        except RuntimeError:
+            pass
+        from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP as RefMLP
+        from vllm_i64.core.loader import _fuse_cpu_projection_layers, _quantize_cpu_dynamic
+        assert os.path.realpath(sys.modules["vllm_i64"].__file__).startswith(os.path.realpath(REF_DIR)), "wrong vllm_i64 imported"
+        for layer in range(L):
+            torch.manual_seed(layer)
+            m = RefMLP(H, E_ * I_, E_, V, shared_expert=S_ > 0, shared_intermediate_size=S_, top_k=K_,
+                       top_k_primary_weight=wl["pw"], shared_output_scale=wl["ss"], routed_output_scale=wl["rs"])
+            if E_ > 1:
+                m.topk_token_to_expert.copy_(torch.from_numpy(synthetic_hash_table(V, E_, K_, layer)))
+            m.eval()
+            if mode == "int8":
+                _fuse_cpu_projection_layers(m)
+                m = _quantize_cpu_dynamic(m)
+            mods.append(m)
+    else:
+        _product_paths()
+        from oracle.cpu_reference import CpuTokenRoutedMLP, quantize_cpu_dynamic, set_cpu_threads
+        threads = set_cpu_threads()
+        for layer in range(L):
+            torch.manual_seed(layer)
+            table = torch.from_numpy(synthetic_hash_table(V, E_, K_, layer)) if E_ > 1 else torch.zeros(K_, V, dtype=torch.long)
+            m = CpuTokenRoutedMLP(H, E_, I_, S_, K_, wl["pw"], wl["rs"], wl["ss"], table)
+            mods.append(quantize_cpu_dynamic(m) if mode == "int8" else m.eval())
 
     def step():
         with torch.no_grad():
@@ -291,97 +517,236 @@ def cpu_reference_run(wl, steps, warmup, mode="int8", max_seconds=25.0, layers_c
         if time.perf_counter() - t0 > max_seconds:
             break
     dt = time.perf_counter() - t0
-    return dict(value=done * N * L / dt, ms_per_step=dt / done * 1e3, steps=done, threads=threads, layers=L,
-                sample=f"{done} step(s) x {L} layer(s) x {N} tokens, {'dynamic INT8 (x86/FBGEMM)' if mode == 'int8' else 'fp32'}"
-                       f", {threads} threads")
+    return dict(value=done * n * L / dt, ms_per_step=dt / done * 1e3, steps=done, threads=threads, layers=L, kind=kind,
+                sample=f"{done} step(s) x {L} layer(s) x {n} tokens of the workload, "
+                       f"{'dynamic INT8 (x86/FBGEMM quantize_dynamic)' if mode == 'int8' else 'fp32'}, {threads} threads, "
+                       + ("the reference's own TokenRoutedMLP + core/loader.py CPU recipe (oracle/_ref)" if kind == "reference"
+                          else "torch-CPU port (oracle/cpu_reference.py)"))
+
+
+def config1_cpu_engine(max_seconds=30.0):
+    """BASELINE config 1 end to end: the reference's CPUEngine on tr-moe-306-shaped random-init weights, 4 prompts x 32
+    tokens, 8 new tokens.  Engine-level tokens/s (prompt + generated) — context only."""
+    try:
+        sys.path.insert(0, REF_DIR)
+        from vllm_i64.models.complexity_deep.model import ComplexityDeepModel
+        from vllm_i64.models.deep_config import ComplexityDeepConfig          # noqa: F401
+    except Exception as exc:
+        return {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
+    return {"unavailable": "engine-level timing not wired (block-level reference timing above is the CPU baseline)"}
+
+
+def reference_gpu_run(wl, steps, warmup, layers_cap=2, max_seconds=25.0):
+    """The "before" number: the reference's own TokenRoutedMLP.forward on cuda bf16 on the workload's batch
+    (its per-expert mask loop: E*K boolean gathers + 3 GEMMs + masked scatter, a host sync per expert)."""
+    from tools.synth_data import synthetic_hash_table
+    sys.path.insert(0, REF_DIR)
+    from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP as RefMLP
+    assert os.path.realpath(sys.modules["vllm_i64"].__file__).startswith(os.path.realpath(REF_DIR)), "wrong vllm_i64 imported"
+    H, E, I, S, V, K, N = (wl[k] for k in "HEISVKN")
+    dev = torch.device("cuda", 0)
+    L = min(wl["L"], layers_cap)
+    mods = []
+    for layer in range(L):
+        torch.manual_seed(layer)
+        m = RefMLP(H, E * I, E, V, shared_expert=S > 0, shared_intermediate_size=S, top_k=K, top_k_primary_weight=wl["pw"],
+                   shared_output_scale=wl["ss"], routed_output_scale=wl["rs"])
+        m.topk_token_to_expert.copy_(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
+        mods.append(m.to(dev).to(torch.bfloat16).eval())
+    x = torch.randn(N, H, device=dev, generator=torch.Generator(device=dev).manual_seed(0)).to(torch.bfloat16)
+    ids = torch.randint(0, V, (N,), device=dev, generator=torch.Generator(device=dev).manual_seed(1))
+
+    def step():
+        with torch.no_grad():
+            for m in mods:
+                m(x, ids)
+
+    for _ in range(max(2, min(warmup, 3))):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    done = 0
+    for _ in range(max(1, steps)):
+        step()
+        done += 1
+        if time.perf_counter() - t0 > max_seconds:
+            break
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1)
+    return {"value": done * N * L / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / done, "steps": done, "layers": L,
+            "what": "the reference's TokenRoutedMLP.forward (layers/token_routed_mlp.py:154-187) on cuda bf16, eager, on this GPU",
+            "tokens_per_step": N}
+
+
+def run_subprocess_json(argv, timeout=240):
+    """Run bench.py in a fresh interpreter (the reference package and this repo's mirror share the name vllm_i64) and
+    parse its JSON line."""
+    try:
+        p = subprocess.run([sys.executable, os.path.abspath(__file__)] + argv, capture_output=True, text=True, timeout=timeout)
+        for ln in reversed(p.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)
+        return {"error": (p.stderr or p.stdout)[-300:]}
+    except Exception as exc:
+        return {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
 
 # ------------------------------------------------------------------------------------------------- expert parallel
-def run_ep(wl, device, rank, world, args):
-    """BASELINE config 5: experts sharded over the ranks, 64K tokens per step in total (strong scaling), NCCL
-    all-to-all over NVLink for the token exchange.  Timed on the device, max over ranks."""
+def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
+    """BASELINE config 5 at N > 1: experts block-partitioned over the ranks, tokens data-parallel (wl.N / world each), the
+    rows cross NVLink through peer memory (csrc/i64b_ep.cu).  CUDA-graph replay of the L-layer step, timed on the device, max
+    over ranks.  Before timing, layer 0's output on every rank is compared with the single-GPU block on that rank's tokens."""
     import torch.distributed as dist
     from vllm_i64 import _C
+    from vllm_i64.kernels.block import I64Block
     from vllm_i64.parallel.expert_parallel import EPTokenRoutedBlock, init_expert_parallel
     from tools.synth_data import synthetic_hash_table
     ep = init_expert_parallel()
-    H, E, I, S, V, K = (wl[k] for k in "HEISVK")
-    L = 4
-    n = args.ep_tokens // world
-    blocks = []
+    H, E, I, S, V, K, L = (wl[k] for k in "HEISVKL")
+    n = wl["N"] // world
     tdt = torch.bfloat16 if args.ep_transport == "bf16" else torch.float32
-    for layer in range(L):
-        g = torch.Generator(device=device).manual_seed(layer)
-
-        def u(shape, fan_in):
-            return (torch.rand(shape, device=device, generator=g) * 2 - 1) / fan_in ** 0.5
-
-        b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep,
-                               transport_dtype=tdt)
-        b.load_bf16(u((E, H, I), H), u((E, H, I), H), u((E, I, H), I), u((S, H), H), u((S, H), H), u((H, S), S))
-        b.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
-        blocks.append(b)
-    x = torch.randn(n, H, device=device, generator=torch.Generator(device=device).manual_seed(100 + rank)).to(torch.bfloat16)
-    ids = torch.randint(0, V, (n,), device=device, generator=torch.Generator(device=device).manual_seed(200 + rank))
-
+    x_host = torch.randn(n, H, generator=torch.Generator().manual_seed(100 + rank)).to(torch.bfloat16).pin_memory()
+    ids_host = torch.randint(0, V, (n,), generator=torch.Generator().manual_seed(200 + rank)).pin_memory()
+    out_host = torch.empty(n, H, dtype=torch.bfloat16).pin_memory()
+    x, ids = x_host.to(device), ids_host.to(device)
     outs = [torch.empty(n, H, dtype=torch.bfloat16, device=device) for _ in range(2)]
 
-    def timed(exchange, steps, warm):
-        def step():
+    # ---- parity gate (layer 0): fp32 transport must be bit-identical to the single-GPU block; the timed transport dtype
+    # within its stated bar against that same output
+    parity = {}
+    ws0 = synth_weights(wl, 0, device)
+    table0 = torch.from_numpy(synthetic_hash_table(V, E, K, 0))
+    single = I64Block(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device)
+    single.load_bf16(*ws0)
+    single.set_table(table0)
+    single.set_debug(_C.DEBUG_NO_FUSED)
+    want = single.forward(x, ids, torch.float32)
+    for name, dt in (("f32", torch.float32), ("bf16", torch.bfloat16)):
+        b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep, transport_dtype=dt)
+        b.load_bf16(*ws0)
+        b.set_table(table0)
+        b.reserve(n)
+        got = b.forward(x, ids, torch.float32)
+        torch.cuda.synchronize(device)
+        if name == "f32":
+            parity["f32_transport"] = "bit-identical" if torch.equal(got, want) else "MISMATCH"
+        else:
+            d = (got - want).abs()
+            parity["bf16_transport_max_rel"] = float(d.max() / want.abs().max())
+            parity["bf16_transport_mean_rel"] = float(d.mean() / want.abs().mean())
+        b.close()
+        del b
+    del single, want, ws0
+    flags = torch.tensor([1.0 if parity["f32_transport"] == "bit-identical" else 0.0, parity["bf16_transport_max_rel"],
+                          parity["bf16_transport_mean_rel"]], device=device, dtype=torch.float64)
+    fl_min, fl_max = flags.clone(), flags.clone()
+    dist.all_reduce(fl_min, op=dist.ReduceOp.MIN)
+    dist.all_reduce(fl_max, op=dist.ReduceOp.MAX)
+    ep_parity = {"f32_transport_vs_single_gpu_block": "bit-identical" if float(fl_min[0]) == 1.0 else "MISMATCH",
+                 "bf16_transport_max_rel_vs_single_gpu_block": float(fl_max[1]),
+                 "bf16_transport_mean_rel_vs_single_gpu_block": float(fl_max[2]),
+                 "bar": "fp32 transport: torch.equal on every rank; bf16 transport: <= 1e-2 max-rel, <= 2.5e-3 mean-rel",
+                 "checked": f"layer 0, all {n} tokens of every rank"}
+    torch.cuda.empty_cache()
+
+    blocks = []
+    for layer in range(L):
+        b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep, transport_dtype=tdt)
+        b.load_bf16(*synth_weights(wl, layer, device))
+        b.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
+        b.reserve(n)
+        blocks.append(b)
+    torch.cuda.synchronize(device)
+
+    def step_device():
+        for i, b in enumerate(blocks):
+            b.forward(x, ids, torch.bfloat16, out=outs[i & 1])
+
+    def step_e2e():
+        x.copy_(x_host, non_blocking=True)
+        ids.copy_(ids_host, non_blocking=True)
+        step_device()
+        out_host.copy_(outs[(L - 1) & 1], non_blocking=True)
+
+    with torch.cuda.stream(stream):
+        step_device()
+        stream.synchronize()
+        _C.launch_count_reset()
+        step_device()
+        stream.synchronize()
+    launches = _C.launch_count()
+    dist.barrier()
+    ms = time_graph(step_device, args.steps, args.warmup, stream, barrier, sampler)
+    e2e_steps = max(3, min(args.steps, 50))
+    ms_e2e = time_graph(step_e2e, e2e_steps, 3, stream, barrier)
+    nccl = None
+    if args.ep_nccl_baseline:
+        # reference-style exchange (split sizes through the host + all_to_all_single each way), eager: the comparison baseline
+        def step_nccl():
             for i, b in enumerate(blocks):
-                b.forward(x, ids, torch.bfloat16, exchange=exchange, out=outs[i & 1])
-        for _ in range(warm):
-            step()
+                b.forward(x, ids, torch.bfloat16, exchange="nccl", out=None)
+        for _ in range(2):
+            step_nccl()
         torch.cuda.synchronize()
         dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(steps):
-            step()
+        for _ in range(3):
+            step_nccl()
         e1.record()
         e1.synchronize()
-        dist.barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t[0]) / steps
-
-    steps = max(3, min(args.steps, 20))
-    ms = timed("peer", steps, 3)                 # product path: NVLink peer-memory exchange fused into the kernels
-    ms_nccl = timed("nccl", max(3, steps // 4), 2)   # reference-style all_to_all_single exchange (baseline)
+        nccl = e0.elapsed_time(e1) / 3
+    t = torch.tensor([ms / args.steps, ms_e2e / e2e_steps, nccl or 0.0], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step, ms_e2e_step, ms_nccl = float(t[0]), float(t[1]), float(t[2])
+    tokens = n * world * L
+    us_layer = ms_step * 1e3 / L
     sent = n * K * (world - 1) / world * H * 2
-    return {"workload": "tr-hash-moe-500m bf16 expert-parallel", "tokens_per_step_total": n * world,
-            "layers_per_step": L, "ms_per_step": ms, "value": n * world * L / (ms * 1e-3), "unit": UNIT,
-            "scaling": "strong", "a2a_bytes_out_per_rank_per_layer": int(sent), "ep_size": world,
-            "transport_dtype": args.ep_transport,
-            "exchange": "NVLink peer memory (dispatch kernel writes into the owners' buffers; GEMM2 epilogue writes "
-                        "outputs home); NCCL only all-gathers the token ids",
-            "nccl_all_to_all_baseline": {"ms_per_step": ms_nccl, "value": n * world * L / (ms_nccl * 1e-3)}}
+    back = sent * (2 if tdt == torch.float32 else 1)
+    flops_rank = block_flops(wl) / world
+    t_tensor = flops_rank / (pk["tf_sust"] * 1e12) * 1e6
+    t_link = max(sent, back) / (NVLINK_GBS * 1e9) * 1e6
+    roof = {"kernel": "expert-parallel layer (dispatch | grouped GEMMs | combine-pull over NVLink)",
+            "bound": "tensor" if t_tensor >= t_link else "nvlink",
+            "achieved": round(flops_rank / (us_layer * 1e-6) / 1e12, 1), "peak": pk["tf_sust"], "unit": "TFLOP/s",
+            "frac": round(max(t_tensor, t_link) / us_layer, 4), "traffic": None,
+            "peak_source": pk["src"] + " bf16 sustained (kernel timed inside a long step); NVLink 770 GB/s per direction measured",
+            "target_us_per_layer": {"tensor": round(t_tensor, 1), "nvlink_one_way": round(t_link, 1)},
+            "us_per_layer": round(us_layer, 2),
+            "nvlink_bytes_per_rank_per_layer": {"dispatch_out": int(sent), "return_in": int(back)}}
+    for b in blocks:
+        b.close()
+    return {"value": tokens / (ms_step * 1e-3), "ms_per_step": ms_step, "launches_per_step": int(launches),
+            "e2e": {"value": tokens / (ms_e2e_step * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e_step,
+                    "h2d_bytes_per_step": n * H * 2 + n * 8, "d2h_bytes_per_step": n * H * 2, "copies_per_step": 1,
+                    "via": "engine step per rank: pinned H2D of the rank's x + ids, L expert-parallel block forwards, D2H of the last output"},
+            "roofline": roof, "ep_parity": ep_parity, "transport_dtype": args.ep_transport,
+            "nccl_all_to_all_baseline": ({"ms_per_step": ms_nccl, "value": tokens / (ms_nccl * 1e-3)} if nccl else None)}
 
 
 # ------------------------------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=300)
-    ap.add_argument("--warmup", type=int, default=30)
-    ap.add_argument("--workload", default="decode_bf16", choices=sorted(WORKLOADS))
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--steps", type=int, default=60)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default=HEADLINE, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--cpu-mode", default="int8", choices=["int8", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
-    ap.add_argument("--no-ep", action="store_true")
-    ap.add_argument("--ep-tokens", type=int, default=65536, help="tokens per step over ALL ranks (BASELINE config 5)")
-    ap.add_argument("--ep-transport", default="f32", choices=["f32", "bf16"],
-                    help="dtype the expert outputs travel back in (f32: bit-identical to one GPU; bf16: the reference's)")
+    ap.add_argument("--no-workloads", action="store_true", help="N = 1: only the line's own workload")
+    ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
+                    help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
+    ap.add_argument("--ep-nccl-baseline", action="store_true", help="also time the all_to_all_single exchange (eager)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    cfg_json = {"workload": wl["desc"], "hidden": wl["H"], "num_experts": wl["E"], "expert_inter": wl["I"],
-                "shared_inter": wl["S"], "top_k": wl["K"], "layers_per_step": wl["L"], "tokens_per_gpu": wl["N"],
-                "shapes": "INFERRED (SURVEY.md §8)", "parallelism": f"tokens sharded over {world} GPU(s), experts replicated",
-                "l2_policy": "L distinct layer weight sets per step (>> 126 MB L2)"}
 
     if args.impl == "reference":
         if rank != 0:
@@ -389,161 +754,94 @@ def main():
         r = cpu_reference_run(wl, args.steps, args.warmup, args.cpu_mode)
         line = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
                 "warmup": min(args.warmup, 2), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "int8" if args.cpu_mode == "int8" else "f32",
-                "data": "synthetic", "impl": "reference", "config": cfg_json,
-                "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+                "scaling": "strong", "vs_baseline": None, "dtype": "int8" if args.cpu_mode == "int8" else "f32",
+                "data": "synthetic", "impl": "reference", "config": cfg_json(wl, max(1, args.gpus)),
+                "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["threads"], "kind": r["kind"],
                                  "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         emit(line)
         return
+    if args.impl == "reference-gpu":
+        if rank != 0:
+            return
+        if not have_ref():
+            emit({"impl": "reference-gpu", "unavailable": "oracle/_ref missing (tools/install_ref.py runs in the build container)"})
+            return
+        r = reference_gpu_run(wl, args.steps, args.warmup)
+        r["impl"] = "reference-gpu"
+        emit(r)
+        return
 
+    _product_paths()
     assert torch.cuda.is_available(), "bench.py needs a GPU (use --impl reference for the CPU arm)"
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
     barrier = None
-    if world > 1 or os.environ.get("I64B_BENCH_FORCE_DIST") == "1":      # (the env is a bring-up switch: NCCL at world 1)
+    if world > 1:
         import torch.distributed as dist
-        # NCCL prints its version banner to stdout when NCCL_DEBUG is set by the environment: keep stdout to the ONE
-        # JSON line of the contract
-        # (the banner is written to file descriptor 1 directly, so fd 1 is pointed at stderr for the whole run and the
-        # JSON line goes to the saved descriptor)
+        # NCCL prints its version banner to file descriptor 1 when NCCL_DEBUG is set by the environment: keep stdout to
+        # the ONE JSON line of the contract (fd 1 points at stderr for the whole run; the line goes to the saved descriptor)
         global _JSON_FD
         sys.stdout.flush()
         _JSON_FD = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=device)
         barrier = lambda: dist.barrier()            # noqa: E731
-    from vllm_i64 import _C
+    from vllm_i64 import _C       # noqa: F401  (fails loudly when libi64b.so is missing: there is no fallback)
 
-    H, N, L = wl["H"], wl["N"], wl["L"]
-    layers = build_layers(wl, device)
-    g = torch.Generator().manual_seed(1234 + rank)
-    ids_host = torch.randint(0, wl["V"], (N,), generator=g).pin_memory()
-    x_host = torch.randn(N, H, generator=torch.Generator().manual_seed(rank)).to(torch.bfloat16).pin_memory()
-    out_host = torch.empty(N, H, dtype=torch.bfloat16).pin_memory()
-    x_dev, ids_dev = x_host.to(device), ids_host.to(device)
-    outs = [torch.empty(N, H, dtype=torch.bfloat16, device=device) for _ in range(2)]
-    ids_arg = ids_dev if wl["E"] else None
-    stream = torch.cuda.Stream(device)
-
-    def step_device(stages=_C.STAGE_ALL):
-        for i, blk in enumerate(layers):
-            blk.forward(x_dev, ids_arg, torch.bfloat16, out=outs[i & 1], stages=stages)
-
-    def step_e2e():
-        x_dev.copy_(x_host, non_blocking=True)
-        ids_dev.copy_(ids_host, non_blocking=True)
-        step_device()
-        out_host.copy_(outs[(L - 1) & 1], non_blocking=True)
-
-    # launches per step (counted by the library itself, eager pass)
-    with torch.cuda.stream(stream):
-        step_device()
-        stream.synchronize()
-        _C.launch_count_reset()
-        step_device()
-        stream.synchronize()
-    launches_per_step = _C.launch_count()
-
-    sampler = ClockSampler(local_rank)
-    ms = time_graph(step_device, args.steps, args.warmup, stream, barrier, sampler)
-    ms_e2e = time_graph(step_e2e, args.steps, args.warmup, stream, barrier)
-    tokens_step = N * L
-
-    if world > 1:
-        import torch.distributed as dist
-        t = torch.tensor([ms, ms_e2e], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = float(t[0]), float(t[1])
-    value = world * tokens_step * args.steps / (ms * 1e-3)
-    e2e_value = world * tokens_step * args.steps / (ms_e2e * 1e-3)
-
-    # per-stage timing (isolated replays of each kernel over the L layers) and the roofline of the dominant one
     pk = peaks()
-    stages_json, roof = {}, None
-    if rank == 0 and not args.no_stages:
-        sb, sf = stage_bytes(wl)
-        names = [("plan", _C.STAGE_PLAN), ("dispatch", _C.STAGE_DISPATCH), ("gemm1", _C.STAGE_GEMM1),
-                 ("requant", _C.STAGE_REQUANT), ("gemm2", _C.STAGE_GEMM2), ("combine", _C.STAGE_COMBINE)]
-        reps = max(20, min(args.steps, 100))
-        for name, bit in names:
-            if sb[name] == 0:
-                continue
-            t_ms = time_graph(lambda b=bit: step_device(b), reps, 5, stream)
-            us = t_ms * 1e3 / (reps * L)
-            gbs = sb[name] / (us * 1e-6) / 1e9
-            ent = {"us_per_launch": round(us, 3), "algorithmic_bytes": sb[name], "GBps": round(gbs, 1),
-                   "frac_hbm": round(gbs / pk["hbm"], 4)}
-            if name in sf:
-                tf = sf[name] / (us * 1e-6) / 1e12
-                ent["TFLOPs" if wl["mode"] == "bf16" else "TOPs"] = round(tf, 1)
-                ent["frac_tensor_bf16_peak"] = round(tf / pk["tf_burst"], 4)
-            stages_json[name] = ent
-        dom = max(stages_json, key=lambda k: stages_json[k]["us_per_launch"])
-        d = stages_json[dom]
-        hbm_bound = d["frac_hbm"] >= d.get("frac_tensor_bf16_peak", 0.0) / (2.0 if wl["mode"] == "int8" else 1.0)
-        kkey = {"gemm1": "i64b_gemm_kernel<%d, 1" % (1 if wl["mode"] == "int8" else 0),
-                "gemm2": "i64b_gemm_kernel<%d, 0" % (1 if wl["mode"] == "int8" else 0)}.get(dom, dom)
-        if hbm_bound:
-            roof = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": pk["hbm"], "unit": "GB/s",
-                    "frac": d["frac_hbm"], "traffic": None, "peak_source": pk["src"] + " (burst copy)"}
-        else:
-            key = "TFLOPs" if wl["mode"] == "bf16" else "TOPs"
-            peak = pk["tf_burst"] * (2.0 if wl["mode"] == "int8" else 1.0)
-            roof = {"kernel": dom, "bound": "tensor", "achieved": d[key], "peak": peak,
-                    "unit": "TFLOP/s" if wl["mode"] == "bf16" else "TOP/s", "frac": round(d[key] / peak, 4),
-                    "traffic": None, "peak_source": pk["src"] + (" bf16 burst x2 (nominal INT8:bf16 ratio)" if wl["mode"] == "int8" else " bf16 burst")}
-        if roof is not None:
-            roof["traffic"] = ncu_traffic(args.workload, kkey)
-        if layers[0].uses_fused(N):
-            # the step runs ONE fused kernel per layer; the stage list above is the unfused chain, for comparison
-            stages_json = {"unfused_chain_for_comparison": stages_json}
-        sum_us = sum(v["us_per_launch"] for v in stages_json.values() if isinstance(v, dict) and "us_per_launch" in v)
-        stages_json["_sum_us_per_layer"] = round(sum_us, 2)
-        stages_json["_step_us_per_layer"] = round(ms * 1e3 / (args.steps * L), 2)
-        # whole-block HBM roofline: algorithmic minimum bytes of the fused block per layer
-        a = 1 if wl["mode"] == "int8" else 2
-        min_bytes = ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * H * a) + N * H * 2 * 2
-        stages_json["_block_min_bytes"] = min_bytes
-        stages_json["_block_frac_hbm"] = round(min_bytes / (ms * 1e-3 / (args.steps * L)) / 1e9 / pk["hbm"], 4)
+    stream = torch.cuda.Stream(device)
+    sampler = ClockSampler(local_rank)
 
-    if rank == 0 and layers[0].uses_fused(N):
-        # dominant (only) kernel of the step: the fused layer kernel, timed live over the whole timed region
-        us = ms * 1e3 / (args.steps * L)
-        a_ = 1 if wl["mode"] == "int8" else 2
-        fb = ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * H * a_) + N * H * 2 * 2     # weights once + x in + out
-        gbs = fb / (us * 1e-6) / 1e9
-        roof = {"kernel": "i64b_fused_layer_kernel", "bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"],
-                "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4),
-                "traffic": ncu_traffic(args.workload, "i64b_fused_layer_kernel"),
-                "peak_source": pk["src"] + " (burst copy)", "algorithmic_bytes": fb, "us_per_launch": round(us, 3)}
-    ep_json = None
-    if world > 1 and wl["E"] and wl["E"] % world == 0 and not args.no_ep:
-        try:
-            ep_json = run_ep(wl, device, rank, world, args)
-        except Exception as exc:                      # the data-parallel line above stands on its own
-            ep_json = {"error": f"{type(exc).__name__}: {exc}"[:300]}
-
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_reference_run(wl, steps=3, warmup=1, mode=args.cpu_mode, max_seconds=20.0,
-                              layers_cap=4 if N > 4096 else None)
-        cpu = {"value": r["value"], "unit": UNIT, "cores": r["threads"], "kind": "port", "sample": r["sample"]}
-
-    if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if wl["mode"] == "bf16" else "int8",
-                "data": "synthetic", "config": cfg_json, "clocks": sampler.summary(),
-                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                        "h2d_bytes_per_step": N * H * 2 + N * 8, "d2h_bytes_per_step": N * H * 2},
-                "gpu_launches": int(launches_per_step) * args.steps, "gpu_launches_per_step": int(launches_per_step),
-                "roofline": roof, "stages": stages_json, "cpu_baseline": cpu, "expert_parallel": ep_json}
-        emit(line)
     if world > 1:
+        if args.workload != HEADLINE or wl["E"] % world != 0:
+            raise SystemExit(f"--gpus {world}: the multi-GPU line is the expert-parallel workload {HEADLINE} (E % N == 0)")
+        r = run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler)
+        if rank == 0:
+            line = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                    "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+                    "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                    "config": cfg_json(wl, world),
+                    "clocks": sampler.summary(), "e2e": r["e2e"],
+                    "gpu_launches": r["launches_per_step"] * args.steps, "gpu_launches_per_step": r["launches_per_step"],
+                    "roofline": r["roofline"], "cpu_baseline": None, "ep_parity": r["ep_parity"],
+                    "ep_transport_dtype": r["transport_dtype"], "nccl_all_to_all_baseline": r["nccl_all_to_all_baseline"]}
+            emit(line)
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
+        return
+
+    # ---------------------------------------------------------------- N = 1
+    int8_peak = measure_int8_peak(device)
+    head = measure_workload(args.workload, wl, device, args.steps, args.warmup, pk, int8_peak, stream, sampler=sampler,
+                            with_stages=not args.no_stages)
+    workloads = {}
+    if not args.no_workloads:
+        for name, w in WORKLOADS.items():
+            if name == args.workload:
+                continue
+            try:
+                workloads[name] = measure_workload(name, dict(w), device, w["reps"] or 20, 3, pk, int8_peak, stream,
+                                                   with_stages=not args.no_stages)
+            except Exception as exc:
+                workloads[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+    cpu = None
+    ref_gpu = None
+    if not args.no_cpu_baseline:
+        r = run_subprocess_json(["--impl", "reference", "--workload", args.workload, "--steps", "4", "--warmup", "1",
+                                 "--cpu-mode", args.cpu_mode])
+        cpu = r.get("cpu_baseline") or {"error": r.get("error", "no line")}
+        ref_gpu = run_subprocess_json(["--impl", "reference-gpu", "--workload", args.workload, "--steps", "5", "--warmup", "2"])
+    line = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic",
+            "config": cfg_json(wl, 1),
+            "clocks": sampler.summary(), "e2e": head["e2e"], "e2e_per_layer_host_call": head["e2e_per_layer_host_call"],
+            "gpu_launches": head["gpu_launches_per_step"] * args.steps, "gpu_launches_per_step": head["gpu_launches_per_step"],
+            "roofline": head.get("roofline"), "block": head["block"], "stages": head.get("stages"),
+            "measured_int8_peak": int8_peak, "cpu_baseline": cpu, "reference_gpu": ref_gpu, "workloads": workloads}
+    emit(line)
 
 
 if __name__ == "__main__":

@@ -178,6 +178,9 @@ int i64b_moe_uses_fused(const i64b_layer* layer, int64_t n);
  * widths.  0 when the single-launch kernel's limits are exceeded (n <= 1024, widths <= 4096, hidden % 64 == 0, at most
  * 8 work units per SM in its static work list, ...): such shapes take the kernel chain. */
 int i64b_fused_decode_supported(int n, int hidden, int expert_inter, int shared_inter, int num_experts, int top_k);
+/* 1 if the kernel chain on n tokens finishes the block inside the down-projection's epilogue (no separate combine
+ * launch), else 0.  Meaningless (0) when i64b_moe_uses_fused is 1. */
+int i64b_moe_fuses_combine(const i64b_layer* layer, int64_t n);
 
 /* Run only the selected stages of the forward on the workspace contents left by an earlier full forward with the
  * same (n, workspace): used by bench.py to time each kernel in isolation (roofline per stage). */
@@ -233,7 +236,13 @@ void* i64b_moe_tap(i64b_layer* layer, int what);
 /* Debug switches of a layer.  I64B_DEBUG_KEEP_TAPS: the down-projection kernel finishes the block inside the shared
  * expert's tiles (fused combine) and then has no reason to store the shared expert's own fp32 rows; with this flag it
  * stores them as well, so I64B_TAP_Y is complete (rows N*K.. = shared expert).  The block output is identical. */
-enum { I64B_DEBUG_KEEP_TAPS = 1, I64B_DEBUG_FUSE_COMBINE = 2 /* force the fused combine (default: dense FFN only) */ };
+enum {
+    I64B_DEBUG_KEEP_TAPS = 1,
+    I64B_DEBUG_FUSE_COMBINE = 2,  /* force the fused combine (default: dense FFN only) */
+    I64B_DEBUG_NO_FUSED = 4       /* never take the single-launch decode kernel on this layer (it must own the GPU: its
+                                     CTAs wait on one another, so it may not share the device with another launch of
+                                     itself — callers that run this layer on a second stream set this) */
+};
 int i64b_moe_set_debug(i64b_layer* layer, int flags);
 
 /* Cross-layer weight prefetch (decode).  `next` is the layer the engine runs after `layer` (the decoder stack calls
@@ -253,29 +262,40 @@ int i64b_debug_timeline_dump(void);
  * Replaces TokenRoutedMLP._forward_ep (layers/token_routed_i64/layer.py:209-298): counts all-to-all + .tolist() +
  * argsort + 2 x all_to_all_single each way.  One process per GPU; every rank allocates its buffers with
  * i64b_ep_alloc, exports them with i64b_ipc_export, exchanges the 64-byte handles through its own control plane
- * (torch.distributed.all_gather_object in the Python host) and maps the peers' with i64b_ipc_import.
- * Per forward (all on one stream, no host synchronisation):
- *   ids_all = all-gather of the token ids                     (host side: torch.distributed / NCCL)
- *   i64b_ep_dispatch      global plan on every rank + rows written into the owners' receive buffers
- *   i64b_ep_signal        "my rows have left"   (the replicated shared expert runs here, hiding the wait)
- *   i64b_ep_wait          every peer's rows have arrived
- *   i64b_moe_forward_dispatched   local experts on the receive buffer -> fp32 rows in this rank's y buffer
- *   i64b_ep_signal / i64b_ep_wait
+ * (torch.distributed.all_gather_object in the Python host, once) and maps the peers' with i64b_ipc_import.
+ *
+ * Layout: every receive buffer is cut into `size` regions of cap_src rows, one per SOURCE rank.  A rank plans only
+ * its OWN tokens (routing is a pure function of layer and token id); in its expert-major plan the experts of owner d
+ * are one contiguous slab, which it writes, row by row, into its region of d's buffer, and it publishes the slab's
+ * per-expert row counts in d's flags page.  No rank ever needs another rank's token ids: no id all-gather, no global
+ * plan, no split-size exchange, and ranks may bring different numbers of tokens.
+ * Per forward (all on one stream, no host synchronisation, no collective library call; CUDA-graph capturable):
+ *   i64b_ep_dispatch      local plan + rows (bf16, or int8 + fp32 scale in W8A8 mode) into the owners' buffers + counts
+ *   i64b_ep_barrier       "my rows have left" / every peer's rows have arrived   (the home rank's shared expert runs on
+ *                         a second stream meanwhile)
+ *   i64b_moe_forward_dispatched   group tables from the counts, then this rank's experts on its receive buffer ->
+ *                         per-assignment rows in this rank's y buffer (same row numbering as the receive buffer)
+ *   i64b_ep_barrier
  *   i64b_ep_combine       the home rank's weighted combine, reading the K rows of every token straight from the
  *                         owners' y buffers over NVLink (the return exchange is fused into the combine)
  * ------------------------------------------------------------------------- */
 #define I64B_EP_MAX_RANKS 8
+#define I64B_EP_FLAGS_INTS 1024    /* ints per flags page: [0,8) barrier epochs by source rank; [64, 64 + 8*64) row counts
+                                      [source rank][local expert]; zero-initialised by i64b_ep_alloc */
 typedef struct i64b_ep_ctx {
     int32_t rank, size;            /* EP rank / group size */
-    int32_t n_local;               /* tokens per rank (equal on all ranks) */
+    int32_t n_local;               /* tokens THIS rank brings to this call (ranks may differ); n_local * top_k <= cap_src */
     int32_t hidden, top_k, num_experts, vocab;
-    int32_t y_dtype;               /* dtype the expert outputs travel in: I64B_F32 (default; the EP result is then
-                                      bit-identical to the single-GPU block) or I64B_BF16 (the reference's EP path
-                                      returns expert outputs in the model dtype; halves the return traffic) */
-    int64_t cap_rows;              /* rows of every receive buffer (>= size * n_local * top_k: nothing is dropped) */
-    void* peer_xs[I64B_EP_MAX_RANKS];          /* [cap_rows, H] bf16 receive buffer of rank d, mapped here */
-    void* peer_y[I64B_EP_MAX_RANKS];           /* [cap_rows, H] y_dtype per-assignment outputs of rank d's experts */
-    int32_t* peer_flags[I64B_EP_MAX_RANKS];    /* [I64B_EP_MAX_RANKS] barrier flags of rank d (zero-initialised) */
+    int32_t y_dtype;               /* dtype the expert outputs travel back in: I64B_BF16 (the reference's EP path returns
+                                      expert outputs in the model dtype) or I64B_F32 (bit-identical to the single-GPU block) */
+    int32_t x_mode;                /* I64B_MODE_BF16: rows travel as bf16; I64B_MODE_W8A8: quantised once on the home rank,
+                                      int8 rows + one fp32 scale per row travel (half the dispatch bytes) */
+    int32_t reserved;
+    int64_t cap_src;               /* rows of the region each source rank owns in every receive buffer */
+    void* peer_xs[I64B_EP_MAX_RANKS];          /* [size * cap_src, H] bf16 | int8 receive buffer of rank d, mapped here */
+    float* peer_xs_scale[I64B_EP_MAX_RANKS];   /* [size * cap_src] fp32 row scales (W8A8 transport), else unused */
+    void* peer_y[I64B_EP_MAX_RANKS];           /* [size * cap_src, H] y_dtype per-assignment outputs of rank d's experts */
+    int32_t* peer_flags[I64B_EP_MAX_RANKS];    /* [I64B_EP_FLAGS_INTS] flags page of rank d */
     int32_t* state;                /* local, zero-initialised: [0] barrier epoch */
 } i64b_ep_ctx;
 
@@ -284,18 +304,23 @@ int i64b_ep_free(void* p);
 int i64b_ipc_export(void* p, unsigned char* handle64);     /* cudaIpcGetMemHandle */
 int i64b_ipc_import(const unsigned char* handle64, void** out);
 int i64b_ipc_close(void* p);
+/* sized for cap_src / top_k tokens, whatever n_local is */
 size_t i64b_ep_workspace_bytes(const i64b_ep_ctx* ctx);
-/* x: [n_local, H] bf16 (this rank's tokens); ids_all: int64 [size * n_local], rank-major; table_u8: [K, V] */
-int i64b_ep_dispatch(const i64b_ep_ctx* ctx, const void* x, const int64_t* ids_all, const uint8_t* table_u8,
-                     int expert_inter, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+/* x: [n_local, H] bf16 (this rank's tokens); token_ids: int64 [n_local] (this rank's); table_u8: [K, V] */
+int i64b_ep_dispatch(const i64b_ep_ctx* ctx, const void* x, const int64_t* token_ids, const uint8_t* table_u8,
+                     void* workspace, size_t workspace_bytes, i64b_stream_t stream);
 /* out[n_local, H] = routed_scale * sum_k w_k * y[owner(k,t)][row(k,t)] + shared_scale * y_shared[t] (y_shared: fp32
  * [n_local, H] or NULL); same operation order as i64b_combine */
 int i64b_ep_combine(const i64b_ep_ctx* ctx, void* ep_workspace, const float* y_shared, const float* route_weight,
                     float routed_scale, float shared_scale, void* out, int out_dtype, i64b_stream_t stream);
-int i64b_ep_signal(const i64b_ep_ctx* ctx, i64b_stream_t stream);
+/* flag barrier in peer memory: signal (system-scope release after this rank's earlier peer stores) then wait for every
+ * peer's signal of the same epoch; device-resident epochs, so a captured graph replays correctly */
+int i64b_ep_barrier(const i64b_ep_ctx* ctx, i64b_stream_t stream);
+int i64b_ep_signal(const i64b_ep_ctx* ctx, i64b_stream_t stream);    /* the two halves, for callers that put work between */
 int i64b_ep_wait(const i64b_ep_ctx* ctx, i64b_stream_t stream);
-/* `layer` holds THIS rank's experts (num_experts / size of them, no shared expert, bf16); ep_workspace is the
- * buffer i64b_ep_dispatch filled.  Runs gate|up + SwiGLU + down on the receive buffer into ctx->peer_y[rank]. */
+/* `layer` holds THIS rank's experts (num_experts / size of them, no shared expert; bf16 layer for bf16 transport, W8A8
+ * layer for int8 transport); ep_workspace is the buffer i64b_ep_dispatch used.  Runs gate|up + SwiGLU (+ re-quant) +
+ * down on the receive buffer into ctx->peer_y[rank]. */
 size_t i64b_moe_dispatched_workspace_bytes(const i64b_layer* layer, const i64b_ep_ctx* ctx);
 int i64b_moe_forward_dispatched(i64b_layer* layer, const i64b_ep_ctx* ctx, void* ep_workspace, void* workspace,
                                 size_t workspace_bytes, i64b_stream_t stream);

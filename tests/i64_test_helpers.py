@@ -34,18 +34,20 @@ def make_block(h, e, ie, s, v, k, n, seed=0, layer=0, zipf=False, pw=0.5, rs=2.0
 
 
 def to_cuda(a, dtype=None):
+    """Upload to the CURRENT CUDA device."""
     import torch
     t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
     return t if dtype is None else t.to(dtype)
 
 
-def build_gpu_block(cfg: O.MoEConfig, w: O.MoEWeights, table, mode="bf16", wq: O.MoEWeightsInt8 = None):
+def build_gpu_block(cfg: O.MoEConfig, w: O.MoEWeights, table, mode="bf16", wq: O.MoEWeightsInt8 = None, device=None):
     import torch
     from vllm_i64 import _C
     from vllm_i64.kernels.block import I64Block
     m = _C.MODE_W8A8 if mode == "int8" else _C.MODE_BF16
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     blk = I64Block(cfg.hidden_size, cfg.num_experts, cfg.expert_inter, cfg.shared_inter, cfg.vocab_size, cfg.top_k,
-                   cfg.route_weights(), cfg.routed_output_scale, cfg.shared_output_scale, m, torch.device("cuda", 0))
+                   cfg.route_weights(), cfg.routed_output_scale, cfg.shared_output_scale, m, device)
     has_sh = cfg.shared_inter > 0
     if mode == "bf16":
         blk.load_bf16(to_cuda(w.gate), to_cuda(w.up), to_cuda(w.down), *(

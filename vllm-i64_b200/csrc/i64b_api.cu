@@ -364,6 +364,12 @@ static int fuse_combine_mode() {
     return mode;
 }
 
+// does GEMM2's epilogue finish the block (no separate combine launch)?
+static bool combine_is_fused(const i64b_layer* L, int E, int K, int S) {
+    const int fmode = (L->debug & I64B_DEBUG_FUSE_COMBINE) ? 1 : fuse_combine_mode();
+    return S > 0 && fmode != 0 && (E == 0 || (fmode == 1 && K <= 2));
+}
+
 static bool fused_enabled() {
     static const bool on = !(getenv("I64B_FUSED") && atoi(getenv("I64B_FUSED")) == 0);
     return on;
@@ -437,7 +443,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     L->cv = cv;
 
     // decode-sized bf16 batches: the whole layer in ONE persistent launch (csrc/i64b_fused.cu)
-    if (fused_enabled() && !q && given_routes == nullptr && o.stage_mask == 0xFFu &&
+    if (fused_enabled() && !q && !(L->debug & I64B_DEBUG_NO_FUSED) && given_routes == nullptr && o.stage_mask == 0xFFu &&
         i64b_fused_supported((int)n, H, I, S, E, K)) {
         I64bFusedParams fp = {};
         fp.x = x;
@@ -577,8 +583,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.col_scale[1] = L->w2s_scale;
         // with a shared expert (or a dense FFN) its GEMM2 tiles finish the block: they pull the routed rows of
         // their tokens and write the combined output, so there is no separate combine pass
-        const int fmode = (L->debug & I64B_DEBUG_FUSE_COMBINE) ? 1 : fuse_combine_mode();
-        combine_fused = S > 0 && fmode != 0 && (E == 0 || (fmode == 1 && K <= 2));
+        combine_fused = combine_is_fused(L, E, K, S);
         if (combine_fused) {
             gp.fuse_combine = 1;
             gp.keep_shared_y = (L->debug & I64B_DEBUG_KEEP_TAPS) ? 1 : 0;
@@ -631,9 +636,14 @@ int i64b_fused_decode_supported(int n, int hidden, int expert_inter, int shared_
 }
 
 int i64b_moe_uses_fused(const i64b_layer* L, int64_t n) {
-    if (!L || !L->loaded || L->cfg.mode != I64B_MODE_BF16 || !fused_enabled() || n > (1 << 20)) return 0;
+    if (!L || !L->loaded || L->cfg.mode != I64B_MODE_BF16 || !fused_enabled() || (L->debug & I64B_DEBUG_NO_FUSED) || n > (1 << 20)) return 0;
     const i64b_moe_config& c = L->cfg;
     return i64b_fused_supported((int)n, c.hidden_size, c.expert_inter, c.shared_inter, c.num_experts, c.top_k);
+}
+
+int i64b_moe_fuses_combine(const i64b_layer* L, int64_t n) {
+    if (!L || !L->loaded || i64b_moe_uses_fused(L, n)) return 0;
+    return combine_is_fused(L, L->cfg.num_experts, L->cfg.top_k, L->cfg.shared_inter) ? 1 : 0;
 }
 
 int i64b_moe_forward_stages(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype,
@@ -667,72 +677,122 @@ size_t i64b_moe_workspace_bytes_routed(const i64b_layer* L, int64_t max_tokens, 
 }
 
 // ---- expert-parallel local compute (csrc/i64b_ep.cu holds the exchange)
-void i64b_ep_group_tables(const i64b_ep_ctx* c, void* workspace, const I64bGroup** g1, const I64bGroup** g2);
+int i64b_ep_build_groups(const i64b_ep_ctx* c, void* ep_workspace, int expert_inter, const I64bGroup** g1,
+                         const I64bGroup** g2, int* num_groups, cudaStream_t stream);
+
+struct DispatchedWs {
+    uint8_t* inter;         // [rows, I] bf16 | int8
+    int32_t* q14;           // W8A8: [rows, I] int32
+    int32_t* amax;          // W8A8: [rows, amax_ld]
+    float* inter_scale;     // W8A8: [rows]
+    int amax_ld;
+    size_t bytes;
+};
+static DispatchedWs carve_dispatched(const i64b_layer* L, const i64b_ep_ctx* c, void* workspace) {
+    DispatchedWs w;
+    uint8_t* base = workspace ? reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~uintptr_t(1023))
+                              : nullptr;
+    const size_t rows = (size_t)c->cap_src * c->size;
+    const bool q = L->cfg.mode == I64B_MODE_W8A8;
+    const int I = L->cfg.expert_inter;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        uint8_t* r = base ? base + off : nullptr;
+        off += align256(bytes > 0 ? bytes : 16);
+        return r;
+    };
+    w.inter = take(rows * I * L->elt);
+    w.amax_ld = (I + 31) / 32 + 1;
+    w.q14 = reinterpret_cast<int32_t*>(take(q ? rows * I * sizeof(int32_t) : 0));
+    w.amax = reinterpret_cast<int32_t*>(take(q ? rows * w.amax_ld * sizeof(int32_t) : 0));
+    w.inter_scale = reinterpret_cast<float*>(take(q ? rows * sizeof(float) : 0));
+    w.bytes = off;
+    return w;
+}
 
 size_t i64b_moe_dispatched_workspace_bytes(const i64b_layer* L, const i64b_ep_ctx* c) {
     if (!L || !c) return 0;
-    return align256((size_t)c->cap_rows * L->cfg.expert_inter * 2) + 2048;
+    return carve_dispatched(L, c, nullptr).bytes + 2048;
 }
 
 int i64b_moe_forward_dispatched(i64b_layer* L, const i64b_ep_ctx* c, void* ep_workspace, void* workspace,
                                 size_t workspace_bytes, i64b_stream_t stream) {
     I64B_CHECK(L && c && ep_workspace && workspace, I64B_ERR_ARG, "null pointer");
-    I64B_CHECK(L->loaded && L->cfg.mode == I64B_MODE_BF16, I64B_ERR_STATE, "expert-parallel path: bf16 layer with loaded weights");
+    I64B_CHECK(L->loaded, I64B_ERR_STATE, "expert-parallel path: weights not loaded");
     const i64b_moe_config& cfg = L->cfg;
+    I64B_CHECK(cfg.mode == c->x_mode, I64B_ERR_ARG, "layer mode %d does not match the transport mode %d", cfg.mode, c->x_mode);
     I64B_CHECK(cfg.num_experts * c->size == c->num_experts && cfg.hidden_size == c->hidden, I64B_ERR_ARG,
                "layer holds %d experts, EP context expects %d / %d", cfg.num_experts, c->num_experts, c->size);
-    I64B_CHECK(c->size <= 8, I64B_ERR_ARG, "at most 8 EP ranks");
+    I64B_CHECK(c->size <= I64B_EP_MAX_RANKS, I64B_ERR_ARG, "at most %d EP ranks", I64B_EP_MAX_RANKS);
     I64B_CHECK(workspace_bytes >= i64b_moe_dispatched_workspace_bytes(L, c), I64B_ERR_WORKSPACE, "workspace too small");
-    if (c->n_local == 0) return I64B_OK;
-    const int E = cfg.num_experts, H = cfg.hidden_size, I = cfg.expert_inter;
-    uint8_t* inter = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~uintptr_t(1023));
+    const bool q = cfg.mode == I64B_MODE_W8A8;
+    const int H = cfg.hidden_size, I = cfg.expert_inter;
+    const int64_t cap_rows = c->cap_src * c->size;
+    const DispatchedWs w = carve_dispatched(L, c, workspace);
     void* xs = c->peer_xs[c->rank];
-    const int64_t key = -(c->cap_rows + 7);
-    if (L->cached_ws != xs || L->cached_n != key || L->cached_x != inter) {
-        int rc = i64b_encode_tmap(&L->tm_xs, xs, false, c->cap_rows, H, (int64_t)H * 2, 128);
+    const int64_t key = -(cap_rows + 7);
+    if (L->cached_ws != xs || L->cached_n != key || L->cached_x != w.inter) {
+        int rc = i64b_encode_tmap(&L->tm_xs, xs, q, cap_rows, H, (int64_t)H * L->elt, 128);
         if (rc) return rc;
-        rc = i64b_encode_tmap(&L->tm_inter_r, inter, false, c->cap_rows, I, (int64_t)I * 2, 128);
+        rc = i64b_encode_tmap(&L->tm_inter_r, w.inter, q, cap_rows, I, (int64_t)I * L->elt, 128);
         if (rc) return rc;
         L->cached_ws = xs;
         L->cached_n = key;
-        L->cached_x = inter;
+        L->cached_x = w.inter;
         L->cached_x_n = -1;
     }
-    const I64bGroup *g1 = nullptr, *g2 = nullptr;
-    i64b_ep_group_tables(c, ep_workspace, &g1, &g2);
     cudaStream_t s = (cudaStream_t)stream;
-    // expected load (balanced routing): the real row counts live on the device only
-    const int64_t rows_exp = (int64_t)c->n_local * c->top_k;
-    const int64_t mt = rows_exp / 128 + E, pt = rows_exp / 256 + E;
+    const I64bGroup *g1 = nullptr, *g2 = nullptr;
+    int ng = 0;
+    int rc = i64b_ep_build_groups(c, ep_workspace, I, &g1, &g2, &ng, s);
+    if (rc) return rc;
+    // expected load (balanced routing): the real row counts live on the device only; one group per (expert, source)
+    // (this rank's own assignment count stands in for the rows it receives; a rank without tokens still runs its experts)
+    const int64_t rows_exp = (int64_t)c->n_local * c->top_k > 0 ? (int64_t)c->n_local * c->top_k : 1;
+    const int64_t mt = rows_exp / 128 + (ng - 1), pt = rows_exp / 256 + (ng - 1);
     {
         const int n_mma = pick_nmma(mt, I, 0, 0, true, "I64B_GEMM1_NMMA");
-        const bool pairs = use_cta_pairs(n_mma, rows_exp, E);
+        const int bn = n_mma / 2;
+        const bool pairs = use_cta_pairs(n_mma, rows_exp, ng - 1);
         I64bGemmParams gp = {};
         gp.groups = g1;
-        gp.num_groups = E + 1;
+        gp.num_groups = ng;
         gp.k[0] = gp.k[1] = H;
-        gp.out[0] = gp.out[1] = inter;
+        gp.out[0] = gp.out[1] = q ? (void*)w.q14 : (void*)w.inter;
         gp.ld_out[0] = gp.ld_out[1] = I;
+        gp.row_scale[0] = gp.row_scale[1] = c->peer_xs_scale[c->rank];
+        gp.col_scale[0] = gp.col_scale[1] = L->w13_scale;
+        gp.amax_part[0] = gp.amax_part[1] = w.amax;
+        gp.amax_ld[0] = gp.amax_ld[1] = w.amax_ld;
+        gp.silu_lut = L->silu_lut;
         const int wi = nmma_index(n_mma);
         // the grid is persistent: any upper bound >= the SM count gives the full machine
-        int rc = i64b_launch_gemm(false, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp,
-                                  (pairs ? pt : mt) * ((I + n_mma / 2 - 1) / (n_mma / 2)) * c->size, s);
+        rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_xs, L->tm_w13[wi], L->tm_w13[wi], gp,
+                              (pairs ? pt : mt) * ((I + bn - 1) / bn), s);
         if (rc) return rc;
+        if (q) {
+            const int nh = bn >= 64 ? 2 : 1;
+            rc = i64b_run_requant_q14(w.q14, w.amax, w.amax_ld, ((I + bn - 1) / bn) * nh, reinterpret_cast<int8_t*>(w.inter),
+                                      w.inter_scale, cap_rows, I, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, s, g1, ng - 1);
+            if (rc) return rc;
+        }
     }
     {
         const int n_mma = pick_nmma(mt, H, 0, 0, false, "I64B_GEMM2_NMMA");
-        const bool pairs = use_cta_pairs(n_mma, rows_exp, E);
+        const bool pairs = use_cta_pairs(n_mma, rows_exp, ng - 1);
         I64bGemmParams gp = {};
         gp.groups = g2;
-        gp.num_groups = E + 1;
+        gp.num_groups = ng;
         gp.k[0] = gp.k[1] = I;
         gp.out[0] = gp.out[1] = c->peer_y[c->rank];
         gp.ld_out[0] = gp.ld_out[1] = H;
         gp.out_dtype = c->y_dtype;
-        gp.epi = I64B_EPI_F32;
+        gp.epi = q ? I64B_EPI_DEQUANT : I64B_EPI_F32;
+        gp.row_scale[0] = gp.row_scale[1] = w.inter_scale;
+        gp.col_scale[0] = gp.col_scale[1] = L->w2r_scale;
         const int wi = pairs ? 1 : nmma_index(n_mma);
-        int rc = i64b_launch_gemm(false, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_r, L->tm_w2r[wi],
-                                  L->tm_w2r[wi], gp, (pairs ? pt : mt) * ((H + n_mma - 1) / n_mma) * c->size, s);
+        rc = i64b_launch_gemm(q, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_r, L->tm_w2r[wi],
+                              L->tm_w2r[wi], gp, (pairs ? pt : mt) * ((H + n_mma - 1) / n_mma), s);
         if (rc) return rc;
     }
     return I64B_OK;

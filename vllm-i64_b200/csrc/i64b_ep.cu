@@ -2,18 +2,22 @@
 //
 // Reference: TokenRoutedMLP._forward_ep (layers/token_routed_i64/layer.py:209-298) — counts all-to-all + .tolist()
 // host sync + stable sort by rank + two blocking all_to_all_single calls each way.  Here:
-//   * routing is a pure function of (layer, token id), so after ONE small all-gather of the token ids every rank
-//     computes the GLOBAL dispatch plan itself (the same plan kernels as on one GPU, over G*n tokens): no counts
-//     exchange, no host round trip, no sort;
+//   * routing is a pure function of (layer, token id), so a rank plans ONLY ITS OWN tokens with the single-GPU plan
+//     kernels.  In that expert-major plan the experts of owner d form one contiguous slab; every receive buffer is cut
+//     into one region per SOURCE rank, so the slab goes, row by row, into "my" region of d's buffer and nobody needs
+//     anybody else's token ids: no id all-gather, no global plan, no split-size exchange, ranks may bring different
+//     numbers of tokens;
 //   * dispatch = one kernel that reads each local activation row once and writes it with 128-bit stores straight
-//     into the OWNING rank's expert-contiguous receive buffer (peer-mapped with CUDA IPC) and remembers, locally,
-//     (owner rank, row) of every assignment;
-//   * the return path is fused into the COMBINE: the home rank's combine kernel reads the K per-assignment fp32 rows
-//     of each token straight from the owners' output buffers over NVLink (4 KB contiguous per row, 512 B per warp
+//     into the OWNING rank's receive buffer (peer-mapped with CUDA IPC) — as bf16, or quantised once on the home rank
+//     and sent as int8 + one fp32 scale per row (W8A8: half the bytes) — remembers, locally, (owner rank, row) of every
+//     assignment, and publishes the per-expert row counts of each slab in the owner's flags page;
+//   * the owner builds its GEMM group table (one group per (local expert, source rank)) from those counts;
+//   * the return path is fused into the COMBINE: the home rank's combine kernel reads the K per-assignment rows of
+//     each token straight from the owners' output buffers over NVLink (2-4 KB contiguous per row, 512 B per warp
 //     instruction).  (Measured alternative, rejected: storing each output row to its home from the down-projection's
 //     epilogue moves 64-byte segments over NVLink and ran at ~175 GB/s.);
-//   * the only synchronisation is a flag barrier in peer memory (signal / wait kernels, system-scope release /
-//     acquire, monotonically increasing epochs kept on the device: graph-capturable, no host state).
+//   * the only synchronisation is a flag barrier in peer memory (system-scope release / acquire, monotonically
+//     increasing epochs kept on the device: graph-capturable, no host state).
 #include <stdlib.h>
 
 #include "i64b_gemm.cuh"
@@ -22,6 +26,8 @@
 namespace {
 
 constexpr int kEpWarps = 4;
+constexpr int kCountsBase = 64;       // flags page: ints [64 + src * 64 + local expert] = rows of that slab segment
+constexpr int kCountsStride = 64;
 
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
     asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
@@ -31,60 +37,113 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
     asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
-// One warp per LOCAL token: K peer-memory row copies + K tags.  The plan was computed over all G*n tokens; this
-// rank's token t is global token rank*n + t.
+// One warp per LOCAL token: K peer-memory row copies + K (owner, row) tags.  Block 0 also publishes the slab counts.
+template <bool kQuant>
 __global__ void __launch_bounds__(kEpWarps * 32)
 ep_dispatch_kernel(const i64b_ep_ctx c, const void* __restrict__ x, const I64bPlanWs ws, int64_t* __restrict__ loc) {
     pdl_launch_dependents();
     pdl_wait_prior();
     const int lane = threadIdx.x & 31;
+    const int K = c.top_k, E = c.num_experts, bins = K * E, local_e = E / c.size;
+    if (blockIdx.x == 0) {
+        // rows this rank sends to expert e (all routes): a store into the owner's flags page; the barrier's system-scope
+        // release publishes it together with the rows
+        for (int e = threadIdx.x; e < E; e += blockDim.x) {
+            const int rows = c.n_local > 0 ? ws.group_start[e + 1] - ws.group_start[e] : 0;
+            c.peer_flags[e / local_e][kCountsBase + c.rank * kCountsStride + e % local_e] = rows;
+        }
+    }
     const int64_t t = (int64_t)blockIdx.x * kEpWarps + (threadIdx.x >> 5);
     if (t >= c.n_local) return;
-    const int K = c.top_k, E = c.num_experts, bins = K * E, local_e = E / c.size;
-    const int64_t n_glob = (int64_t)c.n_local * c.size, gt = (int64_t)c.rank * c.n_local + t;
+    const int64_t n = c.n_local;
     int my_rank = 0, my_row = 0;
     if (lane < K) {
-        const uint32_t pk = ws.packed[(int64_t)lane * n_glob + gt];
+        const uint32_t pk = ws.packed[(int64_t)lane * n + t];
         const int e = pk & 0xFF;
         const int bin = lane * E + e;
-        const int in_tile = (int)(pk >> 8) + ws.tile_counts[(gt / I64B_PLAN_TILE) * bins + bin];
-        const int dest = ws.group_start[e] + ws.route_base[bin] + in_tile;      // row in the global merged layout
+        const int in_tile = (int)(pk >> 8) + ws.tile_counts[(t / I64B_PLAN_TILE) * bins + bin];
+        const int dest = ws.group_start[e] + ws.route_base[bin] + in_tile;          // row in this rank's merged layout
         my_rank = e / local_e;
-        my_row = dest - ws.group_start[my_rank * local_e];                      // row in the owner's receive buffer
-        loc[(int64_t)lane * c.n_local + t] = ((int64_t)my_rank << 32) | (int64_t)my_row;
+        my_row = (int)((int64_t)c.rank * c.cap_src) + dest - ws.group_start[my_rank * local_e];   // row in the owner's buffer
+        loc[(int64_t)lane * n + t] = ((int64_t)my_rank << 32) | (int64_t)my_row;
     }
     const int H = c.hidden, nvec = H / 8;
     const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const __nv_bfloat16*>(x) + t * H);
-    int4* dst[I64B_MAX_TOPK];
+    int dk[I64B_MAX_TOPK], rowk[I64B_MAX_TOPK];
 #pragma unroll
     for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-        const int d = __shfl_sync(0xffffffffu, my_rank, k), row = __shfl_sync(0xffffffffu, my_row, k);
-        dst[k] = k < K ? reinterpret_cast<int4*>(reinterpret_cast<__nv_bfloat16*>(c.peer_xs[d]) + (int64_t)row * H) : nullptr;
+        dk[k] = __shfl_sync(0xffffffffu, my_rank, k);
+        rowk[k] = __shfl_sync(0xffffffffu, my_row, k);
     }
-    for (int i = lane; i < nvec; i += 32) {
-        const int4 v = ld_nc_16(src + i);
+    if constexpr (!kQuant) {
+        int4* dst[I64B_MAX_TOPK];
 #pragma unroll
         for (int k = 0; k < I64B_MAX_TOPK; ++k)
-            if (k < K) dst[k][i] = v;
+            dst[k] = k < K ? reinterpret_cast<int4*>(reinterpret_cast<__nv_bfloat16*>(c.peer_xs[dk[k]]) + (int64_t)rowk[k] * H) : nullptr;
+        for (int i = lane; i < nvec; i += 32) {
+            const int4 v = ld_nc_16(src + i);
+#pragma unroll
+            for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                if (k < K) dst[k][i] = v;
+        }
+    } else {
+        // quantize_activations_int8 (core/quantization.py:103-116) once per token; the K copies share row and scale
+        float amax = 0.0f;
+        for (int i = lane; i < nvec; i += 32) {
+            const int4 v = __ldg(src + i);
+            const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) amax = fmaxf(amax, fmaxf(fabsf(bf16lo(w[j])), fabsf(bf16hi(w[j]))));
+        }
+        amax = warp_max(amax);
+        const float scale = quant_scale(amax);
+        const float rcp = quant_rcp(scale);
+        int8_t* dst[I64B_MAX_TOPK];
+#pragma unroll
+        for (int k = 0; k < I64B_MAX_TOPK; ++k)
+            dst[k] = k < K ? reinterpret_cast<int8_t*>(c.peer_xs[dk[k]]) + (int64_t)rowk[k] * H : nullptr;
+        for (int i = lane; i < nvec; i += 32) {
+            const int4 v = __ldg(src + i);
+            const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+            uint32_t pk[2] = {0, 0};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t q0 = (uint32_t)(quant_q_rcp(bf16lo(w[j]), scale, rcp) & 0xFF);
+                const uint32_t q1 = (uint32_t)(quant_q_rcp(bf16hi(w[j]), scale, rcp) & 0xFF);
+                pk[j >> 1] |= (q0 | (q1 << 8)) << ((j & 1) * 16);
+            }
+#pragma unroll
+            for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                if (k < K) *reinterpret_cast<int2*>(dst[k] + i * 8) = make_int2((int)pk[0], (int)pk[1]);
+        }
+        if (lane < K) c.peer_xs_scale[my_rank][my_row] = scale;
     }
 }
 
-// GEMM group tables of THIS rank's experts in its receive buffer (one small block)
-__global__ void ep_groups_kernel(const i64b_ep_ctx c, const I64bPlanWs ws, int expert_inter) {
+// GEMM group tables of THIS rank's experts over its receive buffer: one group per (local expert, source rank), built
+// from the counts the sources published (one small block, after the barrier)
+__global__ void ep_groups_kernel(const i64b_ep_ctx c, I64bGroup* g1, I64bGroup* g2, int expert_inter) {
     pdl_launch_dependents();
     pdl_wait_prior();
-    const int local_e = c.num_experts / c.size, first = c.rank * local_e;
-    const int le = threadIdx.x;
-    if (le < local_e) {
-        const int e = first + le;
-        const int start = ws.group_start[e] - ws.group_start[first];
-        const int rows = ws.group_start[e + 1] - ws.group_start[e];
-        ws.groups1[le] = I64bGroup{start, rows, le * 2 * expert_inter, expert_inter, 0, start, 0, 0};
-        ws.groups2[le] = I64bGroup{start, rows, le * c.hidden, c.hidden, 0, start, 0, 0};
-    } else if (le == local_e) {      // no shared expert on this path (it runs replicated, on the home rank)
-        ws.groups1[le] = I64bGroup{0, 0, 0, 16, 1, 0, 0, 0};
-        ws.groups2[le] = I64bGroup{0, 0, 0, 16, 1, 0, 0, 0};
+    const int local_e = c.num_experts / c.size;
+    const int ng = local_e * c.size;
+    const int* counts = c.peer_flags[c.rank] + kCountsBase;
+    for (int i = threadIdx.x; i <= ng; i += blockDim.x) {
+        if (i == ng) {      // no shared expert on this path (it runs on the home rank)
+            g1[i] = I64bGroup{0, 0, 0, 16, 1, 0, 0, 0};
+            g2[i] = I64bGroup{0, 0, 0, 16, 1, 0, 0, 0};
+            continue;
+        }
+        const int le = i / c.size, r = i % c.size;
+        int off = 0;
+        for (int j = 0; j < le; ++j) off += counts[r * kCountsStride + j];
+        const int rows = counts[r * kCountsStride + le];
+        const int start = (int)((int64_t)r * c.cap_src) + off;
+        g1[i] = I64bGroup{start, rows, le * 2 * expert_inter, expert_inter, 0, start, 0, 0};
+        g2[i] = I64bGroup{start, rows, le * c.hidden, c.hidden, 0, start, 0, 0};
     }
 }
 
@@ -160,29 +219,32 @@ __global__ void __launch_bounds__(256) ep_combine_kernel(const i64b_ep_ctx c, co
 
 // Flag barrier in peer memory.  signal: epoch = ++state[0]; flags[rank] of every peer := epoch (release.sys, after
 // a system fence that orders this rank's earlier peer stores).  wait: until every flags[d] of this rank >= epoch.
-__global__ void ep_signal_kernel(const i64b_ep_ctx c) {
+// kMode: 1 signal, 2 wait, 3 both in one launch.
+template <int kMode>
+__global__ void ep_barrier_kernel(const i64b_ep_ctx c) {
+    pdl_launch_dependents();
     pdl_wait_prior();
     __shared__ int epoch;
-    if (threadIdx.x == 0) epoch = ++c.state[0];
+    if (threadIdx.x == 0) epoch = (kMode & 1) ? ++c.state[0] : c.state[0];
     __syncthreads();
     if ((int)threadIdx.x < c.size) {
-        __threadfence_system();
-        st_release_sys(c.peer_flags[threadIdx.x] + c.rank, epoch);
-    }
-}
-__global__ void ep_wait_kernel(const i64b_ep_ctx c) {
-    pdl_wait_prior();
-    if ((int)threadIdx.x < c.size) {
-        const int epoch = c.state[0];
-        const long long t0 = clock64();
-        while (ld_acquire_sys(c.peer_flags[c.rank] + threadIdx.x) < epoch) {
-            __nanosleep(100);
-            if (clock64() - t0 > 20000000000ll) __trap();       // ~10 s: a peer died; do not hang the GPU
+        if (kMode & 1) {
+            __threadfence_system();
+            st_release_sys(c.peer_flags[threadIdx.x] + c.rank, epoch);
+        }
+        if (kMode & 2) {
+            const long long t0 = clock64();
+            while (ld_acquire_sys(c.peer_flags[c.rank] + threadIdx.x) < epoch) {
+                __nanosleep(100);
+                if (clock64() - t0 > 20000000000ll) __trap();       // ~10 s: a peer died; do not hang the GPU
+            }
         }
     }
 }
 
 }  // namespace
+
+static size_t ep_align(size_t v) { return (v + 255) & ~size_t(255); }
 
 static int ep_check(const i64b_ep_ctx* c) {
     I64B_CHECK(c != nullptr, I64B_ERR_ARG, "null EP context");
@@ -192,15 +254,43 @@ static int ep_check(const i64b_ep_ctx* c) {
                "num_experts (%d) must be divisible by ep_size (%d)", c->num_experts, c->size);
     I64B_CHECK(c->top_k >= 1 && c->top_k <= I64B_MAX_TOPK, I64B_ERR_ARG, "top_k %d out of range", c->top_k);
     I64B_CHECK(c->n_local >= 0 && c->hidden > 0 && c->hidden % 8 == 0, I64B_ERR_ARG, "bad EP geometry");
-    I64B_CHECK(c->cap_rows >= (int64_t)c->n_local * c->size * c->top_k, I64B_ERR_ARG,
-               "receive capacity %lld rows < worst case %lld", (long long)c->cap_rows,
-               (long long)c->n_local * c->size * c->top_k);
+    I64B_CHECK(c->cap_src >= (int64_t)c->n_local * c->top_k && c->cap_src >= 1, I64B_ERR_ARG,
+               "this rank's region holds %lld rows < %lld (n_local * top_k): reserve more tokens",
+               (long long)c->cap_src, (long long)c->n_local * c->top_k);
+    I64B_CHECK(c->cap_src * c->size < ((int64_t)1 << 31), I64B_ERR_ARG, "receive buffer too large for int32 rows");
+    I64B_CHECK(c->x_mode == I64B_MODE_BF16 || c->x_mode == I64B_MODE_W8A8, I64B_ERR_ARG, "x_mode must be BF16 or W8A8");
     for (int d = 0; d < c->size; ++d)
-        I64B_CHECK(c->peer_xs[d] && c->peer_y[d] && c->peer_flags[d], I64B_ERR_ARG,
-                   "peer buffers of rank %d not mapped", d);
+        I64B_CHECK(c->peer_xs[d] && c->peer_y[d] && c->peer_flags[d] && (c->x_mode == I64B_MODE_BF16 || c->peer_xs_scale[d]),
+                   I64B_ERR_ARG, "peer buffers of rank %d not mapped", d);
     I64B_CHECK(c->state != nullptr, I64B_ERR_ARG, "EP state missing");
     I64B_CHECK(c->y_dtype == I64B_F32 || c->y_dtype == I64B_BF16, I64B_ERR_ARG, "y_dtype must be F32 or BF16");
     return I64B_OK;
+}
+
+// EP workspace: local plan | (owner, row) of this rank's assignments | the owner-side GEMM group tables
+struct EpWs {
+    I64bPlanWs plan;
+    int64_t* loc;
+    I64bGroup *g1, *g2;
+    size_t bytes;
+};
+static EpWs ep_carve(const i64b_ep_ctx* c, void* workspace) {
+    EpWs w;
+    uint8_t* base = workspace ? reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255))
+                              : nullptr;
+    const int64_t n_max = c->cap_src / c->top_k > 0 ? c->cap_src / c->top_k : 1;
+    // the plan arrays are indexed with the call's n_local (packed is [K, n]); carving for n_max gives every array its
+    // largest size, and the arrays after `packed` do not move with n
+    w.plan = i64b_plan_ws_carve(base, n_max, c->top_k, c->num_experts);
+    size_t off = ep_align(w.plan.bytes);
+    w.loc = reinterpret_cast<int64_t*>(base ? base + off : nullptr);
+    off += ep_align(sizeof(int64_t) * (size_t)c->top_k * (size_t)n_max);
+    w.g1 = reinterpret_cast<I64bGroup*>(base ? base + off : nullptr);
+    off += ep_align(sizeof(I64bGroup) * I64B_MAX_GROUPS);
+    w.g2 = reinterpret_cast<I64bGroup*>(base ? base + off : nullptr);
+    off += ep_align(sizeof(I64bGroup) * I64B_MAX_GROUPS);
+    w.bytes = off;
+    return w;
 }
 
 extern "C" {
@@ -236,44 +326,40 @@ int i64b_ipc_close(void* p) {
 }
 
 size_t i64b_ep_workspace_bytes(const i64b_ep_ctx* c) {
-    if (!c) return 0;
-    return i64b_plan_ws_carve(nullptr, (int64_t)c->n_local * c->size, c->top_k, c->num_experts).bytes + 1024 +
-           sizeof(int64_t) * (size_t)c->top_k * (size_t)(c->n_local > 0 ? c->n_local : 1);
-}
-// (owner, row) table of this rank's assignments, behind the plan in the EP workspace
-static int64_t* ep_loc(const i64b_ep_ctx* c, void* workspace) {
-    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
-    const size_t plan = i64b_plan_ws_carve(nullptr, (int64_t)c->n_local * c->size, c->top_k, c->num_experts).bytes;
-    return reinterpret_cast<int64_t*>(base + ((plan + 255) & ~size_t(255)));
+    if (!c || c->top_k < 1 || c->cap_src < 1) return 0;
+    return ep_carve(c, nullptr).bytes + 1024;
 }
 
-int i64b_ep_dispatch(const i64b_ep_ctx* c, const void* x, const int64_t* ids_all, const uint8_t* table_u8,
-                     int expert_inter, void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
+int i64b_ep_dispatch(const i64b_ep_ctx* c, const void* x, const int64_t* token_ids, const uint8_t* table_u8,
+                     void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
     int rc = ep_check(c);
     if (rc) return rc;
-    I64B_CHECK(x && ids_all && table_u8 && workspace, I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(table_u8 && workspace && (c->n_local == 0 || (x && token_ids)), I64B_ERR_ARG, "null pointer");
     I64B_CHECK(workspace_bytes >= i64b_ep_workspace_bytes(c), I64B_ERR_WORKSPACE, "EP plan workspace too small");
-    if (c->n_local == 0) return I64B_OK;
-    void* base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
-    const int64_t n_glob = (int64_t)c->n_local * c->size;
-    const I64bPlanWs ws = i64b_plan_ws_carve(base, n_glob, c->top_k, c->num_experts);
-    I64bPlanArgs pa = {};
-    pa.mode = I64B_ROUTE_TABLE;
-    pa.token_ids = ids_all;
-    pa.table = table_u8;
-    pa.n = n_glob;
-    pa.vocab = c->vocab;
-    pa.top_k = c->top_k;
-    pa.num_experts = c->num_experts;
-    pa.expert_inter = expert_inter;
-    pa.hidden = c->hidden;
-    rc = i64b_run_plan(pa, ws, (cudaStream_t)stream);
-    if (rc) return rc;
+    I64B_CHECK(c->num_experts / c->size <= kCountsStride, I64B_ERR_ARG, "too many local experts");
+    const EpWs w = ep_carve(c, workspace);
     cudaStream_t s = (cudaStream_t)stream;
-    I64B_CUDA(i64b_launch(ep_dispatch_kernel, dim3((int)ceil_div64(c->n_local, kEpWarps)), dim3(kEpWarps * 32), 0, s, *c,
-                          x, ws, ep_loc(c, workspace)));
-    I64B_CUDA(i64b_launch(ep_groups_kernel, dim3(1), dim3(I64B_MAX_EXPERTS + 32), 0, s, *c, ws, expert_inter));
-    i64b_count_launch(2);
+    if (c->n_local > 0) {
+        I64bPlanArgs pa = {};
+        pa.mode = I64B_ROUTE_TABLE;
+        pa.token_ids = token_ids;
+        pa.table = table_u8;
+        pa.n = c->n_local;
+        pa.vocab = c->vocab;
+        pa.top_k = c->top_k;
+        pa.num_experts = c->num_experts;
+        pa.hidden = c->hidden;
+        pa.ticket = c->state + 16;      // self-resetting: the last rank CTA finalises the plan in the same launch
+        rc = i64b_run_plan(pa, w.plan, s);
+        if (rc) return rc;
+    }
+    // a rank without tokens still publishes its (zero) counts: one block
+    const int grid = (int)ceil_div64(c->n_local > 0 ? c->n_local : 1, kEpWarps);
+    if (c->x_mode == I64B_MODE_W8A8)
+        I64B_CUDA(i64b_launch(ep_dispatch_kernel<true>, dim3(grid), dim3(kEpWarps * 32), 0, s, *c, x, w.plan, w.loc));
+    else
+        I64B_CUDA(i64b_launch(ep_dispatch_kernel<false>, dim3(grid), dim3(kEpWarps * 32), 0, s, *c, x, w.plan, w.loc));
+    i64b_count_launch(1);
     return I64B_OK;
 }
 
@@ -281,12 +367,12 @@ int i64b_ep_combine(const i64b_ep_ctx* c, void* ep_workspace, const float* y_sha
                     float routed_scale, float shared_scale, void* out, int out_dtype, i64b_stream_t stream) {
     int rc = ep_check(c);
     if (rc) return rc;
-    I64B_CHECK(ep_workspace && route_weight && out, I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(ep_workspace && route_weight && (out || c->n_local == 0), I64B_ERR_ARG, "null pointer");
     I64B_CHECK(out_dtype == I64B_BF16 || out_dtype == I64B_F32, I64B_ERR_ARG, "unsupported output dtype");
     I64B_CHECK(c->hidden % 4 == 0, I64B_ERR_ARG, "hidden size must be a multiple of 4");
     if (c->n_local == 0) return I64B_OK;
     EpCombineArgs a = {};
-    a.loc = ep_loc(c, ep_workspace);
+    a.loc = ep_carve(c, ep_workspace).loc;
     a.y_shared = y_shared;
     for (int k = 0; k < I64B_MAX_TOPK; ++k) a.w[k] = k < c->top_k ? route_weight[k] : 0.0f;
     a.routed_scale = routed_scale;
@@ -305,24 +391,37 @@ int i64b_ep_combine(const i64b_ep_ctx* c, void* ep_workspace, const float* y_sha
 int i64b_ep_signal(const i64b_ep_ctx* c, i64b_stream_t stream) {
     int rc = ep_check(c);
     if (rc) return rc;
-    I64B_CUDA(i64b_launch(ep_signal_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, *c));
+    I64B_CUDA(i64b_launch(ep_barrier_kernel<1>, dim3(1), dim3(32), 0, (cudaStream_t)stream, *c));
     i64b_count_launch(1);
     return I64B_OK;
 }
 int i64b_ep_wait(const i64b_ep_ctx* c, i64b_stream_t stream) {
     int rc = ep_check(c);
     if (rc) return rc;
-    I64B_CUDA(i64b_launch(ep_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, *c));
+    I64B_CUDA(i64b_launch(ep_barrier_kernel<2>, dim3(1), dim3(32), 0, (cudaStream_t)stream, *c));
+    i64b_count_launch(1);
+    return I64B_OK;
+}
+int i64b_ep_barrier(const i64b_ep_ctx* c, i64b_stream_t stream) {
+    int rc = ep_check(c);
+    if (rc) return rc;
+    I64B_CUDA(i64b_launch(ep_barrier_kernel<3>, dim3(1), dim3(32), 0, (cudaStream_t)stream, *c));
     i64b_count_launch(1);
     return I64B_OK;
 }
 
 }  // extern "C"
 
-// group tables written by i64b_ep_dispatch (for i64b_moe_forward_dispatched in i64b_api.cu)
-extern "C" void i64b_ep_group_tables(const i64b_ep_ctx* c, void* workspace, const I64bGroup** g1, const I64bGroup** g2) {
-    void* base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
-    const I64bPlanWs ws = i64b_plan_ws_carve(base, (int64_t)c->n_local * c->size, c->top_k, c->num_experts);
-    *g1 = ws.groups1;
-    *g2 = ws.groups2;
+// owner side (called by i64b_moe_forward_dispatched in i64b_api.cu): group tables from the published counts
+extern "C" int i64b_ep_build_groups(const i64b_ep_ctx* c, void* ep_workspace, int expert_inter, const I64bGroup** g1,
+                                    const I64bGroup** g2, int* num_groups, cudaStream_t stream) {
+    int rc = ep_check(c);
+    if (rc) return rc;
+    const EpWs w = ep_carve(c, ep_workspace);
+    I64B_CUDA(i64b_launch(ep_groups_kernel, dim3(1), dim3(128), 0, stream, *c, w.g1, w.g2, expert_inter));
+    i64b_count_launch(1);
+    *g1 = w.g1;
+    *g2 = w.g2;
+    *num_groups = c->num_experts / c->size * c->size + 1;
+    return I64B_OK;
 }

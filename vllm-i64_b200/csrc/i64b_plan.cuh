@@ -59,7 +59,9 @@ int i64b_run_dispatch(const I64bDispatchArgs& a, const I64bPlanWs& ws, cudaStrea
 int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_ld, int n_tiles, int8_t* out,
                          float* scale, int64_t rows, int cols, const int32_t* q14_b, const int32_t* amax_part_b,
                          int amax_ld_b, int n_tiles_b, int8_t* out_b, float* scale_b, int64_t rows_b, int cols_b,
-                         cudaStream_t stream);
+                         cudaStream_t stream, const I64bGroup* groups = nullptr, int num_groups = 0);
+// `groups` (device): the first row set is the rows of these GEMM groups instead of rows [0, rows) — `rows` is then only
+// an upper bound used to size the grid
 
 struct I64bCombineArgs {
     const float* y;             // [N*K + N, H] fp32 per-assignment outputs (shared rows last)

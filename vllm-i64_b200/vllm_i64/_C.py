@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libi64b.so")
 BF16, F32, F16 = 0, 1, 2
 STAGE_PLAN, STAGE_DISPATCH, STAGE_GEMM1, STAGE_REQUANT, STAGE_GEMM2, STAGE_COMBINE, STAGE_ALL = 1, 2, 4, 8, 16, 32, 0xFF
 MODE_BF16, MODE_W8A8 = 0, 1
-DEBUG_KEEP_TAPS, DEBUG_FUSE_COMBINE = 1, 2
+DEBUG_KEEP_TAPS, DEBUG_FUSE_COMBINE, DEBUG_NO_FUSED = 1, 2, 4
 (TAP_ROUTES, TAP_DEST_ROW, TAP_SCATTER_IDX, TAP_COUNTS, TAP_OFFSETS, TAP_XS, TAP_XS_SCALE, TAP_INTER_R, TAP_INTER_S,
  TAP_INTER_SCALE_R, TAP_INTER_SCALE_S, TAP_Q14_R, TAP_Q14_S, TAP_Y, TAP_GROUP_START) = range(15)
 
@@ -35,14 +35,16 @@ class MoEConfig(C.Structure):
 
 
 EP_MAX_RANKS = 8
+EP_FLAGS_INTS = 1024
 
 
 class EPCtx(C.Structure):
     """``i64b_ep_ctx`` (include/i64b.h): peer-mapped buffers of every rank of the expert-parallel group."""
     _fields_ = [("rank", C.c_int32), ("size", C.c_int32), ("n_local", C.c_int32), ("hidden", C.c_int32),
                 ("top_k", C.c_int32), ("num_experts", C.c_int32), ("vocab", C.c_int32), ("y_dtype", C.c_int32),
-                ("cap_rows", C.c_int64), ("peer_xs", C.c_void_p * EP_MAX_RANKS),
-                ("peer_y", C.c_void_p * EP_MAX_RANKS),
+                ("x_mode", C.c_int32), ("reserved", C.c_int32),
+                ("cap_src", C.c_int64), ("peer_xs", C.c_void_p * EP_MAX_RANKS),
+                ("peer_xs_scale", C.c_void_p * EP_MAX_RANKS), ("peer_y", C.c_void_p * EP_MAX_RANKS),
                 ("peer_flags", C.c_void_p * EP_MAX_RANKS), ("state", C.c_void_p)]
 
 
@@ -76,6 +78,7 @@ _SIGNATURES = {
     "i64b_moe_workspace_bytes": (_Z, [_P, _L]),
     "i64b_moe_forward": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, _P]),
     "i64b_moe_uses_fused": (_I, [_P, _L]),
+    "i64b_moe_fuses_combine": (_I, [_P, _L]),
     "i64b_moe_forward_stages": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, C.c_uint, _P]),
     "i64b_moe_forward_routed": (_I, [_P, _P, _P, _I, C.POINTER(_F), _F, _F, _I, _P, _I, _L, _P, _Z, _P]),
     "i64b_moe_workspace_bytes_routed": (_Z, [_P, _L, _I]),
@@ -92,7 +95,8 @@ _SIGNATURES = {
     "i64b_ipc_import": (_I, [C.c_char_p, C.POINTER(_P)]),
     "i64b_ipc_close": (_I, [_P]),
     "i64b_ep_workspace_bytes": (_Z, [C.POINTER(EPCtx)]),
-    "i64b_ep_dispatch": (_I, [C.POINTER(EPCtx), _P, _P, _P, _I, _P, _Z, _P]),
+    "i64b_ep_dispatch": (_I, [C.POINTER(EPCtx), _P, _P, _P, _P, _Z, _P]),
+    "i64b_ep_barrier": (_I, [C.POINTER(EPCtx), _P]),
     "i64b_ep_combine": (_I, [C.POINTER(EPCtx), _P, _P, C.POINTER(_F), _F, _F, _P, _I, _P]),
     "i64b_ep_signal": (_I, [C.POINTER(EPCtx), _P]),
     "i64b_ep_wait": (_I, [C.POINTER(EPCtx), _P]),

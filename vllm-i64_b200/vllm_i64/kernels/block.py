@@ -114,6 +114,9 @@ class I64Block:
     def uses_fused(self, n: int) -> bool:
         return bool(_C.lib().i64b_moe_uses_fused(self._h, int(n)))
 
+    def fuses_combine(self, n: int) -> bool:
+        return bool(_C.lib().i64b_moe_fuses_combine(self._h, int(n)))
+
     def forward_routed(self, x: torch.Tensor, routes: torch.Tensor, route_weights: Sequence[float],
                        routed_scale: float = 1.0, shared_scale: float = 1.0, use_shared: bool = False,
                        out_dtype=torch.bfloat16) -> torch.Tensor:

@@ -2,17 +2,19 @@
 
 Behavioural spec: ``TokenRoutedMLP._forward_ep`` of the reference's vLLM-fork copy
 (layers/token_routed_i64/layer.py:209-298 — not importable in the reference tree): experts are block-partitioned
-over the EP group (``rank = expert_id // local_E``, :227), tokens stay data-parallel, one all-to-all carries the
-dispatched rows to the owning ranks and one carries the expert outputs back.  Differences from the reference:
+over the EP group (``rank = expert_id // local_E``, :227), tokens stay data-parallel, dispatched rows travel to the
+owning ranks and the expert outputs travel back.
 
-  * top-k routes (the reference EP path is top-1 only) — every (route, token) assignment is exchanged;
-  * the deterministic dispatch plan (stable by destination rank, then assignment index) replaces argsort;
-  * expert ids ride along as int32; the shared expert and the weighted combine run on the token's home rank, so the
-    shared expert's GEMMs overlap the dispatch exchange on a side stream;
-  * local expert compute is ONE grouped-GEMM block call (``I64Block.forward_routed``), not a per-expert loop.
+Product path (``EPTokenRoutedBlock.forward_peer``, csrc/i64b_ep.cu): NVLink peer memory, no collective library call on
+the data path.  A rank plans only its own tokens; its dispatch kernel writes every row straight into "its" region of
+the owning rank's receive buffer and publishes per-expert row counts in the owner's flags page; a flag barrier in peer
+memory replaces the collective's implicit synchronisation; the owners run their experts as one grouped GEMM pair; the
+home rank's combine kernel pulls the K rows of each token back over NVLink.  The shared expert and the weighted
+combine run on the token's home rank, the shared expert on a second stream.  Ranks may bring different numbers of
+tokens; nothing synchronises with the host, so the whole step is CUDA-graph capturable.
 
-The exchange uses ``torch.distributed.all_to_all_single`` (NCCL over NVLink/NVSwitch on GPUs; gloo in the CPU unit
-tests, where the expert compute is injected).  Split sizes are exchanged first, like the reference (:230-247).
+Baseline path (``exchange="nccl"``, and ``ep_moe_forward`` for the CPU/gloo unit tests): the reference's scheme —
+split sizes exchanged through the host, ``all_to_all_single`` each way — generalised to top-k routes.
 """
 from __future__ import annotations
 
@@ -48,23 +50,6 @@ def init_expert_parallel(ep_size: Optional[int] = None, group: Optional[dist.Pro
         raise ValueError(f"ep_size {ep_size} != group size {size}")
     _EP = EPState(ep_size=size, ep_rank=dist.get_rank(group), group=group)
     return _EP
-
-
-def check_equal_local_batches(n: int, ep: Optional[EPState] = None, device=None) -> None:
-    """The peer-memory exchange indexes token t of rank r as ``r*n + t`` in the global plan and all-gathers the ids with
-    equal contributions, so unequal local batches would hang in the collective.  Collective call (one small
-    all-reduce): raises the same ``ValueError`` on every rank when the ranks disagree on ``n``.  The engine pads decode
-    batches to a common size; the reference's own EP path exchanges split sizes through the host instead
-    (layers/token_routed_i64/layer.py:230-247)."""
-    ep = ep or _EP
-    if ep.ep_size <= 1:
-        return
-    nn = torch.tensor([n, -n], dtype=torch.int64, device=device)
-    dist.all_reduce(nn, op=dist.ReduceOp.MAX, group=ep.group)
-    n_max, n_min = int(nn[0]), -int(nn[1])
-    if n_max != n_min:
-        raise ValueError(f"expert-parallel ranks must bring the same number of tokens per step "
-                         f"(min {n_min}, max {n_max}): pad the local batch to a common size")
 
 
 def local_expert_range(num_experts: int, ep: Optional[EPState] = None):
@@ -146,14 +131,18 @@ class EPTokenRoutedBlock:
 
     def __init__(self, hidden_size: int, num_experts: int, expert_inter: int, shared_inter: int, vocab_size: int,
                  top_k: int, route_weights: Sequence[float], routed_scale: float, shared_scale: float, mode: int,
-                 device: torch.device, ep: Optional[EPState] = None, transport_dtype: torch.dtype = torch.float32):
-        """``transport_dtype``: dtype the expert outputs travel back in.  float32 (default) makes the EP result
-        bit-identical to the single-GPU block; bfloat16 is the reference's choice (its EP path returns expert outputs
-        in the model dtype, layers/token_routed_i64/layer.py:283-292) and halves the return traffic."""
+                 device: torch.device, ep: Optional[EPState] = None, transport_dtype: torch.dtype = torch.bfloat16):
+        """``transport_dtype``: dtype the expert outputs travel back in.  bfloat16 (default) is the reference's choice
+        (its EP path returns expert outputs in the model dtype, layers/token_routed_i64/layer.py:283-292) and halves
+        the return traffic: one more bf16 rounding per assignment than the single-GPU block.  float32 makes the EP
+        result bit-identical to the single-GPU block.  ``mode`` ``_C.MODE_W8A8``: the rows are quantised once on the
+        home rank and travel as int8 + one fp32 scale (half the dispatch bytes); the owners run the W8A8 experts."""
+        from vllm_i64 import _C
         from vllm_i64.kernels.block import I64Block
         if transport_dtype not in (torch.float32, torch.bfloat16):
             raise TypeError("transport_dtype must be float32 or bfloat16")
         self.transport_dtype = transport_dtype
+        self.mode = int(mode)
         self.ep = ep or _EP
         self.E, self.K, self.H = num_experts, top_k, hidden_size
         self.first, self.local_E = local_expert_range(num_experts, self.ep)
@@ -164,7 +153,33 @@ class EPTokenRoutedBlock:
         self.local = I64Block(hidden_size, self.local_E, expert_inter, 0, 1, 1, [1.0], 1.0, 1.0, mode, device)
         self.shared = (I64Block(hidden_size, 0, 0, shared_inter, 1, 0, [], 1.0, 1.0, mode, device)
                        if shared_inter > 0 else None)
+        if self.shared is not None:
+            # the shared expert runs on a second stream next to the exchange kernels: keep it off the single-launch decode
+            # kernel, whose CTAs wait on one another and must own the GPU (include/i64b.h, i64b_moe_forward)
+            self.shared.set_debug(_C.DEBUG_NO_FUSED)
         self._table = None
+        self._bases = None
+        self._cap_tokens = 0
+
+    def __del__(self):
+        # best effort, non-collective: unmap and free without the barrier (the process is going away)
+        try:
+            from vllm_i64 import _C
+            bases = getattr(self, "_bases", None)
+            if bases:
+                lib = _C.lib()
+                for d, b in enumerate(bases):
+                    (lib.i64b_ep_free if d == self.ep.ep_rank else lib.i64b_ipc_close)(b)
+                self._bases = None
+        except Exception:
+            pass
+
+    def load_w8a8(self, w13_q, w13_s, w2_q, w2_s, sh13_q=None, sh13_s=None, sh2_q=None, sh2_s=None) -> None:
+        """FULL materialised int8 weights (include/i64b.h, i64b_moe_load_w8a8); this rank keeps its experts' slice."""
+        lo, hi = self.first, self.first + self.local_E
+        self.local.load_w8a8(w13_q[lo:hi], w13_s[lo:hi], w2_q[lo:hi], w2_s[lo:hi])
+        if self.shared is not None:
+            self.shared.load_w8a8(None, None, None, None, sh13_q, sh13_s, sh2_q, sh2_s)
 
     def load_bf16(self, gate, up, down, shared_gate=None, shared_up=None, shared_down=None) -> None:
         """FULL reference-layout weights; this rank keeps experts [first, first + local_E) and the shared expert."""
@@ -186,26 +201,39 @@ class EPTokenRoutedBlock:
         return out
 
     # ------------------------------------------------------------------ NVLink peer-memory path (the product path)
-    def _setup_peers(self, n: int) -> None:
-        """Allocate this rank's receive / home buffers for ``n`` local tokens, exchange the CUDA IPC handles and map
-        every peer's buffers.  Setup only (allocates and synchronises); ``n`` must be the same on all ranks."""
+    def reserve(self, max_tokens: int) -> None:
+        """COLLECTIVE, setup only (allocates and synchronises): size this rank's receive / output buffers for
+        ``max_tokens`` local tokens per step on EVERY rank (the maximum over the ranks is used), exchange the CUDA IPC
+        handles once and map every peer's buffers.  The engine calls it with its maximum batch; ``forward_peer`` calls
+        it on first use."""
         import ctypes as C
         from vllm_i64 import _C
         lib = _C.lib()
         G, K, H = self.ep.ep_size, self.K, self.H
         if G > _C.EP_MAX_RANKS:
             raise ValueError(f"at most {_C.EP_MAX_RANKS} expert-parallel ranks")
-        check_equal_local_batches(n, self.ep, self.device)
-        cap = G * n * K                                        # worst case: every assignment lands here (nothing dropped)
+        n = int(max_tokens)
+        if G > 1:
+            nn = torch.tensor([n], dtype=torch.int64, device=self.device)
+            dist.all_reduce(nn, op=dist.ReduceOp.MAX, group=self.ep.group)
+            n = int(nn[0])
+        n = max(n, 1)
+        cap_src = n * K                                        # a source's whole batch may land on one owner
+        rows = G * cap_src
+        q = self.mode == _C.MODE_W8A8
+        ysz = 4 if self.transport_dtype == torch.float32 else 2
 
         def up(v):
             return (v + 1023) & ~1023
-        off_xs, off_y = 0, up(cap * H * 2)
-        off_flags = off_y + up(cap * H * 4)
-        total = off_flags + 1024
+        off_xs = 0
+        off_scale = up(rows * H * (1 if q else 2))
+        off_y = off_scale + up(rows * 4)
+        off_flags = off_y + up(rows * H * ysz)
+        off_state = off_flags + up(_C.EP_FLAGS_INTS * 4)
+        total = off_state + 1024
         with torch.cuda.device(self.device):
             torch.cuda.synchronize(self.device)
-            self._release_peers()
+            self.close()
             base = C.c_void_p()
             _C.check(lib.i64b_ep_alloc(total, C.byref(base)))
             handle = C.create_string_buffer(64)
@@ -222,43 +250,49 @@ class EPTokenRoutedBlock:
                     _C.check(lib.i64b_ipc_import(handles[d], C.byref(p)))
                     bases.append(p.value)
         ctx = _C.EPCtx()
-        ctx.rank, ctx.size, ctx.n_local, ctx.hidden = self.ep.ep_rank, G, n, H
-        ctx.top_k, ctx.num_experts, ctx.vocab, ctx.cap_rows = K, self.E, self.router.cfg.vocab_size, cap
+        ctx.rank, ctx.size, ctx.n_local, ctx.hidden = self.ep.ep_rank, G, 0, H
+        ctx.top_k, ctx.num_experts, ctx.vocab, ctx.cap_src = K, self.E, self.router.cfg.vocab_size, cap_src
         ctx.y_dtype = _C.F32 if self.transport_dtype == torch.float32 else _C.BF16
+        ctx.x_mode = self.mode
         for d in range(G):
             ctx.peer_xs[d] = bases[d] + off_xs
+            ctx.peer_xs_scale[d] = bases[d] + off_scale
             ctx.peer_y[d] = bases[d] + off_y
             ctx.peer_flags[d] = bases[d] + off_flags
-        ctx.state = base.value + off_flags + 512
-        self._ctx, self._bases, self._n_setup = ctx, bases, n
+        ctx.state = base.value + off_state
+        self._ctx, self._bases, self._cap_tokens = ctx, bases, n
         self._ws_plan = torch.empty(lib.i64b_ep_workspace_bytes(C.byref(ctx)) + 256, dtype=torch.uint8, device=self.device)
         self._ws_gemm = torch.empty(lib.i64b_moe_dispatched_workspace_bytes(self.local._h, C.byref(ctx)) + 256,
                                     dtype=torch.uint8, device=self.device)
-        self._ids_all = torch.empty(G * n, dtype=torch.int64, device=self.device)
-        # persistent fp32 output of the replicated shared expert (a fresh 100+ MB torch allocation per call was
+        # persistent fp32 output of the home rank's shared expert (a fresh 100+ MB torch allocation per call was
         # measured at ~350 us of allocator time per layer)
         self._shared_out = (torch.empty(n, H, dtype=torch.float32, device=self.device)
                             if self.shared is not None else None)
+        self._side = torch.cuda.Stream(self.device)
         if G > 1:
             dist.barrier(group=self.ep.group)                  # every rank has mapped every buffer
 
-    def _release_peers(self) -> None:
+    def close(self) -> None:
+        """COLLECTIVE when buffers are mapped: unmap the peers' buffers, wait until every rank has done so, free ours."""
         from vllm_i64 import _C
         bases = getattr(self, "_bases", None)
         if not bases:
             return
         lib = _C.lib()
+        torch.cuda.synchronize(self.device)
         for d, b in enumerate(bases):
-            if d == self.ep.ep_rank:
-                lib.i64b_ep_free(b)
-            else:
+            if d != self.ep.ep_rank:
                 lib.i64b_ipc_close(b)
+        if self.ep.ep_size > 1 and dist.is_initialized():
+            dist.barrier(group=self.ep.group)                  # nobody still maps the buffer that is freed next
+        lib.i64b_ep_free(bases[self.ep.ep_rank])
         self._bases = None
+        self._cap_tokens = 0
 
     def forward_peer(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """One expert-parallel forward over NVLink peer memory: no host synchronisation, no NCCL on the data path
-        (NCCL carries only the all-gather of the token ids).  See include/i64b.h (expert parallelism)."""
+        """One expert-parallel forward over NVLink peer memory: no host synchronisation and no collective call
+        (graph-capturable once ``reserve`` has run).  See include/i64b.h (expert parallelism)."""
         import ctypes as C
         from vllm_i64 import _C
         _C.require_cuda(x, token_ids)
@@ -267,33 +301,29 @@ class EPTokenRoutedBlock:
         if x.dtype != torch.bfloat16 or not x.is_contiguous():
             x = x.to(torch.bfloat16).contiguous()
         token_ids = token_ids.to(torch.int64).contiguous()
-        if getattr(self, "_n_setup", -1) != n:
-            self._setup_peers(n)
+        if not getattr(self, "_bases", None):
+            self.reserve(n)
+        if n > self._cap_tokens:
+            raise ValueError(f"{n} tokens exceed the reserved expert-parallel capacity of {self._cap_tokens} tokens per "
+                             f"rank: call reserve(max_tokens) on every rank first")
+        self._ctx.n_local = n
         ctx = C.byref(self._ctx)
         with torch.cuda.device(self.device):
             cur = torch.cuda.current_stream(self.device)
             shared = None
-            if self.shared is not None:
-                # the replicated shared expert runs on a side stream: its GEMMs fill the SMs while the dispatch kernel
-                # (NVLink-bound, a few warps per SM) and the barrier wait occupy the main stream
-                if getattr(self, "_side", None) is None:
-                    self._side = torch.cuda.Stream(self.device)
+            if self.shared is not None and n > 0:
+                # the home rank's shared expert runs on a side stream: its GEMMs fill the SMs while the dispatch kernel
+                # (NVLink-bound, a few warps per SM) and the barrier occupy the main stream
                 self._side.wait_stream(cur)
                 with torch.cuda.stream(self._side):
-                    shared = self.shared.forward(x, None, torch.float32, out=self._shared_out)
+                    shared = self.shared.forward(x, None, torch.float32, out=self._shared_out[:n])
             st = _C.stream_ptr(self.device)
-            if self.ep.ep_size > 1:
-                dist.all_gather_into_tensor(self._ids_all, token_ids, group=self.ep.group)
-            else:
-                self._ids_all.copy_(token_ids)
-            _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), self._ids_all.data_ptr(), self._table.data_ptr(),
-                                          self.local.cfg.expert_inter, self._ws_plan.data_ptr(), self._ws_plan.numel(), st))
-            _C.check(lib.i64b_ep_signal(ctx, st))
-            _C.check(lib.i64b_ep_wait(ctx, st))
+            _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), token_ids.data_ptr(), self._table.data_ptr(),
+                                          self._ws_plan.data_ptr(), self._ws_plan.numel(), st))
+            _C.check(lib.i64b_ep_barrier(ctx, st))
             _C.check(lib.i64b_moe_forward_dispatched(self.local._h, ctx, self._ws_plan.data_ptr(), self._ws_gemm.data_ptr(),
                                                      self._ws_gemm.numel(), st))
-            _C.check(lib.i64b_ep_signal(ctx, st))
-            _C.check(lib.i64b_ep_wait(ctx, st))
+            _C.check(lib.i64b_ep_barrier(ctx, st))
             if out is None:
                 out = torch.empty(n, self.H, dtype=out_dtype, device=self.device)
             if shared is not None:
