@@ -170,6 +170,13 @@ size_t i64b_moe_workspace_bytes(const i64b_layer* layer, int64_t max_tokens);
  * DenseSwiGLUMLP.forward / DenseMLP.forward (models/complexity_deep/model.py:250-255, layers/dense_mlp.py:46-97). */
 int i64b_moe_forward(i64b_layer* layer, const void* x, const int64_t* token_ids, void* out, int out_dtype,
                      int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+/* Contract of the single-launch decode kernel (bf16 layers, n <= 1024 — i64b_moe_uses_fused): its CTAs wait on one
+ * another (GEMM1 -> GEMM2 -> combine inside one launch) and it is launched with one CTA per SM, so it completes only if
+ * the whole grid becomes resident.  ONE such launch may be in flight per device at a time: issue decode-sized forwards of
+ * one device on ONE stream (as the reference's engine does: one step at a time, cpu/engine.py:195-198), or set
+ * I64B_DEBUG_NO_FUSED on layers that run on a second stream / next to another process under MPS (they then take the
+ * kernel chain, which has no inter-CTA waits).  Every in-kernel wait is bounded (__trap after ~2 s), never a hang.
+ * The layer handle is not internally locked: one forward per layer at a time. */
 
 /* 1 if i64b_moe_forward on n tokens takes the single-launch fused decode kernel (bf16, n <= 1024; env
  * I64B_FUSED=0 disables it), else 0 (plan / dispatch / GEMM1 / GEMM2 / combine as separate launches). */

@@ -52,6 +52,8 @@ struct i64b_layer {
     float* w2s_scale = nullptr;
     int16_t* silu_lut = nullptr;
     int* sync = nullptr;         // fused-kernel counters (persistent, zero between launches)
+    int32_t* counts = nullptr;   // [K, E] per-route expert histogram of THIS layer's last forward (not in the shared workspace:
+    int32_t* offsets = nullptr;  // last_expert_counts() must not return another layer's numbers) and its exclusive scan
     const uint8_t* table = nullptr;
     bool loaded = false;
     int debug = 0;               // I64B_DEBUG_* bits (i64b_moe_set_debug)
@@ -94,6 +96,8 @@ static void carve_packed(i64b_layer* L, uint8_t* base, size_t* total) {
     L->w2s_scale = reinterpret_cast<float*>(take(sizeof(float) * c.hidden_size));
     L->silu_lut = reinterpret_cast<int16_t*>(take(sizeof(int16_t) * I64B_SILU_LUT_SIZE));
     L->sync = reinterpret_cast<int*>(take(sizeof(int) * I64B_SYNC_INTS));
+    L->counts = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * I64B_MAX_BINS));
+    L->offsets = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * I64B_MAX_BINS));
     if (total) *total = off;
 }
 
@@ -415,7 +419,9 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     void* base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~uintptr_t(1023));
     i64b_layer view = *L;     // carve with the effective (possibly overridden) geometry
     view.cfg = c;
-    const i64b_layer::Carve cv = carve_ws(&view, base, n);
+    i64b_layer::Carve cv = carve_ws(&view, base, n);
+    cv.plan.counts = L->counts;          // per-layer storage (the workspace is shared by all layers of a stream)
+    cv.plan.offsets = L->offsets;
     I64B_CHECK(workspace_bytes >= cv.bytes + 1024, I64B_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes,
                cv.bytes + 1024);
     cudaStream_t s = (cudaStream_t)stream;

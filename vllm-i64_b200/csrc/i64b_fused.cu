@@ -496,6 +496,9 @@ i64b_fused_layer_kernel(const __grid_constant__ CUtensorMap tm_x,
             named_bar_sync(1, 128);
             if (warp == 2 && lane == 0) TL(17);
             const bool taps = (int)blockIdx.x == G - 1 && p.tap_routes != nullptr;   // a CTA whose epilogue warps have slack (last CTA: one late unit at most)
+            // the taps live in the workspace the previous kernel of the stream may still be reading (a chain-path combine
+            // or GEMM2 that has already released its dependents): nothing is stored there before it has finished
+            if (taps) pdl_wait_prior();
 #pragma unroll 1
             for (int e = pw4; e < E; e += 4) {
                 const uint32_t pat = (uint32_t)e * 0x01010101u;
@@ -894,11 +897,12 @@ int i64b_fused_supported(int n, int hidden, int expert_inter, int shared_inter, 
 int i64b_launch_fused(const CUtensorMap& tm_x, const CUtensorMap& tm_w13, const CUtensorMap& tm_inter_r, const CUtensorMap& tm_inter_s,
                       const CUtensorMap& tm_w2r, const CUtensorMap& tm_w2s, const I64bFusedParams& p,
                       cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[I64B_MAX_DEVICES] = {};      // function attributes are per device
+    const int dev = i64b_current_device();
+    if (!configured[dev]) {
         I64B_CUDA(cudaFuncSetAttribute(i64b_fused_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         I64B_CUDA(cudaFuncSetAttribute(i64b_fused_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        configured = true;
+        configured[dev] = true;
     }
     const int grid = i64b_num_sms();
     static const bool dbg_tl = getenv("I64B_DEBUG_TIMELINE") != nullptr;

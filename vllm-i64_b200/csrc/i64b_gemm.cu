@@ -754,10 +754,11 @@ int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap&
                 const I64bGemmParams& p, int grid, cudaStream_t stream) {
     auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma, kCtas>;
     constexpr int smem = StageCfg<kNMma, kCtas>::kSmem;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[I64B_MAX_DEVICES] = {};      // function attributes are per device (one table per instantiation)
+    const int dev = i64b_current_device();
+    if (!configured[dev]) {
         I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
+        configured[dev] = true;
     }
     static const int dbg_flags = getenv("I64B_DEBUG_FLAGS") ? atoi(getenv("I64B_DEBUG_FLAGS")) : 0;
     static const bool dbg_tl = getenv("I64B_DEBUG_TIMELINE") != nullptr;
@@ -803,15 +804,21 @@ int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap&
 
 }  // namespace
 
-int i64b_num_sms() {
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-            sms = 148;
+int i64b_current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= I64B_MAX_DEVICES) dev = 0;
+    return dev;
+}
+
+int i64b_num_sms() {        // of the CURRENT device (a process may drive several)
+    static int sms[I64B_MAX_DEVICES] = {};
+    const int dev = i64b_current_device();
+    if (sms[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        sms[dev] = v;
     }
-    return sms;
+    return sms[dev];
 }
 
 int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t rows, int64_t cols,

@@ -14,7 +14,7 @@ import torch
 from vllm_i64 import _C
 from vllm_i64.kernels.block import I64Block
 
-_CACHE: Dict[Tuple, I64Block] = {}
+_CACHE: Dict[Tuple, Tuple[I64Block, tuple]] = {}
 _CACHE_MAX = 64
 
 
@@ -22,19 +22,42 @@ def _key(*tensors: torch.Tensor) -> Tuple:
     return tuple((t.data_ptr(), t._version, tuple(t.shape), t.dtype) for t in tensors)
 
 
+def _lookup(key: Tuple, tensors) -> "I64Block | None":
+    """A hit needs the SAME tensor objects to be alive: an address alone may have been recycled by the allocator for
+    another tensor after the original was freed (the entry holds weak references to its key tensors)."""
+    ent = _CACHE.get(key)
+    if ent is None:
+        return None
+    blk, refs = ent
+    if all(r() is t for r, t in zip(refs, tensors)):
+        return blk
+    del _CACHE[key]
+    return None
+
+
+def _store(key: Tuple, tensors, blk: I64Block) -> None:
+    import weakref
+    if len(_CACHE) >= _CACHE_MAX:
+        _CACHE.clear()
+    _CACHE[key] = (blk, tuple(weakref.ref(t) for t in tensors))
+
+
+def invalidate_cache() -> None:
+    """Drop every packed block (call after rewriting weight tensors through ``.data``, which ``_version`` cannot see)."""
+    _CACHE.clear()
+
+
 def _cached_block(gate_up_proj: torch.Tensor, down_proj: torch.Tensor, num_experts: int) -> I64Block:
     key = _key(gate_up_proj, down_proj)
-    blk = _CACHE.get(key)
+    blk = _lookup(key, (gate_up_proj, down_proj))
     if blk is None:
         e, h, two_i = gate_up_proj.shape
         inter = two_i // 2
         if e != num_experts or down_proj.shape != (e, inter, h):
             raise RuntimeError("gate_up_proj must be [E,H,2I] and down_proj [E,I,H]")
-        if len(_CACHE) >= _CACHE_MAX:
-            _CACHE.clear()
         blk = I64Block(h, e, inter, 0, 1, 1, [1.0], 1.0, 1.0, _C.MODE_BF16, gate_up_proj.device)
         blk.load_bf16(gate_up_proj[:, :, :inter], gate_up_proj[:, :, inter:], down_proj)
-        _CACHE[key] = blk
+        _store(key, (gate_up_proj, down_proj), blk)
     return blk
 
 
@@ -61,18 +84,17 @@ def fused_token_routed_forward_int8(x: torch.Tensor, gate_up_int8: torch.Tensor,
     if x.shape[0] == 0:
         return x
     _C.require_cuda(x, gate_up_int8, down_int8, expert_ids)
-    key = _key(gate_up_int8, gate_up_scale, down_int8, down_scale)
-    blk = _CACHE.get(key)
+    srcs = (gate_up_int8, gate_up_scale, down_int8, down_scale)
+    key = _key(*srcs)
+    blk = _lookup(key, srcs)
     if blk is None:
         gu = (gate_up_int8.float() * gate_up_scale.unsqueeze(-1).float())
         dn = (down_int8.float() * down_scale.unsqueeze(-1).float())
         e, h, two_i = gu.shape
         inter = two_i // 2
-        if len(_CACHE) >= _CACHE_MAX:
-            _CACHE.clear()
         blk = I64Block(h, e, inter, 0, 1, 1, [1.0], 1.0, 1.0, _C.MODE_BF16, x.device)
         blk.load_bf16(gu[:, :, :inter], gu[:, :, inter:], dn)
-        _CACHE[key] = blk
+        _store(key, srcs, blk)
     out = blk.forward_routed(x, expert_ids.view(1, -1), [1.0], 1.0, 1.0, False,
                              torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32)
     return out if out.dtype == x.dtype else out.to(x.dtype)

@@ -28,7 +28,9 @@ class _DenseBlockMixin:
 
     def _ensure_block(self, device: torch.device) -> I64Block:
         gate, up, down = self._weights()
-        key = (device, self.quantization, tuple((t.data_ptr(), t._version) for t in (gate, up, down)))
+        # identity + storage + in-place version; writes through ``.data`` are invisible to it: see invalidate()
+        key = (device, self.quantization, tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in (gate, up, down)),
+               tuple(id(p) for p in self.parameters()))
         if self._block is not None and self._block_key == key:
             return self._block
         inter, hidden = gate.shape
@@ -49,6 +51,15 @@ class _DenseBlockMixin:
         self.quantization = "int8"
         self._block = None
         return self
+
+    def invalidate(self) -> None:
+        """Drop the packed block (call after rewriting weights through ``.data``; ``load_state_dict`` does it itself)."""
+        self._block = None
+        self._block_key = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        super()._load_from_state_dict(*args, **kwargs)
+        self.invalidate()
 
     def _run(self, x: torch.Tensor) -> torch.Tensor:
         _C.require_cuda(x)

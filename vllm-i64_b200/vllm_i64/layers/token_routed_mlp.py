@@ -101,15 +101,45 @@ class TokenRoutedMLP(nn.Module):
 
     def _scales(self):
         if self.use_shared_expert and self.use_shared_routed_gates:
-            return float(self.routed_output_gate), float(self.shared_output_gate)
+            # one D2H read per (re)pack, never per forward: the learned gates are constants at inference time
+            g = torch.stack([self.routed_output_gate.detach().float(), self.shared_output_gate.detach().float()]).tolist()
+            return g[0], g[1]
         return self.routed_output_scale, (self.shared_output_scale if self.use_shared_expert else 1.0)
 
+    def _param_tensors(self):
+        """The live parameter / buffer tensors the packed block is derived from, WITHOUT building temporaries (the
+        materialised form holds one nn.Linear per expert)."""
+        ts = []
+        if hasattr(self, "expert_gate_up"):
+            ts += [m.weight for m in self.expert_gate_up] + [m.weight for m in self.expert_down]
+        elif hasattr(self, "gate_up_proj_w"):
+            ts += [self.gate_up_proj_w, self.down_proj_w]
+        else:
+            ts += [self.gate_proj_w, self.up_proj_w, self.down_proj_w]
+        if self.use_shared_expert:
+            ts += ([self.shared_gate_up.weight] if hasattr(self, "shared_gate_up")
+                   else [self.shared_gate.weight, self.shared_up.weight]) + [self.shared_down.weight]
+            if self.use_shared_routed_gates:
+                ts += [self.routed_output_gate, self.shared_output_gate]
+        ts.append(self.topk_token_to_expert)
+        return ts
+
     def _state_key(self):
-        ts = [t for t in (*self._expert_tensors(), *self._shared_tensors(), self.topk_token_to_expert) if t is not None]
-        key = [(t.data_ptr(), t._version, tuple(t.shape)) for t in ts]
-        if self.use_shared_expert and self.use_shared_routed_gates:
-            key.append((self.routed_output_gate._version, self.shared_output_gate._version))
-        return (self.quantization, self.tp_size, tuple(key))
+        """Identity + storage + in-place version of every source tensor.  Catches ``param.copy_()``, ``load_state_dict``,
+        re-assignment and ``.to(device)``.  It cannot see writes through ``.data`` (``p.data.copy_(w)`` does not bump
+        ``_version``): the module's own loaders (``load_full_weights``, ``_load_from_state_dict``) invalidate explicitly,
+        anything else that rewrites weights in place after the first forward must call ``invalidate()``."""
+        return (self.quantization, self.tp_size,
+                tuple((id(t), t.data_ptr(), t._version, tuple(t.shape)) for t in self._param_tensors()))
+
+    def invalidate(self) -> None:
+        """Drop the packed block: the next forward re-packs from the current parameters."""
+        self._block = None
+        self._block_key = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        super()._load_from_state_dict(*args, **kwargs)
+        self.invalidate()
 
     def _ensure_block(self, device: torch.device) -> I64Block:
         key = (device, self._state_key())
@@ -233,7 +263,7 @@ class TokenRoutedMLP(nn.Module):
         self.gate_proj_w.data.copy_(full_gate[:, :, lo:hi])
         self.up_proj_w.data.copy_(full_up[:, :, lo:hi])
         self.down_proj_w.data.copy_(full_down[:, lo:hi, :])
-        self._block = None
+        self.invalidate()
 
     # per-expert token histogram of the last forward (what /v1/experts re-derives on the host, api/_admin.py:464-562)
     def last_expert_counts(self) -> torch.Tensor:
