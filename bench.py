@@ -682,6 +682,28 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
     ms = time_graph(step_device, args.steps, args.warmup, stream, barrier, sampler)
     e2e_steps = max(3, min(args.steps, 50))
     ms_e2e = time_graph(step_e2e, e2e_steps, 3, stream, barrier)
+    timeline = None
+    if args.ep_timeline:
+        # per-stage device time of one layer, eager launches with CUDA events between the C-ABI calls (mean over 5 steps of
+        # layer 1; the barrier entries contain the wait for the slowest peer); the shared expert runs on its own stream
+        acc = {}
+        for it in range(7):
+            blocks[1].timeline = []
+            with torch.cuda.stream(stream):
+                step_device()
+            stream.synchronize()
+            tl = blocks[1].timeline
+            if it >= 2:
+                for (_, e_prev), (name, ev) in zip(tl[:-1], tl[1:]):
+                    acc.setdefault(name, []).append(e_prev.elapsed_time(ev) * 1e3)
+            blocks[1].timeline = None
+        names = list(acc)
+        tt = torch.tensor([float(np.mean(acc[k])) for k in names], device=device, dtype=torch.float64)
+        tmax = tt.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        timeline = {"rank0_us": {k: round(float(v), 1) for k, v in zip(names, tt.tolist())},
+                    "max_over_ranks_us": {k: round(float(v), 1) for k, v in zip(names, tmax.tolist())},
+                    "how": "eager launches, CUDA events between the C-ABI calls of layer 1, mean of 5 steps"}
     nccl = None
     if args.ep_nccl_baseline:
         # reference-style exchange (split sizes through the host + all_to_all_single each way), eager: the comparison baseline
@@ -723,7 +745,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
             "e2e": {"value": tokens / (ms_e2e_step * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e_step,
                     "h2d_bytes_per_step": n * H * 2 + n * 8, "d2h_bytes_per_step": n * H * 2, "copies_per_step": 1,
                     "via": "engine step per rank: pinned H2D of the rank's x + ids, L expert-parallel block forwards, D2H of the last output"},
-            "roofline": roof, "ep_parity": ep_parity, "transport_dtype": args.ep_transport,
+            "roofline": roof, "ep_parity": ep_parity, "transport_dtype": args.ep_transport, "ep_timeline": timeline,
             "nccl_all_to_all_baseline": ({"ms_per_step": ms_nccl, "value": tokens / (ms_nccl * 1e-3)} if nccl else None)}
 
 
@@ -742,6 +764,7 @@ def main():
     ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
     ap.add_argument("--ep-nccl-baseline", action="store_true", help="also time the all_to_all_single exchange (eager)")
+    ap.add_argument("--ep-timeline", action="store_true", help="also report per-stage device times of one EP layer (eager)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
@@ -805,7 +828,8 @@ def main():
                     "clocks": sampler.summary(), "e2e": r["e2e"],
                     "gpu_launches": r["launches_per_step"] * args.steps, "gpu_launches_per_step": r["launches_per_step"],
                     "roofline": r["roofline"], "cpu_baseline": None, "ep_parity": r["ep_parity"],
-                    "ep_transport_dtype": r["transport_dtype"], "nccl_all_to_all_baseline": r["nccl_all_to_all_baseline"]}
+                    "ep_transport_dtype": r["transport_dtype"], "nccl_all_to_all_baseline": r["nccl_all_to_all_baseline"],
+                    "ep_timeline": r["ep_timeline"]}
             emit(line)
         import torch.distributed as dist
         dist.barrier()

@@ -160,6 +160,7 @@ class EPTokenRoutedBlock:
         self._table = None
         self._bases = None
         self._cap_tokens = 0
+        self.timeline = None
 
     def __del__(self):
         # best effort, non-collective: unmap and free without the barrier (the process is going away)
@@ -318,19 +319,33 @@ class EPTokenRoutedBlock:
                 with torch.cuda.stream(self._side):
                     shared = self.shared.forward(x, None, torch.float32, out=self._shared_out[:n])
             st = _C.stream_ptr(self.device)
+            tl = self.timeline          # bring-up: a list collects (stage, event) pairs of this call (eager runs only)
+
+            def mark(name):
+                if tl is not None:
+                    ev = torch.cuda.Event(enable_timing=True)
+                    ev.record(cur)
+                    tl.append((name, ev))
+            mark("start")
             _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), token_ids.data_ptr(), self._table.data_ptr(),
                                           self._ws_plan.data_ptr(), self._ws_plan.numel(), st))
+            mark("plan+dispatch")
             _C.check(lib.i64b_ep_barrier(ctx, st))
+            mark("barrier1")
             _C.check(lib.i64b_moe_forward_dispatched(self.local._h, ctx, self._ws_plan.data_ptr(), self._ws_gemm.data_ptr(),
                                                      self._ws_gemm.numel(), st))
+            mark("groups+gemm1+gemm2")
             _C.check(lib.i64b_ep_barrier(ctx, st))
+            mark("barrier2")
             if out is None:
                 out = torch.empty(n, self.H, dtype=out_dtype, device=self.device)
             if shared is not None:
                 cur.wait_stream(self._side)
+            mark("join shared-expert stream")
             wts = (C.c_float * 4)(*[self.w[i] if i < len(self.w) else 0.0 for i in range(4)])
             _C.check(lib.i64b_ep_combine(ctx, self._ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
                                          out.data_ptr(), _C.dtype_code(out), st))
+            mark("combine (pull)")
         return out
 
     def forward(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
