@@ -116,6 +116,18 @@ int i64b_quantize_rows_int8(const void* x, int dtype, int8_t* q, float* scale, i
 int i64b_dequantize_int8(const int8_t* q, const float* scale, float* out, int64_t rows, int64_t cols,
                          i64b_stream_t stream);
 
+/* Fused residual-add + RMSNorm (+ per-token INT8 quantisation) — the step in front of the block:
+ *     h = residual + x ; y = rmsnorm(h) * weight ; (q, scale) = quantize_rows_int8(y)
+ * in ONE pass over the rows.  x, residual (nullable), weight [H] have dtype BF16 or F32; hidden_out (nullable, needs
+ * residual) receives h — the next residual; normed_out (nullable) y in the same dtype; q_out/scale_out (nullable) the
+ * int8 form the W8A8 block consumes as x_preq (i64b_moe_forward_preq).  bf16 rounds where the reference's eager path
+ * rounds (layers/rmsnorm.py:86-90: "(x.float()*norm).type_as(x) * weight"); F32 is the contract of the reference's own
+ * kernel: y = x*rrms*weight in fp32.  Replaces models/complexity_deep/model.py:358-361 (residual add + post-attention
+ * norm as separate elementwise kernels), I64_rmsnorm_forward / I64_rmsnorm_quant_forward (csrc/I64_rmsnorm.cu:41-190),
+ * kernels/triton/I64_fused_rmsnorm_quant.py. */
+int i64b_add_rmsnorm(const void* x, const void* residual, const void* weight, int dtype, float eps, void* hidden_out,
+                     void* normed_out, int8_t* q_out, float* scale_out, int64_t n, int hidden, i64b_stream_t stream);
+
 /* ---------------------------------------------------------------------------
  * The block as one object  (a2, a3, a4, a5, a12)
  * ------------------------------------------------------------------------- */
@@ -170,6 +182,12 @@ size_t i64b_moe_workspace_bytes(const i64b_layer* layer, int64_t max_tokens);
  * DenseSwiGLUMLP.forward / DenseMLP.forward (models/complexity_deep/model.py:250-255, layers/dense_mlp.py:46-97). */
 int i64b_moe_forward(i64b_layer* layer, const void* x, const int64_t* token_ids, void* out, int out_dtype,
                      int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
+/* The same forward on activations the caller has ALREADY quantised (x_preq of the reference: layers/dense_mlp.py:46-58,
+ * core/quantization.py:124,157-158 — produced by the fused RMSNorm+quant, i64b_add_rmsnorm): x_q int8 [N,H], x_scale fp32
+ * [N].  W8A8 layers only.  Skips the absmax/quantise pass of the dispatch (rows and scales are copied) and the shared
+ * expert reads x_q in place; the result is bit-identical to i64b_moe_forward on the rows x_q was quantised from. */
+int i64b_moe_forward_preq(i64b_layer* layer, const int8_t* x_q, const float* x_scale, const int64_t* token_ids, void* out,
+                          int out_dtype, int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
 /* Contract of the single-launch decode kernel (bf16 layers, n <= 1024 — i64b_moe_uses_fused): its CTAs wait on one
  * another (GEMM1 -> GEMM2 -> combine inside one launch) and it is launched with one CTA per SM, so it completes only if
  * the whole grid becomes resident.  ONE such launch may be in flight per device at a time: issue decode-sized forwards of

@@ -550,6 +550,33 @@ def ep_forward_virtual(x_per_rank: Sequence[np.ndarray], ids_per_rank: Sequence[
 
 
 # --------------------------------------------------------------------------- #
+# f1 — residual add + RMSNorm (+ activation quant): the step in front of the block
+# --------------------------------------------------------------------------- #
+
+def add_rmsnorm(x: np.ndarray, residual: Optional[np.ndarray], weight: np.ndarray, eps: float,
+                bf16: bool) -> Tuple[np.ndarray, np.ndarray]:
+    """``hidden = residual + hidden; hidden = post_attention_layernorm(hidden)`` (models/complexity_deep/model.py:358-361)
+    with the eager ``RMSNorm.forward`` (layers/rmsnorm.py:86-90):
+    ``norm = x.float().pow(2).mean(-1).add(eps).rsqrt(); (x.float()*norm).type_as(x) * weight``.
+    ``bf16``: inputs hold bf16 values and every tensor the reference materialises in bf16 is rounded here (the sum, the
+    ``type_as`` and the weight product); otherwise plain fp32 (also the contract of csrc/I64_rmsnorm.cu:98-190:
+    ``x*rrms*weight``).  The row mean is taken in fp64 and rounded to fp32: the reference's fp32 reduction order is
+    unspecified, so parity on the normalised rows is "equal up to one unit in the last place on isolated elements".
+    Returns (new residual h, normalised rows y)."""
+    x = np.asarray(x, np.float32)
+    h = x if residual is None else (np.asarray(residual, np.float32) + x).astype(np.float32)
+    if bf16 and residual is not None:
+        h = round_bf16(h)
+    ms = (h.astype(np.float64) ** 2).mean(axis=-1, keepdims=True).astype(np.float32)
+    r = (1.0 / np.sqrt((ms + np.float32(eps)).astype(np.float64))).astype(np.float32)
+    n1 = (h * r).astype(np.float32)
+    w = np.asarray(weight, np.float32)
+    if bf16:
+        return h, round_bf16((round_bf16(n1) * w).astype(np.float32))
+    return h, (n1 * w).astype(np.float32)
+
+
+# --------------------------------------------------------------------------- #
 # tolerance metric used by every floating-point parity test
 # --------------------------------------------------------------------------- #
 

@@ -1,0 +1,192 @@
+"""GPU parity of the round-2 widening steps: the fused residual-add + RMSNorm (+ INT8 quant) in front of the block
+ with x_preq consumed by the W8A8 block, the learned output gates (use_shared_routed_gates), the bf16 bar
+pinned by the reference's own bf16 run, and the chain→fused launch order on one stream."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import i64_oracle as O
+import i64_test_helpers as Hh
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available():
+    pytest.skip("CUDA device required", allow_module_level=True)
+
+from vllm_i64 import _C  # noqa: E402
+from vllm_i64.kernels.cuda import get_i64_cuda_ops  # noqa: E402
+
+DEV = torch.device("cuda", 0)
+
+
+def cu(a, dtype=None):
+    return Hh.to_cuda(a, dtype)
+
+
+def _ulp_bf16(a, b):
+    ia = (np.asarray(a, np.float32).view(np.int32) >> 16).astype(np.int64)
+    ib = (np.asarray(b, np.float32).view(np.int32) >> 16).astype(np.int64)
+    return np.abs(ia - ib)
+
+
+# --------------------------------------------------------------------------------------------------- f1: add + RMSNorm + quant
+def test_add_rmsnorm_golden(golden):
+    g = golden("tiny_norm.npz")
+    ops = get_i64_cuda_ops()
+    eps = float(g["eps"])
+    # bf16: new residual bit-exact; normalised rows equal up to one bf16 ulp on isolated elements (fp32 row-sum order)
+    h, y, qs = ops.add_rmsnorm(cu(g["attn_bf16"], torch.bfloat16), cu(g["resid_bf16"], torch.bfloat16),
+                               cu(g["w_bf16"], torch.bfloat16), eps, quantize=True)
+    np.testing.assert_array_equal(h.float().cpu().numpy(), g["h_bf16"])
+    d = _ulp_bf16(y.float().cpu().numpy(), g["y_bf16"])
+    assert d.max() <= 1 and (d > 0).mean() < 2e-3, (d.max(), (d > 0).mean())
+    # (q, scale) are the reference's quantize_activations_int8 of the rows this kernel produced: bit-exact
+    q_ref, s_ref = O.quantize_rows_int8(y.float().cpu().numpy())
+    np.testing.assert_array_equal(qs[0].cpu().numpy(), q_ref)
+    np.testing.assert_array_equal(qs[1].reshape(-1).cpu().numpy(), s_ref.reshape(-1))
+    same = (d == 0).all(axis=1)          # rows where the normalised values agree with the reference agree in int8 too
+    np.testing.assert_array_equal(qs[0].cpu().numpy()[same], g["q_bf16"][same])
+    # fp32 (contract of csrc/I64_rmsnorm.cu: x*rrms*weight)
+    h32, y32, qs32 = ops.add_rmsnorm(cu(g["attn"]), cu(g["resid"]), cu(g["w"]), eps, quantize=True)
+    np.testing.assert_array_equal(h32.cpu().numpy(), g["h_f32"])
+    np.testing.assert_allclose(y32.cpu().numpy(), g["y_f32"], rtol=1e-6, atol=1e-7)
+    q_ref, s_ref = O.quantize_rows_int8(y32.cpu().numpy())
+    np.testing.assert_array_equal(qs32[0].cpu().numpy(), q_ref)
+    # the reference's op names: rmsnorm_forward / rmsnorm_quant_forward (csrc/I64_binding.cu)
+    y_only = ops.rmsnorm_forward(cu(g["h_f32"]), cu(g["w"]), eps)
+    np.testing.assert_array_equal(y_only.cpu().numpy(), y32.cpu().numpy())
+    q2, s2 = ops.rmsnorm_quant_forward(cu(g["h_f32"]), cu(g["w"]), eps)
+    np.testing.assert_array_equal(q2.cpu().numpy(), qs32[0].cpu().numpy())
+    assert s2.shape == (g["attn"].shape[0], 1)
+
+
+@pytest.mark.parametrize("n,h", [(1, 1024), (256, 1024), (4099, 2048), (300, 64)])
+def test_add_rmsnorm_vs_oracle(n, h):
+    rng = np.random.RandomState(n + h)
+    x = Hh.bf16_round(rng.randn(n, h).astype(np.float32))
+    r = Hh.bf16_round((rng.randn(n, h) * 2).astype(np.float32))
+    w = Hh.bf16_round((1 + 0.2 * rng.randn(h)).astype(np.float32))
+    hh, y, qs = get_i64_cuda_ops().add_rmsnorm(cu(x, torch.bfloat16), cu(r, torch.bfloat16), cu(w, torch.bfloat16), 1e-6, quantize=True)
+    ho, yo = O.add_rmsnorm(x, r, w, 1e-6, bf16=True)
+    np.testing.assert_array_equal(hh.float().cpu().numpy(), ho)
+    d = _ulp_bf16(y.float().cpu().numpy(), yo)
+    assert d.max() <= 1 and (d > 0).mean() < 2e-3, (d.max(), (d > 0).mean())
+    q_ref, s_ref = O.quantize_rows_int8(y.float().cpu().numpy())
+    np.testing.assert_array_equal(qs[0].cpu().numpy(), q_ref)
+    np.testing.assert_array_equal(qs[1].reshape(-1).cpu().numpy(), s_ref.reshape(-1))
+
+
+@pytest.mark.parametrize("case", [(256, 8, 64, 128, 1000, 2, 300), (1024, 8, 512, 1280, 32000, 2, 2000), (512, 0, 0, 1024, 100, 0, 700)])
+def test_x_preq_is_bit_identical(case):
+    """The W8A8 block fed with x_preq (int8 rows + scales from the fused norm) == the block fed with the normalised rows."""
+    h, e, ie, s, v, k, n = case
+    rng = np.random.RandomState(n)
+    if e:
+        cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=n)
+        wq = O.quantize_moe_weights(w)
+        blk = Hh.build_gpu_block(cfg, w, table, "int8", wq)
+        it = cu(ids)
+    else:
+        from vllm_i64.kernels.block import I64Block
+        from vllm_i64.core.quantization import quantize_int8
+        x = Hh.bf16_round(rng.randn(n, h).astype(np.float32))
+        g_, u_, d_ = (cu(Hh.bf16_round(rng.uniform(-0.05, 0.05, sh).astype(np.float32))) for sh in ((s, h), (s, h), (h, s)))
+        blk = I64Block(h, 0, 0, s, 1, 0, [], 1.0, 1.0, _C.MODE_W8A8, DEV)
+        q13, s13 = quantize_int8(torch.cat([g_, u_], 0).contiguous())
+        q2, s2 = quantize_int8(d_.contiguous())
+        blk.load_w8a8(None, None, None, None, q13, s13, q2, s2)
+        it = None
+    resid = Hh.bf16_round(rng.randn(n, h).astype(np.float32))
+    wn = Hh.bf16_round((1 + 0.1 * rng.randn(h)).astype(np.float32))
+    _, y, (q, sc) = get_i64_cuda_ops().add_rmsnorm(cu(x, torch.bfloat16), cu(resid, torch.bfloat16), cu(wn, torch.bfloat16),
+                                                  1e-6, quantize=True)
+    a = blk.forward(y, it, torch.float32)
+    b = blk.forward_preq(q, sc, it, torch.float32)
+    assert torch.equal(a, b)
+    assert a.abs().max() > 0
+
+
+def test_dense_mlp_consumes_x_preq():
+    from vllm_i64.layers.dense_mlp import DenseMLP
+    torch.manual_seed(0)
+    m = DenseMLP(256, 512).to(DEV).to(torch.bfloat16).quantize_w8a8()
+    x = torch.randn(77, 256, device=DEV).to(torch.bfloat16)
+    q, sc = get_i64_cuda_ops().quantize_int8(x)
+    assert torch.equal(m(x), m(x, x_preq=(q, sc)))
+
+
+# --------------------------------------------------------------------------------------------------- learned output gates
+def test_use_shared_routed_gates_matches_oracle():
+    """forward with use_shared_routed_gates=True: out = routed_output_gate * routed + shared_output_gate * shared
+    (layers/token_routed_mlp.py:174-178)."""
+    from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP
+    h, e, ie, s, v, k, n = 256, 4, 64, 128, 800, 2, 333
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=21, rs=0.7, ss=1.9)
+    m = TokenRoutedMLP(h, e * ie, e, v, shared_expert=True, shared_intermediate_size=s, top_k=k, top_k_primary_weight=0.5,
+                       use_shared_routed_gates=True, shared_gate_init=1.9, routed_gate_init=0.7,
+                       shared_output_scale=123.0, routed_output_scale=456.0)       # the fixed scales must be ignored
+    with torch.no_grad():
+        m.gate_proj_w.copy_(torch.from_numpy(w.gate)); m.up_proj_w.copy_(torch.from_numpy(w.up))
+        m.down_proj_w.copy_(torch.from_numpy(w.down))
+        m.shared_gate.weight.copy_(torch.from_numpy(w.shared_gate)); m.shared_up.weight.copy_(torch.from_numpy(w.shared_up))
+        m.shared_down.weight.copy_(torch.from_numpy(w.shared_down))
+        m.topk_token_to_expert.copy_(torch.from_numpy(table))
+    m = m.to(DEV)
+    out = m(cu(x), cu(ids))
+    ref = O.moe_block_fp32(x, ids, table, w, cfg, inter_bf16=True)
+    Hh.assert_close(out.cpu().numpy(), ref, "learned gates")
+    with torch.no_grad():           # a gate update re-packs (parameter _version is part of the cache key)
+        m.routed_output_gate.fill_(0.0)
+    out0 = m(cu(x), cu(ids))
+    cfg0 = O.MoEConfig(h, e, ie, v, top_k=k, primary_weight=0.5, shared_inter=s, shared_output_scale=1.9, routed_output_scale=0.0)
+    Hh.assert_close(out0.cpu().numpy(), O.moe_block_fp32(x, ids, table, w, cfg0, inter_bf16=True), "routed gate = 0")
+
+
+# --------------------------------------------------------------------------------------------------- the bf16 bar, pinned
+def test_bf16_block_is_closer_to_fp32_than_the_reference_bf16(golden):
+    """north_star asks ≤1e-3 mean-rel against the oracle in fp32.  The golden holds the reference's OWN bf16 forward next to
+    its fp32 forward: that reference-bf16 sits at ~4e-3 from fp32.  The B200 bf16 block (fp32 accumulation, ONE bf16
+    rounding of the SwiGLU intermediate) must be strictly closer to the reference's fp32 output than the reference's bf16
+    path is, on every metric, and within 1e-3 of the oracle that models that single rounding."""
+    g = golden("tiny_block_bf16.npz")
+    hh, e, ie, s, v, k = (int(t) for t in g["cfg"])
+    w = O.MoEWeights(g["gate"], g["up"], g["down"], g["shared_gate"], g["shared_up"], g["shared_down"])
+    cfg = O.MoEConfig(hh, e, ie, v, top_k=k, primary_weight=0.5, shared_inter=s, shared_output_scale=1.0, routed_output_scale=2.0)
+    for fused in (True, False):
+        blk = Hh.build_gpu_block(cfg, w, g["table"], "bf16")
+        if not fused:
+            blk.set_debug(_C.DEBUG_NO_FUSED)
+        out = blk.forward(cu(g["x"], torch.bfloat16), cu(g["ids"]), torch.float32).cpu().numpy()
+        ours = O.rel_errors(out, g["y_f32"])
+        ref = O.rel_errors(g["y_bf16"], g["y_f32"])
+        assert ours[0] < ref[0] and ours[1] < ref[1], (fused, ours, ref)
+        assert ours[1] <= 0.5 * ref[1], (fused, ours, ref)
+        Hh.assert_close(out, O.moe_block_fp32(g["x"], g["ids"], g["table"], w, cfg, inter_bf16=True), "vs single-rounding oracle")
+
+
+# --------------------------------------------------------------------------------------------------- chain then fused
+def test_chain_layer_followed_by_fused_layer_on_one_stream():
+    """A chain-path forward (W8A8 layer, or forward_routed) followed immediately by a fused decode forward on the same
+    stream and workspace: the fused kernel's early CTAs must not overwrite workspace rows the chain's tail still reads
+    (debug taps are stored only after griddepcontrol.wait), and each layer reports its OWN expert histogram."""
+    h, e, ie, s, v, k, n = 256, 8, 64, 128, 1000, 2, 96
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=31)
+    cfg2, w2, table2, _, _ = Hh.make_block(h, e, ie, s, v, k, n, seed=32, layer=3)
+    chain = Hh.build_gpu_block(cfg, w, table, "int8", O.quantize_moe_weights(w))
+    fused = Hh.build_gpu_block(cfg2, w2, table2, "bf16")
+    assert fused.uses_fused(n) and not chain.uses_fused(n)
+    xt, it = cu(x, torch.bfloat16), cu(ids)
+    want_a = chain.forward(xt, it, torch.float32).clone()
+    torch.cuda.synchronize()
+    want_b = fused.forward(xt, it, torch.float32).clone()
+    torch.cuda.synchronize()
+    for _ in range(50):
+        a = chain.forward(xt, it, torch.float32)
+        b = fused.forward(xt, it, torch.float32)
+        assert torch.equal(a, want_a) and torch.equal(b, want_b)
+    ca = chain.tap(_C.TAP_COUNTS, (k, e), torch.int32).cpu().numpy()
+    cb = fused.tap(_C.TAP_COUNTS, (k, e), torch.int32).cpu().numpy()
+    ra, rb = O.route_table(ids, table, n, e), O.route_table(ids, table2, n, e)
+    for r in range(k):
+        np.testing.assert_array_equal(ca[r], np.bincount(ra[r], minlength=e))
+        np.testing.assert_array_equal(cb[r], np.bincount(rb[r], minlength=e))

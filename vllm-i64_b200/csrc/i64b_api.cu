@@ -387,6 +387,7 @@ struct FwdOpts {
     bool use_shared = true;
     bool override_scales = false;
     unsigned stage_mask = 0xFFu;            // I64B_STAGE_* bits (per-stage timing replays)
+    const float* preq_scale = nullptr;      // x is int8 [N,H] quantised by the caller (x_preq), these are its row scales
 };
 
 static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_ids, const FwdOpts& o,
@@ -412,6 +413,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         c.shared_scale = o.shared_scale;
     }
     const bool q = c.mode == I64B_MODE_W8A8;
+    const bool preq = o.preq_scale != nullptr;
+    I64B_CHECK(!preq || q, I64B_ERR_ARG, "pre-quantised activations need a W8A8 layer");
     const int E = c.num_experts, K = c.top_k, H = c.hidden_size, I = c.expert_inter, S = c.shared_inter;
     I64B_CHECK(E == 0 || given_routes != nullptr || token_ids == nullptr || L->table != nullptr, I64B_ERR_STATE,
                "routing table not set (call i64b_moe_set_table)");
@@ -492,12 +495,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     pa.expert_inter = I;
     pa.shared_inter = S;
     pa.hidden = H;
-    // bf16: the shared expert (and a dense FFN) multiplies the caller's x in place; W8A8 needs the quantised copy
-    const bool shared_from_x = !q && S > 0;
+    // bf16: the shared expert (and a dense FFN) multiplies the caller's x in place; W8A8 needs the quantised copy unless
+    // the caller already brings int8 rows (x_preq)
+    const bool shared_from_x = (!q || preq) && S > 0;
     pa.shared_from_x = shared_from_x ? 1 : 0;
     pa.ticket = L->sync + 3 * I64B_SYNC_STRIDE;     // free slot of the layer's persistent counter area
     if (shared_from_x && (L->cached_x != x || L->cached_x_n != n)) {
-        int rcx = i64b_encode_tmap(&L->tm_x, x, false, n, H, (int64_t)H * 2, 128);
+        int rcx = i64b_encode_tmap(&L->tm_x, x, preq, n, H, (int64_t)H * L->elt, 128);
         if (rcx) return rcx;
         L->cached_x = x;
         L->cached_x_n = n;
@@ -515,7 +519,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.hidden = H;
     da.top_k = K;
     da.num_experts = E;
-    da.quantize = q ? 1 : 0;
+    da.quantize = (q && !preq) ? 1 : 0;
+    da.preq_scale = o.preq_scale;
     da.shared_copy = (S > 0 && !shared_from_x) ? 1 : 0;
     da.xs = cv.xs;
     da.xs_scale = cv.xs_scale;
@@ -546,7 +551,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.out[1] = q ? (void*)cv.q14_s : (void*)cv.inter_s;
         gp.ld_out[0] = I;
         gp.ld_out[1] = S;
-        gp.row_scale[0] = gp.row_scale[1] = cv.xs_scale;
+        gp.row_scale[0] = cv.xs_scale;
+        gp.row_scale[1] = preq ? o.preq_scale : cv.xs_scale;      // shared expert on the caller's int8 rows: its scales, by token
         gp.col_scale[0] = gp.col_scale[1] = L->w13_scale;
         gp.amax_part[0] = cv.amax_r;
         gp.amax_part[1] = cv.amax_s;
@@ -635,6 +641,14 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
 int i64b_moe_forward(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype, int64_t n,
                      void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
     return moe_forward_impl(L, x, token_ids, FwdOpts(), out, out_dtype, n, workspace, workspace_bytes, stream);
+}
+
+int i64b_moe_forward_preq(i64b_layer* L, const int8_t* x_q, const float* x_scale, const int64_t* token_ids, void* out,
+                          int out_dtype, int64_t n, void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
+    I64B_CHECK(x_scale != nullptr || n == 0, I64B_ERR_ARG, "null scales");
+    FwdOpts o;
+    o.preq_scale = x_scale;
+    return moe_forward_impl(L, x_q, token_ids, o, out, out_dtype, n, workspace, workspace_bytes, stream);
 }
 
 int i64b_fused_decode_supported(int n, int hidden, int expert_inter, int shared_inter, int num_experts, int top_k) {

@@ -83,11 +83,25 @@ ep_dispatch_kernel(const i64b_ep_ctx c, const void* __restrict__ x, const I64bPl
 #pragma unroll
         for (int k = 0; k < I64B_MAX_TOPK; ++k)
             dst[k] = k < K ? reinterpret_cast<int4*>(reinterpret_cast<__nv_bfloat16*>(c.peer_xs[dk[k]]) + (int64_t)rowk[k] * H) : nullptr;
-        for (int i = lane; i < nvec; i += 32) {
-            const int4 v = ld_nc_16(src + i);
+        // the whole row (H <= 2048: 8 vectors per lane) is requested before the first peer store leaves, so a warp pays one
+        // local-memory latency per token, not one per 512 bytes
+        constexpr int kV = 8;
+        for (int i0 = 0; i0 < nvec; i0 += 32 * kV) {
+            int4 v[kV];
 #pragma unroll
-            for (int k = 0; k < I64B_MAX_TOPK; ++k)
-                if (k < K) dst[k][i] = v;
+            for (int j = 0; j < kV; ++j) {
+                const int i = i0 + j * 32 + lane;
+                if (i < nvec) v[j] = ld_nc_16(src + i);
+            }
+#pragma unroll
+            for (int j = 0; j < kV; ++j) {
+                const int i = i0 + j * 32 + lane;
+                if (i < nvec) {
+#pragma unroll
+                    for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                        if (k < K) dst[k][i] = v[j];
+                }
+            }
         }
     } else {
         // quantize_activations_int8 (core/quantization.py:103-116) once per token; the K copies share row and scale
@@ -157,62 +171,100 @@ struct EpCombineArgs {
     void* out;
     int out_dtype;
 };
+struct Row8 { float v[8]; };
+__device__ __forceinline__ void combine_accumulate(Row8& o, const Row8& y, float w, bool first) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = first ? __fmul_rn(w, y.v[j]) : __fadd_rn(o.v[j], __fmul_rn(w, y.v[j]));
+}
+// 8 consecutive columns of one peer row: one 16-byte load (bf16 transport) or two (fp32)
+__device__ __forceinline__ void ep_issue_row_load(const i64b_ep_ctx& c, int64_t l, int col8, int4& a, int4& b) {
+    const void* base = c.peer_y[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)];
+    const int64_t row = l & 0xffffffffll;
+    if (c.y_dtype == I64B_F32) {
+        const int4* p = reinterpret_cast<const int4*>(reinterpret_cast<const float*>(base) + row * c.hidden) + 2 * col8;
+        a = ld_nc_16(p);
+        b = ld_nc_16(p + 1);
+    } else {
+        a = ld_nc_16(reinterpret_cast<const int4*>(reinterpret_cast<const __nv_bfloat16*>(base) + row * c.hidden) + col8);
+        b = make_int4(0, 0, 0, 0);
+    }
+}
+__device__ __forceinline__ Row8 ep_unpack_row(int y_dtype, const int4& a, const int4& b) {
+    Row8 r;
+    if (y_dtype == I64B_F32) {
+        r.v[0] = __int_as_float(a.x); r.v[1] = __int_as_float(a.y); r.v[2] = __int_as_float(a.z); r.v[3] = __int_as_float(a.w);
+        r.v[4] = __int_as_float(b.x); r.v[5] = __int_as_float(b.y); r.v[6] = __int_as_float(b.z); r.v[7] = __int_as_float(b.w);
+    } else {
+        const uint32_t w[4] = {(uint32_t)a.x, (uint32_t)a.y, (uint32_t)a.z, (uint32_t)a.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { r.v[2 * j] = bf16lo(w[j]); r.v[2 * j + 1] = bf16hi(w[j]); }
+    }
+    return r;
+}
+// One item = 8 output columns of one token.  A thread keeps kItems items in flight: all (owner, row) tags first, then all
+// peer loads (K per item, 16 bytes each over NVLink), then the local shared-expert rows, then the arithmetic.
+constexpr int kCombItems = 2;
 __global__ void __launch_bounds__(256) ep_combine_kernel(const i64b_ep_ctx c, const EpCombineArgs a) {
     pdl_launch_dependents();
     pdl_wait_prior();
-    const int hv = c.hidden / 4;
-    const int64_t total = (int64_t)c.n_local * hv;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t t = i / hv;
-        const int col = (int)(i % hv);
-        float4 yk[I64B_MAX_TOPK];
+    const int h8 = c.hidden / 8;
+    const int64_t total = (int64_t)c.n_local * h8;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += stride * kCombItems) {
+        int64_t loc[kCombItems][I64B_MAX_TOPK];
+        int4 ya[kCombItems][I64B_MAX_TOPK], yb[kCombItems][I64B_MAX_TOPK];
 #pragma unroll
-        for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-            if (k < c.top_k) {
-                const int64_t l = __ldg(a.loc + (int64_t)k * c.n_local + t);
-                const void* base = c.peer_y[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)];
-                const int64_t row = l & 0xffffffffll;
-                if (c.y_dtype == I64B_F32) {
-                    const int4 v = ld_nc_16(reinterpret_cast<const int4*>(reinterpret_cast<const float*>(base) + row * c.hidden) + col);
-                    yk[k] = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w));
-                } else {
-                    const uint2 v = *(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(base) + row * c.hidden) + col);
-                    yk[k] = make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xffff0000u),
-                                        __uint_as_float(v.y << 16), __uint_as_float(v.y & 0xffff0000u));
-                }
+        for (int u = 0; u < kCombItems; ++u) {
+            const int64_t i = i0 + u * stride;
+            const int64_t t = i < total ? i / h8 : 0;
+#pragma unroll
+            for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                if (k < c.top_k) loc[u][k] = __ldg(a.loc + (int64_t)k * c.n_local + t);
+        }
+#pragma unroll
+        for (int u = 0; u < kCombItems; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < total) {
+                const int col8 = (int)(i % h8);
+#pragma unroll
+                for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                    if (k < c.top_k) ep_issue_row_load(c, loc[u][k], col8, ya[u][k], yb[u][k]);
             }
         }
-        float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-            if (k < c.top_k) {
-                const float w = a.w[k];
-                const float4 y = yk[k];
-                if (k == 0) {
-                    o = make_float4(__fmul_rn(w, y.x), __fmul_rn(w, y.y), __fmul_rn(w, y.z), __fmul_rn(w, y.w));
-                } else {
-                    o.x = __fadd_rn(o.x, __fmul_rn(w, y.x));
-                    o.y = __fadd_rn(o.y, __fmul_rn(w, y.y));
-                    o.z = __fadd_rn(o.z, __fmul_rn(w, y.z));
-                    o.w = __fadd_rn(o.w, __fmul_rn(w, y.w));
-                }
+        for (int u = 0; u < kCombItems; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i >= total) break;
+            const int64_t t = i / h8;
+            const int col8 = (int)(i % h8);
+            Row8 o;
+#pragma unroll
+            for (int k = 0; k < I64B_MAX_TOPK; ++k)
+                if (k < c.top_k) combine_accumulate(o, ep_unpack_row(c.y_dtype, ya[u][k], yb[u][k]), a.w[k], k == 0);
+            const float rs = a.routed_scale;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o.v[j] = __fmul_rn(rs, o.v[j]);
+            if (a.y_shared != nullptr) {
+                const float4* sp = reinterpret_cast<const float4*>(a.y_shared + t * c.hidden) + 2 * col8;
+                const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+                const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+                const float ss = a.shared_scale;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o.v[j] = __fadd_rn(o.v[j], __fmul_rn(ss, sv[j]));
             }
-        }
-        const float rs = a.routed_scale;
-        o = make_float4(__fmul_rn(rs, o.x), __fmul_rn(rs, o.y), __fmul_rn(rs, o.z), __fmul_rn(rs, o.w));
-        if (a.y_shared != nullptr) {
-            const float4 y = __ldg(reinterpret_cast<const float4*>(a.y_shared + t * c.hidden) + col);
-            const float ss = a.shared_scale;
-            o.x = __fadd_rn(o.x, __fmul_rn(ss, y.x));
-            o.y = __fadd_rn(o.y, __fmul_rn(ss, y.y));
-            o.z = __fadd_rn(o.z, __fmul_rn(ss, y.z));
-            o.w = __fadd_rn(o.w, __fmul_rn(ss, y.w));
-        }
-        if (a.out_dtype == I64B_F32) {
-            reinterpret_cast<float4*>(a.out)[i] = o;
-        } else {
-            __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
-            reinterpret_cast<uint2*>(a.out)[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+            if (a.out_dtype == I64B_F32) {
+                float4* op = reinterpret_cast<float4*>(a.out) + 2 * i;
+                op[0] = make_float4(o.v[0], o.v[1], o.v[2], o.v[3]);
+                op[1] = make_float4(o.v[4], o.v[5], o.v[6], o.v[7]);
+            } else {
+                uint32_t pk[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    __nv_bfloat162 v2 = __floats2bfloat162_rn(o.v[2 * j], o.v[2 * j + 1]);
+                    pk[j] = *reinterpret_cast<uint32_t*>(&v2);
+                }
+                reinterpret_cast<int4*>(a.out)[i] = make_int4((int)pk[0], (int)pk[1], (int)pk[2], (int)pk[3]);
+            }
         }
     }
 }
@@ -369,7 +421,6 @@ int i64b_ep_combine(const i64b_ep_ctx* c, void* ep_workspace, const float* y_sha
     if (rc) return rc;
     I64B_CHECK(ep_workspace && route_weight && (out || c->n_local == 0), I64B_ERR_ARG, "null pointer");
     I64B_CHECK(out_dtype == I64B_BF16 || out_dtype == I64B_F32, I64B_ERR_ARG, "unsupported output dtype");
-    I64B_CHECK(c->hidden % 4 == 0, I64B_ERR_ARG, "hidden size must be a multiple of 4");
     if (c->n_local == 0) return I64B_OK;
     EpCombineArgs a = {};
     a.loc = ep_carve(c, ep_workspace).loc;
@@ -379,8 +430,8 @@ int i64b_ep_combine(const i64b_ep_ctx* c, void* ep_workspace, const float* y_sha
     a.shared_scale = shared_scale;
     a.out = out;
     a.out_dtype = out_dtype;
-    const int64_t total = (int64_t)c->n_local * (c->hidden / 4);
-    const int64_t blocks = ceil_div64(total, 256);
+    const int64_t total = (int64_t)c->n_local * (c->hidden / 8);
+    const int64_t blocks = ceil_div64(total, 256 * kCombItems);
     const int64_t cap = (int64_t)i64b_num_sms() * 8;
     I64B_CUDA(i64b_launch(ep_combine_kernel, dim3((int)(blocks < cap ? blocks : cap)), dim3(256), 0, (cudaStream_t)stream,
                           *c, a));

@@ -43,6 +43,8 @@ struct I64bDispatchArgs {
     int hidden;
     int top_k, num_experts;
     int quantize;               // 1: per-row int8 quantisation fused into the scatter
+    const float* preq_scale;    // non-null: x is ALREADY int8 [N, H] with these per-token scales (x_preq from the fused
+                                // RMSNorm+quant): rows and scales are copied, nothing is re-quantised (quantize must be 0)
     int shared_copy;            // 1: also write row N*K + t (token order) for the shared expert
     void* xs;                   // [N*K (+N), H] bf16 or int8
     float* xs_scale;            // [N*K (+N)] (quantize)

@@ -68,6 +68,7 @@ _SIGNATURES = {
     "i64b_silu_hadamard": (_I, [_P, _P, _L, _I, _I, _P]),
     "i64b_quantize_rows_int8": (_I, [_P, _I, _P, _P, _L, _L, _P]),
     "i64b_dequantize_int8": (_I, [_P, _P, _P, _L, _L, _P]),
+    "i64b_add_rmsnorm": (_I, [_P, _P, _P, _I, _F, _P, _P, _P, _P, _L, _I, _P]),
     "i64b_moe_create": (_I, [C.POINTER(MoEConfig), C.POINTER(_P)]),
     "i64b_moe_destroy": (None, [_P]),
     "i64b_moe_set_scales": (_I, [_P, C.POINTER(_F), _I, _F, _F]),
@@ -77,6 +78,7 @@ _SIGNATURES = {
     "i64b_moe_set_table": (_I, [_P, _P]),
     "i64b_moe_workspace_bytes": (_Z, [_P, _L]),
     "i64b_moe_forward": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, _P]),
+    "i64b_moe_forward_preq": (_I, [_P, _P, _P, _P, _P, _I, _L, _P, _Z, _P]),
     "i64b_moe_uses_fused": (_I, [_P, _L]),
     "i64b_moe_fuses_combine": (_I, [_P, _L]),
     "i64b_moe_forward_stages": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, C.c_uint, _P]),

@@ -7,3 +7,9 @@ layer reads + the expert-parallel exchange).  Everything else of the reference (
 server) runs unchanged on top of these modules.
 """
 __version__ = "0.1.0"
+
+# overlay on an installed reference package of the same name, when there is one (see _overlay.py)
+from vllm_i64 import _overlay as _ov  # noqa: E402
+
+_ov.extend(__name__, globals())
+patch_reference_models = _ov.patch_reference_models

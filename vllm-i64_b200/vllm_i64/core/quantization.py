@@ -118,3 +118,10 @@ def quantize_experts(gate_up: torch.Tensor, down: torch.Tensor, config: QuantCon
     gq, gs = quantize_int8(gate_up)
     dq, ds = quantize_int8(down)
     return {"method": "int8", "gate_up_int8": gq, "gate_up_scale": gs, "down_int8": dq, "down_scale": ds}
+
+
+# names the reference's module has and this one does not (INT4 helpers, capability flags): taken from the reference when
+# this package runs as an overlay on it; load-time helpers called on CPU tensors delegate to the reference's own code
+from vllm_i64 import _overlay as _ov  # noqa: E402
+
+_REF_MOD = _ov.fill(__name__, globals())

@@ -111,6 +111,30 @@ class I64Block:
                                                  _C.stream_ptr(self.device)))
         return out
 
+    def forward_preq(self, x_q: torch.Tensor, x_scale: torch.Tensor, token_ids: Optional[torch.Tensor],
+                     out_dtype=torch.bfloat16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """W8A8 forward on rows the caller has already quantised (``x_preq = (int8 [N,H], fp32 scale [N])`` from the
+        fused RMSNorm+quant): no absmax / quantise pass, bit-identical to ``forward`` on the un-quantised rows."""
+        _C.require_cuda(x_q, x_scale, token_ids)
+        if x_q.dtype != torch.int8:
+            raise TypeError("x_q must be int8")
+        x_q = x_q.contiguous()
+        x_scale = x_scale.reshape(-1).to(torch.float32).contiguous()
+        n = x_q.shape[0]
+        if x_scale.numel() != n:
+            raise RuntimeError("x_scale must hold one scale per row of x_q")
+        if token_ids is not None:
+            token_ids = token_ids.to(torch.int64).contiguous()
+        if out is None:
+            out = self._out(n, out_dtype)
+        lib = _C.lib()
+        with torch.cuda.device(self.device):
+            ws = _C.workspace(self.device, lib.i64b_moe_workspace_bytes(self._h, n))
+            _C.check(lib.i64b_moe_forward_preq(self._h, x_q.data_ptr(), x_scale.data_ptr(), _C.ptr(token_ids),
+                                               out.data_ptr(), _C.dtype_code(out), n, ws.data_ptr(), ws.numel(),
+                                               _C.stream_ptr(self.device)))
+        return out
+
     def uses_fused(self, n: int) -> bool:
         return bool(_C.lib().i64b_moe_uses_fused(self._h, int(n)))
 

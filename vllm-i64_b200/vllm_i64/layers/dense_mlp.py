@@ -61,16 +61,22 @@ class _DenseBlockMixin:
         super()._load_from_state_dict(*args, **kwargs)
         self.invalidate()
 
-    def _run(self, x: torch.Tensor) -> torch.Tensor:
+    def _run(self, x: torch.Tensor, x_preq=None) -> torch.Tensor:
         _C.require_cuda(x)
         blk = self._ensure_block(x.device)
         x2 = x.reshape(-1, x.shape[-1])
         tp = get_tp()
+        use_preq = x_preq is not None and self.quantization == "int8"
+
+        def fwd(odt):
+            if use_preq:          # (int8 rows, per-token scale) from the fused RMSNorm+quant: no second quantisation pass
+                return blk.forward_preq(x_preq[0].reshape(x2.shape), x_preq[1], None, odt)
+            return blk.forward(x2, None, odt)
         if tp.tp_size > 1:
-            out = all_reduce(blk.forward(x2, None, torch.float32))
+            out = all_reduce(fwd(torch.float32))
             return out.to(x.dtype).reshape(x.shape)
         odt = torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32
-        out = blk.forward(x2, None, odt)
+        out = fwd(odt)
         return (out if out.dtype == x.dtype else out.to(x.dtype)).reshape(x.shape)
 
 
@@ -91,9 +97,10 @@ class DenseMLP(_DenseBlockMixin, nn.Module):
         return self.gate_proj.linear.weight, self.up_proj.linear.weight, self.down_proj.linear.weight
 
     def forward(self, x: torch.Tensor, x_preq=None, **kwargs) -> torch.Tensor:
-        """``x_preq`` (int8, scale) from a fused RMSNorm+quant is accepted for signature compatibility; the block
-        re-derives identical values from ``x`` (same quantisation rule), so it is not needed."""
-        return self._run(x)
+        """``x_preq = (int8 [N,H], scale [N,1])`` from the fused RMSNorm+quant (layers/dense_mlp.py:46-58 of the
+        reference): in W8A8 mode the block consumes it directly (``i64b_moe_forward_preq``) and skips its own
+        quantisation pass; the result is bit-identical either way (same quantisation rule)."""
+        return self._run(x, x_preq)
 
 
 class DenseSwiGLUMLP(_DenseBlockMixin, nn.Module):

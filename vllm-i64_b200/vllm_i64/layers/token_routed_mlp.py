@@ -206,16 +206,25 @@ class TokenRoutedMLP(nn.Module):
         out = all_reduce(out)
         return out.to(x.dtype).reshape(x.shape)
 
-    def forward(self, x: torch.Tensor, token_ids: Optional[torch.Tensor] = None, **kwargs) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, token_ids: Optional[torch.Tensor] = None, x_preq=None, **kwargs) -> torch.Tensor:
+        """``x_preq = (int8 [N,H], scale)`` (optional, W8A8 mode): rows already quantised by the fused RMSNorm+quant in
+        front of the block (``get_i64_cuda_ops().add_rmsnorm(..., quantize=True)``); the block then skips its own
+        absmax / quantise pass.  Same result bit for bit."""
         _C.require_cuda(x)
         blk = self._ensure_block(x.device)
         x2 = x.reshape(-1, self.hidden_size)
         ids = None if token_ids is None else token_ids.reshape(-1)
+        use_preq = x_preq is not None and self.quantization == "int8"
+
+        def fwd(odt):
+            if use_preq:
+                return blk.forward_preq(x_preq[0].reshape(x2.shape), x_preq[1], ids, odt)
+            return blk.forward(x2, ids, odt)
         if self.tp_size > 1:
-            out = all_reduce(blk.forward(x2, ids, torch.float32))
+            out = all_reduce(fwd(torch.float32))
             return out.to(x.dtype).reshape(x.shape)
         odt = torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32
-        out = blk.forward(x2, ids, odt)
+        out = fwd(odt)
         return (out if out.dtype == x.dtype else out.to(x.dtype)).reshape(x.shape)
 
     def fuse_shared_gate_up(self) -> bool:

@@ -145,3 +145,8 @@ def all_reduce(tensor: torch.Tensor) -> torch.Tensor:
         return tensor
     dist.all_reduce(tensor, group=_TP.tp_group)
     return tensor
+
+
+from vllm_i64 import _overlay as _ov  # noqa: E402
+
+_ov.fill(__name__, globals())
