@@ -50,6 +50,8 @@ def _t(a, dev, dt=None):
 
 def _worker(rank, world, port, case, ret):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    if case.get("lsu", False):
+        os.environ["I64B_EP_TMA"] = "0"      # read once when the library first dispatches: the workers are fresh processes
     dev = torch.device("cuda", rank)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=_PG_TIMEOUT)
@@ -185,3 +187,8 @@ def test_ep_config5_shape(world):
 def test_ep_zipf_skew(world):
     """Zipf(1.1)-distributed token ids: a few experts (and so a few ranks) receive most of the rows."""
     _run(world, {"shape": SMALL, "n_per": ("each", 512), "zipf": True})
+
+
+def test_ep_load_store_kernels():
+    """I64B_EP_TMA=0: the load/store-unit dispatch and combine kernels (the path for rows the bulk-copy ring cannot hold)."""
+    _run(2, {"shape": SMALL, "n_per": ("ramp", 0), "lsu": True})

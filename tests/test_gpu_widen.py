@@ -69,8 +69,11 @@ def test_add_rmsnorm_vs_oracle(n, h):
     hh, y, qs = get_i64_cuda_ops().add_rmsnorm(cu(x, torch.bfloat16), cu(r, torch.bfloat16), cu(w, torch.bfloat16), 1e-6, quantize=True)
     ho, yo = O.add_rmsnorm(x, r, w, 1e-6, bf16=True)
     np.testing.assert_array_equal(hh.float().cpu().numpy(), ho)
+    # two roundings to bf16 follow the fp32 row statistic (type_as, then the weight product): a last-bit difference in the
+    # statistic (reduction order, rsqrt) can move an element by one bf16 ulp at the first rounding and, rarely, one more at
+    # the second.  Bar: <= 2 ulp, on fewer than 0.2 % of the elements (measured: ~1e-5 of them differ at all).
     d = _ulp_bf16(y.float().cpu().numpy(), yo)
-    assert d.max() <= 1 and (d > 0).mean() < 2e-3, (d.max(), (d > 0).mean())
+    assert d.max() <= 2 and (d > 0).mean() < 2e-3 and (d > 1).mean() < 1e-4, (d.max(), (d > 0).mean())
     q_ref, s_ref = O.quantize_rows_int8(y.float().cpu().numpy())
     np.testing.assert_array_equal(qs[0].cpu().numpy(), q_ref)
     np.testing.assert_array_equal(qs[1].reshape(-1).cpu().numpy(), s_ref.reshape(-1))
