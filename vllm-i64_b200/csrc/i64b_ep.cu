@@ -297,7 +297,7 @@ __device__ __forceinline__ void mbar_wait_trap(uint64_t* bar, uint32_t parity) {
 }
 
 constexpr int kTmaThreads = 128;
-constexpr int kTmaChunk = 256;          // tokens whose (owner, row) tags a block stages in shared memory at a time
+constexpr int kTmaChunk = 128;          // tokens whose (owner, row) tags a block stages in shared memory at a time
 constexpr int kDispDepth = 8;           // rows in flight per block (dispatch)
 
 // Dispatch, bf16 transport: block b owns a contiguous token range.  All threads decode the plan of a chunk of tokens into
@@ -506,6 +506,17 @@ __global__ void ep_barrier_kernel(const i64b_ep_ctx c) {
 
 static size_t ep_align(size_t v) { return (v + 255) & ~size_t(255); }
 // I64B_EP_TMA=0 selects the load/store-unit versions of the dispatch and combine kernels (kept for comparison)
+constexpr int kTmaSmemMax = 96 * 1024;       // dynamic shared memory the bulk-copy kernels may ask for (ring of rows / stages)
+static int ep_configure_tma() {           // function attributes are per device
+    static bool configured[I64B_MAX_DEVICES] = {};
+    const int dev = i64b_current_device();
+    if (!configured[dev]) {
+        I64B_CUDA(cudaFuncSetAttribute(ep_dispatch_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemMax));
+        I64B_CUDA(cudaFuncSetAttribute(ep_combine_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemMax));
+        configured[dev] = true;
+    }
+    return I64B_OK;
+}
 static bool ep_use_tma() {
     static const bool on = !(getenv("I64B_EP_TMA") && atoi(getenv("I64B_EP_TMA")) == 0);
     return on;
@@ -622,7 +633,8 @@ int i64b_ep_dispatch(const i64b_ep_ctx* c, const void* x, const int64_t* token_i
     const int grid = (int)ceil_div64(c->n_local > 0 ? c->n_local : 1, kEpWarps);
     if (c->x_mode == I64B_MODE_W8A8) {
         I64B_CUDA(i64b_launch(ep_dispatch_kernel<true>, dim3(grid), dim3(kEpWarps * 32), 0, s, *c, x, w.plan, w.loc));
-    } else if (ep_use_tma() && c->hidden * 2 * kDispDepth <= 48 * 1024 && c->hidden % 8 == 0) {
+    } else if (ep_use_tma() && c->hidden * 2 * kDispDepth <= kTmaSmemMax && c->hidden % 8 == 0) {
+        if (int rc = ep_configure_tma()) return rc;
         // bulk-copy dispatch: contiguous token ranges, about four blocks per SM
         const int64_t nn = c->n_local > 0 ? c->n_local : 1;
         const int64_t blocks = nn < (int64_t)i64b_num_sms() * 4 ? nn : (int64_t)i64b_num_sms() * 4;
@@ -653,9 +665,10 @@ int i64b_ep_combine(const i64b_ep_ctx* c, void* ep_workspace, const float* y_sha
     a.out_dtype = out_dtype;
     {
         const int stage = c->top_k * c->hidden * (c->y_dtype == I64B_F32 ? 4 : 2) + (y_shared ? c->hidden * 4 : 0);
-        int depth = 48 * 1024 / stage;
+        int depth = kTmaSmemMax / stage;
         if (depth > 6) depth = 6;
         if (ep_use_tma() && depth >= 2) {
+            if (int rc = ep_configure_tma()) return rc;
             const int64_t nn = c->n_local;
             const int64_t blocks = nn < (int64_t)i64b_num_sms() * 4 ? nn : (int64_t)i64b_num_sms() * 4;
             const int tpb = (int)ceil_div64(nn, blocks);

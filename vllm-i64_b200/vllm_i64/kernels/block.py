@@ -31,6 +31,13 @@ class I64Block:
         self._packed: Optional[torch.Tensor] = None
         self._table_u8: Optional[torch.Tensor] = None
 
+    def __deepcopy__(self, memo):
+        """A packed block is not copied with its module (the handle owns device memory): the copy packs its own lazily."""
+        return None
+
+    def __reduce__(self):
+        return (type(None), ())
+
     def __del__(self):
         h = getattr(self, "_h", None)
         if h is not None and h.value:

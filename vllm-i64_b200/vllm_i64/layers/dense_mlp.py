@@ -14,11 +14,12 @@ import torch
 import torch.nn as nn
 
 from vllm_i64 import _C
+from vllm_i64.kernels import torch_ops
 from vllm_i64.kernels.block import I64Block
 from vllm_i64.parallel.tensor_parallel import ColumnParallelLinear, RowParallelLinear, all_reduce, get_tp
 
 
-class _DenseBlockMixin:
+class _DenseBlockMixin(torch_ops.TracedLayer):
     quantization = "none"
     _block: Optional[I64Block] = None
     _block_key = None
@@ -46,6 +47,9 @@ class _DenseBlockMixin:
                 blk.load_w8a8(None, None, None, None, q13, s13, q2, s2)
         self._block, self._block_key = blk, key
         return blk
+
+    def _forward_eager(self, x, token_ids=None, x_preq=None):
+        return self._run(x, x_preq)
 
     def quantize_w8a8(self):
         self.quantization = "int8"
@@ -85,6 +89,7 @@ class DenseMLP(_DenseBlockMixin, nn.Module):
 
     def __init__(self, hidden_size: int, intermediate_size: int):
         super().__init__()
+        torch_ops.register_layer(self)
         tp = get_tp()
         self.hidden_size = hidden_size
         self.intermediate_size = intermediate_size
@@ -100,6 +105,8 @@ class DenseMLP(_DenseBlockMixin, nn.Module):
         """``x_preq = (int8 [N,H], scale [N,1])`` from the fused RMSNorm+quant (layers/dense_mlp.py:46-58 of the
         reference): in W8A8 mode the block consumes it directly (``i64b_moe_forward_preq``) and skips its own
         quantisation pass; the result is bit-identical either way (same quantisation rule)."""
+        if torch.compiler.is_compiling():
+            return torch_ops.token_routed_mlp(x, None, x_preq, self)
         return self._run(x, x_preq)
 
 
@@ -108,6 +115,7 @@ class DenseSwiGLUMLP(_DenseBlockMixin, nn.Module):
 
     def __init__(self, config):
         super().__init__()
+        torch_ops.register_layer(self)
         self.gate_proj = nn.Linear(config.hidden_size, config.intermediate_size, bias=False)
         self.up_proj = nn.Linear(config.hidden_size, config.intermediate_size, bias=False)
         self.down_proj = nn.Linear(config.intermediate_size, config.hidden_size, bias=False)
@@ -119,6 +127,8 @@ class DenseSwiGLUMLP(_DenseBlockMixin, nn.Module):
         return self.gate_proj.weight, self.up_proj.weight, self.down_proj.weight
 
     def forward(self, x, token_ids=None, **kwargs):
+        if torch.compiler.is_compiling():
+            return torch_ops.token_routed_mlp(x, None, None, self)
         return self._run(x)
 
     def fuse_gate_up(self) -> bool:

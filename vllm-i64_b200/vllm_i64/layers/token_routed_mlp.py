@@ -17,11 +17,12 @@ import torch
 import torch.nn as nn
 
 from vllm_i64 import _C
+from vllm_i64.kernels import torch_ops
 from vllm_i64.kernels.block import I64Block
 from vllm_i64.parallel.tensor_parallel import all_reduce, get_tp
 
 
-class TokenRoutedMLP(nn.Module):
+class TokenRoutedMLP(torch_ops.TracedLayer, nn.Module):
     def __init__(self, hidden_size: int, intermediate_size: int, num_experts: int, vocab_size: int,
                  shared_expert: bool = False, shared_intermediate_size: int = 0, top_k: int = 1,
                  top_k_primary_weight: Optional[float] = None, use_shared_routed_gates: bool = False,
@@ -69,6 +70,7 @@ class TokenRoutedMLP(nn.Module):
             nn.init.kaiming_uniform_(w, a=5 ** 0.5)
 
         self.quantization = "none"        # "none" (bf16) | "int8" (dynamic W8A8)
+        torch_ops.register_layer(self)
         self._block: Optional[I64Block] = None
         self._block_key = None
 
@@ -209,7 +211,13 @@ class TokenRoutedMLP(nn.Module):
     def forward(self, x: torch.Tensor, token_ids: Optional[torch.Tensor] = None, x_preq=None, **kwargs) -> torch.Tensor:
         """``x_preq = (int8 [N,H], scale)`` (optional, W8A8 mode): rows already quantised by the fused RMSNorm+quant in
         front of the block (``get_i64_cuda_ops().add_rmsnorm(..., quantize=True)``); the block then skips its own
-        absmax / quantise pass.  Same result bit for bit."""
+        absmax / quantise pass.  Same result bit for bit.  While ``torch.compile`` traces, the whole forward is one
+        ``vllm_i64::token_routed_mlp`` node (kernels/torch_ops.py; fused_i64_moe.py:123-142 of the reference)."""
+        if torch.compiler.is_compiling():
+            return torch_ops.token_routed_mlp(x, token_ids, x_preq, self)
+        return self._forward_eager(x, token_ids, x_preq)
+
+    def _forward_eager(self, x: torch.Tensor, token_ids: Optional[torch.Tensor] = None, x_preq=None) -> torch.Tensor:
         _C.require_cuda(x)
         blk = self._ensure_block(x.device)
         x2 = x.reshape(-1, self.hidden_size)
