@@ -628,7 +628,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
         b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep, transport_dtype=dt)
         b.load_bf16(*ws0)
         b.set_table(table0)
-        b.reserve(n)
+        b.reserve(n, lanes=args.ep_lanes or None)
         got = b.forward(x, ids, torch.float32)
         torch.cuda.synchronize(device)
         if name == "f32":
@@ -657,7 +657,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
         b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep, transport_dtype=tdt)
         b.load_bf16(*synth_weights(wl, layer, device))
         b.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, layer)))
-        b.reserve(n)
+        b.reserve(n, lanes=args.ep_lanes or None)
         blocks.append(b)
     torch.cuda.synchronize(device)
 
@@ -683,6 +683,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
     e2e_steps = max(3, min(args.steps, 50))
     ms_e2e = time_graph(step_e2e, e2e_steps, 3, stream, barrier)
     timeline = None
+    names = []
     if args.ep_timeline:
         # per-stage device time of one layer, eager launches with CUDA events between the C-ABI calls (mean over 5 steps of
         # layer 1; the barrier entries contain the wait for the slowest peer); the shared expert runs on its own stream
@@ -698,6 +699,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
                     acc.setdefault(name, []).append(e_prev.elapsed_time(ev) * 1e3)
             blocks[1].timeline = None
         names = list(acc)
+    if args.ep_timeline and names:
         tt = torch.tensor([float(np.mean(acc[k])) for k in names], device=device, dtype=torch.float64)
         tmax = tt.clone()
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -739,6 +741,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
             "target_us_per_layer": {"tensor": round(t_tensor, 1), "nvlink_one_way": round(t_link, 1)},
             "us_per_layer": round(us_layer, 2),
             "nvlink_bytes_per_rank_per_layer": {"dispatch_out": int(sent), "return_in": int(back)}}
+    blocks_lanes = blocks[0]._lanes
     for b in blocks:
         b.close()
     return {"value": tokens / (ms_step * 1e-3), "ms_per_step": ms_step, "launches_per_step": int(launches),
@@ -746,6 +749,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
                     "h2d_bytes_per_step": n * H * 2 + n * 8, "d2h_bytes_per_step": n * H * 2, "copies_per_step": 1,
                     "via": "engine step per rank: pinned H2D of the rank's x + ids, L expert-parallel block forwards, D2H of the last output"},
             "roofline": roof, "ep_parity": ep_parity, "transport_dtype": args.ep_transport, "ep_timeline": timeline,
+            "ep_lanes": len(blocks_lanes),
             "nccl_all_to_all_baseline": ({"ms_per_step": ms_nccl, "value": tokens / (ms_nccl * 1e-3)} if nccl else None)}
 
 
@@ -763,6 +767,8 @@ def main():
     ap.add_argument("--no-workloads", action="store_true", help="N = 1: only the line's own workload")
     ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
+    ap.add_argument("--ep-lanes", type=int, default=0,
+                    help="N > 1: micro-batch lanes per expert-parallel forward (0 = the library's default)")
     ap.add_argument("--ep-nccl-baseline", action="store_true", help="also time the all_to_all_single exchange (eager)")
     ap.add_argument("--ep-timeline", action="store_true", help="also report per-stage device times of one EP layer (eager)")
     args = ap.parse_args()
@@ -829,7 +835,7 @@ def main():
                     "gpu_launches": r["launches_per_step"] * args.steps, "gpu_launches_per_step": r["launches_per_step"],
                     "roofline": r["roofline"], "cpu_baseline": None, "ep_parity": r["ep_parity"],
                     "ep_transport_dtype": r["transport_dtype"], "nccl_all_to_all_baseline": r["nccl_all_to_all_baseline"],
-                    "ep_timeline": r["ep_timeline"]}
+                    "ep_timeline": r["ep_timeline"], "ep_lanes": r["ep_lanes"]}
             emit(line)
         import torch.distributed as dist
         dist.barrier()

@@ -81,7 +81,7 @@ def _worker(rank, world, port, case, ret):
                 sh = (_t(wq.sh13_q, dev), _t(wq.sh13_s, dev), _t(wq.sh2_q, dev), _t(wq.sh2_s, dev)) if s else ()
                 blk.load_w8a8(_t(wq.w13_q, dev), _t(wq.w13_s, dev), _t(wq.w2_q, dev), _t(wq.w2_s, dev), *sh)
             blk.set_table(torch.from_numpy(table))
-            blk.reserve(max(n_per))
+            blk.reserve(max(n_per), lanes=case.get("lanes"))
             return blk
 
         if hi > lo:
@@ -192,3 +192,10 @@ def test_ep_zipf_skew(world):
 def test_ep_load_store_kernels():
     """I64B_EP_TMA=0: the load/store-unit dispatch and combine kernels (the path for rows the bulk-copy ring cannot hold)."""
     _run(2, {"shape": SMALL, "n_per": ("ramp", 0), "lsu": True})
+
+
+@pytest.mark.parametrize("world,lanes", [(1, 2), (2, 2), (2, 3), (4, 2), (8, 2), (8, 4)])
+def test_ep_micro_batch_lanes(world, lanes):
+    """The forward cut into micro-batches on their own buffers and streams (unequal batches, one rank without tokens, so some
+    lanes are empty): same bits as the single-GPU block, graph replay included; W8A8 bit-exact."""
+    _run(world, {"shape": SMALL, "n_per": ("ramp", 0) if world > 1 else ("equal", 333), "lanes": lanes, "w8a8": True})

@@ -8,7 +8,8 @@ it, so the shim lives on the Python side of the boundary):
 
   * the six ops, reference names and argument order, CUDA implementations = ``kernel_loader.I64Ops`` (one C-ABI call
     each), fake impls giving the output shapes / dtypes;
-  * ``add_rmsnorm``            — the fused residual-add + RMSNorm (+ INT8 quant) in front of the block (SURVEY 8f-1);
+  * ``add_rmsnorm``            — the fused residual-add + RMSNorm (+ INT8 quant) in front of the block:
+    ``(h, y, q, scale)``; ``h`` is empty without a residual, ``q`` / ``scale`` are empty without ``quantize``;
   * ``token_routed_mlp``       — one whole ``TokenRoutedMLP`` / ``DenseMLP`` forward as ONE graph node (the layer is looked
     up by an integer id, so the op's arguments are tensors and ints only); ``forward()`` of those modules routes
     through it while ``torch.compile`` is tracing, so a compiled model has no graph break at the block.
@@ -96,10 +97,10 @@ def _fused_route_scatter(token_ids, hidden, num_experts):
 
 
 def _add_rmsnorm(x, residual, weight, eps, quantize):
-    from vllm_i64.kernels.cuda import add_rmsnorm
-    h, y, qs = add_rmsnorm(x, residual, weight, eps, quantize=quantize, want_normed=True)
-    if h is None:
-        h = x
+    from vllm_i64.kernels.cuda import get_i64_cuda_ops
+    h, y, qs = get_i64_cuda_ops().add_rmsnorm(x, residual, weight, eps, quantize=quantize, want_normed=True)
+    if h is None:                        # no residual: nothing was added (an op may not return its input)
+        h = x.new_empty(0)
     if qs is None:
         q = torch.empty(0, dtype=torch.int8, device=x.device)
         s = torch.empty(0, dtype=torch.float32, device=x.device)
@@ -143,7 +144,7 @@ def _fake_add_rmsnorm(x, residual, weight, eps, quantize):
     n = x.numel() // x.shape[-1]
     q = torch.empty(x.shape if quantize else (0,), dtype=torch.int8, device=x.device)
     s = torch.empty((n, 1) if quantize else (0,), dtype=torch.float32, device=x.device)
-    return torch.empty_like(x), torch.empty_like(x), q, s
+    return (torch.empty_like(x) if residual is not None else x.new_empty(0)), torch.empty_like(x), q, s
 
 
 def _fake_token_routed_mlp(x, token_ids, x_q, x_scale, layer_id):

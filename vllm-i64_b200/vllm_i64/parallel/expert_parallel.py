@@ -18,6 +18,7 @@ split sizes exchanged through the host, ``all_to_all_single`` each way — gener
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Callable, List, Optional, Sequence
 
@@ -125,6 +126,11 @@ def ep_moe_forward(x: torch.Tensor, routes: torch.Tensor, num_experts: int,
     return combine_fn(y, shared)
 
 
+class _Lane:
+    """One micro-batch pipeline of an EPTokenRoutedBlock: peer-mapped buffers + flags (ctx), workspaces, stream."""
+    __slots__ = ("ctx", "bases", "cap", "ws_plan", "ws_gemm", "shared_out", "stream", "dispatched")
+
+
 class EPTokenRoutedBlock:
     """The block with its routed experts sharded over the EP group (GPU).  Holds two C-ABI blocks: the local
     experts (E/G of them, no shared expert) and the replicated dense shared expert."""
@@ -158,6 +164,7 @@ class EPTokenRoutedBlock:
             # kernel, whose CTAs wait on one another and must own the GPU (include/i64b.h, i64b_moe_forward)
             self.shared.set_debug(_C.DEBUG_NO_FUSED)
         self._table = None
+        self._lanes = None
         self._bases = None
         self._cap_tokens = 0
         self.timeline = None
@@ -166,12 +173,13 @@ class EPTokenRoutedBlock:
         # best effort, non-collective: unmap and free without the barrier (the process is going away)
         try:
             from vllm_i64 import _C
-            bases = getattr(self, "_bases", None)
-            if bases:
+            lanes = getattr(self, "_lanes", None)
+            if lanes:
                 lib = _C.lib()
-                for d, b in enumerate(bases):
-                    (lib.i64b_ep_free if d == self.ep.ep_rank else lib.i64b_ipc_close)(b)
-                self._bases = None
+                for lane in lanes:
+                    for d, b in enumerate(lane.bases):
+                        (lib.i64b_ep_free if d == self.ep.ep_rank else lib.i64b_ipc_close)(b)
+                self._lanes = None
         except Exception:
             pass
 
@@ -202,11 +210,16 @@ class EPTokenRoutedBlock:
         return out
 
     # ------------------------------------------------------------------ NVLink peer-memory path (the product path)
-    def reserve(self, max_tokens: int) -> None:
+    def reserve(self, max_tokens: int, lanes: Optional[int] = None) -> None:
         """COLLECTIVE, setup only (allocates and synchronises): size this rank's receive / output buffers for
         ``max_tokens`` local tokens per step on EVERY rank (the maximum over the ranks is used), exchange the CUDA IPC
         handles once and map every peer's buffers.  The engine calls it with its maximum batch; ``forward_peer`` calls
-        it on first use."""
+        it on first use.
+
+        ``lanes``: a forward cuts its tokens into that many micro-batches, each with its own buffers, flags and stream,
+        started one dispatch apart — while one lane's rows cross NVLink the other lane's GEMMs own the tensor cores.
+        Every rank must use the same number (default: env ``I64B_EP_LANES``, else 2 from 4096 tokens per rank up,
+        1 below — decided on the all-reduced maximum, so the ranks agree)."""
         import ctypes as C
         from vllm_i64 import _C
         lib = _C.lib()
@@ -219,7 +232,11 @@ class EPTokenRoutedBlock:
             dist.all_reduce(nn, op=dist.ReduceOp.MAX, group=self.ep.group)
             n = int(nn[0])
         n = max(n, 1)
-        cap_src = n * K                                        # a source's whole batch may land on one owner
+        if lanes is None:
+            lanes = int(os.environ.get("I64B_EP_LANES", "0")) or (2 if (G > 1 and n >= 4096) else 1)
+        lanes = max(1, min(int(lanes), 8))
+        n_lane = -(-n // lanes)
+        cap_src = n_lane * K                                   # a source's whole micro-batch may land on one owner
         rows = G * cap_src
         q = self.mode == _C.MODE_W8A8
         ysz = 4 if self.transport_dtype == torch.float32 else 2
@@ -235,58 +252,76 @@ class EPTokenRoutedBlock:
         with torch.cuda.device(self.device):
             torch.cuda.synchronize(self.device)
             self.close()
-            base = C.c_void_p()
-            _C.check(lib.i64b_ep_alloc(total, C.byref(base)))
-            handle = C.create_string_buffer(64)
-            _C.check(lib.i64b_ipc_export(base, handle))
+            mine = []
+            for _ in range(lanes):
+                base = C.c_void_p()
+                _C.check(lib.i64b_ep_alloc(total, C.byref(base)))
+                handle = C.create_string_buffer(64)
+                _C.check(lib.i64b_ipc_export(base, handle))
+                mine.append((base, bytes(handle.raw)))
             handles = [None] * G
             if G > 1:
-                dist.all_gather_object(handles, bytes(handle.raw), group=self.ep.group)
-            bases = []
-            for d in range(G):
-                if d == self.ep.ep_rank:
-                    bases.append(base.value)
-                else:
-                    p = C.c_void_p()
-                    _C.check(lib.i64b_ipc_import(handles[d], C.byref(p)))
-                    bases.append(p.value)
-        ctx = _C.EPCtx()
-        ctx.rank, ctx.size, ctx.n_local, ctx.hidden = self.ep.ep_rank, G, 0, H
-        ctx.top_k, ctx.num_experts, ctx.vocab, ctx.cap_src = K, self.E, self.router.cfg.vocab_size, cap_src
-        ctx.y_dtype = _C.F32 if self.transport_dtype == torch.float32 else _C.BF16
-        ctx.x_mode = self.mode
-        for d in range(G):
-            ctx.peer_xs[d] = bases[d] + off_xs
-            ctx.peer_xs_scale[d] = bases[d] + off_scale
-            ctx.peer_y[d] = bases[d] + off_y
-            ctx.peer_flags[d] = bases[d] + off_flags
-        ctx.state = base.value + off_state
-        self._ctx, self._bases, self._cap_tokens = ctx, bases, n
-        self._ws_plan = torch.empty(lib.i64b_ep_workspace_bytes(C.byref(ctx)) + 256, dtype=torch.uint8, device=self.device)
-        self._ws_gemm = torch.empty(lib.i64b_moe_dispatched_workspace_bytes(self.local._h, C.byref(ctx)) + 256,
-                                    dtype=torch.uint8, device=self.device)
-        # persistent fp32 output of the home rank's shared expert (a fresh 100+ MB torch allocation per call was
-        # measured at ~350 us of allocator time per layer)
-        self._shared_out = (torch.empty(n, H, dtype=torch.float32, device=self.device)
-                            if self.shared is not None else None)
-        self._side = torch.cuda.Stream(self.device)
+                dist.all_gather_object(handles, [h for _, h in mine], group=self.ep.group)
+            self._lanes = []
+            for li in range(lanes):
+                base = mine[li][0]
+                bases = []
+                for d in range(G):
+                    if d == self.ep.ep_rank:
+                        bases.append(base.value)
+                    else:
+                        p = C.c_void_p()
+                        _C.check(lib.i64b_ipc_import(handles[d][li], C.byref(p)))
+                        bases.append(p.value)
+                ctx = _C.EPCtx()
+                ctx.rank, ctx.size, ctx.n_local, ctx.hidden = self.ep.ep_rank, G, 0, H
+                ctx.top_k, ctx.num_experts, ctx.vocab, ctx.cap_src = K, self.E, self.router.cfg.vocab_size, cap_src
+                ctx.y_dtype = _C.F32 if self.transport_dtype == torch.float32 else _C.BF16
+                ctx.x_mode = self.mode
+                for d in range(G):
+                    ctx.peer_xs[d] = bases[d] + off_xs
+                    ctx.peer_xs_scale[d] = bases[d] + off_scale
+                    ctx.peer_y[d] = bases[d] + off_y
+                    ctx.peer_flags[d] = bases[d] + off_flags
+                ctx.state = base.value + off_state
+                lane = _Lane()
+                lane.ctx, lane.bases, lane.cap = ctx, bases, n_lane
+                lane.ws_plan = torch.empty(lib.i64b_ep_workspace_bytes(C.byref(ctx)) + 256, dtype=torch.uint8,
+                                           device=self.device)
+                lane.ws_gemm = torch.empty(lib.i64b_moe_dispatched_workspace_bytes(self.local._h, C.byref(ctx)) + 256,
+                                           dtype=torch.uint8, device=self.device)
+                # persistent fp32 output of the home rank's shared expert (a fresh 100+ MB torch allocation per call
+                # was measured at ~350 us of allocator time per layer)
+                lane.shared_out = (torch.empty(n_lane, H, dtype=torch.float32, device=self.device)
+                                   if self.shared is not None else None)
+                lane.stream = torch.cuda.Stream(self.device)
+                lane.dispatched = torch.cuda.Event()
+                self._lanes.append(lane)
+        self._cap_tokens = n_lane * lanes
+        l0 = self._lanes[0]
+        # single-lane names (tools/ep_probe.py, bring-up)
+        self._ctx, self._bases, self._ws_plan, self._ws_gemm = l0.ctx, l0.bases, l0.ws_plan, l0.ws_gemm
+        self._shared_out, self._side = l0.shared_out, l0.stream
         if G > 1:
             dist.barrier(group=self.ep.group)                  # every rank has mapped every buffer
 
     def close(self) -> None:
         """COLLECTIVE when buffers are mapped: unmap the peers' buffers, wait until every rank has done so, free ours."""
         from vllm_i64 import _C
-        bases = getattr(self, "_bases", None)
-        if not bases:
+        lanes = getattr(self, "_lanes", None)
+        if not lanes:
             return
         lib = _C.lib()
         torch.cuda.synchronize(self.device)
-        for d, b in enumerate(bases):
-            if d != self.ep.ep_rank:
-                lib.i64b_ipc_close(b)
+        for lane in lanes:
+            for d, b in enumerate(lane.bases):
+                if d != self.ep.ep_rank:
+                    lib.i64b_ipc_close(b)
         if self.ep.ep_size > 1 and dist.is_initialized():
-            dist.barrier(group=self.ep.group)                  # nobody still maps the buffer that is freed next
-        lib.i64b_ep_free(bases[self.ep.ep_rank])
+            dist.barrier(group=self.ep.group)                  # nobody still maps the buffers that are freed next
+        for lane in lanes:
+            lib.i64b_ep_free(lane.bases[self.ep.ep_rank])
+        self._lanes = None
         self._bases = None
         self._cap_tokens = 0
 
@@ -302,22 +337,29 @@ class EPTokenRoutedBlock:
         if x.dtype != torch.bfloat16 or not x.is_contiguous():
             x = x.to(torch.bfloat16).contiguous()
         token_ids = token_ids.to(torch.int64).contiguous()
-        if not getattr(self, "_bases", None):
+        if not getattr(self, "_lanes", None):
             self.reserve(n)
         if n > self._cap_tokens:
             raise ValueError(f"{n} tokens exceed the reserved expert-parallel capacity of {self._cap_tokens} tokens per "
                              f"rank: call reserve(max_tokens) on every rank first")
-        self._ctx.n_local = n
-        ctx = C.byref(self._ctx)
+        if out is None:
+            out = torch.empty(n, self.H, dtype=out_dtype, device=self.device)
+        wts = (C.c_float * 4)(*[self.w[i] if i < len(self.w) else 0.0 for i in range(4)])
+        lanes = self._lanes
         with torch.cuda.device(self.device):
             cur = torch.cuda.current_stream(self.device)
+            if len(lanes) > 1:
+                return self._forward_lanes(x, token_ids, out, wts, cur)
+            lane = lanes[0]
+            lane.ctx.n_local = n
+            ctx = C.byref(lane.ctx)
             shared = None
             if self.shared is not None and n > 0:
                 # the home rank's shared expert runs on a side stream: its GEMMs fill the SMs while the dispatch kernel
                 # (NVLink-bound, a few warps per SM) and the barrier occupy the main stream
-                self._side.wait_stream(cur)
-                with torch.cuda.stream(self._side):
-                    shared = self.shared.forward(x, None, torch.float32, out=self._shared_out[:n])
+                lane.stream.wait_stream(cur)
+                with torch.cuda.stream(lane.stream):
+                    shared = self.shared.forward(x, None, torch.float32, out=lane.shared_out[:n])
             st = _C.stream_ptr(self.device)
             tl = self.timeline          # bring-up: a list collects (stage, event) pairs of this call (eager runs only)
 
@@ -328,24 +370,64 @@ class EPTokenRoutedBlock:
                     tl.append((name, ev))
             mark("start")
             _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), token_ids.data_ptr(), self._table.data_ptr(),
-                                          self._ws_plan.data_ptr(), self._ws_plan.numel(), st))
+                                          lane.ws_plan.data_ptr(), lane.ws_plan.numel(), st))
             mark("plan+dispatch")
             _C.check(lib.i64b_ep_barrier(ctx, st))
             mark("barrier1")
-            _C.check(lib.i64b_moe_forward_dispatched(self.local._h, ctx, self._ws_plan.data_ptr(), self._ws_gemm.data_ptr(),
-                                                     self._ws_gemm.numel(), st))
+            _C.check(lib.i64b_moe_forward_dispatched(self.local._h, ctx, lane.ws_plan.data_ptr(), lane.ws_gemm.data_ptr(),
+                                                     lane.ws_gemm.numel(), st))
             mark("groups+gemm1+gemm2")
             _C.check(lib.i64b_ep_barrier(ctx, st))
             mark("barrier2")
-            if out is None:
-                out = torch.empty(n, self.H, dtype=out_dtype, device=self.device)
             if shared is not None:
-                cur.wait_stream(self._side)
+                cur.wait_stream(lane.stream)
             mark("join shared-expert stream")
-            wts = (C.c_float * 4)(*[self.w[i] if i < len(self.w) else 0.0 for i in range(4)])
-            _C.check(lib.i64b_ep_combine(ctx, self._ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
+            _C.check(lib.i64b_ep_combine(ctx, lane.ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
                                          out.data_ptr(), _C.dtype_code(out), st))
             mark("combine (pull)")
+        return out
+
+    def _forward_lanes(self, x, token_ids, out, wts, cur) -> torch.Tensor:
+        """Micro-batch pipeline: lane i handles tokens [cuts[i], cuts[i+1]) on its own stream and buffers, in the order
+        dispatch -> shared expert (local, covers the wait for the peers' rows) -> barrier -> routed GEMMs -> barrier ->
+        combine; lane i+1 starts when lane i's dispatch has been issued, so exchange kernels of one lane run next to GEMMs
+        of the other.  Per-token arithmetic does not depend on the cut, so the result equals the single-lane one bit for
+        bit.  Every rank runs every lane (an empty micro-batch still publishes its zero counts and joins the barriers)."""
+        import ctypes as C
+        from vllm_i64 import _C
+        lib = _C.lib()
+        n = x.shape[0]
+        L = len(self._lanes)
+        per = -(-n // L) if n else 0
+        prev = None
+        for li, lane in enumerate(self._lanes):
+            lo, hi = min(n, li * per), min(n, (li + 1) * per)
+            m = hi - lo
+            lane.ctx.n_local = m
+            ctx = C.byref(lane.ctx)
+            s = lane.stream
+            s.wait_stream(cur)
+            if prev is not None:
+                s.wait_event(prev.dispatched)
+            with torch.cuda.stream(s):
+                st = s.cuda_stream
+                xs, ids = x[lo:hi], token_ids[lo:hi]
+                _C.check(lib.i64b_ep_dispatch(ctx, xs.data_ptr() if m else None, ids.data_ptr() if m else None,
+                                              self._table.data_ptr(), lane.ws_plan.data_ptr(), lane.ws_plan.numel(), st))
+                lane.dispatched.record(s)
+                shared = None
+                if self.shared is not None and m > 0:
+                    shared = self.shared.forward(xs, None, torch.float32, out=lane.shared_out[:m])
+                _C.check(lib.i64b_ep_barrier(ctx, st))
+                _C.check(lib.i64b_moe_forward_dispatched(self.local._h, ctx, lane.ws_plan.data_ptr(),
+                                                         lane.ws_gemm.data_ptr(), lane.ws_gemm.numel(), st))
+                _C.check(lib.i64b_ep_barrier(ctx, st))
+                o = out[lo:hi]
+                _C.check(lib.i64b_ep_combine(ctx, lane.ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
+                                             o.data_ptr() if m else None, _C.dtype_code(out), st))
+            prev = lane
+        for lane in self._lanes:
+            cur.wait_stream(lane.stream)
         return out
 
     def forward(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
