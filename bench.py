@@ -742,6 +742,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
             "us_per_layer": round(us_layer, 2),
             "nvlink_bytes_per_rank_per_layer": {"dispatch_out": int(sent), "return_in": int(back)}}
     blocks_lanes = blocks[0]._lanes
+    comm_sms = {"dispatch": blocks[0]._comm_dispatch, "combine": blocks[0]._comm_combine}
     for b in blocks:
         b.close()
     return {"value": tokens / (ms_step * 1e-3), "ms_per_step": ms_step, "launches_per_step": int(launches),
@@ -749,7 +750,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
                     "h2d_bytes_per_step": n * H * 2 + n * 8, "d2h_bytes_per_step": n * H * 2, "copies_per_step": 1,
                     "via": "engine step per rank: pinned H2D of the rank's x + ids, L expert-parallel block forwards, D2H of the last output"},
             "roofline": roof, "ep_parity": ep_parity, "transport_dtype": args.ep_transport, "ep_timeline": timeline,
-            "ep_lanes": len(blocks_lanes),
+            "ep_lanes": len(blocks_lanes), "ep_comm_sms": comm_sms,
             "nccl_all_to_all_baseline": ({"ms_per_step": ms_nccl, "value": tokens / (ms_nccl * 1e-3)} if nccl else None)}
 
 
@@ -835,7 +836,7 @@ def main():
                     "gpu_launches": r["launches_per_step"] * args.steps, "gpu_launches_per_step": r["launches_per_step"],
                     "roofline": r["roofline"], "cpu_baseline": None, "ep_parity": r["ep_parity"],
                     "ep_transport_dtype": r["transport_dtype"], "nccl_all_to_all_baseline": r["nccl_all_to_all_baseline"],
-                    "ep_timeline": r["ep_timeline"], "ep_lanes": r["ep_lanes"]}
+                    "ep_timeline": r["ep_timeline"], "ep_lanes": r["ep_lanes"], "ep_comm_sms": r["ep_comm_sms"]}
             emit(line)
         import torch.distributed as dist
         dist.barrier()

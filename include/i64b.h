@@ -278,6 +278,12 @@ int i64b_moe_set_debug(i64b_layer* layer, int flags);
  * 26.2 / 25.3 us with — the layer is bound by its dependency chain, not by where the weights come from). */
 int i64b_moe_set_next(i64b_layer* layer, const i64b_layer* next);
 
+/* GEMM launches of this layer use at most max_ctas CTAs (0 = one per SM, the default).  The expert-parallel host leaves
+ * a few SMs to the NVLink exchange kernels that run next to the shared expert's GEMMs on another stream: a 210 KB GEMM
+ * CTA per SM leaves no shared memory for them otherwise, and they would queue behind the whole GEMM.  Results do not
+ * depend on it (the tile -> CTA assignment never enters the arithmetic). */
+int i64b_moe_set_cta_limit(i64b_layer* layer, int max_ctas);
+
 /* Bring-up only (env I64B_DEBUG_TIMELINE=1): after replaying a CUDA graph of fused decode layers, print the per-CTA
  * globaltimer stamps of the last two layers to stderr.  Synchronises the device.  Returns 0 when no timeline exists. */
 int i64b_debug_timeline_dump(void);
@@ -315,7 +321,9 @@ typedef struct i64b_ep_ctx {
                                       expert outputs in the model dtype) or I64B_F32 (bit-identical to the single-GPU block) */
     int32_t x_mode;                /* I64B_MODE_BF16: rows travel as bf16; I64B_MODE_W8A8: quantised once on the home rank,
                                       int8 rows + one fp32 scale per row travel (half the dispatch bytes) */
-    int32_t reserved;
+    int32_t comm_ctas;             /* > 0: the dispatch / combine kernels use this many CTAs (one per SM, large shared memory),
+                                      leaving the other SMs to GEMMs that run next to them on other streams (the layers
+                                      doing so carry i64b_moe_set_cta_limit(layer, SMs - comm_ctas)); 0: every SM */
     int64_t cap_src;               /* rows of the region each source rank owns in every receive buffer */
     void* peer_xs[I64B_EP_MAX_RANKS];          /* [size * cap_src, H] bf16 | int8 receive buffer of rank d, mapped here */
     float* peer_xs_scale[I64B_EP_MAX_RANKS];   /* [size * cap_src] fp32 row scales (W8A8 transport), else unused */

@@ -57,6 +57,7 @@ struct i64b_layer {
     const uint8_t* table = nullptr;
     bool loaded = false;
     int debug = 0;               // I64B_DEBUG_* bits (i64b_moe_set_debug)
+    int cta_limit = 0;           // CTAs the GEMM launches of this layer may use (0 = every SM; i64b_moe_set_cta_limit)
     const i64b_layer* next = nullptr;   // layer whose weights the fused decode kernel prefetches into L2
     CUtensorMap tm_w13[3], tm_w2r[3], tm_w2s[3];   // per n_mma choice (box rows differ)
     // activation tensor maps, valid for (ws_base, n)
@@ -342,6 +343,13 @@ int i64b_moe_set_debug(i64b_layer* L, int flags) {
     return I64B_OK;
 }
 
+int i64b_moe_set_cta_limit(i64b_layer* L, int max_ctas) {
+    I64B_CHECK(L, I64B_ERR_ARG, "null layer");
+    I64B_CHECK(max_ctas >= 0, I64B_ERR_ARG, "negative CTA limit");
+    L->cta_limit = max_ctas;
+    return I64B_OK;
+}
+
 int i64b_moe_set_next(i64b_layer* L, const i64b_layer* next) {
     I64B_CHECK(L, I64B_ERR_ARG, "null layer");
     I64B_CHECK(next == nullptr || next->loaded, I64B_ERR_STATE, "next layer has no weights yet");
@@ -390,10 +398,17 @@ struct FwdOpts {
     const float* preq_scale = nullptr;      // x is int8 [N,H] quantised by the caller (x_preq), these are its row scales
 };
 
+struct CtaLimitScope {          // the layer's GEMM CTA limit applies to the launches of one forward call
+    int prev;
+    explicit CtaLimitScope(int limit) : prev(i64b_set_gemm_cta_limit(limit)) {}
+    ~CtaLimitScope() { i64b_set_gemm_cta_limit(prev); }
+};
+
 static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_ids, const FwdOpts& o,
                             void* out, int out_dtype, int64_t n, void* workspace, size_t workspace_bytes,
                             i64b_stream_t stream) {
     I64B_CHECK(L, I64B_ERR_ARG, "null layer");
+    CtaLimitScope cta_scope(L->cta_limit);
     const int32_t* given_routes = o.given_routes;
     I64B_CHECK(L->loaded, I64B_ERR_STATE, "weights not loaded (call i64b_moe_load_bf16 / i64b_moe_load_w8a8)");
     I64B_CHECK(out_dtype == I64B_BF16 || out_dtype == I64B_F32, I64B_ERR_ARG, "unsupported output dtype %d", out_dtype);
@@ -739,6 +754,7 @@ int i64b_moe_forward_dispatched(i64b_layer* L, const i64b_ep_ctx* c, void* ep_wo
                                 size_t workspace_bytes, i64b_stream_t stream) {
     I64B_CHECK(L && c && ep_workspace && workspace, I64B_ERR_ARG, "null pointer");
     I64B_CHECK(L->loaded, I64B_ERR_STATE, "expert-parallel path: weights not loaded");
+    CtaLimitScope cta_scope(L->cta_limit);
     const i64b_moe_config& cfg = L->cfg;
     I64B_CHECK(cfg.mode == c->x_mode, I64B_ERR_ARG, "layer mode %d does not match the transport mode %d", cfg.mode, c->x_mode);
     I64B_CHECK(cfg.num_experts * c->size == c->num_experts && cfg.hidden_size == c->hidden, I64B_ERR_ARG,

@@ -296,184 +296,195 @@ __device__ __forceinline__ void mbar_wait_trap(uint64_t* bar, uint32_t parity) {
         if (clock64() - t0 > 20000000000ll) __trap();
 }
 
-constexpr int kTmaThreads = 128;
-constexpr int kTmaChunk = 128;          // tokens whose (owner, row) tags a block stages in shared memory at a time
-constexpr int kDispDepth = 8;           // rows in flight per block (dispatch)
+constexpr int kTmaWarps = 8;            // independent streaming warps per block, each with its own ring and barriers
+constexpr int kTmaMaxDepth = 8;
+constexpr int kTmaSmemBudget = 200 * 1024;
 
-// Dispatch, bf16 transport: block b owns a contiguous token range.  All threads decode the plan of a chunk of tokens into
-// shared memory (and into `loc` for the combine); then ONE thread streams the rows: bulk load row -> shared memory, K bulk
-// stores shared memory -> the owners' receive buffers over NVLink, kDispDepth rows in flight.
-__global__ void __launch_bounds__(kTmaThreads)
+// Dispatch, bf16 transport.  Every WARP owns a contiguous token range and a ring of `depth` rows in shared memory: lane 0
+// streams the rows (bulk load row -> ring slot, then K bulk stores slot -> the owners' receive buffers over NVLink, the loads
+// running depth-1 rows ahead); every 32 tokens all lanes decode the plan of the next 32 tokens into shared memory (and into
+// `loc` for the combine).  No block-level synchronisation; a block is just kTmaWarps such warps sharing an SM.
+__global__ void __launch_bounds__(kTmaWarps * 32)
 ep_dispatch_tma_kernel(const i64b_ep_ctx c, const void* __restrict__ x, const I64bPlanWs ws, int64_t* __restrict__ loc,
-                       int tokens_per_block) {
+                       int depth) {
     extern __shared__ __align__(128) uint8_t smem_dyn[];
-    __shared__ uint64_t full_bar[kDispDepth];
-    __shared__ int64_t s_loc[kTmaChunk * I64B_MAX_TOPK];
+    __shared__ uint64_t full_bar[kTmaWarps][kTmaMaxDepth];
+    __shared__ int64_t s_loc[kTmaWarps][32 * I64B_MAX_TOPK];
     pdl_launch_dependents();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int K = c.top_k, E = c.num_experts, bins = K * E, local_e = E / c.size;
     const uint32_t row_bytes = (uint32_t)c.hidden * 2;
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < kDispDepth; ++i) mbar_init(&full_bar[i], 1);
+    uint8_t* ring = smem_dyn + (size_t)warp * depth * row_bytes;
+    uint64_t* full = full_bar[warp];
+    if (lane == 0) {
+        for (int i = 0; i < depth; ++i) mbar_init(&full[i], 1);
         fence_barrier_init();
     }
+    __syncwarp();
     pdl_wait_prior();
     if (blockIdx.x == 0)
         for (int e = threadIdx.x; e < E; e += blockDim.x) {
             const int rows = c.n_local > 0 ? ws.group_start[e + 1] - ws.group_start[e] : 0;
             c.peer_flags[e / local_e][kCountsBase + c.rank * kCountsStride + e % local_e] = rows;
         }
-    __syncthreads();
     const int64_t n = c.n_local;
-    const int64_t t_begin = (int64_t)blockIdx.x * tokens_per_block;
-    const int64_t t_end = min(n, t_begin + tokens_per_block);
-    uint32_t seq = 0;                                    // rows this block has streamed (ring position, barrier parity)
-    for (int64_t t0 = t_begin; t0 < t_end; t0 += kTmaChunk) {
-        const int cnt = (int)min((int64_t)kTmaChunk, t_end - t0);
-        for (int i = threadIdx.x; i < cnt * K; i += blockDim.x) {
-            const int k = i / cnt, tt = i - k * cnt;
-            const int64_t t = t0 + tt;
-            const uint32_t pk = ws.packed[(int64_t)k * n + t];
-            const int e = pk & 0xFF;
-            const int bin = k * E + e;
-            const int in_tile = (int)(pk >> 8) + ws.tile_counts[(t / I64B_PLAN_TILE) * bins + bin];
-            const int dest = ws.group_start[e] + ws.route_base[bin] + in_tile;
-            const int owner = e / local_e;
-            const int row = (int)((int64_t)c.rank * c.cap_src) + dest - ws.group_start[owner * local_e];
-            const int64_t l = ((int64_t)owner << 32) | (int64_t)row;
-            loc[(int64_t)k * n + t] = l;
-            s_loc[tt * K + k] = l;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            const uint8_t* xb = reinterpret_cast<const uint8_t*>(x);
-            auto load_row = [&](int j, uint32_t sq) {
-                const int slot = (int)(sq % kDispDepth);
-                mbar_arrive_expect_tx(&full_bar[slot], row_bytes);
-                bulk_load(smem_dyn + (size_t)slot * row_bytes, xb + (t0 + j) * (int64_t)row_bytes, row_bytes, &full_bar[slot]);
-            };
-            const int pre = min(cnt, kDispDepth - 1);
-            for (int j = 0; j < pre; ++j) load_row(j, seq + j);
-            for (int j = 0; j < cnt; ++j) {
-                const uint32_t sq = seq + j;
-                const int slot = (int)(sq % kDispDepth);
-                mbar_wait_trap(&full_bar[slot], (sq / kDispDepth) & 1u);
-                const uint8_t* src = smem_dyn + (size_t)slot * row_bytes;
-                for (int k = 0; k < K; ++k) {
-                    const int64_t l = s_loc[j * K + k];
-                    bulk_store(reinterpret_cast<uint8_t*>(c.peer_xs[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)]) +
-                                   (l & 0xffffffffll) * (int64_t)row_bytes, src, row_bytes);
-                }
-                bulk_commit();
-                if (j + kDispDepth - 1 < cnt) {
-                    bulk_wait_read<1>();          // the stores of row j-1 have read their slot: it takes row j + depth - 1
-                    load_row(j + kDispDepth - 1, sq + kDispDepth - 1);
-                }
+    const int64_t warps_total = (int64_t)gridDim.x * kTmaWarps;
+    const int64_t per = (n + warps_total - 1) / warps_total;
+    const int64_t t_begin = ((int64_t)blockIdx.x * kTmaWarps + warp) * per;
+    const int total = (int)max((int64_t)0, min(n, t_begin + per) - t_begin);
+    const uint8_t* xb = reinterpret_cast<const uint8_t*>(x) + t_begin * (int64_t)row_bytes;
+    auto load_row = [&](int j) {                      // lane 0
+        const int slot = j % depth;
+        mbar_arrive_expect_tx(&full[slot], row_bytes);
+        bulk_load(ring + (size_t)slot * row_bytes, xb + (int64_t)j * row_bytes, row_bytes, &full[slot]);
+    };
+    if (lane == 0)
+        for (int j = 0; j < min(total, depth - 1); ++j) load_row(j);
+    for (int j = 0; j < total; ++j) {
+        if ((j & 31) == 0) {                          // the plan of the next 32 tokens -> (owner, row) tags
+            __syncwarp();
+            const int cnt = min(32, total - j);
+            for (int i = lane; i < cnt * K; i += 32) {
+                const int k = i / cnt, tt = i - k * cnt;
+                const int64_t t = t_begin + j + tt;
+                const uint32_t pk = ws.packed[(int64_t)k * n + t];
+                const int e = pk & 0xFF;
+                const int bin = k * E + e;
+                const int in_tile = (int)(pk >> 8) + ws.tile_counts[(t / I64B_PLAN_TILE) * bins + bin];
+                const int dest = ws.group_start[e] + ws.route_base[bin] + in_tile;
+                const int owner = e / local_e;
+                const int row = (int)((int64_t)c.rank * c.cap_src) + dest - ws.group_start[owner * local_e];
+                const int64_t l = ((int64_t)owner << 32) | (int64_t)row;
+                loc[(int64_t)k * n + t] = l;
+                s_loc[warp][tt * K + k] = l;
             }
-            bulk_wait_read<0>();
-            seq += (uint32_t)cnt;
+            __syncwarp();
         }
-        __syncthreads();
+        if (lane == 0) {
+            const int slot = j % depth;
+            mbar_wait_trap(&full[slot], (uint32_t)(j / depth) & 1u);
+            const uint8_t* src = ring + (size_t)slot * row_bytes;
+            for (int k = 0; k < K; ++k) {
+                const int64_t l = s_loc[warp][(j & 31) * K + k];
+                bulk_store(reinterpret_cast<uint8_t*>(c.peer_xs[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)]) +
+                               (l & 0xffffffffll) * (int64_t)row_bytes, src, row_bytes);
+            }
+            bulk_commit();
+            if (j + depth - 1 < total) {
+                bulk_wait_read<1>();                  // the stores of row j-1 have read their slot: it takes row j + depth - 1
+                load_row(j + depth - 1);
+            }
+        }
     }
-    if (threadIdx.x == 0) bulk_wait_all();
+    if (lane == 0) bulk_wait_all();
 }
 
-// Combine on the home rank: per token, ONE thread pulls the K per-assignment rows from their owners (one bulk copy per row
-// over NVLink) and the local shared-expert row into a shared-memory stage; all threads then apply the weights in the
-// reference's operation order and write the output row.  kDepth tokens in flight per block.
-__global__ void __launch_bounds__(kTmaThreads)
-ep_combine_tma_kernel(const i64b_ep_ctx c, const EpCombineArgs a, int tokens_per_block, int depth, int stage_bytes) {
+// Combine on the home rank.  Every WARP owns a contiguous token range and a ring of `depth` stages; lane 0 pulls, per token,
+// the K per-assignment rows from their owners (one bulk copy per row over NVLink) and the local shared-expert row into a
+// stage; the 32 lanes then apply the weights in the reference's operation order and write the output row.
+__global__ void __launch_bounds__(kTmaWarps * 32)
+ep_combine_tma_kernel(const i64b_ep_ctx c, const EpCombineArgs a, int depth, int stage_bytes) {
     extern __shared__ __align__(128) uint8_t smem_dyn[];
-    __shared__ uint64_t full_bar[8];
-    __shared__ int64_t s_loc[kTmaChunk * I64B_MAX_TOPK];
+    __shared__ uint64_t full_bar[kTmaWarps][kTmaMaxDepth];
+    __shared__ int64_t s_loc[kTmaWarps][2][32 * I64B_MAX_TOPK];
     pdl_launch_dependents();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int K = c.top_k, H = c.hidden;
     const uint32_t ybytes = (uint32_t)H * (c.y_dtype == I64B_F32 ? 4u : 2u);
     const uint32_t sbytes = a.y_shared ? (uint32_t)H * 4u : 0u;
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < depth; ++i) mbar_init(&full_bar[i], 1);
+    uint8_t* ring = smem_dyn + (size_t)warp * depth * stage_bytes;
+    uint64_t* full = full_bar[warp];
+    if (lane == 0) {
+        for (int i = 0; i < depth; ++i) mbar_init(&full[i], 1);
         fence_barrier_init();
     }
+    __syncwarp();
     pdl_wait_prior();
-    __syncthreads();
     const int64_t n = c.n_local;
-    const int64_t t_begin = (int64_t)blockIdx.x * tokens_per_block;
-    const int64_t t_end = min(n, t_begin + tokens_per_block);
+    const int64_t warps_total = (int64_t)gridDim.x * kTmaWarps;
+    const int64_t per = (n + warps_total - 1) / warps_total;
+    const int64_t t_begin = ((int64_t)blockIdx.x * kTmaWarps + warp) * per;
+    const int total = (int)max((int64_t)0, min(n, t_begin + per) - t_begin);
     const int h8 = H / 8;
-    uint32_t seq = 0;
-    for (int64_t t0 = t_begin; t0 < t_end; t0 += kTmaChunk) {
-        const int cnt = (int)min((int64_t)kTmaChunk, t_end - t0);
-        for (int i = threadIdx.x; i < cnt * K; i += blockDim.x) {
+    auto load_tags = [&](int chunk) {                  // all lanes: (owner, row) tags of tokens [32*chunk, 32*chunk + 32)
+        const int j0 = chunk * 32;
+        const int cnt = min(32, total - j0);
+        for (int i = lane; i < cnt * K; i += 32) {
             const int k = i / cnt, tt = i - k * cnt;
-            s_loc[tt * K + k] = __ldg(a.loc + (int64_t)k * n + t0 + tt);
+            s_loc[warp][chunk & 1][tt * K + k] = __ldg(a.loc + (int64_t)k * n + t_begin + j0 + tt);
         }
-        __syncthreads();
-        auto load_token = [&](int j, uint32_t sq) {        // thread 0 only
-            const int slot = (int)(sq % (uint32_t)depth);
-            uint8_t* st = smem_dyn + (size_t)slot * stage_bytes;
-            mbar_arrive_expect_tx(&full_bar[slot], K * ybytes + sbytes);
-            for (int k = 0; k < K; ++k) {
-                const int64_t l = s_loc[j * K + k];
-                bulk_load(st + (size_t)k * ybytes,
-                          reinterpret_cast<const uint8_t*>(c.peer_y[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)]) +
-                              (l & 0xffffffffll) * (int64_t)ybytes, ybytes, &full_bar[slot]);
-            }
-            if (sbytes) bulk_load(st + (size_t)K * ybytes, a.y_shared + (t0 + j) * (int64_t)H, sbytes, &full_bar[slot]);
-        };
-        if (threadIdx.x == 0)
-            for (int j = 0; j < min(cnt, depth); ++j) load_token(j, seq + j);
-        for (int j = 0; j < cnt; ++j) {
-            const uint32_t sq = seq + j;
-            const int slot = (int)(sq % (uint32_t)depth);
-            mbar_wait_trap(&full_bar[slot], (sq / (uint32_t)depth) & 1u);
-            const uint8_t* st = smem_dyn + (size_t)slot * stage_bytes;
-            const int64_t t = t0 + j;
-            for (int c8 = threadIdx.x; c8 < h8; c8 += blockDim.x) {
-                Row8 o;
+    };
+    auto load_token = [&](int j) {                     // lane 0
+        const int slot = j % depth;
+        uint8_t* st = ring + (size_t)slot * stage_bytes;
+        mbar_arrive_expect_tx(&full[slot], K * ybytes + sbytes);
+        const int64_t* tags = s_loc[warp][(j >> 5) & 1] + (j & 31) * K;
+        for (int k = 0; k < K; ++k) {
+            const int64_t l = tags[k];
+            bulk_load(st + (size_t)k * ybytes,
+                      reinterpret_cast<const uint8_t*>(c.peer_y[(int)(l >> 32) & (I64B_EP_MAX_RANKS - 1)]) +
+                          (l & 0xffffffffll) * (int64_t)ybytes, ybytes, &full[slot]);
+        }
+        if (sbytes) bulk_load(st + (size_t)K * ybytes, a.y_shared + (t_begin + j) * (int64_t)H, sbytes, &full[slot]);
+    };
+    if (total > 0) load_tags(0);
+    if (total > 32) load_tags(1);
+    __syncwarp();
+    if (lane == 0)
+        for (int j = 0; j < min(total, depth); ++j) load_token(j);
+    for (int j = 0; j < total; ++j) {
+        if ((j & 31) == 0 && j > 0 && j + 32 < total) {          // tokens ahead may belong to the next 32: fetch their tags now
+            load_tags((j >> 5) + 1);
+            __syncwarp();
+        }
+        const int slot = j % depth;
+        mbar_wait_trap(&full[slot], (uint32_t)(j / depth) & 1u);
+        const uint8_t* st = ring + (size_t)slot * stage_bytes;
+        const int64_t t = t_begin + j;
+        for (int c8 = lane; c8 < h8; c8 += 32) {
+            Row8 o;
 #pragma unroll
-                for (int k = 0; k < I64B_MAX_TOPK; ++k) {
-                    if (k < K) {
-                        const uint8_t* yr = st + (size_t)k * ybytes;
-                        int4 ya, yb = make_int4(0, 0, 0, 0);
-                        if (c.y_dtype == I64B_F32) {
-                            ya = *reinterpret_cast<const int4*>(yr + (size_t)c8 * 32);
-                            yb = *reinterpret_cast<const int4*>(yr + (size_t)c8 * 32 + 16);
-                        } else {
-                            ya = *reinterpret_cast<const int4*>(yr + (size_t)c8 * 16);
-                        }
-                        combine_accumulate(o, ep_unpack_row(c.y_dtype, ya, yb), a.w[k], k == 0);
+            for (int k = 0; k < I64B_MAX_TOPK; ++k) {
+                if (k < K) {
+                    const uint8_t* yr = st + (size_t)k * ybytes;
+                    int4 ya, yb = make_int4(0, 0, 0, 0);
+                    if (c.y_dtype == I64B_F32) {
+                        ya = *reinterpret_cast<const int4*>(yr + (size_t)c8 * 32);
+                        yb = *reinterpret_cast<const int4*>(yr + (size_t)c8 * 32 + 16);
+                    } else {
+                        ya = *reinterpret_cast<const int4*>(yr + (size_t)c8 * 16);
                     }
-                }
-                const float rs = a.routed_scale;
-#pragma unroll
-                for (int q = 0; q < 8; ++q) o.v[q] = __fmul_rn(rs, o.v[q]);
-                if (sbytes) {
-                    const float4* sp = reinterpret_cast<const float4*>(st + (size_t)K * ybytes) + 2 * c8;
-                    const float4 s0 = sp[0], s1 = sp[1];
-                    const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-                    const float ss = a.shared_scale;
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) o.v[q] = __fadd_rn(o.v[q], __fmul_rn(ss, sv[q]));
-                }
-                const int64_t i = t * h8 + c8;
-                if (a.out_dtype == I64B_F32) {
-                    float4* op = reinterpret_cast<float4*>(a.out) + 2 * i;
-                    op[0] = make_float4(o.v[0], o.v[1], o.v[2], o.v[3]);
-                    op[1] = make_float4(o.v[4], o.v[5], o.v[6], o.v[7]);
-                } else {
-                    uint32_t pk[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        __nv_bfloat162 v2 = __floats2bfloat162_rn(o.v[2 * q], o.v[2 * q + 1]);
-                        pk[q] = *reinterpret_cast<uint32_t*>(&v2);
-                    }
-                    reinterpret_cast<int4*>(a.out)[i] = make_int4((int)pk[0], (int)pk[1], (int)pk[2], (int)pk[3]);
+                    combine_accumulate(o, ep_unpack_row(c.y_dtype, ya, yb), a.w[k], k == 0);
                 }
             }
-            __syncthreads();                               // every thread has read the stage: it takes token j + depth
-            if (threadIdx.x == 0 && j + depth < cnt) load_token(j + depth, sq + (uint32_t)depth);
+            const float rs = a.routed_scale;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) o.v[q] = __fmul_rn(rs, o.v[q]);
+            if (sbytes) {
+                const float4* sp = reinterpret_cast<const float4*>(st + (size_t)K * ybytes) + 2 * c8;
+                const float4 s0 = sp[0], s1 = sp[1];
+                const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+                const float ss = a.shared_scale;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) o.v[q] = __fadd_rn(o.v[q], __fmul_rn(ss, sv[q]));
+            }
+            const int64_t i = t * h8 + c8;
+            if (a.out_dtype == I64B_F32) {
+                float4* op = reinterpret_cast<float4*>(a.out) + 2 * i;
+                op[0] = make_float4(o.v[0], o.v[1], o.v[2], o.v[3]);
+                op[1] = make_float4(o.v[4], o.v[5], o.v[6], o.v[7]);
+            } else {
+                uint32_t pk[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    __nv_bfloat162 v2 = __floats2bfloat162_rn(o.v[2 * q], o.v[2 * q + 1]);
+                    pk[q] = *reinterpret_cast<uint32_t*>(&v2);
+                }
+                reinterpret_cast<int4*>(a.out)[i] = make_int4((int)pk[0], (int)pk[1], (int)pk[2], (int)pk[3]);
+            }
         }
-        seq += (uint32_t)cnt;
-        __syncthreads();
+        __syncwarp();                                  // every lane has read the stage: it takes token j + depth
+        if (lane == 0 && j + depth < total) load_token(j + depth);
     }
 }
 
@@ -506,7 +517,7 @@ __global__ void ep_barrier_kernel(const i64b_ep_ctx c) {
 
 static size_t ep_align(size_t v) { return (v + 255) & ~size_t(255); }
 // I64B_EP_TMA=0 selects the load/store-unit versions of the dispatch and combine kernels (kept for comparison)
-constexpr int kTmaSmemMax = 96 * 1024;       // dynamic shared memory the bulk-copy kernels may ask for (ring of rows / stages)
+constexpr int kTmaSmemMax = kTmaSmemBudget;   // dynamic shared memory the bulk-copy kernels may ask for (rings of rows / stages)
 static int ep_configure_tma() {           // function attributes are per device
     static bool configured[I64B_MAX_DEVICES] = {};
     const int dev = i64b_current_device();
@@ -633,14 +644,14 @@ int i64b_ep_dispatch(const i64b_ep_ctx* c, const void* x, const int64_t* token_i
     const int grid = (int)ceil_div64(c->n_local > 0 ? c->n_local : 1, kEpWarps);
     if (c->x_mode == I64B_MODE_W8A8) {
         I64B_CUDA(i64b_launch(ep_dispatch_kernel<true>, dim3(grid), dim3(kEpWarps * 32), 0, s, *c, x, w.plan, w.loc));
-    } else if (ep_use_tma() && c->hidden * 2 * kDispDepth <= kTmaSmemMax && c->hidden % 8 == 0) {
+    } else if (ep_use_tma() && c->hidden % 8 == 0 && kTmaSmemBudget / (kTmaWarps * c->hidden * 2) >= 2) {
         if (int rc = ep_configure_tma()) return rc;
-        // bulk-copy dispatch: contiguous token ranges, about four blocks per SM
-        const int64_t nn = c->n_local > 0 ? c->n_local : 1;
-        const int64_t blocks = nn < (int64_t)i64b_num_sms() * 4 ? nn : (int64_t)i64b_num_sms() * 4;
-        const int tpb = (int)ceil_div64(nn, blocks);
-        I64B_CUDA(i64b_launch(ep_dispatch_tma_kernel, dim3((int)ceil_div64(nn, tpb)), dim3(kTmaThreads),
-                              (size_t)c->hidden * 2 * kDispDepth, s, *c, x, w.plan, w.loc, tpb));
+        // bulk-copy dispatch: one block of streaming warps per SM, or per SM of the exchange partition (ctx->comm_ctas)
+        int depth = kTmaSmemBudget / (kTmaWarps * c->hidden * 2);
+        if (depth > kTmaMaxDepth) depth = kTmaMaxDepth;
+        const int blocks = c->comm_ctas > 0 ? c->comm_ctas : i64b_num_sms();
+        I64B_CUDA(i64b_launch(ep_dispatch_tma_kernel, dim3(blocks), dim3(kTmaWarps * 32),
+                              (size_t)kTmaWarps * depth * c->hidden * 2, s, *c, x, w.plan, w.loc, depth));
     } else {
         I64B_CUDA(i64b_launch(ep_dispatch_kernel<false>, dim3(grid), dim3(kEpWarps * 32), 0, s, *c, x, w.plan, w.loc));
     }
@@ -665,15 +676,13 @@ int i64b_ep_combine(const i64b_ep_ctx* c, void* ep_workspace, const float* y_sha
     a.out_dtype = out_dtype;
     {
         const int stage = c->top_k * c->hidden * (c->y_dtype == I64B_F32 ? 4 : 2) + (y_shared ? c->hidden * 4 : 0);
-        int depth = kTmaSmemMax / stage;
-        if (depth > 6) depth = 6;
+        int depth = kTmaSmemBudget / (kTmaWarps * stage);
+        if (depth > 4) depth = 4;
         if (ep_use_tma() && depth >= 2) {
             if (int rc = ep_configure_tma()) return rc;
-            const int64_t nn = c->n_local;
-            const int64_t blocks = nn < (int64_t)i64b_num_sms() * 4 ? nn : (int64_t)i64b_num_sms() * 4;
-            const int tpb = (int)ceil_div64(nn, blocks);
-            I64B_CUDA(i64b_launch(ep_combine_tma_kernel, dim3((int)ceil_div64(nn, tpb)), dim3(kTmaThreads),
-                                  (size_t)stage * depth, (cudaStream_t)stream, *c, a, tpb, depth, stage));
+            const int blocks = c->comm_ctas > 0 ? c->comm_ctas : i64b_num_sms();
+            I64B_CUDA(i64b_launch(ep_combine_tma_kernel, dim3(blocks), dim3(kTmaWarps * 32),
+                                  (size_t)kTmaWarps * depth * stage, (cudaStream_t)stream, *c, a, depth, stage));
             i64b_count_launch(1);
             return I64B_OK;
         }

@@ -841,6 +841,15 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
     return I64B_OK;
 }
 
+// Upper bound on the CTAs of the GEMM launches made by the calling thread (0 = every SM).  The expert-parallel path leaves a
+// few SMs to the NVLink exchange kernels that run next to the GEMMs on other streams (i64b_moe_set_cta_limit).
+static thread_local int g_gemm_cta_limit = 0;
+int i64b_set_gemm_cta_limit(int limit) {
+    const int prev = g_gemm_cta_limit;
+    g_gemm_cta_limit = limit > 0 ? limit : 0;
+    return prev;
+}
+
 int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream) {
@@ -849,7 +858,8 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
     I64B_CHECK(p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
                p.num_groups);
     I64B_CHECK(p.k[0] > 0 && p.k[1] > 0, I64B_ERR_ARG, "K must be positive");
-    const int sms = i64b_num_sms();
+    int sms = i64b_num_sms();
+    if (g_gemm_cta_limit > 0 && g_gemm_cta_limit < sms) sms = g_gemm_cta_limit >= 2 ? g_gemm_cta_limit : 2;
     if (ctas == 2) {        // max_tiles counts pair units here
         const int pairs = sms / 2;
         const int grid2 = 2 * (int)(max_tiles < pairs ? max_tiles : pairs);

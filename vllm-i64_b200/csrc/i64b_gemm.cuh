@@ -56,4 +56,5 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
                      int64_t max_tiles, cudaStream_t stream);
 
 int i64b_num_sms();
+int i64b_set_gemm_cta_limit(int limit);      // thread-local; returns the previous value
 void i64b_count_launch(int n = 1);

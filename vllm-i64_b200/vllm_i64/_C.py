@@ -42,7 +42,7 @@ class EPCtx(C.Structure):
     """``i64b_ep_ctx`` (include/i64b.h): peer-mapped buffers of every rank of the expert-parallel group."""
     _fields_ = [("rank", C.c_int32), ("size", C.c_int32), ("n_local", C.c_int32), ("hidden", C.c_int32),
                 ("top_k", C.c_int32), ("num_experts", C.c_int32), ("vocab", C.c_int32), ("y_dtype", C.c_int32),
-                ("x_mode", C.c_int32), ("reserved", C.c_int32),
+                ("x_mode", C.c_int32), ("comm_ctas", C.c_int32),
                 ("cap_src", C.c_int64), ("peer_xs", C.c_void_p * EP_MAX_RANKS),
                 ("peer_xs_scale", C.c_void_p * EP_MAX_RANKS), ("peer_y", C.c_void_p * EP_MAX_RANKS),
                 ("peer_flags", C.c_void_p * EP_MAX_RANKS), ("state", C.c_void_p)]
@@ -89,6 +89,7 @@ _SIGNATURES = {
     "i64b_moe_tap": (_P, [_P, _I]),
     "i64b_moe_set_debug": (_I, [_P, _I]),
     "i64b_moe_set_next": (_I, [_P, _P]),
+    "i64b_moe_set_cta_limit": (_I, [_P, _I]),
     "i64b_debug_timeline_dump": (_I, []),
     "i64b_fused_decode_supported": (_I, [_I, _I, _I, _I, _I, _I]),
     "i64b_ep_alloc": (_I, [_Z, C.POINTER(_P)]),

@@ -199,6 +199,11 @@ class I64Block:
         """``_C.DEBUG_KEEP_TAPS``: keep the shared expert's own rows in TAP_Y (the fused combine does not need them)."""
         _C.check(_C.lib().i64b_moe_set_debug(self._h, int(flags)))
 
+    def set_cta_limit(self, max_ctas: int) -> None:
+        """GEMM launches of this block use at most ``max_ctas`` CTAs (0 = one per SM): include/i64b.h,
+        i64b_moe_set_cta_limit."""
+        _C.check(_C.lib().i64b_moe_set_cta_limit(self._h, int(max_ctas)))
+
     def tap(self, what: int, shape, dtype: torch.dtype) -> torch.Tensor:
         with torch.cuda.device(self.device):
             return _C.tap_tensor(self._h, what, shape, dtype, self.device)

@@ -236,6 +236,17 @@ class EPTokenRoutedBlock:
             lanes = int(os.environ.get("I64B_EP_LANES", "0")) or (2 if (G > 1 and n >= 4096) else 1)
         lanes = max(1, min(int(lanes), 8))
         n_lane = -(-n // lanes)
+        # SM partition: the exchange kernels get `comm_sms` SMs of their own while GEMMs run next to them (the shared
+        # expert next to the dispatch; with several lanes, every GEMM next to the other lanes' exchange).  A GEMM CTA
+        # takes ~210 KB of shared memory: without the partition the exchange kernels would queue behind whole GEMMs.
+        sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        comm = int(os.environ.get("I64B_EP_COMM_SMS", "16")) if G > 1 else 0
+        comm = max(0, min(comm, sms // 2))
+        self._comm_dispatch = comm if (self.shared is not None or lanes > 1) else 0
+        self._comm_combine = comm if lanes > 1 else 0
+        if self.shared is not None:
+            self.shared.set_cta_limit(sms - comm if self._comm_dispatch else 0)
+        self.local.set_cta_limit(sms - comm if (comm and lanes > 1) else 0)
         cap_src = n_lane * K                                   # a source's whole micro-batch may land on one owner
         rows = G * cap_src
         q = self.mode == _C.MODE_W8A8
@@ -369,6 +380,7 @@ class EPTokenRoutedBlock:
                     ev.record(cur)
                     tl.append((name, ev))
             mark("start")
+            lane.ctx.comm_ctas = self._comm_dispatch
             _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), token_ids.data_ptr(), self._table.data_ptr(),
                                           lane.ws_plan.data_ptr(), lane.ws_plan.numel(), st))
             mark("plan+dispatch")
@@ -382,6 +394,7 @@ class EPTokenRoutedBlock:
             if shared is not None:
                 cur.wait_stream(lane.stream)
             mark("join shared-expert stream")
+            lane.ctx.comm_ctas = self._comm_combine
             _C.check(lib.i64b_ep_combine(ctx, lane.ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
                                          out.data_ptr(), _C.dtype_code(out), st))
             mark("combine (pull)")
@@ -404,6 +417,7 @@ class EPTokenRoutedBlock:
             lo, hi = min(n, li * per), min(n, (li + 1) * per)
             m = hi - lo
             lane.ctx.n_local = m
+            lane.ctx.comm_ctas = self._comm_dispatch       # == _comm_combine with several lanes
             ctx = C.byref(lane.ctx)
             s = lane.stream
             s.wait_stream(cur)
