@@ -1,4 +1,12 @@
-"""Phase timing of the expert-parallel forward (bring-up tool): torchrun --nproc-per-node G tools/ep_probe.py"""
+"""Isolated timing of the expert-parallel exchange kernels (bring-up tool):
+
+    python -m torch.distributed.run --nproc-per-node G --master-addr 127.0.0.1 tools/ep_probe.py
+
+Config-5 geometry, 64K tokens in total.  After one full forward (so that every buffer holds real data), each kernel is timed
+ALONE, 10 back-to-back launches between two events after a group barrier (nothing else runs on the GPU), for every exchange
+partition size in I64B_EP_PROBE_CTAS (default "0,16,32"): plan + dispatch, combine.  Prints GB/s over NVLink (remote rows only)
+and over HBM (all bytes the kernel touches locally).  I64B_EP_TMA=0 selects the load/store kernels.
+"""
 import ctypes as C
 import os
 import sys
@@ -24,55 +32,74 @@ u = lambda shape, f: (torch.rand(shape, device=dev, generator=g) * 2 - 1) / f **
 b = EPTokenRoutedBlock(H, E, I, S, V, K, [0.5, 0.5], 2.0, 1.0, _C.MODE_BF16, dev, ep)
 b.load_bf16(u((E, H, I), H), u((E, H, I), H), u((E, I, H), I), u((S, H), H), u((S, H), H), u((H, S), S))
 b.set_table(torch.from_numpy(synthetic_hash_table(V, E, K, 0)))
+b.reserve(n, lanes=1)
 x = torch.randn(n, H, device=dev).to(torch.bfloat16)
 ids = torch.randint(0, V, (n,), device=dev)
-for _ in range(3):
+for _ in range(2):
     b.forward(x, ids)
+torch.cuda.synchronize()
 lib = _C.lib()
-ctx = C.byref(b._ctx)
+lane = b._lanes[0]
+ctx = C.byref(lane.ctx)
 st = _C.stream_ptr(dev)
-names, evs = [], []
-shared_buf = torch.empty(n, H, dtype=torch.float32, device=dev)
+shared = lane.shared_out[:n]
 out = torch.empty(n, H, dtype=torch.bfloat16, device=dev)
+wts = (C.c_float * 4)(0.5, 0.5, 0, 0)
+remote = n * K * (world - 1) / world * H * 2
+REPS = 10
 
 
-def mark(name):
-    e = torch.cuda.Event(enable_timing=True)
-    e.record()
-    names.append(name)
-    evs.append(e)
-
-
-for it in range(3):
-    names.clear(); evs.clear()
-    torch.cuda.synchronize(); dist.barrier()
-    mark("start")
-    if world > 1:
-        dist.all_gather_into_tensor(b._ids_all, ids)
-    mark("allgather")
-    _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), b._ids_all.data_ptr(), b._table.data_ptr(), I, b._ws_plan.data_ptr(), b._ws_plan.numel(), st))
-    mark("plan+dispatch")
-    _C.check(lib.i64b_ep_signal(ctx, st))
-    mark("signal")
-    shared = shared_buf
-    b.shared.forward(x, None, torch.float32, out=shared, stages=_C.STAGE_PLAN)
-    mark("sh_plan")
-    b.shared.forward(x, None, torch.float32, out=shared, stages=_C.STAGE_GEMM1)
-    mark("sh_gemm1")
-    b.shared.forward(x, None, torch.float32, out=shared, stages=_C.STAGE_GEMM2)
-    mark("sh_gemm2")
-    _C.check(lib.i64b_ep_wait(ctx, st))
-    mark("wait1")
-    _C.check(lib.i64b_moe_forward_dispatched(b.local._h, ctx, b._ws_plan.data_ptr(), b._ws_gemm.data_ptr(), b._ws_gemm.numel(), st))
-    mark("gemms+return")
-    _C.check(lib.i64b_ep_signal(ctx, st)); _C.check(lib.i64b_ep_wait(ctx, st))
-    mark("barrier2")
-    wts = (C.c_float * 4)(0.5, 0.5, 0, 0)
-    _C.check(lib.i64b_ep_combine(ctx, b._ws_plan.data_ptr(), shared.data_ptr(), wts, 2.0, 1.0, out.data_ptr(), _C.dtype_code(out), st))
-    mark("combine")
+def timed(fn):
     torch.cuda.synchronize()
-    if rank == 0 and it == 2:
-        print(f"EP{world} n_local={n}: " + "  ".join(f"{names[i]}={evs[i-1].elapsed_time(evs[i])*1e3:.0f}us" for i in range(1, len(evs)))
-              + f"  total={evs[0].elapsed_time(evs[-1])*1e3:.0f}us")
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(REPS):
+        fn()
+    e1.record()
+    e1.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) * 1e3 / REPS], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t[0])
+
+
+def dispatch():
+    _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), ids.data_ptr(), b._table.data_ptr(), lane.ws_plan.data_ptr(),
+                                  lane.ws_plan.numel(), st))
+
+
+def combine():
+    _C.check(lib.i64b_ep_combine(ctx, lane.ws_plan.data_ptr(), shared.data_ptr(), wts, 2.0, 1.0, out.data_ptr(),
+                                 _C.dtype_code(out), st))
+
+
+def gemms():
+    _C.check(lib.i64b_moe_forward_dispatched(b.local._h, ctx, lane.ws_plan.data_ptr(), lane.ws_gemm.data_ptr(),
+                                             lane.ws_gemm.numel(), st))
+
+
+def shared_gemms():
+    b.shared.forward(x, None, torch.float32, out=shared)
+
+
+for ctas in [int(v) for v in os.environ.get("I64B_EP_PROBE_CTAS", "0,16,32").split(",")]:
+    lane.ctx.comm_ctas = ctas
+    td = timed(dispatch)
+    tc = timed(combine)
+    if rank == 0:
+        hbm_d = n * H * 2 * (1 + K / world)                     # x read + local rows written
+        hbm_c = n * H * (2 * K / world + 4 + 2) + remote        # local y rows + shared fp32 + out (+ peers reading our y)
+        print(f"EP{world} n_local={n} ctas={ctas or 'all'}: plan+dispatch {td:7.1f} us  ({remote / td * 1e-3:6.1f} GB/s NVLink out, "
+              f"{hbm_d / td * 1e-3:7.1f} GB/s local)   combine {tc:7.1f} us ({remote / tc * 1e-3:6.1f} GB/s NVLink in, "
+              f"{hbm_c / tc * 1e-3:7.1f} GB/s local)", flush=True)
+b.local.set_cta_limit(0)
+b.shared.set_cta_limit(0)
+tg, ts = timed(gemms), timed(shared_gemms)
+b.local.set_cta_limit(132)
+b.shared.set_cta_limit(132)
+tg2, ts2 = timed(gemms), timed(shared_gemms)
+if rank == 0:
+    print(f"EP{world}: routed GEMMs {tg:.1f} us (132 CTAs: {tg2:.1f})   shared GEMMs {ts:.1f} us (132 CTAs: {ts2:.1f})", flush=True)
 dist.barrier()
+b.close()
 dist.destroy_process_group()
