@@ -661,7 +661,15 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
         blocks.append(b)
     torch.cuda.synchronize(device)
 
+    plan_stream = torch.cuda.Stream(device)
+
     def step_device():
+        if not args.no_ep_plan_ahead:
+            # the engine knows the step's token ids up front: every layer's dispatch plan is made on a side stream while the
+            # earlier layers run (routing depends on ids and the layer's table only; scheduler pre-route)
+            plan_stream.wait_stream(torch.cuda.current_stream(device))
+            for b in blocks:
+                b.plan_ahead(ids, plan_stream)
         for i, b in enumerate(blocks):
             b.forward(x, ids, torch.bfloat16, out=outs[i & 1])
 
@@ -750,7 +758,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
                     "h2d_bytes_per_step": n * H * 2 + n * 8, "d2h_bytes_per_step": n * H * 2, "copies_per_step": 1,
                     "via": "engine step per rank: pinned H2D of the rank's x + ids, L expert-parallel block forwards, D2H of the last output"},
             "roofline": roof, "ep_parity": ep_parity, "transport_dtype": args.ep_transport, "ep_timeline": timeline,
-            "ep_lanes": len(blocks_lanes), "ep_comm_sms": comm_sms,
+            "ep_lanes": len(blocks_lanes), "ep_comm_sms": comm_sms, "ep_plan_ahead": not args.no_ep_plan_ahead,
             "nccl_all_to_all_baseline": ({"ms_per_step": ms_nccl, "value": tokens / (ms_nccl * 1e-3)} if nccl else None)}
 
 
@@ -770,6 +778,8 @@ def main():
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
     ap.add_argument("--ep-lanes", type=int, default=0,
                     help="N > 1: micro-batch lanes per expert-parallel forward (0 = the library's default)")
+    ap.add_argument("--no-ep-plan-ahead", action="store_true",
+                    help="N > 1: plan every layer inside its own forward instead of up front on a side stream")
     ap.add_argument("--ep-nccl-baseline", action="store_true", help="also time the all_to_all_single exchange (eager)")
     ap.add_argument("--ep-timeline", action="store_true", help="also report per-stage device times of one EP layer (eager)")
     args = ap.parse_args()
@@ -836,7 +846,7 @@ def main():
                     "gpu_launches": r["launches_per_step"] * args.steps, "gpu_launches_per_step": r["launches_per_step"],
                     "roofline": r["roofline"], "cpu_baseline": None, "ep_parity": r["ep_parity"],
                     "ep_transport_dtype": r["transport_dtype"], "nccl_all_to_all_baseline": r["nccl_all_to_all_baseline"],
-                    "ep_timeline": r["ep_timeline"], "ep_lanes": r["ep_lanes"], "ep_comm_sms": r["ep_comm_sms"]}
+                    "ep_timeline": r["ep_timeline"], "ep_lanes": r["ep_lanes"], "ep_comm_sms": r["ep_comm_sms"], "ep_plan_ahead": r["ep_plan_ahead"]}
             emit(line)
         import torch.distributed as dist
         dist.barrier()

@@ -339,7 +339,14 @@ int i64b_ipc_import(const unsigned char* handle64, void** out);
 int i64b_ipc_close(void* p);
 /* sized for cap_src / top_k tokens, whatever n_local is */
 size_t i64b_ep_workspace_bytes(const i64b_ep_ctx* ctx);
-/* x: [n_local, H] bf16 (this rank's tokens); token_ids: int64 [n_local] (this rank's); table_u8: [K, V] */
+/* The plan half of i64b_ep_dispatch alone.  Routing is a pure function of (layer, token id), so an engine that knows the
+ * step's token ids can plan EVERY layer of the step up front on a side stream (the scheduler pre-route of
+ * engine/i64_scheduler.py:293-298, here per layer because every layer has its own table): i64b_ep_dispatch called with
+ * token_ids == NULL then uses the plan found in the workspace (same ctx->n_local) and only moves rows. */
+int i64b_ep_plan(const i64b_ep_ctx* ctx, const int64_t* token_ids, const uint8_t* table_u8, void* workspace,
+                 size_t workspace_bytes, i64b_stream_t stream);
+/* x: [n_local, H] bf16 (this rank's tokens); token_ids: int64 [n_local] (this rank's), or NULL after i64b_ep_plan;
+ * table_u8: [K, V] */
 int i64b_ep_dispatch(const i64b_ep_ctx* ctx, const void* x, const int64_t* token_ids, const uint8_t* table_u8,
                      void* workspace, size_t workspace_bytes, i64b_stream_t stream);
 /* out[n_local, H] = routed_scale * sum_k w_k * y[owner(k,t)][row(k,t)] + shared_scale * y_shared[t] (y_shared: fp32

@@ -92,6 +92,13 @@ def _worker(rank, world, port, case, ret):
         out_again = blk.forward(xl, il, torch.float32)                  # barrier epochs / buffer reuse
         torch.cuda.synchronize(dev)
         assert torch.equal(out, out_again), "peer path is not run-to-run identical"
+        # plan made ahead on a side stream (scheduler pre-route): same bits
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        blk.plan_ahead(il, side)
+        out_planned = blk.forward(xl, il, torch.float32)
+        torch.cuda.synchronize(dev)
+        assert torch.equal(out, out_planned), "plan_ahead changes the result"
         if case.get("nccl", False):
             out_nccl = blk.forward(xl, il, torch.float32, exchange="nccl")  # reference-style all_to_all_single exchange
             assert torch.equal(out, out_nccl), "peer-memory and NCCL exchanges disagree"

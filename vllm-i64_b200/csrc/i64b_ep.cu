@@ -617,27 +617,41 @@ size_t i64b_ep_workspace_bytes(const i64b_ep_ctx* c) {
     return ep_carve(c, nullptr).bytes + 1024;
 }
 
+static int ep_run_plan(const i64b_ep_ctx* c, const int64_t* token_ids, const uint8_t* table_u8, const EpWs& w, cudaStream_t s) {
+    I64bPlanArgs pa = {};
+    pa.mode = I64B_ROUTE_TABLE;
+    pa.token_ids = token_ids;
+    pa.table = table_u8;
+    pa.n = c->n_local;
+    pa.vocab = c->vocab;
+    pa.top_k = c->top_k;
+    pa.num_experts = c->num_experts;
+    pa.hidden = c->hidden;
+    pa.ticket = c->state + 16;      // self-resetting: the last rank CTA finalises the plan in the same launch
+    return i64b_run_plan(pa, w.plan, s);
+}
+
+int i64b_ep_plan(const i64b_ep_ctx* c, const int64_t* token_ids, const uint8_t* table_u8, void* workspace,
+                 size_t workspace_bytes, i64b_stream_t stream) {
+    int rc = ep_check(c);
+    if (rc) return rc;
+    I64B_CHECK(table_u8 && workspace && (c->n_local == 0 || token_ids), I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(workspace_bytes >= i64b_ep_workspace_bytes(c), I64B_ERR_WORKSPACE, "EP plan workspace too small");
+    if (c->n_local == 0) return I64B_OK;
+    return ep_run_plan(c, token_ids, table_u8, ep_carve(c, workspace), (cudaStream_t)stream);
+}
+
 int i64b_ep_dispatch(const i64b_ep_ctx* c, const void* x, const int64_t* token_ids, const uint8_t* table_u8,
                      void* workspace, size_t workspace_bytes, i64b_stream_t stream) {
     int rc = ep_check(c);
     if (rc) return rc;
-    I64B_CHECK(table_u8 && workspace && (c->n_local == 0 || (x && token_ids)), I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(table_u8 && workspace && (c->n_local == 0 || x), I64B_ERR_ARG, "null pointer");
     I64B_CHECK(workspace_bytes >= i64b_ep_workspace_bytes(c), I64B_ERR_WORKSPACE, "EP plan workspace too small");
     I64B_CHECK(c->num_experts / c->size <= kCountsStride, I64B_ERR_ARG, "too many local experts");
     const EpWs w = ep_carve(c, workspace);
     cudaStream_t s = (cudaStream_t)stream;
-    if (c->n_local > 0) {
-        I64bPlanArgs pa = {};
-        pa.mode = I64B_ROUTE_TABLE;
-        pa.token_ids = token_ids;
-        pa.table = table_u8;
-        pa.n = c->n_local;
-        pa.vocab = c->vocab;
-        pa.top_k = c->top_k;
-        pa.num_experts = c->num_experts;
-        pa.hidden = c->hidden;
-        pa.ticket = c->state + 16;      // self-resetting: the last rank CTA finalises the plan in the same launch
-        rc = i64b_run_plan(pa, w.plan, s);
+    if (c->n_local > 0 && token_ids != nullptr) {      // token_ids == NULL: the workspace holds i64b_ep_plan's plan
+        rc = ep_run_plan(c, token_ids, table_u8, w, s);
         if (rc) return rc;
     }
     // a rank without tokens still publishes its (zero) counts: one block

@@ -99,6 +99,7 @@ _SIGNATURES = {
     "i64b_ipc_close": (_I, [_P]),
     "i64b_ep_workspace_bytes": (_Z, [C.POINTER(EPCtx)]),
     "i64b_ep_dispatch": (_I, [C.POINTER(EPCtx), _P, _P, _P, _P, _Z, _P]),
+    "i64b_ep_plan": (_I, [C.POINTER(EPCtx), _P, _P, _P, _Z, _P]),
     "i64b_ep_barrier": (_I, [C.POINTER(EPCtx), _P]),
     "i64b_ep_combine": (_I, [C.POINTER(EPCtx), _P, _P, C.POINTER(_F), _F, _F, _P, _I, _P]),
     "i64b_ep_signal": (_I, [C.POINTER(EPCtx), _P]),

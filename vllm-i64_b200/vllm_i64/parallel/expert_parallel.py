@@ -167,6 +167,7 @@ class EPTokenRoutedBlock:
         self._lanes = None
         self._bases = None
         self._cap_tokens = 0
+        self._planned = None
         self.timeline = None
 
     def __del__(self):
@@ -218,8 +219,10 @@ class EPTokenRoutedBlock:
 
         ``lanes``: a forward cuts its tokens into that many micro-batches, each with its own buffers, flags and stream,
         started one dispatch apart — while one lane's rows cross NVLink the other lane's GEMMs own the tensor cores.
-        Every rank must use the same number (default: env ``I64B_EP_LANES``, else 2 from 4096 tokens per rank up,
-        1 below — decided on the all-reduced maximum, so the ranks agree)."""
+        Every rank must use the same number.  Default 1 (env ``I64B_EP_LANES`` overrides): measured on B200 at 2 and 8
+        GPUs the pipeline LOSES (config 5, 64K tokens: 193 us/layer with one lane, 271-299 us with two) — the exchange
+        kernels are fast only with all SMs behind them (a 16-SM partition pulls at 230 GB/s, all SMs at 520), and twice
+        as many half-sized GEMMs and barriers cost more than the overlap returns.  Kept because it is exact and tested."""
         import ctypes as C
         from vllm_i64 import _C
         lib = _C.lib()
@@ -233,7 +236,7 @@ class EPTokenRoutedBlock:
             n = int(nn[0])
         n = max(n, 1)
         if lanes is None:
-            lanes = int(os.environ.get("I64B_EP_LANES", "0")) or (2 if (G > 1 and n >= 4096) else 1)
+            lanes = int(os.environ.get("I64B_EP_LANES", "0")) or 1
         lanes = max(1, min(int(lanes), 8))
         n_lane = -(-n // lanes)
         # SM partition: the exchange kernels get `comm_sms` SMs of their own while GEMMs run next to them (the shared
@@ -336,6 +339,32 @@ class EPTokenRoutedBlock:
         self._bases = None
         self._cap_tokens = 0
 
+    def plan_ahead(self, token_ids: torch.Tensor, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """Compute this layer's dispatch plan for ``token_ids`` now, on ``stream`` (default: the current one), ahead of
+        the ``forward`` that will use it.  Routing depends on the token ids only, so an engine can plan every layer of
+        a step on a side stream while earlier layers run (include/i64b.h, i64b_ep_plan); the next ``forward`` with the
+        SAME ``token_ids`` tensor waits for the plan and only moves rows.  Single-lane path only (a no-op otherwise)."""
+        import ctypes as C
+        from vllm_i64 import _C
+        n = token_ids.numel()
+        if not getattr(self, "_lanes", None):
+            self.reserve(n)
+        if len(self._lanes) != 1 or n == 0:
+            return
+        if n > self._cap_tokens:
+            raise ValueError(f"{n} tokens exceed the reserved expert-parallel capacity of {self._cap_tokens}")
+        if token_ids.dtype != torch.int64 or not token_ids.is_contiguous():
+            raise TypeError("plan_ahead: contiguous int64 token ids")
+        lane = self._lanes[0]
+        lane.ctx.n_local = n
+        with torch.cuda.device(self.device):
+            s = stream or torch.cuda.current_stream(self.device)
+            _C.check(_C.lib().i64b_ep_plan(C.byref(lane.ctx), token_ids.data_ptr(), self._table.data_ptr(),
+                                           lane.ws_plan.data_ptr(), lane.ws_plan.numel(), s.cuda_stream))
+            ev = torch.cuda.Event()
+            ev.record(s)
+        self._planned = (token_ids.data_ptr(), n, ev)
+
     def forward_peer(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One expert-parallel forward over NVLink peer memory: no host synchronisation and no collective call
@@ -381,7 +410,12 @@ class EPTokenRoutedBlock:
                     tl.append((name, ev))
             mark("start")
             lane.ctx.comm_ctas = self._comm_dispatch
-            _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), token_ids.data_ptr(), self._table.data_ptr(),
+            ids_ptr = token_ids.data_ptr()
+            planned, self._planned = self._planned, None
+            if planned is not None and planned[0] == ids_ptr and planned[1] == n and n > 0:
+                cur.wait_event(planned[2])                 # plan_ahead made the plan: rows only
+                ids_ptr = None
+            _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), ids_ptr, self._table.data_ptr(),
                                           lane.ws_plan.data_ptr(), lane.ws_plan.numel(), st))
             mark("plan+dispatch")
             _C.check(lib.i64b_ep_barrier(ctx, st))
