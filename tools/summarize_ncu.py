@@ -13,6 +13,7 @@ os.makedirs(out_dir, exist_ok=True)
 def short(name):
     name = re.sub(r"^void ", "", name)
     name = name.replace("<unnamed>::", "")
+    name = re.sub(r"\((bool|int|unsigned int)\)", "", name)          # template arguments print as (bool)0, (int)256
     return name.split("(")[0][:90]
 
 
@@ -28,7 +29,7 @@ for path in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", f"{tag}_launches_*
         except ValueError:
             pass
     tot = sum(sum(v) for v in agg.values())
-    lines = [f"# ncu launch list, workload {wl}: python bench.py --workload {wl} --steps 2 --warmup 3 --no-cpu-baseline --no-stages",
+    lines = [f"# ncu launch list, workload {wl}: python bench.py --workload {wl} --steps 2 --warmup 3 --no-cpu-baseline --no-stages --no-workloads",
              "# ncu --metrics gpu__time_duration.sum --clock-control none (per-launch times are cold-cache and serialised: compare SHARES)",
              f"{'kernel':<92s} {'launches':>8s} {'mean_ns':>10s} {'share':>7s}"]
     for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
@@ -83,5 +84,9 @@ for path in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", f"{tag}_full_*.ncu
 for wl, t in traffic.items():
     for k in list(t):
         t[k] = sum(t[k]) / len(t[k])          # dram__bytes_read.sum + dram__bytes_write.sum per launch
-json.dump(traffic, open(os.path.join(out_dir, "ncu_traffic.json"), "w"), indent=1)
+tpath = os.path.join(out_dir, "ncu_traffic.json")
+merged = json.load(open(tpath)) if os.path.exists(tpath) else {}
+for wl, t in traffic.items():
+    merged.setdefault(wl, {}).update(t)
+json.dump(merged, open(tpath, "w"), indent=1)
 print(traffic)
