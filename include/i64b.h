@@ -264,9 +264,12 @@ void* i64b_moe_tap(i64b_layer* layer, int what);
 enum {
     I64B_DEBUG_KEEP_TAPS = 1,
     I64B_DEBUG_FUSE_COMBINE = 2,  /* force the fused combine (default: dense FFN only) */
-    I64B_DEBUG_NO_FUSED = 4       /* never take the single-launch decode kernel on this layer (it must own the GPU: its
+    I64B_DEBUG_NO_FUSED = 4,      /* never take the single-launch decode kernel on this layer (it must own the GPU: its
                                      CTAs wait on one another, so it may not share the device with another launch of
                                      itself — callers that run this layer on a second stream set this) */
+    I64B_DEBUG_TRI = 8,           /* take the token-major fused down projection whenever the shape allows (top-2 bf16
+                                     blocks, E*E <= 64; default: only when the expert-pair groups are tall enough) */
+    I64B_DEBUG_NO_TRI = 16        /* never take it (per-assignment fp32 rows + combine_kernel) */
 };
 int i64b_moe_set_debug(i64b_layer* layer, int flags);
 

@@ -75,8 +75,10 @@ struct i64b_layer {
         float *xs_scale, *inter_scale_r, *inter_scale_s, *y;
         int32_t *q14_r, *q14_s, *amax_r, *amax_s;
         int amax_ld_r, amax_ld_s;
+        I64bTriWs tri;          // token-major layout (fused down projection)
         size_t bytes;
     } cv;
+    CUtensorMap tm_cat;         // [N, 2I+S] token-major intermediates over inter_r | inter_s (valid with cached_ws)
 };
 
 static int w13_rows(const i64b_moe_config& c) { return c.num_experts * 2 * c.expert_inter + 2 * c.shared_inter; }
@@ -135,6 +137,11 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
     cv.amax_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * cv.amax_ld_s : 0));
     const int64_t slabs = c.shared_inter > 0 ? (c.shared_inter + 511) / 512 : 1;
     cv.y = reinterpret_cast<float*>(take(sizeof(float) * (R + slabs * nn) * c.hidden_size));
+    {
+        const bool tri_shape = c.top_k == 2 && c.num_experts >= 1 && c.num_experts * c.num_experts <= I64B_MAX_EXPERTS;
+        cv.tri = i64b_tri_ws_carve(p ? p + off : nullptr, tri_shape ? n : 0, c.top_k, tri_shape ? c.num_experts : 1);
+        off += align256(cv.tri.bytes);
+    }
     cv.bytes = off;
     return cv;
 }
@@ -382,6 +389,19 @@ static bool combine_is_fused(const i64b_layer* L, int E, int K, int S) {
     return S > 0 && fmode != 0 && (E == 0 || (fmode == 1 && K <= 2));
 }
 
+// Token-major fused down projection (i64b_launch_gemm_tri): GEMM2 + combine in one kernel, no fp32 per-assignment rows.
+// I64B_TRI: 0 never, 1 whenever the shape allows, unset = when the pair groups are tall enough for 256-row units (every
+// group is padded to a multiple of 256 rows: at 16K tokens and 56 pairs that padding costs more than the y traffic saves).
+static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t n, bool plain_call) {
+    static const int mode = getenv("I64B_TRI") ? atoi(getenv("I64B_TRI")) : -1;
+    const int E = c.num_experts;
+    if (mode == 0 || !plain_call || c.mode != I64B_MODE_BF16 || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
+    if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 128 != 0) return false;
+    if (L->debug & (I64B_DEBUG_KEEP_TAPS | I64B_DEBUG_FUSE_COMBINE | I64B_DEBUG_NO_TRI)) return false;
+    if (mode == 1 || (L->debug & I64B_DEBUG_TRI)) return true;
+    return n >= (int64_t)E * (E - 1) * 768;
+}
+
 static bool fused_enabled() {
     static const bool on = !(getenv("I64B_FUSED") && atoi(getenv("I64B_FUSED")) == 0);
     return on;
@@ -461,10 +481,16 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         } else {
             L->tm_inter_s = L->tm_inter_r;
         }
+        if (E > 0 && K == 2 && !q) {
+            rc = i64b_encode_tmap(&L->tm_cat, cv.inter_r, false, n, 2 * I + S, (int64_t)(2 * I + S) * 2, 128);
+            if (rc) return rc;
+        }
         L->cached_ws = base;
         L->cached_n = cache_key;
     }
     L->cv = cv;
+    const bool tri = tri_selected(L, c, n, given_routes == nullptr && !o.override_scales);
+    cv.tri.ticket = cv.plan.sync + 1;
 
     // decode-sized bf16 batches: the whole layer in ONE persistent launch (csrc/i64b_fused.cu)
     if (fused_enabled() && !q && !(L->debug & I64B_DEBUG_NO_FUSED) && given_routes == nullptr && o.stage_mask == 0xFFu &&
@@ -525,6 +551,10 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     if (o.stage_mask & I64B_STAGE_PLAN) {
         rc = i64b_run_plan(pa, cv.plan, s);
         if (rc) return rc;
+        if (tri) {
+            rc = i64b_run_tri_plan(cv.plan, cv.tri, n, E, H, s);
+            if (rc) return rc;
+        }
     }
 
     // 2. fused (quantize-and-)scatter
@@ -542,6 +572,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.routes_out = cv.routes;
     da.scatter_idx_out = cv.scatter_idx;
     da.dest_row_out = cv.dest_row;
+    da.tri = tri ? 1 : 0;
+    da.tw = cv.tri;
     if (o.stage_mask & I64B_STAGE_DISPATCH) {
         rc = i64b_run_dispatch(da, cv.plan, s);
         if (rc) return rc;
@@ -574,6 +606,15 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.amax_ld[0] = cv.amax_ld_r;
         gp.amax_ld[1] = cv.amax_ld_s;
         gp.silu_lut = L->silu_lut;
+        if (tri) {      // SwiGLU rows go straight to their token's row of the [N, 2I+S] buffer
+            gp.out[0] = gp.out[1] = cv.inter_r;
+            gp.ld_out[0] = gp.ld_out[1] = 2 * I + S;
+            gp.rowmap[0] = cv.tri.rowmap;
+            gp.rowmap[1] = cv.tri.pos;
+            gp.tri_col[0] = 0;
+            gp.tri_col[1] = I;
+            gp.tri_col[2] = 2 * I;
+        }
         const int wi = nmma_index(n_mma);
         const bool pairs = use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0));
         const int64_t tiles = pairs ? pt_r * ((I + bn - 1) / bn) + pt_s * ((S + bn - 1) / bn)
@@ -590,6 +631,28 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
                                       reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, S > 0 ? n : 0, S, s);
             if (rc) return rc;
         }
+    }
+
+    // 4'. token-major blocks: down projections of both routes and of the shared expert + the weighted combine, one kernel
+    if (tri) {
+        I64bGemmParams gp = {};
+        gp.groups = cv.tri.groups;
+        gp.num_groups = E * E;
+        gp.k[0] = I;
+        gp.k[1] = S;
+        for (int k = 0; k < I64B_MAX_TOPK; ++k) gp.w[k] = k < K ? c.route_weight[k] : 0.0f;
+        gp.routed_scale = c.routed_scale;
+        gp.shared_scale = c.shared_scale;
+        gp.final_out = out;
+        gp.final_dtype = out_dtype;
+        gp.ld_final = H;
+        gp.row_tok = cv.tri.tok;
+        const int64_t units = n / 256 + (int64_t)E * E;
+        if (o.stage_mask & I64B_STAGE_GEMM2) {
+            rc = i64b_launch_gemm_tri(false, L->tm_cat, L->tm_w2r[0], L->tm_w2s[0], gp, units * (H / 128), s);
+            if (rc) return rc;
+        }
+        return I64B_OK;
     }
 
     // 4. GEMM2: down projections -> per-assignment fp32 outputs
@@ -678,6 +741,7 @@ int i64b_moe_uses_fused(const i64b_layer* L, int64_t n) {
 
 int i64b_moe_fuses_combine(const i64b_layer* L, int64_t n) {
     if (!L || !L->loaded || i64b_moe_uses_fused(L, n)) return 0;
+    if (tri_selected(L, L->cfg, n, true)) return 1;
     return combine_is_fused(L, L->cfg.num_experts, L->cfg.top_k, L->cfg.shared_inter) ? 1 : 0;
 }
 

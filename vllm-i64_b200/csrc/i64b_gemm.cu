@@ -121,6 +121,33 @@ __device__ __forceinline__ void warp_store_block(uint32_t st_addr, const uint32_
     }
 }
 
+// The same block with every row at its own address: lane i supplies `my_off`, the byte offset of row i from gbase.
+__device__ __forceinline__ void warp_store_block_rows(uint32_t st_addr, const uint32_t (&v)[16], uint8_t* gbase,
+                                                      int64_t my_off, int rows_valid, int bytes_valid, int lane) {
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};"
+                     :: "r"(st_addr + lane * kStagePitch + j * 16), "r"(v[4 * j]), "r"(v[4 * j + 1]), "r"(v[4 * j + 2]),
+                        "r"(v[4 * j + 3]) : "memory");
+    __syncwarp();
+    const int piece = lane & 3;
+    const int rr = (lane >> 3) + 4 * ((lane >> 2) & 1);
+    int4 d[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(d[i].x), "=r"(d[i].y), "=r"(d[i].z), "=r"(d[i].w)
+                     : "r"(st_addr + (i * 8 + rr) * kStagePitch + piece * 16));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = i * 8 + rr;
+        const int64_t off = __shfl_sync(0xffffffffu, my_off, row);
+        if (row < rows_valid && piece * 16 < bytes_valid)
+            *reinterpret_cast<int4*>(gbase + off + piece * 16) = d[i];
+    }
+}
+
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
     int v;
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -536,6 +563,17 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             if constexpr (kDual && !kInt8) {
                 uint8_t* obase = reinterpret_cast<uint8_t*>(p.out[w]) + (out_row0 * p.ld_out[w] + colw0) * 2;
                 const int64_t pitch = p.ld_out[w] * 2;
+                // token-major layout: this lane's row goes to its token's row of the [N, 2I+S] buffer
+                const bool scatter = p.rowmap[w] != nullptr;
+                int64_t my_off = 0;
+                if (scatter) {
+                    obase = reinterpret_cast<uint8_t*>(p.out[w]);
+                    if (valid) {
+                        const int m = __ldg(p.rowmap[w] + out_row0 + lane);
+                        const int col = w ? p.tri_col[2] : p.tri_col[(m >> 30) & 1];
+                        my_off = ((int64_t)(m & 0x3FFFFFFF) * p.ld_out[w] + col + colw0) * 2;
+                    }
+                }
 #pragma unroll 1
                 for (int c = 0; c < kColsW; c += 32) {
                     if (colw0 + c >= n_out) break;
@@ -552,7 +590,10 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                             o[j] = pack_bf16x2(h0, h1);
                         }
                     }
-                    warp_store_block(st_addr, o, obase + c * 2, pitch, rows_valid, min(64, (n_out - colw0 - c) * 2), lane);
+                    if (scatter)
+                        warp_store_block_rows(st_addr, o, obase + c * 2, my_off, rows_valid, min(64, (n_out - colw0 - c) * 2), lane);
+                    else
+                        warp_store_block(st_addr, o, obase + c * 2, pitch, rows_valid, min(64, (n_out - colw0 - c) * 2), lane);
                 }
             } else if constexpr (kDual && kInt8) {
                 uint8_t* obase = reinterpret_cast<uint8_t*>(p.out[w]) + (out_row0 * p.ld_out[w] + colw0) * 4;
@@ -732,6 +773,218 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused down projection + combine over the token-major layout (i64b_gemm.cuh, i64b_launch_gemm_tri).
+// CTA pairs (M = 256 per unit), N = 128 output columns per tile, K in up to three segments — route 0, route 1, shared
+// expert — each accumulating into its OWN 128-column TMEM slot; four slots rotate, so the next tile's first segment
+// runs under this tile's epilogue.  The epilogue reads the three accumulators of a token and applies
+//     o = w0*y0;  o = o + w1*y1;  o = rs*o;  o = o + ss*y_shared                 layers/token_routed_mlp.py:156-185
+// with the same roundings as combine_kernel, then writes the token's output row.  Nothing else leaves the SM.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kTriN = 128;
+__global__ void __launch_bounds__(kThreads, 1)
+i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
+                     const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ I64bGemmParams p) {
+    using Cfg = StageCfg<kTriN, 2>;
+    constexpr int kStages = Cfg::kStages;
+    constexpr int kStageB = Cfg::kStageB;              // this CTA's 64 weight rows
+    constexpr int kBlockK = 64;
+    constexpr uint32_t kTmemCols = 512;                // four accumulator slots of 128 columns
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + kStages * kStageA;
+    uint8_t* misc = sB + kStages * kStageB;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tfull_bar = empty_bar + kStages;         // [4]
+    uint64_t* tempty_bar = tfull_bar + 4;              // [4]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 4);
+    int* prefix = reinterpret_cast<int*>(tmem_ptr + 2);
+    I64bGroup* sg = reinterpret_cast<I64bGroup*>(misc + 512);
+    uint8_t* stage_base = misc + kMiscBytes;
+    static_assert((2 * 8 + 2 * 4) * 8 + 8 + 4 * (I64B_MAX_GROUPS + 1) <= 512, "barrier area");
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int unit0 = (int)blockIdx.x / 2;
+    const int unit_step = (int)gridDim.x / 2;
+    pdl_launch_dependents();
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB0);
+        tma_prefetch_desc(&tmB1);
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 4; ++i) {
+            mbar_init(&tfull_bar[i], 1);
+            mbar_init(&tempty_bar[i], kEpiWarps * 2);
+        }
+        fence_barrier_init();
+    } else if (warp == 1) {
+        tmem_alloc_cta2<kTmemCols>(tmem_ptr);
+    }
+    cluster_sync_all();
+    pdl_wait_prior();
+
+    const int ng = p.num_groups;
+    for (int i = threadIdx.x; i < ng; i += kThreads) sg[i] = p.groups[i];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int g = 0; g < ng; ++g) {
+            prefix[g] = acc;
+            acc += ((sg[g].rows + 2 * kBlockM - 1) / (2 * kBlockM)) * ((sg[g].n_out + kTriN - 1) / kTriN);
+        }
+        prefix[ng] = acc;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const int total_tiles = prefix[ng];
+    const int nkb_r = p.k[0] / kBlockK, nkb_s = p.k[1] / kBlockK;       // k-blocks per routed segment / of the shared one
+    const int nseg = nkb_s > 0 ? 3 : 2;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0, g = 0;
+            uint32_t phase = 0;
+            for (int tile = unit0; tile < total_tiles; tile += unit_step) {
+                TileCoord tc;
+                decode_tile<kTriN, 2>(tile, g, prefix, sg, tc, rank);
+                const I64bGroup grp = sg[tc.g];
+                const int a_row = grp.row_start + tc.m_t * kBlockM;
+                const int n0 = tc.n_t * kTriN + rank * (kTriN / 2);
+                int a_col = 0;
+                for (int seg = 0; seg < nseg; ++seg) {
+                    const CUtensorMap* tb = seg == 2 ? &tmB1 : &tmB0;
+                    const int b_row = (seg == 0 ? grp.w_row_base : (seg == 1 ? grp.pad0 : 0)) + n0;
+                    const int nkb = seg == 2 ? nkb_s : nkb_r;
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (kStageA + kStageB));
+                        tma_load_2d_cta2(sA + stage * kStageA, &tmA, &full_bar[stage], a_col + kb * kBlockK, a_row,
+                                         I64B_L2_EVICT_NORMAL);
+                        tma_load_2d_cta2(sB + stage * kStageB, tb, &full_bar[stage], kb * kBlockK, b_row,
+                                         I64B_L2_EVICT_NORMAL);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                    a_col += nkb * kBlockK;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = make_idesc<false, kTriN, 2>();
+            int stage = 0, iter = 0;
+            uint32_t phase = 0;
+            for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
+                for (int seg = 0; seg < nseg; ++seg) {
+                    const int use = nseg * iter + seg;          // uses of the accumulator slots so far
+                    const int slot = use & 3;
+                    mbar_wait(&tempty_bar[slot], ((use >> 2) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + slot * kTriN;
+                    const int nkb = seg == 2 ? nkb_s : nkb_r;
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tc_fence_after();
+                        const uint64_t a_desc = make_sw128_kmajor_desc(sA + stage * kStageA);
+                        const uint64_t b_desc = make_sw128_kmajor_desc(sB + stage * kStageB);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        umma_commit_cta2(&empty_bar[stage]);
+                        if (kb == nkb - 1) umma_commit_cta2(&tfull_bar[slot]);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const int h = (warp - 2) >> 2;
+        const int r = q * 32 + lane;
+        constexpr int kColsW = kTriN / 2;
+        const int cbase = h * kColsW;
+        const uint32_t st_addr = smem_u32(stage_base + (warp - 2) * kEpiWarpBytes);
+        const bool f32out = p.final_dtype == I64B_F32;
+        const int fsz = f32out ? 4 : 2;
+        const float w0 = p.w[0], w1 = p.w[1], rs = p.routed_scale, ss = p.shared_scale;
+        int g = 0, iter = 0;
+        for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
+            TileCoord tc;
+            decode_tile<kTriN, 2>(tile, g, prefix, sg, tc, rank);
+            const I64bGroup grp = sg[tc.g];
+            const int row_in_group = tc.m_t * kBlockM + r;
+            const bool valid = row_in_group < grp.rows;
+            const int rows_valid = min(32, max(0, grp.rows - (tc.m_t * kBlockM + q * 32)));
+            const int colw0 = tc.n_t * kTriN + cbase;
+            int64_t my_off = 0;
+            if (valid) my_off = ((int64_t)__ldg(p.row_tok + grp.row_start + row_in_group) * p.ld_final + colw0) * fsz;
+            uint32_t taddr[3];
+#pragma unroll
+            for (int seg = 0; seg < 3; ++seg) {
+                const int use = nseg * iter + (seg < nseg ? seg : 0);
+                taddr[seg] = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(use & 3) * kTriN + cbase;
+                if (seg < nseg) mbar_wait(&tfull_bar[use & 3], (use >> 2) & 1);
+            }
+            tc_fence_after();
+            uint8_t* obase = reinterpret_cast<uint8_t*>(p.final_out);
+#pragma unroll 1
+            for (int c = 0; c < kColsW; c += 32) {
+                uint32_t a0[32], a1[32];
+                tmem_ld_32x32(taddr[0] + c, a0);
+                tmem_ld_32x32(taddr[1] + c, a1);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    float o = __fmul_rn(w0, __uint_as_float(a0[j]));
+                    o = __fadd_rn(o, __fmul_rn(w1, __uint_as_float(a1[j])));
+                    a0[j] = __float_as_uint(__fmul_rn(rs, o));
+                }
+                if (nseg == 3) {
+                    tmem_ld_32x32(taddr[2] + c, a1);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        a0[j] = __float_as_uint(__fadd_rn(__uint_as_float(a0[j]), __fmul_rn(ss, __uint_as_float(a1[j]))));
+                }
+                uint32_t blk[16];
+                if (f32out) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) blk[j] = a0[j];
+                    warp_store_block_rows(st_addr, blk, obase + c * 4, my_off, rows_valid, 64, lane);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) blk[j] = a0[16 + j];
+                    warp_store_block_rows(st_addr, blk, obase + (c + 16) * 4, my_off, rows_valid, 64, lane);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        blk[j] = pack_bf16x2(__uint_as_float(a0[2 * j]), __uint_as_float(a0[2 * j + 1]));
+                    warp_store_block_rows(st_addr, blk, obase + c * 2, my_off, rows_valid, 64, lane);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0)
+                for (int seg = 0; seg < nseg; ++seg) mbar_arrive_leader(&tempty_bar[(nseg * iter + seg) & 3]);
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_cta2<kTmemCols>(tmem_base);
+    }
+}
+
 typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                         CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
@@ -841,6 +1094,9 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
     return I64B_OK;
 }
 
+int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
+                         const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
+
 // Upper bound on the CTAs of the GEMM launches made by the calling thread (0 = every SM).  The expert-parallel path leaves a
 // few SMs to the NVLink exchange kernels that run next to the GEMMs on other streams (i64b_moe_set_cta_limit).
 static thread_local int g_gemm_cta_limit = 0;
@@ -879,4 +1135,29 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
 #undef I64B_DISPATCH
     i64b_set_error("unsupported GEMM tile configuration n_mma=%d", n_mma);
     return I64B_ERR_ARG;
+}
+
+int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
+                         const I64bGemmParams& p, int64_t max_units, cudaStream_t stream) {
+    if (max_units <= 0) return I64B_OK;
+    I64B_CHECK(!is_int8, I64B_ERR_ARG, "the fused down projection is bf16 only");
+    I64B_CHECK(p.groups != nullptr && p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
+               p.num_groups);
+    I64B_CHECK(p.k[0] > 0 && p.k[0] % 64 == 0 && p.k[1] >= 0 && p.k[1] % 64 == 0, I64B_ERR_ARG,
+               "K segments must be multiples of 64 (got %d, %d)", p.k[0], p.k[1]);
+    I64B_CHECK(p.row_tok && p.final_out, I64B_ERR_ARG, "null pointer");
+    constexpr int smem = StageCfg<kTriN, 2>::kSmem;
+    static bool configured[I64B_MAX_DEVICES] = {};
+    const int dev = i64b_current_device();
+    if (!configured[dev]) {
+        I64B_CUDA(cudaFuncSetAttribute(i64b_gemm_tri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured[dev] = true;
+    }
+    int sms = i64b_num_sms();
+    if (g_gemm_cta_limit > 0 && g_gemm_cta_limit < sms) sms = g_gemm_cta_limit >= 2 ? g_gemm_cta_limit : 2;
+    const int pairs = sms / 2;
+    const int grid = 2 * (int)(max_units < pairs ? max_units : pairs);
+    I64B_CUDA(i64b_launch_cluster(i64b_gemm_tri_kernel, dim3(grid), dim3(kThreads), smem, stream, 2, tmA, tmB0, tmB1, p));
+    i64b_count_launch();
+    return I64B_OK;
 }

@@ -37,6 +37,13 @@ struct I64bGemmParams {
     int32_t final_dtype;
     int64_t ld_final;
     int32_t* tile_done;        // counter of drained routed (tile, epilogue-warp) pairs, zero at launch
+    // token-major layout (I64bTriWs).  GEMM1 (dual, bf16): output rows are scattered — rowmap[0][r] = pair-order row |
+    // (route << 30) of dispatched row r, rowmap[1][t] = pair-order row of token t — and land at column tri_col[route]
+    // (tri_col[2] for the shared expert) of the [N, ld_out] buffer.  The fused down projection (i64b_launch_gemm_tri)
+    // reads it back with K segments k[0], k[0], k[1] and writes row row_tok[r] of final_out.
+    const int32_t* rowmap[2];
+    int32_t tri_col[3];
+    const int32_t* row_tok;
     // bring-up instrumentation (env I64B_DEBUG_FLAGS / I64B_DEBUG_TIMELINE; never set in production)
     uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores
     long long* debug_timeline; // [grid, 8] clock64 offsets per CTA
@@ -54,6 +61,16 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
 int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream);
+
+// Fused down projection + combine over the token-major layout (top-2 routed experts + optional shared expert), CTA
+// pairs, three TMEM accumulators per tile:
+//   out[row_tok[r]] = rs * (w0 * A[r, 0:I] · W2[e0]^T + w1 * A[r, I:2I] · W2[e1]^T) + ss * A[r, 2I:2I+S] · W2s^T
+// in the reference's fp32 operation order (layers/token_routed_mlp.py:156-185).  tmA: [N, 2I+S] (128-row boxes);
+// tmB0 / tmB1: routed / shared down-projection weights with 64-row boxes; p.groups: one group per expert pair
+// (w_row_base = e0*H, pad0 = e1*H); p.k[0] = I, p.k[1] = S (0: no shared expert).  max_units: upper bound on the number of
+// 256-row units.
+int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
+                         const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
 
 int i64b_num_sms();
 int i64b_set_gemm_cta_limit(int limit);      // thread-local; returns the previous value

@@ -37,6 +37,27 @@ struct I64bPlanArgs {
 // route + per-tile stable ranks + finalisation (counts, offsets, group tables). 1-2 launches.
 int i64b_run_plan(const I64bPlanArgs& a, const I64bPlanWs& ws, cudaStream_t stream);
 
+// Token-major layout for the fused down projection (top-2 blocks): tokens stably sorted by their ordered expert pair
+// (e0, e1).  All three SwiGLU intermediates of a token (route 0, route 1, shared expert) then sit in ONE row of a
+// [N, 2*I_e + S] buffer, a pair's rows are contiguous, and a single grouped GEMM over K = 2*I_e + S with three TMEM
+// accumulators per tile produces y0, y1 and y_shared of the same token in the same CTA: the combine happens in that
+// GEMM's epilogue and the fp32 per-assignment outputs never exist in memory.
+struct I64bTriWs {
+    uint32_t* packed;     // [N]   pair id (8 bits) | rank inside the 1024-token tile (24 bits)
+    int32_t* tile_base;   // [tiles, E*E]  per-tile histogram, then in place: exclusive base over tiles
+    int32_t* pair_start;  // [E*E + 1]
+    int32_t* pos;         // [N]   token -> row in pair order
+    int32_t* tok;         // [N]   row in pair order -> token
+    int32_t* rowmap;      // [N*K] expert-major dispatched row -> pair-order row | (route << 30)
+    I64bGroup* groups;    // [E*E] one GEMM group per pair (w_row_base = e0*H, pad0 = e1*H)
+    int32_t* ticket;      // self-resetting last-CTA counter
+    size_t bytes;
+};
+I64bTriWs i64b_tri_ws_carve(void* base, int64_t n, int top_k, int num_experts);
+// after i64b_run_plan (reads the plan's packed expert ids): 1 launch
+int i64b_run_tri_plan(const I64bPlanWs& plan, const I64bTriWs& tri, int64_t n, int num_experts, int hidden,
+                      cudaStream_t stream);
+
 struct I64bDispatchArgs {
     const void* x;              // [N, H] bf16 (fused path) or raw rows
     int64_t n;
@@ -52,6 +73,8 @@ struct I64bDispatchArgs {
     int32_t* routes_out;        // [K, N]
     int32_t* scatter_idx_out;   // [K, N]
     int32_t* dest_row_out;      // [K, N]
+    int tri;                    // 1: also fill tw.pos / tw.tok / tw.rowmap (token-major layout, top_k == 2)
+    I64bTriWs tw;
 };
 int i64b_run_dispatch(const I64bDispatchArgs& a, const I64bPlanWs& ws, cudaStream_t stream);
 
