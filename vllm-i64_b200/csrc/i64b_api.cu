@@ -396,7 +396,7 @@ static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t 
     static const int mode = getenv("I64B_TRI") ? atoi(getenv("I64B_TRI")) : -1;
     const int E = c.num_experts;
     if (mode == 0 || !plain_call || c.mode != I64B_MODE_BF16 || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
-    if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 128 != 0) return false;
+    if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 256 != 0) return false;
     if (L->debug & (I64B_DEBUG_KEEP_TAPS | I64B_DEBUG_FUSE_COMBINE | I64B_DEBUG_NO_TRI)) return false;
     if (mode == 1 || (L->debug & I64B_DEBUG_TRI)) return true;
     return n >= (int64_t)E * (E - 1) * 768;
@@ -649,7 +649,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.row_tok = cv.tri.tok;
         const int64_t units = n / 256 + (int64_t)E * E;
         if (o.stage_mask & I64B_STAGE_GEMM2) {
-            rc = i64b_launch_gemm_tri(false, L->tm_cat, L->tm_w2r[0], L->tm_w2s[0], gp, units * (H / 128), s);
+            rc = i64b_launch_gemm_tri(false, L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp, units * ((H + 255) / 256), s);
             if (rc) return rc;
         }
         return I64B_OK;

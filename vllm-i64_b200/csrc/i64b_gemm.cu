@@ -775,21 +775,25 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 
 // ---------------------------------------------------------------------------------------------------------------
 // Fused down projection + combine over the token-major layout (i64b_gemm.cuh, i64b_launch_gemm_tri).
-// CTA pairs (M = 256 per unit), N = 128 output columns per tile, K in up to three segments — route 0, route 1, shared
-// expert — each accumulating into its OWN 128-column TMEM slot; four slots rotate, so the next tile's first segment
-// runs under this tile's epilogue.  The epilogue reads the three accumulators of a token and applies
-//     o = w0*y0;  o = o + w1*y1;  o = rs*o;  o = o + ss*y_shared                 layers/token_routed_mlp.py:156-185
-// with the same roundings as combine_kernel, then writes the token's output row.  Nothing else leaves the SM.
+// CTA pairs (M = 256 per unit), N = 256 output columns per tile (narrower tiles are bound by the SM's operand ingest: a
+// 128-column version ran at 0.45 of the tensor peak), K in up to three segments — route 0, route 1, shared expert.
+// TMEM holds two 256-column accumulators:
+//     segment 0 -> acc0, segment 1 -> acc1
+//     epilogue 1:  acc0 <- rs * (w0*acc0 + w1*acc1)      (tcgen05.ld / tcgen05.st; acc1 is released as soon as it is read)
+//     segment 2 -> acc1  (the shared expert; runs while epilogue 1 still rewrites acc0)
+//     epilogue 2:  out[token] = acc0 + ss*acc1
+// i.e.  o = w0*y0;  o = o + w1*y1;  o = rs*o;  o = o + ss*y_shared  with the roundings of combine_kernel
+// (layers/token_routed_mlp.py:156-185).  The fp32 per-assignment rows never leave the SM.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int kTriN = 128;
+constexpr int kTriN = 256;
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
                      const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ I64bGemmParams p) {
     using Cfg = StageCfg<kTriN, 2>;
     constexpr int kStages = Cfg::kStages;
-    constexpr int kStageB = Cfg::kStageB;              // this CTA's 64 weight rows
+    constexpr int kStageB = Cfg::kStageB;              // this CTA's 128 weight rows
     constexpr int kBlockK = 64;
-    constexpr uint32_t kTmemCols = 512;                // four accumulator slots of 128 columns
+    constexpr uint32_t kTmemCols = 512;                // acc0 | acc1
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;
@@ -797,8 +801,8 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     uint8_t* misc = sB + kStages * kStageB;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
     uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* tfull_bar = empty_bar + kStages;         // [4]
-    uint64_t* tempty_bar = tfull_bar + 4;              // [4]
+    uint64_t* tfull_bar = empty_bar + kStages;         // [3]: segment s complete
+    uint64_t* tempty_bar = tfull_bar + 4;              // [0]: acc1 read by epilogue 1;  [1]: both accumulators drained
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 4);
     int* prefix = reinterpret_cast<int*>(tmem_ptr + 2);
     I64bGroup* sg = reinterpret_cast<I64bGroup*>(misc + 512);
@@ -820,10 +824,8 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             mbar_init(&full_bar[i], 1);
             mbar_init(&empty_bar[i], 1);
         }
-        for (int i = 0; i < 4; ++i) {
-            mbar_init(&tfull_bar[i], 1);
-            mbar_init(&tempty_bar[i], kEpiWarps * 2);
-        }
+        for (int i = 0; i < 3; ++i) mbar_init(&tfull_bar[i], 1);
+        for (int i = 0; i < 2; ++i) mbar_init(&tempty_bar[i], kEpiWarps * 2);
         fence_barrier_init();
     } else if (warp == 1) {
         tmem_alloc_cta2<kTmemCols>(tmem_ptr);
@@ -884,12 +886,12 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             int stage = 0, iter = 0;
             uint32_t phase = 0;
             for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
+                const uint32_t par = (uint32_t)iter & 1u;
                 for (int seg = 0; seg < nseg; ++seg) {
-                    const int use = nseg * iter + seg;          // uses of the accumulator slots so far
-                    const int slot = use & 3;
-                    mbar_wait(&tempty_bar[slot], ((use >> 2) & 1) ^ 1);
+                    if (seg == 0) mbar_wait(&tempty_bar[1], par ^ 1);        // the previous tile's accumulators are drained
+                    if (seg == 2) mbar_wait(&tempty_bar[0], par);            // epilogue 1 of THIS tile has read acc1
                     tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + slot * kTriN;
+                    const uint32_t d_tmem = tmem_base + (seg == 0 ? 0 : kTriN);
                     const int nkb = seg == 2 ? nkb_s : nkb_r;
                     for (int kb = 0; kb < nkb; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
@@ -900,7 +902,7 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         for (int k = 0; k < 4; ++k)
                             umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         umma_commit_cta2(&empty_bar[stage]);
-                        if (kb == nkb - 1) umma_commit_cta2(&tfull_bar[slot]);
+                        if (kb == nkb - 1) umma_commit_cta2(&tfull_bar[seg]);
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -916,8 +918,28 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const bool f32out = p.final_dtype == I64B_F32;
         const int fsz = f32out ? 4 : 2;
         const float w0 = p.w[0], w1 = p.w[1], rs = p.routed_scale, ss = p.shared_scale;
+        uint8_t* obase = reinterpret_cast<uint8_t*>(p.final_out);
+        const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + cbase;      // acc0, this warp's lanes and columns
+        const uint32_t t1 = t0 + kTriN;                                           // acc1
         int g = 0, iter = 0;
+        auto store_chunk = [&](const uint32_t (&v)[32], int c, int64_t my_off, int rows_valid) {
+            uint32_t blk[16];
+            if (f32out) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) blk[j] = v[j];
+                warp_store_block_rows(st_addr, blk, obase + c * 4, my_off, rows_valid, 64, lane);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) blk[j] = v[16 + j];
+                warp_store_block_rows(st_addr, blk, obase + (c + 16) * 4, my_off, rows_valid, 64, lane);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    blk[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+                warp_store_block_rows(st_addr, blk, obase + c * 2, my_off, rows_valid, 64, lane);
+            }
+        };
         for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
+            const uint32_t par = (uint32_t)iter & 1u;
             TileCoord tc;
             decode_tile<kTriN, 2>(tile, g, prefix, sg, tc, rank);
             const I64bGroup grp = sg[tc.g];
@@ -927,20 +949,15 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             const int colw0 = tc.n_t * kTriN + cbase;
             int64_t my_off = 0;
             if (valid) my_off = ((int64_t)__ldg(p.row_tok + grp.row_start + row_in_group) * p.ld_final + colw0) * fsz;
-            uint32_t taddr[3];
-#pragma unroll
-            for (int seg = 0; seg < 3; ++seg) {
-                const int use = nseg * iter + (seg < nseg ? seg : 0);
-                taddr[seg] = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(use & 3) * kTriN + cbase;
-                if (seg < nseg) mbar_wait(&tfull_bar[use & 3], (use >> 2) & 1);
-            }
+            mbar_wait(&tfull_bar[0], par);
+            mbar_wait(&tfull_bar[1], par);
             tc_fence_after();
-            uint8_t* obase = reinterpret_cast<uint8_t*>(p.final_out);
+            // epilogue 1: the routed part; with a shared expert it goes back into acc0, else straight out
 #pragma unroll 1
             for (int c = 0; c < kColsW; c += 32) {
                 uint32_t a0[32], a1[32];
-                tmem_ld_32x32(taddr[0] + c, a0);
-                tmem_ld_32x32(taddr[1] + c, a1);
+                tmem_ld_32x32(t0 + c, a0);
+                tmem_ld_32x32(t1 + c, a1);
                 tmem_ld_wait();
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
@@ -948,32 +965,31 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     o = __fadd_rn(o, __fmul_rn(w1, __uint_as_float(a1[j])));
                     a0[j] = __float_as_uint(__fmul_rn(rs, o));
                 }
-                if (nseg == 3) {
-                    tmem_ld_32x32(taddr[2] + c, a1);
+                if (nseg == 3) tmem_st_32x32(t0 + c, a0);
+                else store_chunk(a0, c, my_off, rows_valid);
+            }
+            if (nseg == 3) {
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(&tempty_bar[0]);       // acc1 may take the shared expert's segment
+                mbar_wait(&tfull_bar[2], par);
+                tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < kColsW; c += 32) {
+                    uint32_t a0[32], a1[32];
+                    tmem_ld_32x32(t0 + c, a0);
+                    tmem_ld_32x32(t1 + c, a1);
                     tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
                         a0[j] = __float_as_uint(__fadd_rn(__uint_as_float(a0[j]), __fmul_rn(ss, __uint_as_float(a1[j]))));
-                }
-                uint32_t blk[16];
-                if (f32out) {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) blk[j] = a0[j];
-                    warp_store_block_rows(st_addr, blk, obase + c * 4, my_off, rows_valid, 64, lane);
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) blk[j] = a0[16 + j];
-                    warp_store_block_rows(st_addr, blk, obase + (c + 16) * 4, my_off, rows_valid, 64, lane);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        blk[j] = pack_bf16x2(__uint_as_float(a0[2 * j]), __uint_as_float(a0[2 * j + 1]));
-                    warp_store_block_rows(st_addr, blk, obase + c * 2, my_off, rows_valid, 64, lane);
+                    store_chunk(a0, c, my_off, rows_valid);
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0)
-                for (int seg = 0; seg < nseg; ++seg) mbar_arrive_leader(&tempty_bar[(nseg * iter + seg) & 3]);
+            if (lane == 0) mbar_arrive_leader(&tempty_bar[1]);
         }
     }
 

@@ -63,10 +63,10 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
                      int64_t max_tiles, cudaStream_t stream);
 
 // Fused down projection + combine over the token-major layout (top-2 routed experts + optional shared expert), CTA
-// pairs, three TMEM accumulators per tile:
+// pairs, 256 x 256 tiles, two TMEM accumulators (the routed sum is folded back into the first one):
 //   out[row_tok[r]] = rs * (w0 * A[r, 0:I] · W2[e0]^T + w1 * A[r, I:2I] · W2[e1]^T) + ss * A[r, 2I:2I+S] · W2s^T
 // in the reference's fp32 operation order (layers/token_routed_mlp.py:156-185).  tmA: [N, 2I+S] (128-row boxes);
-// tmB0 / tmB1: routed / shared down-projection weights with 64-row boxes; p.groups: one group per expert pair
+// tmB0 / tmB1: routed / shared down-projection weights with 128-row boxes; p.groups: one group per expert pair
 // (w_row_base = e0*H, pad0 = e1*H); p.k[0] = I, p.k[1] = S (0: no shared expert).  max_units: upper bound on the number of
 // 256-row units.
 int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
