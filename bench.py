@@ -60,6 +60,7 @@ WORKLOADS = {
                           pw=1.0, rs=1.0, ss=1.0, L=4, N=16384, mode="bf16", reps=40),
 }
 HEADLINE = "ep64k_bf16"
+E2E_CHUNKS = 0              # --e2e-chunks
 METRIC, UNIT = "moe_ffn_tokens_per_s", "tokens/s"
 NVLINK_GBS = 770.0          # measured peer copy per direction per GPU on this pool (B200_PROFILING.md)
 _JSON_FD = None
@@ -355,11 +356,14 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
         for i, blk in enumerate(layers):
             blk.forward(x_dev, ids_arg, torch.bfloat16, out=outs[i & 1], stages=stages)
 
+    # the engine step with HOST buffers: micro-batched so that the PCIe copies run under the kernels (HostStepPipeline);
+    # small batches are one micro-batch = copy in, L forwards, copy out
+    from vllm_i64.kernels.block import HostStepPipeline
+    e2e_chunks = E2E_CHUNKS or (4 if N >= 32768 else (2 if N >= 8192 else 1))
+    pipe = HostStepPipeline(layers, N, chunks=e2e_chunks)
+
     def step_e2e():
-        x_dev.copy_(x_host, non_blocking=True)
-        ids_dev.copy_(ids_host, non_blocking=True)
-        step_device()
-        out_host.copy_(outs[(L - 1) & 1], non_blocking=True)
+        pipe.run(x_host, ids_host if wl["E"] else None, out_host)
 
     # the per-layer plugin call with HOST buffers (i64b_moe_forward_host: H2D + forward + D2H inside the C ABI call)
     staging = layers[0].make_staging(N)
@@ -385,8 +389,10 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
            "us_per_layer": round(us_layer, 3), "steps": steps, "dtype": "bf16" if wl["mode"] == "bf16" else "int8",
            "gpu_launches_per_step": int(launches_per_step),
            "e2e": {"value": N * L * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / e2e_steps,
-                   "h2d_bytes_per_step": N * H * 2 + N * 8, "d2h_bytes_per_step": N * H * 2, "copies_per_step": 1,
-                   "via": "engine step: one pinned H2D of x + ids, L block forwards, one D2H of the last output"},
+                   "h2d_bytes_per_step": N * H * 2 + (N * 8 if wl["E"] else 0), "d2h_bytes_per_step": N * H * 2,
+                   "copies_per_step": e2e_chunks,
+                   "via": f"engine step (HostStepPipeline): pinned H2D of x + ids, L block forwards, D2H of the last output, "
+                          f"in {e2e_chunks} micro-batch(es) whose copies run under the kernels of their neighbours"},
            "e2e_per_layer_host_call": {
                "value": N * L * max(3, min(steps, 20)) / (ms_host * 1e-3), "unit": UNIT, "copies_per_step": L,
                "h2d_bytes_per_step": L * (N * H * 2 + N * 8), "d2h_bytes_per_step": L * N * H * 2,
@@ -776,6 +782,8 @@ def main():
     ap.add_argument("--no-workloads", action="store_true", help="N = 1: only the line's own workload")
     ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
+    ap.add_argument("--e2e-chunks", type=int, default=0,
+                    help="N = 1: micro-batches of the end-to-end step (0 = 4 from 32K tokens, 2 from 8K, else 1)")
     ap.add_argument("--ep-lanes", type=int, default=0,
                     help="N > 1: micro-batch lanes per expert-parallel forward (0 = the library's default)")
     ap.add_argument("--ep-plan-ahead", action="store_true",
@@ -784,6 +792,8 @@ def main():
     ap.add_argument("--ep-nccl-baseline", action="store_true", help="also time the all_to_all_single exchange (eager)")
     ap.add_argument("--ep-timeline", action="store_true", help="also report per-stage device times of one EP layer (eager)")
     args = ap.parse_args()
+    global E2E_CHUNKS
+    E2E_CHUNKS = args.e2e_chunks
     wl = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

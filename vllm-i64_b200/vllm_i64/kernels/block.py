@@ -207,3 +207,83 @@ class I64Block:
     def tap(self, what: int, shape, dtype: torch.dtype) -> torch.Tensor:
         with torch.cuda.device(self.device):
             return _C.tap_tensor(self._h, what, shape, dtype, self.device)
+
+
+class HostStepPipeline:
+    """An engine step over HOST buffers (the reference's engine hands every step's hidden states to the layer stack,
+    engine/i64_engine.py; here the buffers are pinned host tensors): the step's tokens are cut into ``chunks``
+    micro-batches and the host->device copy of micro-batch c+1 and the device->host copy of c-1 run on their own streams
+    under the block forwards of c.  The tokens of an FFN block are independent, so the cut changes no bit of the result;
+    it only keeps PCIe and the SMs busy at the same time (a 64K-token bf16 step moves 134 MB each way: 2 x 2.6 ms of
+    copies around 3.5 ms of kernels when done one after the other).
+
+    ``layers`` are applied to the SAME input rows, the last layer's output is returned (the shape of bench.py's synthetic
+    step); ``chain=True`` feeds every layer the previous layer's output instead (a decoder stack without attention).
+    No host synchronisation; capturable in a CUDA graph.
+    """
+
+    def __init__(self, layers: Sequence["I64Block"], max_tokens: int, chunks: int = 4, out_dtype=torch.bfloat16):
+        if not layers:
+            raise ValueError("no layers")
+        self.layers = list(layers)
+        self.device = self.layers[0].device
+        self.hidden = self.layers[0].cfg.hidden_size
+        self.chunks = max(1, int(chunks))
+        self.per = -(-int(max_tokens) // self.chunks)
+        self.max_tokens = self.per * self.chunks
+        dev, h = self.device, self.hidden
+        self.x = [torch.empty(self.per, h, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.ids = [torch.empty(self.per, dtype=torch.int64, device=dev) for _ in range(2)]
+        self.out = [[torch.empty(self.per, h, dtype=out_dtype, device=dev) for _ in range(2)] for _ in range(2)]
+        self.h2d = torch.cuda.Stream(dev)
+        self.d2h = torch.cuda.Stream(dev)
+
+    def run(self, x_host: torch.Tensor, ids_host: Optional[torch.Tensor], out_host: torch.Tensor,
+            chain: bool = False) -> None:
+        n = x_host.shape[0]
+        if n > self.max_tokens:
+            raise ValueError(f"{n} tokens exceed the pipeline's capacity of {self.max_tokens}")
+        if x_host.dtype != torch.bfloat16 or out_host.dtype != self.out[0][0].dtype:
+            raise TypeError("x_host must be bfloat16 and out_host of the pipeline's output dtype")
+        per = -(-n // self.chunks) if n else 0
+        with torch.cuda.device(self.device):
+            cur = torch.cuda.current_stream(self.device)
+            self.h2d.wait_stream(cur)
+            self.d2h.wait_stream(cur)
+            computed, copied_out = [], []
+            for c in range(self.chunks):
+                lo, hi = min(n, c * per), min(n, (c + 1) * per)
+                m = hi - lo
+                if m == 0:
+                    break
+                s = c & 1
+                with torch.cuda.stream(self.h2d):
+                    if c >= 2:
+                        self.h2d.wait_event(computed[c - 2])          # the kernels of micro-batch c-2 have read this slot
+                    self.x[s][:m].copy_(x_host[lo:hi], non_blocking=True)
+                    if ids_host is not None:
+                        self.ids[s][:m].copy_(ids_host[lo:hi], non_blocking=True)
+                    arrived = torch.cuda.Event()
+                    arrived.record(self.h2d)
+                cur.wait_event(arrived)
+                if c >= 2:
+                    cur.wait_event(copied_out[c - 2])                 # its output buffers have left for the host
+                src = self.x[s][:m]
+                ids = self.ids[s][:m] if ids_host is not None else None
+                last = None
+                for i, blk in enumerate(self.layers):
+                    last = self.out[s][i & 1][:m]
+                    blk.forward(src, ids, last.dtype, out=last)
+                    if chain:
+                        src = last
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                computed.append(ev)
+                with torch.cuda.stream(self.d2h):
+                    self.d2h.wait_event(ev)
+                    out_host[lo:hi].copy_(last, non_blocking=True)
+                    ev2 = torch.cuda.Event()
+                    ev2.record(self.d2h)
+                    copied_out.append(ev2)
+            cur.wait_stream(self.h2d)
+            cur.wait_stream(self.d2h)
