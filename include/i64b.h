@@ -206,6 +206,10 @@ int i64b_fused_decode_supported(int n, int hidden, int expert_inter, int shared_
 /* 1 if the kernel chain on n tokens finishes the block inside the down-projection's epilogue (no separate combine
  * launch), else 0.  Meaningless (0) when i64b_moe_uses_fused is 1. */
 int i64b_moe_fuses_combine(const i64b_layer* layer, int64_t n);
+/* Which form of the token-major fused down projection a plain forward of n tokens takes: 0 none (GEMM2 + combine),
+ * 1 three accumulators folded in the epilogue (bit-identical to GEMM2 + combine_kernel), 2 one accumulator over
+ * K = 2*I_e + S with the scales — all powers of two — folded into the SwiGLU rows. */
+int i64b_moe_tri_form(const i64b_layer* layer, int64_t n);
 
 /* Run only the selected stages of the forward on the workspace contents left by an earlier full forward with the
  * same (n, workspace): used by bench.py to time each kernel in isolation (roofline per stage). */
@@ -269,8 +273,14 @@ enum {
                                      itself — callers that run this layer on a second stream set this) */
     I64B_DEBUG_TRI = 8,           /* take the token-major fused down projection whenever the shape allows (top-2 bf16
                                      blocks, E*E <= 64; default: only when the expert-pair groups are tall enough) */
-    I64B_DEBUG_NO_TRI = 16        /* never take it (per-assignment fp32 rows + combine_kernel) */
+    I64B_DEBUG_NO_TRI = 16,       /* never take it (per-assignment fp32 rows + combine_kernel) */
+    I64B_DEBUG_TRI_FOLD = 32      /* fused down projection: keep the three-accumulator form (bit-identical to GEMM2 +
+                                     combine_kernel) even when the scales are powers of two and the single-accumulator
+                                     form (scales folded into the SwiGLU rows, one sum over K = 2*I_e + S) would be taken */
 };
+/* auto selection of the fused down projection: at least this many tokens per unordered expert pair, E(E-1)/2 pairs */
+#define I64B_TRI_MIN_ROWS_ONEACC 192
+#define I64B_TRI_MIN_ROWS_FOLD 384
 int i64b_moe_set_debug(i64b_layer* layer, int flags);
 
 /* Cross-layer weight prefetch (decode).  `next` is the layer the engine runs after `layer` (the decoder stack calls

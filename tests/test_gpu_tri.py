@@ -1,8 +1,13 @@
 """Token-major fused down projection (i64b_launch_gemm_tri): GEMM2 of both routes and of the shared expert + the weighted
-combine in ONE kernel, three TMEM accumulators per tile, no fp32 per-assignment rows in memory.  It applies the same fp32
-operations in the same order as GEMM2 + combine_kernel, so the bar is BIT IDENTITY with that chain (and the chain's own
-bar against the oracle).  Cases: small and config-5 geometry, no shared expert, skewed ids (empty / tiny / huge pair
-groups), token counts that are not a multiple of any tile, both output dtypes, unequal route weights, graph replay."""
+combine in ONE kernel, no fp32 per-assignment rows in memory.  Two forms:
+* three accumulators folded in the epilogue: the same fp32 operations in the same order as GEMM2 + combine_kernel, so the
+  bar is BIT IDENTITY with that chain (and the chain's own bar against the oracle);
+* one accumulator (route weights x routed scale and the shared scale all powers of two — the named models): the scales go
+  into the SwiGLU rows in GEMM1's epilogue (exact) and the block output is one sum over K = 2*I_e + S.  Same products, a
+  different fp32 summation order: the bar is the oracle's, plus a few fp32 ulps from the chain.
+Cases: small and config-5 geometry, no shared expert, skewed ids (empty / tiny / huge pair groups), both orders of a pair
+and colliding routes (e0 == e1), token counts that are not a multiple of any tile, both output dtypes, unequal route
+weights, scales other than 1, graph replay."""
 import numpy as np
 import pytest
 import torch
@@ -22,29 +27,47 @@ CASES = [
     dict(id="small-noshared", shape=(256, 4, 64, 0, 1000, 2), n=517),
     dict(id="tiny-n", shape=(256, 8, 64, 128, 1000, 2), n=5),
     dict(id="zipf", shape=(256, 8, 128, 192, 5000, 2), n=3001, zipf=True),
+    dict(id="collisions", shape=(256, 4, 64, 128, 1000, 2), n=900, collide=3),
     dict(id="weights-95-05", shape=(256, 4, 64, 128, 1000, 2), n=1300, pw=0.95),
     dict(id="config5-8k", shape=(1024, 8, 512, 1280, 32000, 2), n=8192, sample=64),
     dict(id="config5-33k", shape=(1024, 8, 512, 1280, 32000, 2), n=33000, sample=32),
 ]
+# the single-accumulator form needs power-of-two scales: (route weight, routed scale, shared scale)
+ONEACC_SCALES = [(0.5, 2.0, 1.0), (0.5, 1.0, 0.5), (0.5, 4.0, 2.0)]
 
 
-def _run(case, out_dtype):
+def _run(case, out_dtype, fold=True, scales=None):
     h, e, ie, s, v, k = case["shape"]
     n = case["n"]
-    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=11, zipf=case.get("zipf", False),
-                                          pw=case.get("pw", 0.5))
+    pw, rs, ss = scales if scales else (case.get("pw", 0.5), 2.0, 1.0)
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=11, zipf=case.get("zipf", False), pw=pw, rs=rs, ss=ss)
+    if case.get("collide"):          # some vocabulary entries route both slots to the same expert
+        table = np.array(table, copy=True)
+        table[1, ::case["collide"]] = table[0, ::case["collide"]]
+    routes = O.route_table(ids, table, n, e)
+    if n > 100:
+        assert (routes[0] < routes[1]).any() and (routes[0] > routes[1]).any(), "both orders of a pair must occur"
     xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
     chain = Hh.build_gpu_block(cfg, w, table, "bf16")
     chain.set_debug(_C.DEBUG_NO_FUSED | _C.DEBUG_NO_TRI)
     tri = Hh.build_gpu_block(cfg, w, table, "bf16")
-    tri.set_debug(_C.DEBUG_NO_FUSED | _C.DEBUG_TRI)
+    tri.set_debug(_C.DEBUG_NO_FUSED | _C.DEBUG_TRI | (_C.DEBUG_TRI_FOLD if fold else 0))
+    assert chain.tri_form(n) == 0
+    assert tri.tri_form(n) == (1 if fold or pw != 0.5 else 2)
     want = chain.forward(xg, ig, out_dtype)
     got = tri.forward(xg, ig, out_dtype)
     again = tri.forward(xg, ig, out_dtype)
     torch.cuda.synchronize()
     assert torch.equal(got, again), "not run-to-run identical"
-    bad = (got != want).any(dim=1).nonzero().flatten()
-    assert bad.numel() == 0, f"{bad.numel()} of {n} rows differ from the GEMM2 + combine chain, first {bad[:8].tolist()}"
+    if tri.tri_form(n) == 1:
+        bad = (got != want).any(dim=1).nonzero().flatten()
+        assert bad.numel() == 0, f"{bad.numel()} of {n} rows differ from the GEMM2 + combine chain, first {bad[:8].tolist()}"
+    else:
+        # same products, one fp32 accumulation instead of three rounded partial sums: a few fp32 ulps of the row's scale
+        # (bf16 output: at most one bf16 ulp where the fp32 values straddle a rounding boundary)
+        d = (got.float() - want.float()).abs().max().item()
+        top = want.float().abs().max().item()
+        assert d <= top * (2e-5 if out_dtype == torch.float32 else 2.0 ** -7), (d, top)
     sample = case.get("sample")
     rows = np.arange(n) if not sample else np.unique(np.linspace(0, n - 1, sample).astype(int))
     ref = O.moe_block_fp32(x[rows], ids[rows], table, w, cfg, inter_bf16=True)
@@ -57,7 +80,19 @@ def _run(case, out_dtype):
 @pytest.mark.parametrize("case", CASES, ids=[c["id"] for c in CASES])
 @pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
 def test_tri_equals_chain(case, out_dtype):
-    _run(case, out_dtype)
+    _run(case, out_dtype, fold=True)
+
+
+@pytest.mark.parametrize("case", [c for c in CASES if "pw" not in c], ids=[c["id"] for c in CASES if "pw" not in c])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+def test_tri_one_accumulator(case, out_dtype):
+    _run(case, out_dtype, fold=False)
+
+
+@pytest.mark.parametrize("scales", ONEACC_SCALES[1:], ids=["half", "x2"])
+def test_tri_one_accumulator_scales_folded_into_gemm1(scales):
+    _run(CASES[0], torch.float32, fold=False, scales=scales)
+    _run(CASES[3], torch.bfloat16, fold=False, scales=scales)
 
 
 def test_tri_graph_replay():
@@ -77,9 +112,32 @@ def test_tri_graph_replay():
     assert torch.equal(out, got)
 
 
+def test_tri_graph_replay_one_accumulator():
+    tri, xg, ig, got = _run(CASES[0], torch.bfloat16, fold=False)
+    out = torch.empty_like(got)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        tri.forward(xg, ig, torch.bfloat16, out=out)
+    s.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        tri.forward(xg, ig, torch.bfloat16, out=out)
+    out.zero_()
+    g.replay()
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, got)
+
+
 def test_tri_is_selected_for_tall_pair_groups():
-    cfg, w, table, ids, x = Hh.make_block(256, 4, 64, 128, 1000, 2, 16, seed=1)
-    blk = Hh.build_gpu_block(cfg, w, table, "bf16")
     lib = _C.lib()
-    assert lib.i64b_moe_fuses_combine(blk._h, 4 * 3 * 768) == 1          # auto: rows per pair >= 768
-    assert lib.i64b_moe_fuses_combine(blk._h, 4 * 3 * 768 - 1) == 0
+    pairs = 4 * 3 // 2
+    cfg, w, table, ids, x = Hh.make_block(256, 4, 64, 128, 1000, 2, 16, seed=1)            # 0.5 / 0.5 x 2.0, 1.0
+    blk = Hh.build_gpu_block(cfg, w, table, "bf16")
+    assert lib.i64b_moe_tri_form(blk._h, pairs * _C.TRI_MIN_ROWS_ONEACC) == 2
+    assert lib.i64b_moe_fuses_combine(blk._h, pairs * _C.TRI_MIN_ROWS_ONEACC) == 1
+    assert lib.i64b_moe_tri_form(blk._h, pairs * _C.TRI_MIN_ROWS_ONEACC - 1) == 0
+    cfg, w, table, ids, x = Hh.make_block(256, 4, 64, 128, 1000, 2, 16, seed=1, pw=0.95)   # not powers of two
+    blk = Hh.build_gpu_block(cfg, w, table, "bf16")
+    assert lib.i64b_moe_tri_form(blk._h, pairs * _C.TRI_MIN_ROWS_FOLD) == 1
+    assert lib.i64b_moe_tri_form(blk._h, pairs * _C.TRI_MIN_ROWS_FOLD - 1) == 0

@@ -390,16 +390,35 @@ static bool combine_is_fused(const i64b_layer* L, int E, int K, int S) {
 }
 
 // Token-major fused down projection (i64b_launch_gemm_tri): GEMM2 + combine in one kernel, no fp32 per-assignment rows.
-// I64B_TRI: 0 never, 1 whenever the shape allows, unset = when the pair groups are tall enough for 256-row units (every
-// group is padded to a multiple of 256 rows: at 16K tokens and 56 pairs that padding costs more than the y traffic saves).
+// Two forms.  When every route weight, the routed scale and the shared scale are powers of two (the named models), the
+// scales are applied to the SwiGLU rows in GEMM1's epilogue (exact) and the down projection is ONE accumulation over
+// K = 2*I_e + S (`one_acc`); otherwise the three segments keep their own accumulators and the epilogue folds them in the
+// reference's operation order (bit-identical to GEMM2 + combine_kernel).
+static bool is_pow2(float v) {
+    int e = 0;
+    return v > 0.0f && v < 3.0e38f && frexpf(v, &e) == 0.5f && e > -100 && e < 100;
+}
+static bool tri_one_acc(const i64b_layer* L, const i64b_moe_config& c) {
+    static const int mode = getenv("I64B_TRI_ONEACC") ? atoi(getenv("I64B_TRI_ONEACC")) : -1;
+    if (mode == 0 || (L->debug & I64B_DEBUG_TRI_FOLD)) return false;
+    for (int k = 0; k < c.top_k; ++k)
+        if (!is_pow2(c.route_weight[k])) return false;
+    return is_pow2(c.routed_scale) && (c.shared_inter == 0 || is_pow2(c.shared_scale));
+}
+// I64B_TRI: 0 never, 1 whenever the shape allows, unset = when the pair groups are tall enough: every group (one per
+// UNORDERED expert pair, E(E-1)/2 of them with distinct routes) is padded to a multiple of 256 rows, ~128 wasted rows per
+// group, which the saved y traffic (12 KB per token) and the combine pass pay for from a few hundred rows per group on.
 static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t n, bool plain_call) {
     static const int mode = getenv("I64B_TRI") ? atoi(getenv("I64B_TRI")) : -1;
+    static const int min_rows = getenv("I64B_TRI_MIN_ROWS") ? atoi(getenv("I64B_TRI_MIN_ROWS")) : 0;
     const int E = c.num_experts;
     if (mode == 0 || !plain_call || c.mode != I64B_MODE_BF16 || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
     if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 256 != 0) return false;
     if (L->debug & (I64B_DEBUG_KEEP_TAPS | I64B_DEBUG_FUSE_COMBINE | I64B_DEBUG_NO_TRI)) return false;
     if (mode == 1 || (L->debug & I64B_DEBUG_TRI)) return true;
-    return n >= (int64_t)E * (E - 1) * 768;
+    const int64_t pairs = (int64_t)E * (E - 1) / 2;
+    const int64_t rows = min_rows > 0 ? min_rows : (tri_one_acc(L, c) ? I64B_TRI_MIN_ROWS_ONEACC : I64B_TRI_MIN_ROWS_FOLD);
+    return n >= pairs * rows;
 }
 
 static bool fused_enabled() {
@@ -614,6 +633,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
             gp.tri_col[0] = 0;
             gp.tri_col[1] = I;
             gp.tri_col[2] = 2 * I;
+            gp.tri_mul[0] = gp.tri_mul[1] = gp.tri_mul[2] = 1.0f;
+            if (tri_one_acc(L, c)) {        // powers of two: the products are exact
+                gp.tri_mul[0] = c.route_weight[0] * c.routed_scale;
+                gp.tri_mul[1] = c.route_weight[1] * c.routed_scale;
+                gp.tri_mul[2] = S > 0 ? c.shared_scale : 1.0f;
+                gp.tri_scaled = (gp.tri_mul[0] != 1.0f || gp.tri_mul[1] != 1.0f || gp.tri_mul[2] != 1.0f) ? 1 : 0;
+            }
         }
         const int wi = nmma_index(n_mma);
         const bool pairs = use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0));
@@ -649,7 +675,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.row_tok = cv.tri.tok;
         const int64_t units = n / 256 + (int64_t)E * E;
         if (o.stage_mask & I64B_STAGE_GEMM2) {
-            rc = i64b_launch_gemm_tri(false, L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp, units * ((H + 255) / 256), s);
+            rc = i64b_launch_gemm_tri(false, tri_one_acc(L, c), L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp,
+                                      units * ((H + 255) / 256), s);
             if (rc) return rc;
         }
         return I64B_OK;
@@ -743,6 +770,11 @@ int i64b_moe_fuses_combine(const i64b_layer* L, int64_t n) {
     if (!L || !L->loaded || i64b_moe_uses_fused(L, n)) return 0;
     if (tri_selected(L, L->cfg, n, true)) return 1;
     return combine_is_fused(L, L->cfg.num_experts, L->cfg.top_k, L->cfg.shared_inter) ? 1 : 0;
+}
+
+int i64b_moe_tri_form(const i64b_layer* L, int64_t n) {
+    if (!L || !L->loaded || i64b_moe_uses_fused(L, n) || !tri_selected(L, L->cfg, n, true)) return 0;
+    return tri_one_acc(L, L->cfg) ? 2 : 1;
 }
 
 int i64b_moe_forward_stages(i64b_layer* L, const void* x, const int64_t* token_ids, void* out, int out_dtype,

@@ -566,12 +566,16 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 // token-major layout: this lane's row goes to its token's row of the [N, 2I+S] buffer
                 const bool scatter = p.rowmap[w] != nullptr;
                 int64_t my_off = 0;
+                float mul = 1.0f;           // one-accumulator down projection: w_k * rs (or ss) folded in here, a power of two
+                const bool use_mul = scatter && p.tri_scaled != 0;
                 if (scatter) {
                     obase = reinterpret_cast<uint8_t*>(p.out[w]);
                     if (valid) {
-                        const int m = __ldg(p.rowmap[w] + out_row0 + lane);
-                        const int col = w ? p.tri_col[2] : p.tri_col[(m >> 30) & 1];
-                        my_off = ((int64_t)(m & 0x3FFFFFFF) * p.ld_out[w] + col + colw0) * 2;
+                        // routed rows: bit 30 = K segment of the pair-order row (0: the pair's lower expert), bit 31 = route
+                        const uint32_t m = (uint32_t)__ldg(p.rowmap[w] + out_row0 + lane);
+                        const int col = w ? p.tri_col[2] : p.tri_col[(m >> 30) & 1u];
+                        mul = w ? p.tri_mul[2] : p.tri_mul[m >> 31];
+                        my_off = ((int64_t)(m & 0x3FFFFFFFu) * p.ld_out[w] + col + colw0) * 2;
                     }
                 }
 #pragma unroll 1
@@ -585,8 +589,12 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         tmem_ld_wait();
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
-                            const float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
-                            const float h1 = silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]);
+                            float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
+                            float h1 = silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]);
+                            if (use_mul) {
+                                h0 = __fmul_rn(h0, mul);
+                                h1 = __fmul_rn(h1, mul);
+                            }
                             o[j] = pack_bf16x2(h0, h1);
                         }
                     }
@@ -785,7 +793,14 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 // i.e.  o = w0*y0;  o = o + w1*y1;  o = rs*o;  o = o + ss*y_shared  with the roundings of combine_kernel
 // (layers/token_routed_mlp.py:156-185).  The fp32 per-assignment rows never leave the SM.
 // ---------------------------------------------------------------------------------------------------------------
+//
+// kOneAcc: every route weight times the routed scale, and the shared scale, is a power of two (the named models: 0.5 / 0.5
+// x 2.0, 1.0).  GEMM1's epilogue has then already multiplied the SwiGLU rows by those factors — exact in bf16 — and the
+// block output is ONE sum over K = 2*I_e + S: the three segments accumulate into the same TMEM accumulator, the two
+// 256-column accumulators alternate between tiles (tile i+1's MMAs run under tile i's epilogue, as in i64b_gemm_kernel),
+// and the epilogue is a plain scattered store.  Same products, one fp32 accumulation instead of three partial sums.
 constexpr int kTriN = 256;
+template <bool kOneAcc>
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
                      const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ I64bGemmParams p) {
@@ -887,22 +902,35 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             uint32_t phase = 0;
             for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
                 const uint32_t par = (uint32_t)iter & 1u;
-                for (int seg = 0; seg < nseg; ++seg) {
-                    if (seg == 0) mbar_wait(&tempty_bar[1], par ^ 1);        // the previous tile's accumulators are drained
-                    if (seg == 2) mbar_wait(&tempty_bar[0], par);            // epilogue 1 of THIS tile has read acc1
+                if constexpr (kOneAcc) {
+                    mbar_wait(&tempty_bar[par], (((uint32_t)iter >> 1) & 1u) ^ 1u);     // this accumulator's previous tile is drained
                     tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + (seg == 0 ? 0 : kTriN);
+                }
+                for (int seg = 0; seg < nseg; ++seg) {
+                    if constexpr (!kOneAcc) {
+                        if (seg == 0) mbar_wait(&tempty_bar[1], par ^ 1);        // the previous tile's accumulators are drained
+                        if (seg == 2) mbar_wait(&tempty_bar[0], par);            // epilogue 1 of THIS tile has read acc1
+                        tc_fence_after();
+                    }
+                    const uint32_t d_tmem = tmem_base + (kOneAcc ? par * kTriN : (seg == 0 ? 0 : kTriN));
                     const int nkb = seg == 2 ? nkb_s : nkb_r;
                     for (int kb = 0; kb < nkb; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
                         tc_fence_after();
                         const uint64_t a_desc = make_sw128_kmajor_desc(sA + stage * kStageA);
                         const uint64_t b_desc = make_sw128_kmajor_desc(sB + stage * kStageB);
+                        const int fresh = kOneAcc ? (seg | kb) : kb;             // 0: the first MMA overwrites the accumulator
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                            umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
                         umma_commit_cta2(&empty_bar[stage]);
-                        if (kb == nkb - 1) umma_commit_cta2(&tfull_bar[seg]);
+                        if (kb == nkb - 1) {
+                            if constexpr (kOneAcc) {
+                                if (seg == nseg - 1) umma_commit_cta2(&tfull_bar[par]);
+                            } else {
+                                umma_commit_cta2(&tfull_bar[seg]);
+                            }
+                        }
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -948,7 +976,27 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             const int rows_valid = min(32, max(0, grp.rows - (tc.m_t * kBlockM + q * 32)));
             const int colw0 = tc.n_t * kTriN + cbase;
             int64_t my_off = 0;
-            if (valid) my_off = ((int64_t)__ldg(p.row_tok + grp.row_start + row_in_group) * p.ld_final + colw0) * fsz;
+            float wa = w0, wb = w1;         // weights of K segments 0 / 1 for this row (bit 30 of row_tok: route 1 sits in segment 0)
+            if (valid) {
+                const int rt = __ldg(p.row_tok + grp.row_start + row_in_group);
+                my_off = ((int64_t)(rt & 0x3FFFFFFF) * p.ld_final + colw0) * fsz;
+                if (rt & 0x40000000) { wa = w1; wb = w0; }
+            }
+            if constexpr (kOneAcc) {
+                mbar_wait(&tfull_bar[par], ((uint32_t)iter >> 1) & 1u);
+                tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < kColsW; c += 32) {
+                    uint32_t a0[32];
+                    tmem_ld_32x32(t0 + par * kTriN + c, a0);
+                    tmem_ld_wait();
+                    store_chunk(a0, c, my_off, rows_valid);
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(&tempty_bar[par]);
+                continue;
+            }
             mbar_wait(&tfull_bar[0], par);
             mbar_wait(&tfull_bar[1], par);
             tc_fence_after();
@@ -961,8 +1009,8 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 tmem_ld_wait();
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    float o = __fmul_rn(w0, __uint_as_float(a0[j]));
-                    o = __fadd_rn(o, __fmul_rn(w1, __uint_as_float(a1[j])));
+                    float o = __fmul_rn(wa, __uint_as_float(a0[j]));          // a + b == b + a: same bits as w0*y0 + w1*y1
+                    o = __fadd_rn(o, __fmul_rn(wb, __uint_as_float(a1[j])));
                     a0[j] = __float_as_uint(__fmul_rn(rs, o));
                 }
                 if (nseg == 3) tmem_st_32x32(t0 + c, a0);
@@ -1110,9 +1158,6 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
     return I64B_OK;
 }
 
-int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
-                         const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
-
 // Upper bound on the CTAs of the GEMM launches made by the calling thread (0 = every SM).  The expert-parallel path leaves a
 // few SMs to the NVLink exchange kernels that run next to the GEMMs on other streams (i64b_moe_set_cta_limit).
 static thread_local int g_gemm_cta_limit = 0;
@@ -1153,8 +1198,8 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
     return I64B_ERR_ARG;
 }
 
-int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
-                         const I64bGemmParams& p, int64_t max_units, cudaStream_t stream) {
+int i64b_launch_gemm_tri(bool is_int8, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
+                         const CUtensorMap& tmB1, const I64bGemmParams& p, int64_t max_units, cudaStream_t stream) {
     if (max_units <= 0) return I64B_OK;
     I64B_CHECK(!is_int8, I64B_ERR_ARG, "the fused down projection is bf16 only");
     I64B_CHECK(p.groups != nullptr && p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
@@ -1163,17 +1208,18 @@ int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap
                "K segments must be multiples of 64 (got %d, %d)", p.k[0], p.k[1]);
     I64B_CHECK(p.row_tok && p.final_out, I64B_ERR_ARG, "null pointer");
     constexpr int smem = StageCfg<kTriN, 2>::kSmem;
-    static bool configured[I64B_MAX_DEVICES] = {};
+    auto kern = one_acc ? i64b_gemm_tri_kernel<true> : i64b_gemm_tri_kernel<false>;
+    static bool configured[2][I64B_MAX_DEVICES] = {};
     const int dev = i64b_current_device();
-    if (!configured[dev]) {
-        I64B_CUDA(cudaFuncSetAttribute(i64b_gemm_tri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured[dev] = true;
+    if (!configured[one_acc ? 1 : 0][dev]) {
+        I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured[one_acc ? 1 : 0][dev] = true;
     }
     int sms = i64b_num_sms();
     if (g_gemm_cta_limit > 0 && g_gemm_cta_limit < sms) sms = g_gemm_cta_limit >= 2 ? g_gemm_cta_limit : 2;
     const int pairs = sms / 2;
     const int grid = 2 * (int)(max_units < pairs ? max_units : pairs);
-    I64B_CUDA(i64b_launch_cluster(i64b_gemm_tri_kernel, dim3(grid), dim3(kThreads), smem, stream, 2, tmA, tmB0, tmB1, p));
+    I64B_CUDA(i64b_launch_cluster(kern, dim3(grid), dim3(kThreads), smem, stream, 2, tmA, tmB0, tmB1, p));
     i64b_count_launch();
     return I64B_OK;
 }

@@ -43,7 +43,9 @@ struct I64bGemmParams {
     // reads it back with K segments k[0], k[0], k[1] and writes row row_tok[r] of final_out.
     const int32_t* rowmap[2];
     int32_t tri_col[3];
-    const int32_t* row_tok;
+    const int32_t* row_tok;    // pair-order row -> token | (bit 30: the token's route 1 sits in K segment 0)
+    int32_t tri_scaled;        // one-accumulator form: GEMM1 multiplies the SwiGLU rows by tri_mul (powers of two: exact)
+    float tri_mul[3];          // w_0 * rs, w_1 * rs (by ROUTE, bit 31 of rowmap), ss
     // bring-up instrumentation (env I64B_DEBUG_FLAGS / I64B_DEBUG_TIMELINE; never set in production)
     uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores
     long long* debug_timeline; // [grid, 8] clock64 offsets per CTA
@@ -64,13 +66,15 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
 
 // Fused down projection + combine over the token-major layout (top-2 routed experts + optional shared expert), CTA
 // pairs, 256 x 256 tiles, two TMEM accumulators (the routed sum is folded back into the first one):
-//   out[row_tok[r]] = rs * (w0 * A[r, 0:I] · W2[e0]^T + w1 * A[r, I:2I] · W2[e1]^T) + ss * A[r, 2I:2I+S] · W2s^T
+//   out[row_tok[r]] = rs * (wa * A[r, 0:I] · W2[ea]^T + wb * A[r, I:2I] · W2[eb]^T) + ss * A[r, 2I:2I+S] · W2s^T
 // in the reference's fp32 operation order (layers/token_routed_mlp.py:156-185).  tmA: [N, 2I+S] (128-row boxes);
-// tmB0 / tmB1: routed / shared down-projection weights with 128-row boxes; p.groups: one group per expert pair
-// (w_row_base = e0*H, pad0 = e1*H); p.k[0] = I, p.k[1] = S (0: no shared expert).  max_units: upper bound on the number of
+// tmB0 / tmB1: routed / shared down-projection weights with 128-row boxes; p.groups: one group per UNORDERED expert pair
+// ea <= eb (w_row_base = ea*H, pad0 = eb*H); (wa, wb) = (w0, w1), swapped for the rows whose route 0 is eb; p.k[0] = I, p.k[1] = S (0: no shared expert).  max_units: upper bound on the number of
 // 256-row units.
-int i64b_launch_gemm_tri(bool is_int8, const CUtensorMap& tmA, const CUtensorMap& tmB0, const CUtensorMap& tmB1,
-                         const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
+// one_acc: the scales are already in the rows of A (GEMM1 epilogue, tri_mul — every factor a power of two), the three
+// segments accumulate into ONE TMEM accumulator and the two accumulators alternate between tiles.
+int i64b_launch_gemm_tri(bool is_int8, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
+                         const CUtensorMap& tmB1, const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
 
 int i64b_num_sms();
 int i64b_set_gemm_cta_limit(int limit);      // thread-local; returns the previous value

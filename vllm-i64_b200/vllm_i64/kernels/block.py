@@ -148,6 +148,10 @@ class I64Block:
     def fuses_combine(self, n: int) -> bool:
         return bool(_C.lib().i64b_moe_fuses_combine(self._h, int(n)))
 
+    def tri_form(self, n: int) -> int:
+        """0: GEMM2 + combine; 1: fused down projection, three accumulators; 2: one accumulator (power-of-two scales)."""
+        return int(_C.lib().i64b_moe_tri_form(self._h, int(n)))
+
     def forward_routed(self, x: torch.Tensor, routes: torch.Tensor, route_weights: Sequence[float],
                        routed_scale: float = 1.0, shared_scale: float = 1.0, use_shared: bool = False,
                        out_dtype=torch.bfloat16) -> torch.Tensor:
