@@ -279,8 +279,8 @@ enum {
                                      form (scales folded into the SwiGLU rows, one sum over K = 2*I_e + S) would be taken */
 };
 /* auto selection of the fused down projection: at least this many tokens per unordered expert pair, E(E-1)/2 pairs */
-#define I64B_TRI_MIN_ROWS_ONEACC 192
-#define I64B_TRI_MIN_ROWS_FOLD 384
+#define I64B_TRI_MIN_ROWS_ONEACC 288
+#define I64B_TRI_MIN_ROWS_FOLD 512
 int i64b_moe_set_debug(i64b_layer* layer, int flags);
 
 /* Cross-layer weight prefetch (decode).  `next` is the layer the engine runs after `layer` (the decoder stack calls
