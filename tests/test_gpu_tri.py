@@ -141,3 +141,71 @@ def test_tri_is_selected_for_tall_pair_groups():
     blk = Hh.build_gpu_block(cfg, w, table, "bf16")
     assert lib.i64b_moe_tri_form(blk._h, pairs * _C.TRI_MIN_ROWS_FOLD) == 1
     assert lib.i64b_moe_tri_form(blk._h, pairs * _C.TRI_MIN_ROWS_FOLD - 1) == 0
+
+
+# ---- W8A8: int8 operands, int32 accumulators, per-segment dequant in the epilogues — bit-exact with the chain AND the oracle
+W8_CASES = [
+    dict(id="small", shape=(256, 4, 128, 128, 1000, 2), n=700),
+    dict(id="zipf", shape=(256, 8, 128, 256, 5000, 2), n=3001, zipf=True),
+    dict(id="collisions-95-05", shape=(512, 4, 256, 128, 1000, 2), n=901, collide=3, pw=0.95),
+    dict(id="config5-8k", shape=(1024, 8, 512, 1280, 32000, 2), n=8192, sample=48),
+]
+
+
+@pytest.mark.parametrize("case", W8_CASES, ids=[c["id"] for c in W8_CASES])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+def test_tri_w8a8_bit_exact(case, out_dtype):
+    h, e, ie, s, v, k = case["shape"]
+    n = case["n"]
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=5, zipf=case.get("zipf", False), pw=case.get("pw", 0.5))
+    if case.get("collide"):
+        table = np.array(table, copy=True)
+        table[1, ::case["collide"]] = table[0, ::case["collide"]]
+    wq = O.quantize_moe_weights(w)
+    xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
+    chain = Hh.build_gpu_block(cfg, w, table, "int8", wq)
+    chain.set_debug(_C.DEBUG_NO_TRI)
+    tri = Hh.build_gpu_block(cfg, w, table, "int8", wq)
+    tri.set_debug(_C.DEBUG_TRI)
+    assert chain.tri_form(n) == 0 and tri.tri_form(n) == 1
+    want = chain.forward(xg, ig, out_dtype)
+    got = tri.forward(xg, ig, out_dtype)
+    again = tri.forward(xg, ig, out_dtype)
+    torch.cuda.synchronize()
+    assert torch.equal(got, again), "not run-to-run identical"
+    bad = (got != want).any(dim=1).nonzero().flatten()
+    assert bad.numel() == 0, f"{bad.numel()} of {n} rows differ from the W8A8 chain, first {bad[:8].tolist()}"
+    if out_dtype == torch.float32:
+        sample = case.get("sample")
+        rows = np.arange(n) if not sample else np.unique(np.linspace(0, n - 1, sample).astype(int))
+        ref = O.moe_block_w8a8(x[rows], ids[rows], table, wq, cfg)
+        assert np.array_equal(got.cpu().numpy()[rows], ref), "W8A8 fused down projection is not bit-exact with the oracle"
+
+
+def test_tri_w8a8_preq_and_graph_replay():
+    """x_preq rows (int8 + scale from the fused RMSNorm+quant) through the token-major path, captured and replayed."""
+    h, e, ie, s, v, k = W8_CASES[0]["shape"]
+    n = 1500
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=6)
+    wq = O.quantize_moe_weights(w)
+    xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
+    tri = Hh.build_gpu_block(cfg, w, table, "int8", wq)
+    tri.set_debug(_C.DEBUG_TRI)
+    want = tri.forward(xg, ig, torch.float32)
+    xq, xs = O.quantize_rows_int8(x)
+    got = tri.forward_preq(Hh.to_cuda(xq), Hh.to_cuda(xs), ig, torch.float32)
+    assert torch.equal(got, want)
+    out = torch.empty_like(want)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        tri.forward(xg, ig, torch.float32, out=out)
+    st.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=st):
+        tri.forward(xg, ig, torch.float32, out=out)
+    out.zero_()
+    g.replay()
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+    assert np.array_equal(want.cpu().numpy(), O.moe_block_w8a8(x, ids, table, wq, cfg))

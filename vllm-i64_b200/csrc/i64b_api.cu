@@ -76,6 +76,7 @@ struct i64b_layer {
         int32_t *q14_r, *q14_s, *amax_r, *amax_s;
         int amax_ld_r, amax_ld_s;
         I64bTriWs tri;          // token-major layout (fused down projection)
+        float* cat_scale;       // W8A8 token-major layout: [3, N] scales of the re-quantised intermediates by pair-order row
         size_t bytes;
     } cv;
     CUtensorMap tm_cat;         // [N, 2I+S] token-major intermediates over inter_r | inter_s (valid with cached_ws)
@@ -141,6 +142,7 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
         const bool tri_shape = c.top_k == 2 && c.num_experts >= 1 && c.num_experts * c.num_experts <= I64B_MAX_EXPERTS;
         cv.tri = i64b_tri_ws_carve(p ? p + off : nullptr, tri_shape ? n : 0, c.top_k, tri_shape ? c.num_experts : 1);
         off += align256(cv.tri.bytes);
+        cv.cat_scale = reinterpret_cast<float*>(take(q && tri_shape ? sizeof(float) * 3 * nn : 0));
     }
     cv.bytes = off;
     return cv;
@@ -400,7 +402,7 @@ static bool is_pow2(float v) {
 }
 static bool tri_one_acc(const i64b_layer* L, const i64b_moe_config& c) {
     static const int mode = getenv("I64B_TRI_ONEACC") ? atoi(getenv("I64B_TRI_ONEACC")) : -1;
-    if (mode == 0 || (L->debug & I64B_DEBUG_TRI_FOLD)) return false;
+    if (mode == 0 || (L->debug & I64B_DEBUG_TRI_FOLD) || c.mode != I64B_MODE_BF16) return false;
     for (int k = 0; k < c.top_k; ++k)
         if (!is_pow2(c.route_weight[k])) return false;
     return is_pow2(c.routed_scale) && (c.shared_inter == 0 || is_pow2(c.shared_scale));
@@ -412,8 +414,14 @@ static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t 
     static const int mode = getenv("I64B_TRI") ? atoi(getenv("I64B_TRI")) : -1;
     static const int min_rows = getenv("I64B_TRI_MIN_ROWS") ? atoi(getenv("I64B_TRI_MIN_ROWS")) : 0;
     const int E = c.num_experts;
-    if (mode == 0 || !plain_call || c.mode != I64B_MODE_BF16 || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
+    if (mode == 0 || !plain_call || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
     if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 256 != 0) return false;
+    if (c.mode == I64B_MODE_W8A8) {     // int8 rows of 128 elements per k-block, a shared expert, rows the re-quantiser holds in registers
+        static const int w8 = getenv("I64B_TRI_W8A8") ? atoi(getenv("I64B_TRI_W8A8")) : 1;
+        if (!w8 || c.shared_inter <= 0 || c.expert_inter % 128 != 0 || c.shared_inter % 128 != 0 || c.expert_inter > 1536 ||
+            c.shared_inter > 1536)
+            return false;
+    }
     if (L->debug & (I64B_DEBUG_KEEP_TAPS | I64B_DEBUG_FUSE_COMBINE | I64B_DEBUG_NO_TRI)) return false;
     if (mode == 1 || (L->debug & I64B_DEBUG_TRI)) return true;
     const int64_t pairs = (int64_t)E * (E - 1) / 2;
@@ -500,8 +508,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         } else {
             L->tm_inter_s = L->tm_inter_r;
         }
-        if (E > 0 && K == 2 && !q) {
-            rc = i64b_encode_tmap(&L->tm_cat, cv.inter_r, false, n, 2 * I + S, (int64_t)(2 * I + S) * 2, 128);
+        if (E > 0 && K == 2 && (2 * I + S) * L->elt % 16 == 0) {
+            rc = i64b_encode_tmap(&L->tm_cat, cv.inter_r, q, n, 2 * I + S, (int64_t)(2 * I + S) * L->elt, 128);
             if (rc) return rc;
         }
         L->cached_ws = base;
@@ -625,7 +633,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.amax_ld[0] = cv.amax_ld_r;
         gp.amax_ld[1] = cv.amax_ld_s;
         gp.silu_lut = L->silu_lut;
-        if (tri) {      // SwiGLU rows go straight to their token's row of the [N, 2I+S] buffer
+        if (tri && !q) {      // SwiGLU rows go straight to their token's row of the [N, 2I+S] buffer
             gp.out[0] = gp.out[1] = cv.inter_r;
             gp.ld_out[0] = gp.ld_out[1] = 2 * I + S;
             gp.rowmap[0] = cv.tri.rowmap;
@@ -652,9 +660,10 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         }
         if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
             rc = i64b_run_requant_q14(cv.q14_r, cv.amax_r, cv.amax_ld_r, ((I + bn - 1) / bn) * nh,
-                                      reinterpret_cast<int8_t*>(cv.inter_r), cv.inter_scale_r, E > 0 ? R : 0, I,
+                                      reinterpret_cast<int8_t*>(cv.inter_r), tri ? cv.cat_scale : cv.inter_scale_r, E > 0 ? R : 0, I,
                                       cv.q14_s, cv.amax_s, cv.amax_ld_s, ((S + bn - 1) / bn) * nh,
-                                      reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, S > 0 ? n : 0, S, s);
+                                      reinterpret_cast<int8_t*>(cv.inter_s), cv.inter_scale_s, S > 0 ? n : 0, S, s, nullptr, 0,
+                                      tri ? &cv.tri : nullptr);
             if (rc) return rc;
         }
     }
@@ -673,9 +682,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.final_dtype = out_dtype;
         gp.ld_final = H;
         gp.row_tok = cv.tri.tok;
+        gp.n_tokens = (int32_t)n;
+        gp.row_scale[0] = cv.cat_scale;         // W8A8: [3, N] by pair-order row
+        gp.col_scale[0] = L->w2r_scale;
+        gp.col_scale[1] = L->w2s_scale;
         const int64_t units = n / 256 + (int64_t)E * E;
         if (o.stage_mask & I64B_STAGE_GEMM2) {
-            rc = i64b_launch_gemm_tri(false, tri_one_acc(L, c), L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp,
+            rc = i64b_launch_gemm_tri(q, tri_one_acc(L, c), L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp,
                                       units * ((H + 255) / 256), s);
             if (rc) return rc;
         }

@@ -87,6 +87,9 @@ __device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ void st_f32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" :: "r"(addr), "f"(v) : "memory");
+}
 __device__ __forceinline__ int ld_shared_s16(uint32_t addr) {
     int v;
     asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(addr));
@@ -799,15 +802,21 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 // block output is ONE sum over K = 2*I_e + S: the three segments accumulate into the same TMEM accumulator, the two
 // 256-column accumulators alternate between tiles (tile i+1's MMAs run under tile i's epilogue, as in i64b_gemm_kernel),
 // and the epilogue is a plain scattered store.  Same products, one fp32 accumulation instead of three partial sums.
+//
+// kInt8 (W8A8, three-accumulator form only): int8 operands, int32 accumulators; the epilogues dequantise every segment with
+// its own per-row (re-quantised intermediate) and per-column (down-projection out-feature) scales,
+// y = float(acc) * (s_row * s_col) as GEMM2's dequant epilogue does (core/quantization.py:173), then combine in the same
+// order — bit-identical to the W8A8 chain and to the oracle.  The folded routed sum goes back into acc0 as fp32 bits.
 constexpr int kTriN = 256;
-template <bool kOneAcc>
+template <bool kOneAcc, bool kInt8>
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
                      const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ I64bGemmParams p) {
     using Cfg = StageCfg<kTriN, 2>;
     constexpr int kStages = Cfg::kStages;
     constexpr int kStageB = Cfg::kStageB;              // this CTA's 128 weight rows
-    constexpr int kBlockK = 64;
+    constexpr int kBlockK = kInt8 ? 128 : 64;          // elements per 128-byte row
+    static_assert(!(kOneAcc && kInt8), "W8A8 segments carry their own scales: no shared accumulator");
     constexpr uint32_t kTmemCols = 512;                // acc0 | acc1
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -897,7 +906,7 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc = make_idesc<false, kTriN, 2>();
+            constexpr uint32_t idesc = make_idesc<kInt8, kTriN, 2>();
             int stage = 0, iter = 0;
             uint32_t phase = 0;
             for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
@@ -921,8 +930,10 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         const uint64_t b_desc = make_sw128_kmajor_desc(sB + stage * kStageB);
                         const int fresh = kOneAcc ? (seg | kb) : kb;             // 0: the first MMA overwrites the accumulator
 #pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
+                        for (int k = 0; k < 4; ++k) {
+                            if constexpr (kInt8) umma_i8_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
+                            else umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
+                        }
                         umma_commit_cta2(&empty_bar[stage]);
                         if (kb == nkb - 1) {
                             if constexpr (kOneAcc) {
@@ -943,6 +954,7 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         constexpr int kColsW = kTriN / 2;
         const int cbase = h * kColsW;
         const uint32_t st_addr = smem_u32(stage_base + (warp - 2) * kEpiWarpBytes);
+        [[maybe_unused]] const uint32_t ws_addr = st_addr + kStageWarpBytes;
         const bool f32out = p.final_dtype == I64B_F32;
         const int fsz = f32out ? 4 : 2;
         const float w0 = p.w[0], w1 = p.w[1], rs = p.routed_scale, ss = p.shared_scale;
@@ -977,10 +989,31 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             const int colw0 = tc.n_t * kTriN + cbase;
             int64_t my_off = 0;
             float wa = w0, wb = w1;         // weights of K segments 0 / 1 for this row (bit 30 of row_tok: route 1 sits in segment 0)
+            [[maybe_unused]] float rsa = 0.0f, rsb = 0.0f, rsS = 0.0f;      // W8A8: this row's activation scales per segment
             if (valid) {
                 const int rt = __ldg(p.row_tok + grp.row_start + row_in_group);
                 my_off = ((int64_t)(rt & 0x3FFFFFFF) * p.ld_final + colw0) * fsz;
                 if (rt & 0x40000000) { wa = w1; wb = w0; }
+                if constexpr (kInt8) {
+                    const float* sc = p.row_scale[0] + grp.row_start + row_in_group;     // [3, n_tokens] by pair-order row
+                    rsa = __ldg(sc);
+                    rsb = __ldg(sc + p.n_tokens);
+                    rsS = __ldg(sc + 2 * (int64_t)p.n_tokens);
+                }
+            }
+            if constexpr (kInt8) {
+                // column scales of this warp's 128 columns: segments 0 / 1 into the (idle until epilogue 2) store staging
+                // block, the shared expert's into the scale block
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < kColsW / 32; ++i) {
+                    const int c = i * 32 + lane;
+                    const bool cv = colw0 + c < grp.n_out;
+                    st_f32(st_addr + c * 4, cv ? __ldg(p.col_scale[0] + grp.w_row_base + colw0 + c) : 0.0f);
+                    st_f32(st_addr + (kColsW + c) * 4, cv ? __ldg(p.col_scale[0] + grp.pad0 + colw0 + c) : 0.0f);
+                    st_f32(ws_addr + c * 4, cv ? __ldg(p.col_scale[1] + colw0 + c) : 0.0f);
+                }
+                __syncwarp();
             }
             if constexpr (kOneAcc) {
                 mbar_wait(&tfull_bar[par], ((uint32_t)iter >> 1) & 1u);
@@ -1008,6 +1041,23 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 tmem_ld_32x32(t1 + c, a1);
                 tmem_ld_wait();
 #pragma unroll
+                if constexpr (kInt8) {
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 sa4 = ld_shared_f4(st_addr + (c + j4 * 4) * 4);
+                        const float4 sb4 = ld_shared_f4(st_addr + (kColsW + c + j4 * 4) * 4);
+                        const float sav[4] = {sa4.x, sa4.y, sa4.z, sa4.w};
+                        const float sbv[4] = {sb4.x, sb4.y, sb4.z, sb4.w};
+#pragma unroll
+                        for (int jj = 0; jj < 4; ++jj) {
+                            const int j = j4 * 4 + jj;
+                            // result_i32.float() * (x_scale * w_scale)                      core/quantization.py:173
+                            a0[j] = __float_as_uint(__fmul_rn((float)(int)a0[j], __fmul_rn(rsa, sav[jj])));
+                            a1[j] = __float_as_uint(__fmul_rn((float)(int)a1[j], __fmul_rn(rsb, sbv[jj])));
+                        }
+                    }
+                }
+#pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     float o = __fmul_rn(wa, __uint_as_float(a0[j]));          // a + b == b + a: same bits as w0*y0 + w1*y1
                     o = __fadd_rn(o, __fmul_rn(wb, __uint_as_float(a1[j])));
@@ -1029,6 +1079,17 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     tmem_ld_32x32(t0 + c, a0);
                     tmem_ld_32x32(t1 + c, a1);
                     tmem_ld_wait();
+#pragma unroll
+                    if constexpr (kInt8) {
+#pragma unroll
+                        for (int j4 = 0; j4 < 8; ++j4) {
+                            const float4 s4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
+                            const float sv[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                            for (int jj = 0; jj < 4; ++jj)
+                                a1[j4 * 4 + jj] = __float_as_uint(__fmul_rn((float)(int)a1[j4 * 4 + jj], __fmul_rn(rsS, sv[jj])));
+                        }
+                    }
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
                         a0[j] = __float_as_uint(__fadd_rn(__uint_as_float(a0[j]), __fmul_rn(ss, __uint_as_float(a1[j]))));
@@ -1201,19 +1262,23 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
 int i64b_launch_gemm_tri(bool is_int8, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
                          const CUtensorMap& tmB1, const I64bGemmParams& p, int64_t max_units, cudaStream_t stream) {
     if (max_units <= 0) return I64B_OK;
-    I64B_CHECK(!is_int8, I64B_ERR_ARG, "the fused down projection is bf16 only");
+    I64B_CHECK(!(is_int8 && one_acc), I64B_ERR_ARG, "the single-accumulator form is bf16 only");
+    I64B_CHECK(!is_int8 || (p.k[1] > 0 && p.k[0] % 128 == 0 && p.k[1] % 128 == 0 && p.row_scale[0] && p.col_scale[0] &&
+                            p.col_scale[1]), I64B_ERR_ARG, "W8A8 fused down projection: shared expert, K %% 128 == 0 and scales");
     I64B_CHECK(p.groups != nullptr && p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
                p.num_groups);
     I64B_CHECK(p.k[0] > 0 && p.k[0] % 64 == 0 && p.k[1] >= 0 && p.k[1] % 64 == 0, I64B_ERR_ARG,
                "K segments must be multiples of 64 (got %d, %d)", p.k[0], p.k[1]);
     I64B_CHECK(p.row_tok && p.final_out, I64B_ERR_ARG, "null pointer");
     constexpr int smem = StageCfg<kTriN, 2>::kSmem;
-    auto kern = one_acc ? i64b_gemm_tri_kernel<true> : i64b_gemm_tri_kernel<false>;
-    static bool configured[2][I64B_MAX_DEVICES] = {};
+    auto kern = is_int8 ? i64b_gemm_tri_kernel<false, true>
+                        : (one_acc ? i64b_gemm_tri_kernel<true, false> : i64b_gemm_tri_kernel<false, false>);
+    static bool configured[3][I64B_MAX_DEVICES] = {};
     const int dev = i64b_current_device();
-    if (!configured[one_acc ? 1 : 0][dev]) {
+    const int which = is_int8 ? 2 : (one_acc ? 1 : 0);
+    if (!configured[which][dev]) {
         I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured[one_acc ? 1 : 0][dev] = true;
+        configured[which][dev] = true;
     }
     int sms = i64b_num_sms();
     if (g_gemm_cta_limit > 0 && g_gemm_cta_limit < sms) sms = g_gemm_cta_limit >= 2 ? g_gemm_cta_limit : 2;

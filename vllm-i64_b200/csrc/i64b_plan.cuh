@@ -84,7 +84,11 @@ int i64b_run_dispatch(const I64bDispatchArgs& a, const I64bPlanWs& ws, cudaStrea
 int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_ld, int n_tiles, int8_t* out,
                          float* scale, int64_t rows, int cols, const int32_t* q14_b, const int32_t* amax_part_b,
                          int amax_ld_b, int n_tiles_b, int8_t* out_b, float* scale_b, int64_t rows_b, int cols_b,
-                         cudaStream_t stream, const I64bGroup* groups = nullptr, int num_groups = 0);
+                         cudaStream_t stream, const I64bGroup* groups = nullptr, int num_groups = 0,
+                         const struct I64bTriWs* tri = nullptr);
+// `tri` (W8A8 fused down projection): the int8 rows go to the token-major [rows_b, 2*cols + cols_b] buffer `out` (routed
+// row r -> row tri->rowmap[r], K segment = its bit 30; shared row t -> row tri->pos[t], last segment) and the scales to
+// `scale` as [3, rows_b] by pair-order row; out_b / scale_b are ignored
 // `groups` (device): the first row set is the rows of these GEMM groups instead of rows [0, rows) — `rows` is then only
 // an upper bound used to size the grid
 
