@@ -209,3 +209,37 @@ def test_tri_w8a8_preq_and_graph_replay():
     torch.cuda.synchronize()
     assert torch.equal(out, want)
     assert np.array_equal(want.cpu().numpy(), O.moe_block_w8a8(x, ids, table, wq, cfg))
+
+
+@pytest.mark.parametrize("form", ["chain", "one_acc"])
+def test_dispatch_copy_overlap_is_bit_identical(form):
+    """From 4096 tokens on, the dispatch row copies run on the layer's second stream under the shared expert's GEMM1
+    (I64B_DEBUG_NO_OVERLAP keeps them on the caller's stream): same kernels, identical output; also inside a captured graph
+    and with the taps of the dispatched rows complete when the forward returns."""
+    n = 6000
+    cfg, w, table, ids, x = Hh.make_block(256, 4, 64, 128, 1000, 2, n, seed=3)
+    xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
+    flags = _C.DEBUG_NO_TRI if form == "chain" else _C.DEBUG_TRI
+    serial = Hh.build_gpu_block(cfg, w, table, "bf16")
+    serial.set_debug(flags | _C.DEBUG_NO_OVERLAP)
+    over = Hh.build_gpu_block(cfg, w, table, "bf16")
+    over.set_debug(flags)
+    want = serial.forward(xg, ig, torch.float32)
+    got = over.forward(xg, ig, torch.float32)
+    torch.cuda.synchronize()
+    assert torch.equal(got, want)
+    out = torch.empty_like(want)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        over.forward(xg, ig, torch.float32, out=out)
+    st.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=st):
+        over.forward(xg, ig, torch.float32, out=out)
+        over.forward(xg, ig, torch.float32, out=out)
+    out.zero_()
+    g.replay()
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+    Hh.assert_close(got.cpu().numpy(), O.moe_block_fp32(x, ids, table, w, cfg, inter_bf16=True), "overlap")

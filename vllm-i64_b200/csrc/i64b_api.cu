@@ -80,7 +80,26 @@ struct i64b_layer {
         size_t bytes;
     } cv;
     CUtensorMap tm_cat;         // [N, 2I+S] token-major intermediates over inter_r | inter_s (valid with cached_ws)
+    // second stream of the layer: the dispatch row copies run there, under the shared expert's GEMM1 (overlap_copy())
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
+
+// The bf16 prefill-sized forward hides its one pure-HBM pass — the dispatch row copies — under the shared expert's GEMM1,
+// which reads the caller's x and needs only the dispatch INDICES: indices on the main stream, copies on the layer's second
+// stream, shared-expert GEMM1 tiles first, routed tiles after the join.  Same kernels, same results.  I64B_OVERLAP=0 turns
+// it off; the streams and events are made at weight load (nothing is created on the forward path).
+static bool overlap_enabled() {
+    static const bool on = !(getenv("I64B_OVERLAP") && atoi(getenv("I64B_OVERLAP")) == 0);
+    return on;
+}
+static int ensure_side_stream(i64b_layer* L) {
+    if (L->side != nullptr || !overlap_enabled()) return I64B_OK;
+    I64B_CUDA(cudaStreamCreateWithFlags(&L->side, cudaStreamNonBlocking));
+    I64B_CUDA(cudaEventCreateWithFlags(&L->ev_fork, cudaEventDisableTiming));
+    I64B_CUDA(cudaEventCreateWithFlags(&L->ev_join, cudaEventDisableTiming));
+    return I64B_OK;
+}
 
 static int w13_rows(const i64b_moe_config& c) { return c.num_experts * 2 * c.expert_inter + 2 * c.shared_inter; }
 
@@ -252,7 +271,13 @@ int i64b_moe_create(const i64b_moe_config* cfg, i64b_layer** out) {
     return I64B_OK;
 }
 
-void i64b_moe_destroy(i64b_layer* layer) { delete layer; }
+void i64b_moe_destroy(i64b_layer* layer) {
+    if (layer == nullptr) return;
+    if (layer->ev_fork) cudaEventDestroy(layer->ev_fork);
+    if (layer->ev_join) cudaEventDestroy(layer->ev_join);
+    if (layer->side) cudaStreamDestroy(layer->side);
+    delete layer;
+}
 
 int i64b_moe_set_scales(i64b_layer* L, const float* route_weight, int top_k, float routed_scale, float shared_scale) {
     I64B_CHECK(L && route_weight && top_k == L->cfg.top_k, I64B_ERR_ARG, "bad set_scales arguments");
@@ -303,6 +328,8 @@ int i64b_moe_load_bf16(i64b_layer* L, const void* gate, const void* up, const vo
     }
     I64B_CUDA(cudaMemsetAsync(L->sync, 0, sizeof(int) * I64B_SYNC_INTS, s));
     int rc = encode_weight_maps(L);
+    if (rc) return rc;
+    rc = ensure_side_stream(L);
     if (rc) return rc;
     L->loaded = true;
     L->cached_ws = nullptr;
@@ -601,7 +628,20 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.dest_row_out = cv.dest_row;
     da.tri = tri ? 1 : 0;
     da.tw = cv.tri;
-    if (o.stage_mask & I64B_STAGE_DISPATCH) {
+    // prefill-sized bf16 blocks with a shared expert: the row copies leave the main stream (see overlap_enabled())
+    static const int overlap_min = env_int("I64B_OVERLAP_MIN_TOKENS", 4096);
+    const bool overlap = L->side != nullptr && !(L->debug & I64B_DEBUG_NO_OVERLAP) && !q && E > 0 && S > 0 && shared_from_x && o.stage_mask == 0xFFu && n >= overlap_min;
+    if (overlap) {
+        da.phase = 1;
+        rc = i64b_run_dispatch(da, cv.plan, s);
+        if (rc) return rc;
+        I64B_CUDA(cudaEventRecord(L->ev_fork, s));
+        I64B_CUDA(cudaStreamWaitEvent(L->side, L->ev_fork, 0));
+        da.phase = 2;
+        rc = i64b_run_dispatch(da, cv.plan, L->side);
+        if (rc) return rc;
+        I64B_CUDA(cudaEventRecord(L->ev_join, L->side));
+    } else if (o.stage_mask & I64B_STAGE_DISPATCH) {
         rc = i64b_run_dispatch(da, cv.plan, s);
         if (rc) return rc;
     }
@@ -653,7 +693,19 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         const bool pairs = use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0));
         const int64_t tiles = pairs ? pt_r * ((I + bn - 1) / bn) + pt_s * ((S + bn - 1) / bn)
                                     : mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
-        if (o.stage_mask & I64B_STAGE_GEMM1) {
+        if (overlap) {      // the shared expert's tiles first (they read x), the routed ones once the row copies have landed
+            const int64_t tiles_s = (pairs ? pt_s : mt_s) * ((S + bn - 1) / bn);
+            I64bGemmParams gs = gp;
+            gs.groups = cv.plan.groups1 + E;
+            gs.num_groups = 1;
+            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_x, L->tm_w13[wi], L->tm_w13[wi], gs, tiles_s, s);
+            if (rc) return rc;
+            I64B_CUDA(cudaStreamWaitEvent(s, L->ev_join, 0));
+            gp.num_groups = E;
+            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, L->tm_x, L->tm_w13[wi], L->tm_w13[wi], gp,
+                                  tiles - tiles_s, s);
+            if (rc) return rc;
+        } else if (o.stage_mask & I64B_STAGE_GEMM1) {
             rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, shared_from_x ? L->tm_x : L->tm_xs,
                                   L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
             if (rc) return rc;

@@ -74,6 +74,9 @@ struct I64bDispatchArgs {
     int32_t* scatter_idx_out;   // [K, N]
     int32_t* dest_row_out;      // [K, N]
     int tri;                    // 1: also fill tw.pos / tw.tok / tw.rowmap (token-major layout, top_k == 2)
+    int phase;                  // 0: indices and rows in one launch; 1: the index outputs only (routes / dest rows / token-major
+                                // maps); 2: the row copies only — the copy then runs on a second stream under the shared expert's
+                                // GEMM1, which needs the indices but not the dispatched rows
     I64bTriWs tw;
 };
 int i64b_run_dispatch(const I64bDispatchArgs& a, const I64bPlanWs& ws, cudaStream_t stream);
