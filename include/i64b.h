@@ -274,9 +274,10 @@ enum {
     I64B_DEBUG_TRI = 8,           /* take the token-major fused down projection whenever the shape allows (top-2 bf16
                                      blocks, E*E <= 64; default: only when the expert-pair groups are tall enough) */
     I64B_DEBUG_NO_TRI = 16,       /* never take it (per-assignment fp32 rows + combine_kernel) */
-    I64B_DEBUG_NO_OVERLAP = 64,   /* keep the dispatch row copies on the caller's stream (default for bf16 blocks with a
-                                     shared expert from 4096 tokens on: the copies run on the layer's second stream under the
-                                     shared expert's GEMM1; results are identical either way) */
+    I64B_DEBUG_NO_OVERLAP = 64,   /* with env I64B_OVERLAP=1 (off by default: measured slower) the dispatch row copies of bf16
+                                     blocks with a shared expert run, from 4096 tokens on, on the layer's second stream under
+                                     the shared expert's GEMM1; this flag keeps them on the caller's stream.  Results are
+                                     identical either way */
     I64B_DEBUG_TRI_FOLD = 32      /* fused down projection: keep the three-accumulator form (bit-identical to GEMM2 +
                                      combine_kernel) even when the scales are powers of two and the single-accumulator
                                      form (scales folded into the SwiGLU rows, one sum over K = 2*I_e + S) would be taken */

@@ -8,6 +8,8 @@ combine in ONE kernel, no fp32 per-assignment rows in memory.  Two forms:
 Cases: small and config-5 geometry, no shared expert, skewed ids (empty / tiny / huge pair groups), both orders of a pair
 and colliding routes (e0 == e1), token counts that are not a multiple of any tile, both output dtypes, unequal route
 weights, scales other than 1, graph replay."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -211,11 +213,12 @@ def test_tri_w8a8_preq_and_graph_replay():
     assert np.array_equal(want.cpu().numpy(), O.moe_block_w8a8(x, ids, table, wq, cfg))
 
 
+@pytest.mark.skipif(os.environ.get("I64B_OVERLAP", "0") in ("", "0"), reason="opt-in path: run with I64B_OVERLAP=1 (measured slower, off by default)")
 @pytest.mark.parametrize("form", ["chain", "one_acc"])
 def test_dispatch_copy_overlap_is_bit_identical(form):
-    """From 4096 tokens on, the dispatch row copies run on the layer's second stream under the shared expert's GEMM1
-    (I64B_DEBUG_NO_OVERLAP keeps them on the caller's stream): same kernels, identical output; also inside a captured graph
-    and with the taps of the dispatched rows complete when the forward returns."""
+    """With I64B_OVERLAP=1, from 4096 tokens on, the dispatch row copies run on the layer's second stream under the shared
+    expert's GEMM1 (I64B_DEBUG_NO_OVERLAP keeps them on the caller's stream): same kernels, identical output, also inside a
+    captured graph."""
     n = 6000
     cfg, w, table, ids, x = Hh.make_block(256, 4, 64, 128, 1000, 2, n, seed=3)
     xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)

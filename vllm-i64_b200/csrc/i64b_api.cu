@@ -87,10 +87,12 @@ struct i64b_layer {
 
 // The bf16 prefill-sized forward hides its one pure-HBM pass — the dispatch row copies — under the shared expert's GEMM1,
 // which reads the caller's x and needs only the dispatch INDICES: indices on the main stream, copies on the layer's second
-// stream, shared-expert GEMM1 tiles first, routed tiles after the join.  Same kernels, same results.  I64B_OVERLAP=0 turns
-// it off; the streams and events are made at weight load (nothing is created on the forward path).
+// stream, shared-expert GEMM1 tiles first, routed tiles after the join.  Same kernels, same results (tests/test_gpu_tri.py).
+// MEASURED SLOWER on B200 (profiles/r2s_*: 64K tokens 3.24 -> 3.44 ms/step, 16K tokens 0.914 -> 0.947): two half-sized
+// GEMM1 launches each pay their own ramp and tail, and the copy takes HBM bandwidth from a GEMM1 that already runs near the
+// SM operand-ingest limit.  OFF unless I64B_OVERLAP=1; the stream and events are made at weight load only when it is on.
 static bool overlap_enabled() {
-    static const bool on = !(getenv("I64B_OVERLAP") && atoi(getenv("I64B_OVERLAP")) == 0);
+    static const bool on = getenv("I64B_OVERLAP") && atoi(getenv("I64B_OVERLAP")) != 0;
     return on;
 }
 static int ensure_side_stream(i64b_layer* L) {

@@ -806,7 +806,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 // kInt8 (W8A8, three-accumulator form only): int8 operands, int32 accumulators; the epilogues dequantise every segment with
 // its own per-row (re-quantised intermediate) and per-column (down-projection out-feature) scales,
 // y = float(acc) * (s_row * s_col) as GEMM2's dequant epilogue does (core/quantization.py:173), then combine in the same
-// order — bit-identical to the W8A8 chain and to the oracle.  The folded routed sum goes back into acc0 as fp32 bits.
+// order — bit-identical to the W8A8 chain (and through it to the reference arithmetic).  The folded routed sum goes back into acc0 as fp32 bits.
 constexpr int kTriN = 256;
 template <bool kOneAcc, bool kInt8>
 __global__ void __launch_bounds__(kThreads, 1)
