@@ -246,3 +246,31 @@ def test_dispatch_copy_overlap_is_bit_identical(form):
     torch.cuda.synchronize()
     assert torch.equal(out, want)
     Hh.assert_close(got.cpu().numpy(), O.moe_block_fp32(x, ids, table, w, cfg, inter_bf16=True), "overlap")
+
+
+@pytest.mark.parametrize("form", ["chain", "one_acc", "fold"])
+@pytest.mark.parametrize("n", [20000, 33001])
+def test_gemm1_row_gather_is_bit_identical(form, n):
+    """Blocks big enough for the CTA-pair GEMM1 make no dispatched copy: GEMM1's producer warp gathers the routed A rows from
+    x (tile::gather4 through the dispatch indices).  Same operands, same MMAs: identical output to the dispatched-copy path
+    (I64B_DEBUG_NO_GATHER), in every down-projection form, zipf ids included (ragged groups, empty tails)."""
+    cfg, w, table, ids, x = Hh.make_block(256, 8, 128, 256, 5000, 2, n, seed=3, zipf=(n % 2 == 1))
+    xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
+    flags = {"chain": _C.DEBUG_NO_TRI, "one_acc": _C.DEBUG_TRI, "fold": _C.DEBUG_TRI | _C.DEBUG_TRI_FOLD}[form]
+    copy = Hh.build_gpu_block(cfg, w, table, "bf16")
+    copy.set_debug(flags | _C.DEBUG_NO_GATHER)
+    gat = Hh.build_gpu_block(cfg, w, table, "bf16")
+    gat.set_debug(flags)
+    _C.launch_count_reset()
+    want = copy.forward(xg, ig, torch.float32)
+    torch.cuda.synchronize()
+    l_copy = _C.launch_count()
+    _C.launch_count_reset()
+    got = gat.forward(xg, ig, torch.float32)
+    again = gat.forward(xg, ig, torch.float32)
+    torch.cuda.synchronize()
+    assert _C.launch_count() == 2 * l_copy, "same number of launches (the dispatch launch writes indices only)"
+    assert torch.equal(got, want) and torch.equal(got, again)
+    rows = np.unique(np.linspace(0, n - 1, 96).astype(int))
+    ref = O.moe_block_fp32(x[rows], ids[rows], table, w, cfg, inter_bf16=True)
+    Hh.assert_close(got.cpu().numpy()[rows], ref, "gather")

@@ -67,10 +67,11 @@ struct i64b_layer {
     const void* cached_x = nullptr;   // fused decode kernel: maps over the caller's x
     int64_t cached_x_n = -1;
     CUtensorMap tm_x;
+    CUtensorMap tm_xg;          // the same x with a one-row box (tile::gather4 source of GEMM1's routed rows)
     // carve of the last forward (debug taps)
     struct Carve {
         I64bPlanWs plan;
-        int32_t *routes, *dest_row, *scatter_idx;
+        int32_t *routes, *dest_row, *scatter_idx, *src_tok;
         uint8_t *xs, *inter_r, *inter_s;
         float *xs_scale, *inter_scale_r, *inter_scale_s, *y;
         int32_t *q14_r, *q14_s, *amax_r, *amax_s;
@@ -143,6 +144,7 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
     cv.routes = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
     cv.dest_row = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
     cv.scatter_idx = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
+    cv.src_tok = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * R));
     cv.xs = take((size_t)T * c.hidden_size * L->elt);
     cv.xs_scale = reinterpret_cast<float*>(take(sizeof(float) * T));
     cv.inter_r = take((size_t)R * c.expert_inter * L->elt);
@@ -458,6 +460,8 @@ static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t 
     return n >= pairs * rows;
 }
 
+static int64_t mt_r_pre(int64_t R, int E) { return E > 0 ? R / 128 + E : 0; }
+
 static bool fused_enabled() {
     static const bool on = !(getenv("I64B_FUSED") && atoi(getenv("I64B_FUSED")) == 0);
     return on;
@@ -600,6 +604,11 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     if (shared_from_x && (L->cached_x != x || L->cached_x_n != n)) {
         int rcx = i64b_encode_tmap(&L->tm_x, x, preq, n, H, (int64_t)H * L->elt, 128);
         if (rcx) return rcx;
+        if (!q) {
+            static const int gbox = env_int("I64B_GATHER_BOX", 1);
+            rcx = i64b_encode_tmap(&L->tm_xg, x, false, n, H, (int64_t)H * 2, gbox);
+            if (rcx) return rcx;
+        }
         L->cached_x = x;
         L->cached_x_n = n;
     }
@@ -630,9 +639,17 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.dest_row_out = cv.dest_row;
     da.tri = tri ? 1 : 0;
     da.tw = cv.tri;
+    // bf16 blocks big enough for the pair kernel: no dispatched copy at all — GEMM1 gathers the routed rows from x
+    static const int gather_mode = env_int("I64B_GATHER", 1);
+    const bool gather = gather_mode != 0 && !(L->debug & I64B_DEBUG_NO_GATHER) && !q && E > 0 && S > 0 && shared_from_x &&
+                        o.stage_mask == 0xFFu && use_cta_pairs(256, T, E + 1) && pick_nmma(mt_r_pre(R, E), I, (n + 127) / 128, S, true, "I64B_GEMM1_NMMA") == 256;
+    if (gather) {
+        da.phase = 1;
+        da.src_tok_out = cv.src_tok;
+    }
     // prefill-sized bf16 blocks with a shared expert: the row copies leave the main stream (see overlap_enabled())
     static const int overlap_min = env_int("I64B_OVERLAP_MIN_TOKENS", 4096);
-    const bool overlap = L->side != nullptr && !(L->debug & I64B_DEBUG_NO_OVERLAP) && !q && E > 0 && S > 0 && shared_from_x && o.stage_mask == 0xFFu && n >= overlap_min;
+    const bool overlap = !gather && L->side != nullptr && !(L->debug & I64B_DEBUG_NO_OVERLAP) && !q && E > 0 && S > 0 && shared_from_x && o.stage_mask == 0xFFu && n >= overlap_min;
     if (overlap) {
         da.phase = 1;
         rc = i64b_run_dispatch(da, cv.plan, s);
@@ -693,6 +710,11 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         }
         const int wi = nmma_index(n_mma);
         const bool pairs = use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0));
+        if (gather) {
+            gp.gather_idx = cv.src_tok;
+            gp.gather_rows = (int32_t)R;
+            gp.n_tokens = (int32_t)n;
+        }
         const int64_t tiles = pairs ? pt_r * ((I + bn - 1) / bn) + pt_s * ((S + bn - 1) / bn)
                                     : mt_r * ((I + bn - 1) / bn) + mt_s * ((S + bn - 1) / bn);
         if (overlap) {      // the shared expert's tiles first (they read x), the routed ones once the row copies have landed
@@ -708,7 +730,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
                                   tiles - tiles_s, s);
             if (rc) return rc;
         } else if (o.stage_mask & I64B_STAGE_GEMM1) {
-            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, L->tm_xs, shared_from_x ? L->tm_x : L->tm_xs,
+            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, gather ? L->tm_xg : L->tm_xs, shared_from_x ? L->tm_x : L->tm_xs,
                                   L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
             if (rc) return rc;
         }

@@ -243,7 +243,7 @@ __device__ __forceinline__ void warp_combine_block(uint32_t st_addr, const uint3
     }
 }
 
-template <bool kInt8, bool kDual, int kNMma, int kCtas>
+template <bool kInt8, bool kDual, int kNMma, int kCtas, bool kGather = false>
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmB1,
@@ -336,7 +336,51 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     const int total_tiles = prefix[ng];
     if (tl && threadIdx.x == 0) tl[1] = clock64() - t0;
 
-    if (warp == 0) {
+    if (warp == 0 && kGather) {
+        // ------------------------------------------------------------------ TMA producer, routed A rows gathered from x
+        // (no dispatched copy): the whole warp runs the loop; per k-block lane l fetches rows 4l..4l+3 of the tile with one
+        // tile::gather4 (4 x 128 bytes, landing where a box load would have put them), lane 0 adds the weight half-tile.
+        static_assert(!kGather || (kCtas == 2 && kDual && !kInt8), "gather: bf16 GEMM1 pair kernel");
+        int stage = 0, g = 0;
+        uint32_t phase = 0;
+        for (int tile = unit0; tile < total_tiles; tile += unit_step) {
+            TileCoord tc;
+            decode_tile<kBnOut, kCtas>(tile, g, prefix, sg, tc, rank);
+            const I64bGroup grp = sg[tc.g];
+            const bool gat = grp.which == 0;
+            const int nkb = (p.k[grp.which] + kBlockK - 1) / kBlockK;
+            const int a_row = grp.row_start + tc.m_t * kBlockM;
+            const int b_row = grp.w_row_base + tc.n_t * kBnOut;
+            int ix[4] = {0, 0, 0, 0};
+            if (gat) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = a_row + 4 * lane + j;
+                    const int t = r < p.gather_rows ? __ldg(p.gather_idx + r) : 0;
+                    ix[j] = min(max(t, 0), p.n_tokens - 1);
+                }
+            }
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (lane == 0) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (kStageA + kStageB));
+                }
+                __syncwarp();
+                if (gat) {
+                    tma_gather4_cta2(sA + stage * kStageA + lane * 512, &tmA0, &full_bar[stage], kb * kBlockK, ix[0], ix[1],
+                                     ix[2], ix[3], I64B_L2_EVICT_NORMAL);
+                } else if (lane == 0) {
+                    tma_load_2d_cta2(sA + stage * kStageA, &tmA1, &full_bar[stage], kb * kBlockK, a_row, I64B_L2_EVICT_NORMAL);
+                }
+                if (lane == 0) {
+                    const int bh = b_row + rank * grp.n_out;
+                    tma_load_2d_cta2(sB + stage * kStageB, grp.which ? &tmB1 : &tmB0, &full_bar[stage], kb * kBlockK, bh,
+                                     I64B_L2_EVICT_NORMAL);
+                }
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             int stage = 0, g = 0;
@@ -1127,10 +1171,10 @@ PFN_tmapEncodeTiled get_encode_fn() {
     return fn;
 }
 
-template <bool kInt8, bool kDual, int kNMma, int kCtas>
+template <bool kInt8, bool kDual, int kNMma, int kCtas, bool kGather = false>
 int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b0, const CUtensorMap& b1,
                 const I64bGemmParams& p, int grid, cudaStream_t stream) {
-    auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma, kCtas>;
+    auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma, kCtas, kGather>;
     constexpr int smem = StageCfg<kNMma, kCtas>::kSmem;
     static bool configured[I64B_MAX_DEVICES] = {};      // function attributes are per device (one table per instantiation)
     const int dev = i64b_current_device();
@@ -1236,11 +1280,16 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
     I64B_CHECK(p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
                p.num_groups);
     I64B_CHECK(p.k[0] > 0 && p.k[1] > 0, I64B_ERR_ARG, "K must be positive");
+    I64B_CHECK(p.gather_idx == nullptr || ctas == 2, I64B_ERR_ARG, "row gather needs the pair kernel");
     int sms = i64b_num_sms();
     if (g_gemm_cta_limit > 0 && g_gemm_cta_limit < sms) sms = g_gemm_cta_limit >= 2 ? g_gemm_cta_limit : 2;
     if (ctas == 2) {        // max_tiles counts pair units here
         const int pairs = sms / 2;
         const int grid2 = 2 * (int)(max_tiles < pairs ? max_tiles : pairs);
+        if (p.gather_idx != nullptr) {
+            I64B_CHECK(!is_int8 && dual, I64B_ERR_ARG, "row gather is built for the bf16 GEMM1 pair kernel");
+            return launch_inst<false, true, 256, 2, true>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+        }
         if (is_int8 && dual) return launch_inst<true, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
         if (is_int8) return launch_inst<true, false, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
         if (dual) return launch_inst<false, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);

@@ -46,6 +46,11 @@ struct I64bGemmParams {
     const int32_t* row_tok;    // pair-order row -> token | (bit 30: the token's route 1 sits in K segment 0)
     int32_t tri_scaled;        // one-accumulator form: GEMM1 multiplies the SwiGLU rows by tri_mul (powers of two: exact)
     float tri_mul[3];          // w_0 * rs, w_1 * rs (by ROUTE, bit 31 of rowmap), ss
+    // GEMM1 without a dispatch pass (pair kernel, bf16): the A rows of the routed groups (which == 0) are gathered from the
+    // caller's x — tmA0 is then a one-row-box map over x — through gather_idx[dispatched row] = token (indices beyond
+    // gather_rows, i.e. the padding of the last m-tile, are not read; every index is clamped to [0, n_tokens))
+    const int32_t* gather_idx;
+    int32_t gather_rows;
     // bring-up instrumentation (env I64B_DEBUG_FLAGS / I64B_DEBUG_TIMELINE; never set in production)
     uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores
     long long* debug_timeline; // [grid, 8] clock64 offsets per CTA
@@ -60,6 +65,7 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
 // max_tiles is an upper bound on the number of (group, m, n) tiles, used only to size the grid.
 // ctas = 2 runs CTA pairs (cta_group::2, M = 256 per MMA; n_mma must be 256): the B tensor maps must then have
 // 128-row boxes (each CTA stages half of the B tile) and max_tiles counts (256-row, n) units.
+// p.gather_idx != nullptr (bf16, dual, ctas == 2 only): see I64bGemmParams::gather_idx.
 int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream);

@@ -73,6 +73,7 @@ struct I64bDispatchArgs {
     int32_t* routes_out;        // [K, N]
     int32_t* scatter_idx_out;   // [K, N]
     int32_t* dest_row_out;      // [K, N]
+    int32_t* src_tok_out;       // [N*K] optional: token of every dispatched row (GEMM1 gathers its A rows through it)
     int tri;                    // 1: also fill tw.pos / tw.tok / tw.rowmap (token-major layout, top_k == 2)
     int phase;                  // 0: indices and rows in one launch; 1: the index outputs only (routes / dest rows / token-major
                                 // maps); 2: the row copies only — the copy then runs on a second stream under the shared expert's
