@@ -278,9 +278,10 @@ enum {
                                      blocks with a shared expert run, from 4096 tokens on, on the layer's second stream under
                                      the shared expert's GEMM1; this flag keeps them on the caller's stream.  Results are
                                      identical either way */
-    I64B_DEBUG_NO_GATHER = 128,   /* bf16 blocks big enough for the CTA-pair GEMM1 skip the dispatch row copies: GEMM1 gathers
-                                     the routed A rows from x (tile::gather4 through the dispatch indices).  This flag keeps
-                                     the dispatched copy.  Results are identical either way */
+    I64B_DEBUG_GATHER = 128,      /* bf16 blocks big enough for the CTA-pair GEMM1: skip the dispatch row copies, GEMM1 gathers
+                                     the routed A rows from x (tile::gather4 through the dispatch indices).  Identical results,
+                                     measured much slower (the gather starves GEMM1's operand ingest): off unless this flag
+                                     or env I64B_GATHER=1 */
     I64B_DEBUG_TRI_FOLD = 32      /* fused down projection: keep the three-accumulator form (bit-identical to GEMM2 +
                                      combine_kernel) even when the scales are powers of two and the single-accumulator
                                      form (scales folded into the SwiGLU rows, one sum over K = 2*I_e + S) would be taken */

@@ -251,16 +251,17 @@ def test_dispatch_copy_overlap_is_bit_identical(form):
 @pytest.mark.parametrize("form", ["chain", "one_acc", "fold"])
 @pytest.mark.parametrize("n", [20000, 33001])
 def test_gemm1_row_gather_is_bit_identical(form, n):
-    """Blocks big enough for the CTA-pair GEMM1 make no dispatched copy: GEMM1's producer warp gathers the routed A rows from
-    x (tile::gather4 through the dispatch indices).  Same operands, same MMAs: identical output to the dispatched-copy path
-    (I64B_DEBUG_NO_GATHER), in every down-projection form, zipf ids included (ragged groups, empty tails)."""
+    """Opt-in (I64B_DEBUG_GATHER; measured slower, off by default): blocks big enough for the CTA-pair GEMM1 make no
+    dispatched copy, GEMM1's producer warp gathers the routed A rows from x (tile::gather4 through the dispatch indices).
+    Same operands, same MMAs: identical output to the dispatched-copy path in every down-projection form, zipf ids included
+    (ragged groups, empty tails)."""
     cfg, w, table, ids, x = Hh.make_block(256, 8, 128, 256, 5000, 2, n, seed=3, zipf=(n % 2 == 1))
     xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
     flags = {"chain": _C.DEBUG_NO_TRI, "one_acc": _C.DEBUG_TRI, "fold": _C.DEBUG_TRI | _C.DEBUG_TRI_FOLD}[form]
     copy = Hh.build_gpu_block(cfg, w, table, "bf16")
-    copy.set_debug(flags | _C.DEBUG_NO_GATHER)
+    copy.set_debug(flags)
     gat = Hh.build_gpu_block(cfg, w, table, "bf16")
-    gat.set_debug(flags)
+    gat.set_debug(flags | _C.DEBUG_GATHER)
     _C.launch_count_reset()
     want = copy.forward(xg, ig, torch.float32)
     torch.cuda.synchronize()

@@ -639,9 +639,12 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.dest_row_out = cv.dest_row;
     da.tri = tri ? 1 : 0;
     da.tw = cv.tri;
-    // bf16 blocks big enough for the pair kernel: no dispatched copy at all — GEMM1 gathers the routed rows from x
-    static const int gather_mode = env_int("I64B_GATHER", 1);
-    const bool gather = gather_mode != 0 && !(L->debug & I64B_DEBUG_NO_GATHER) && !q && E > 0 && S > 0 && shared_from_x &&
+    // GEMM1 without a dispatched copy: the pair kernel's producer gathers the routed rows from x with tile::gather4.  Bit-
+    // identical (tests/test_gpu_tri.py) and MEASURED MUCH SLOWER on B200 (profiles/r2t_*: 64K tokens 3.24 -> 4.58 ms/step):
+    // 32 four-row requests per k-block feed the SM at well under the rate of one 128-row box, and GEMM1 is bound by exactly
+    // that operand ingest.  Opt-in only (I64B_GATHER=1 or I64B_DEBUG_GATHER on the layer).
+    static const int gather_mode = env_int("I64B_GATHER", 0);
+    const bool gather = (gather_mode != 0 || (L->debug & I64B_DEBUG_GATHER)) && !q && E > 0 && S > 0 && shared_from_x &&
                         o.stage_mask == 0xFFu && use_cta_pairs(256, T, E + 1) && pick_nmma(mt_r_pre(R, E), I, (n + 127) / 128, S, true, "I64B_GEMM1_NMMA") == 256;
     if (gather) {
         da.phase = 1;

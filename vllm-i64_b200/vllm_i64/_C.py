@@ -17,7 +17,7 @@ BF16, F32, F16 = 0, 1, 2
 STAGE_PLAN, STAGE_DISPATCH, STAGE_GEMM1, STAGE_REQUANT, STAGE_GEMM2, STAGE_COMBINE, STAGE_ALL = 1, 2, 4, 8, 16, 32, 0xFF
 MODE_BF16, MODE_W8A8 = 0, 1
 DEBUG_KEEP_TAPS, DEBUG_FUSE_COMBINE, DEBUG_NO_FUSED, DEBUG_TRI, DEBUG_NO_TRI, DEBUG_TRI_FOLD = 1, 2, 4, 8, 16, 32
-DEBUG_NO_OVERLAP, DEBUG_NO_GATHER = 64, 128
+DEBUG_NO_OVERLAP, DEBUG_GATHER = 64, 128
 TRI_MIN_ROWS_ONEACC, TRI_MIN_ROWS_FOLD = 288, 512      # include/i64b.h
 (TAP_ROUTES, TAP_DEST_ROW, TAP_SCATTER_IDX, TAP_COUNTS, TAP_OFFSETS, TAP_XS, TAP_XS_SCALE, TAP_INTER_R, TAP_INTER_S,
  TAP_INTER_SCALE_R, TAP_INTER_SCALE_S, TAP_Q14_R, TAP_Q14_S, TAP_Y, TAP_GROUP_START) = range(15)
