@@ -33,7 +33,7 @@ enum {
 };
 
 enum { I64B_BF16 = 0, I64B_F32 = 1, I64B_F16 = 2 };
-enum { I64B_MODE_BF16 = 0, I64B_MODE_W8A8 = 1 };
+enum { I64B_MODE_BF16 = 0, I64B_MODE_W8A8 = 1, I64B_MODE_FP8 = 2 };
 
 const char* i64b_last_error(void);
 int i64b_version(void);
@@ -139,7 +139,7 @@ typedef struct {
     int32_t shared_inter;       /* S, 0 = no shared expert */
     int32_t vocab_size;         /* V */
     int32_t top_k;              /* K in [1,4] */
-    int32_t mode;               /* I64B_MODE_BF16 | I64B_MODE_W8A8 */
+    int32_t mode;               /* I64B_MODE_BF16 | I64B_MODE_W8A8 | I64B_MODE_FP8 */
     int32_t reserved;
     float route_weight[4];      /* w0 = primary, others (1-w0)/(K-1)  (layers/token_routed_mlp.py:53-58,158) */
     float routed_scale;         /* routed_output_scale or routed_output_gate (:174-185) */
@@ -170,6 +170,16 @@ int i64b_moe_load_bf16(i64b_layer* layer, const void* gate, const void* up, cons
 int i64b_moe_load_w8a8(i64b_layer* layer, const int8_t* w13_q, const float* w13_s, const int8_t* w2_q,
                        const float* w2_s, const int8_t* sh13_q, const float* sh13_s, const int8_t* sh2_q,
                        const float* sh2_s, void* packed, i64b_stream_t stream);
+
+/* FP8 (f4): the block with E4M3 weights and dynamically quantised E4M3 activations, fp32 accumulation on the tensor cores
+ * (tcgen05 kind::f8f6f4).  Semantics of core/fp8.py: weights quantised per out-row (quantize_fp8, :75-110: scale =
+ * absmax / 448), activations per token row (quantize_activations_fp8, :113-129), every projection
+ * y = (x_q . w_q^T) * (x_scale x w_scale) (fp8_linear / fp8_fused_gate_up via torch._scaled_mm, :137-245), the SwiGLU rows
+ * rounded to bf16 and re-quantised per row in front of the down projection (layers/dense_mlp.py:75-83).  Same layouts as
+ * i64b_moe_load_w8a8 with E4M3 bytes (torch.float8_e4m3fn viewed as uint8) in place of the int8 ones. */
+int i64b_moe_load_fp8(i64b_layer* layer, const uint8_t* w13_q, const float* w13_s, const uint8_t* w2_q,
+                      const float* w2_s, const uint8_t* sh13_q, const float* sh13_s, const uint8_t* sh2_q,
+                      const float* sh2_s, void* packed, i64b_stream_t stream);
 
 /* uint8 routing table [K,V] (device, from i64b_pack_table); kept by pointer. */
 int i64b_moe_set_table(i64b_layer* layer, const uint8_t* table_u8);

@@ -483,6 +483,108 @@ def moe_block_w8a8(x: np.ndarray, token_ids: Optional[np.ndarray], table: np.nda
 
 
 # --------------------------------------------------------------------------- #
+# f4 — FP8 E4M3 block (core/fp8.py; layers/dense_mlp.py:75-83)
+# --------------------------------------------------------------------------- #
+
+FP8_MAX = np.float32(448.0)
+
+
+def e4m3_round(x: np.ndarray) -> np.ndarray:
+    """fp32 -> nearest ``float8_e4m3fn`` value (round to nearest even), returned as fp32.  4 exponent bits (bias 7),
+    3 mantissa bits, no infinities: normals 2^-6 .. 448 with a quantum of 2^(e-3), subnormals in steps of 2^-9.
+    Inputs are expected inside [-448, 448] (the reference clamps first, core/fp8.py:99-102,127)."""
+    x = np.asarray(x, dtype=np.float32)
+    _, ex = np.frexp(x)                                # x = m * 2^ex, 0.5 <= |m| < 1  ->  floor(log2|x|) = ex - 1
+    e = np.maximum(ex.astype(np.int32) - 1, -6)         # below 2^-6 the subnormal quantum 2^-9 applies
+    quantum = np.ldexp(np.float32(1.0), e - 3).astype(np.float32)
+    q = (np.rint(x.astype(np.float64) / quantum) * quantum).astype(np.float32)
+    return np.clip(q, -FP8_MAX, FP8_MAX)
+
+
+def e4m3_encode(v: np.ndarray) -> np.ndarray:
+    """Byte pattern (uint8) of values that are already exactly representable in e4m3fn (output of e4m3_round)."""
+    v = np.asarray(v, dtype=np.float32)
+    sign = (np.signbit(v)).astype(np.uint8) << 7
+    a = np.abs(v)
+    m, ex = np.frexp(a)
+    e = ex.astype(np.int32) - 1
+    normal = a >= np.float32(2.0 ** -6)
+    mant_n = np.rint((a / np.ldexp(np.float32(1.0), e) - 1.0) * 8).astype(np.int32)
+    mant_s = np.rint(a / np.float32(2.0 ** -9)).astype(np.int32)
+    byte = np.where(normal, ((e + 7) << 3) | mant_n, mant_s).astype(np.uint8)
+    return (sign | byte).astype(np.uint8)
+
+
+def quantize_rows_fp8(x: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """``quantize_activations_fp8`` (core/fp8.py:113-129) and ``quantize_fp8(per_channel=True)`` (:75-110): per row
+    ``scale = max(absmax, 1e-12) / 448`` and ``q = e4m3((x / scale).clamp(-448, 448))``, all in IEEE fp32.
+    Returns ``(q as fp32 values, scale [rows, 1])``."""
+    x32 = np.ascontiguousarray(x, dtype=np.float32)
+    absmax = np.maximum(np.max(np.abs(x32), axis=-1, keepdims=True), np.float32(1e-12)).astype(np.float32)
+    scale = (absmax / FP8_MAX).astype(np.float32)
+    q = e4m3_round(np.clip((x32 / scale).astype(np.float32), -FP8_MAX, FP8_MAX))
+    return q, scale
+
+
+def scaled_mm(a_q: np.ndarray, a_s: np.ndarray, bt_q: np.ndarray, b_s: np.ndarray) -> np.ndarray:
+    """``torch._scaled_mm(x_fp8, w_fp8.T, scale_a=[M,1], scale_b=[1,N])`` (core/fp8.py:176-182): the fp8 products are exact
+    in fp32, the sum is the tensor core's (fp64 here: the comparison is by tolerance), then ``* (scale_a * scale_b)``."""
+    acc = (a_q.astype(np.float64) @ bt_q.astype(np.float64).T).astype(np.float32)
+    return (acc * (a_s.reshape(-1, 1).astype(np.float32) * b_s.reshape(1, -1).astype(np.float32))).astype(np.float32)
+
+
+def fp8_swiglu(x: Optional[np.ndarray], w13_q, w13_s, w2_q, w2_s, x_preq=None) -> np.ndarray:
+    """One expert in FP8 (layers/dense_mlp.py:75-83): ``fp8_fused_gate_up`` -> ``silu(gate) * up`` -> ``fp8_linear`` (which
+    re-quantises its input per row).  The SwiGLU rows are held in bf16 (the reference's activations are bf16 tensors)."""
+    x_q, x_s = x_preq if x_preq is not None else quantize_rows_fp8(x)
+    gu = scaled_mm(x_q, x_s, w13_q, w13_s)
+    inter = w13_q.shape[0] // 2
+    h = round_bf16(_silu(gu[:, :inter]) * gu[:, inter:])
+    h_q, h_s = quantize_rows_fp8(h)
+    return scaled_mm(h_q, h_s, w2_q, w2_s)
+
+
+def quantize_moe_weights_fp8(w: MoEWeights) -> MoEWeightsInt8:
+    """The materialised ``(out,in)`` forms of ``quantize_moe_weights`` quantised with ``quantize_fp8`` (per out-row);
+    the ``*_q`` fields hold the E4M3 VALUES as fp32 (``e4m3_encode`` gives the bytes)."""
+    e = w.gate.shape[0]
+    w13 = np.concatenate([np.transpose(w.gate, (0, 2, 1)), np.transpose(w.up, (0, 2, 1))], axis=1)
+    w2 = np.transpose(w.down, (0, 2, 1))
+    q13, s13, q2, s2 = [], [], [], []
+    for i in range(e):
+        q, s = quantize_rows_fp8(w13[i]); q13.append(q); s13.append(s[:, 0])
+        q, s = quantize_rows_fp8(w2[i]); q2.append(q); s2.append(s[:, 0])
+    out = MoEWeightsInt8(np.stack(q13) if e else None, np.stack(s13) if e else None, np.stack(q2) if e else None,
+                         np.stack(s2) if e else None)
+    if w.shared_gate is not None:
+        q, s_ = quantize_rows_fp8(np.concatenate([w.shared_gate, w.shared_up], axis=0)); out.sh13_q, out.sh13_s = q, s_[:, 0]
+        q, s_ = quantize_rows_fp8(w.shared_down); out.sh2_q, out.sh2_s = q, s_[:, 0]
+    return out
+
+
+def moe_block_fp8(x: np.ndarray, token_ids: Optional[np.ndarray], table: np.ndarray, wq: MoEWeightsInt8,
+                  cfg: MoEConfig) -> np.ndarray:
+    """a3 with every expert (routed and shared) evaluated by :func:`fp8_swiglu`; the activations are quantised once per
+    token (the same row serves both routes and the shared expert, as ``x_preq`` does for W8A8)."""
+    n = x.shape[0]
+    x_q, x_s = quantize_rows_fp8(x)
+    routed = []
+    if cfg.num_experts > 0:
+        routes = route_table(token_ids, table, n, cfg.num_experts)
+        for r in range(cfg.top_k):
+            y = np.zeros((n, cfg.hidden_size), dtype=np.float32)
+            for e in range(cfg.num_experts):
+                rows = np.nonzero(routes[r] == e)[0]
+                if rows.size:
+                    y[rows] = fp8_swiglu(None, wq.w13_q[e], wq.w13_s[e], wq.w2_q[e], wq.w2_s[e], x_preq=(x_q[rows], x_s[rows]))
+            routed.append(y)
+    shared = fp8_swiglu(None, wq.sh13_q, wq.sh13_s, wq.sh2_q, wq.sh2_s, x_preq=(x_q, x_s)) if wq.sh13_q is not None else None
+    if not routed:
+        return shared
+    return combine_fp32(routed, shared, cfg)
+
+
+# --------------------------------------------------------------------------- #
 # a11 / a13 — weight-only INT8 forms
 # --------------------------------------------------------------------------- #
 

@@ -134,6 +134,7 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
     const int64_t nn = n > 0 ? n : 1;
     const int64_t R = nn * c.top_k, T = R + nn;
     const bool q = c.mode == I64B_MODE_W8A8;
+    const bool q8 = q || c.mode == I64B_MODE_FP8;      // FP8 keeps its bf16 SwiGLU rows where W8A8 keeps the Q14 integers
     cv.plan = i64b_plan_ws_carve(p, n, c.top_k, c.num_experts);
     size_t off = cv.plan.bytes;
     auto take = [&](size_t bytes) {
@@ -155,8 +156,8 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
     // 2*ceil(I/128) for BN = 128, which exceeds ceil(I/32) only for I <= 32
     cv.amax_ld_r = (c.expert_inter + 31) / 32 + 1;
     cv.amax_ld_s = (c.shared_inter + 31) / 32 + 1;
-    cv.q14_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * c.expert_inter : 0));
-    cv.q14_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * c.shared_inter : 0));
+    cv.q14_r = reinterpret_cast<int32_t*>(take(q8 ? sizeof(int32_t) * R * c.expert_inter : 0));
+    cv.q14_s = reinterpret_cast<int32_t*>(take(q8 ? sizeof(int32_t) * nn * c.shared_inter : 0));
     cv.amax_r = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * R * cv.amax_ld_r : 0));
     cv.amax_s = reinterpret_cast<int32_t*>(take(q ? sizeof(int32_t) * nn * cv.amax_ld_s : 0));
     const int64_t slabs = c.shared_inter > 0 ? (c.shared_inter + 511) / 512 : 1;
@@ -195,7 +196,7 @@ __global__ void transpose16_kernel(const uint16_t* __restrict__ src, uint16_t* _
 
 static int encode_weight_maps(i64b_layer* L) {
     const i64b_moe_config& c = L->cfg;
-    const bool q = c.mode == I64B_MODE_W8A8;
+    const bool q = c.mode != I64B_MODE_BF16;        // one-byte operands (int8 or E4M3)
     for (int i = 0; i < 3; ++i) {
         const int n_mma = kNMmaChoices[i];
         int rc = i64b_encode_tmap(&L->tm_w13[i], L->w13, q, w13_rows(c), c.hidden_size,
@@ -251,8 +252,9 @@ const int16_t* i64b_silu_lut_q7(void) { return kSiluLutQ7; }
 int i64b_moe_create(const i64b_moe_config* cfg, i64b_layer** out) {
     I64B_CHECK(cfg && out, I64B_ERR_ARG, "null argument");
     const i64b_moe_config& c = *cfg;
-    I64B_CHECK(c.mode == I64B_MODE_BF16 || c.mode == I64B_MODE_W8A8, I64B_ERR_ARG, "unknown mode %d", c.mode);
-    const int kalign = c.mode == I64B_MODE_W8A8 ? 16 : 8;   // 16-byte TMA pitch
+    I64B_CHECK(c.mode == I64B_MODE_BF16 || c.mode == I64B_MODE_W8A8 || c.mode == I64B_MODE_FP8, I64B_ERR_ARG, "unknown mode %d",
+               c.mode);
+    const int kalign = c.mode != I64B_MODE_BF16 ? 16 : 8;   // 16-byte TMA pitch
     I64B_CHECK(c.hidden_size > 0 && c.hidden_size % 16 == 0, I64B_ERR_ARG, "hidden_size %d must be a multiple of 16",
                c.hidden_size);
     I64B_CHECK(c.num_experts >= 0 && c.num_experts <= I64B_MAX_EXPERTS, I64B_ERR_ARG, "num_experts %d not in [0,%d]",
@@ -270,7 +272,7 @@ int i64b_moe_create(const i64b_moe_config* cfg, i64b_layer** out) {
     I64B_CHECK(L != nullptr, I64B_ERR_ARG, "out of host memory");
     L->cfg = c;
     if (c.num_experts == 0) L->cfg.top_k = 0;
-    L->elt = c.mode == I64B_MODE_W8A8 ? 1 : 2;
+    L->elt = c.mode != I64B_MODE_BF16 ? 1 : 2;
     *out = L;
     return I64B_OK;
 }
@@ -340,11 +342,11 @@ int i64b_moe_load_bf16(i64b_layer* L, const void* gate, const void* up, const vo
     return I64B_OK;
 }
 
-int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, const int8_t* w2_q, const float* w2_s,
-                       const int8_t* sh13_q, const float* sh13_s, const int8_t* sh2_q, const float* sh2_s, void* packed,
-                       i64b_stream_t stream) {
+static int load_bytes(i64b_layer* L, int mode, const int8_t* w13_q, const float* w13_s, const int8_t* w2_q, const float* w2_s,
+                      const int8_t* sh13_q, const float* sh13_s, const int8_t* sh2_q, const float* sh2_s, void* packed,
+                      i64b_stream_t stream) {
     I64B_CHECK(L && packed, I64B_ERR_ARG, "null argument");
-    I64B_CHECK(L->cfg.mode == I64B_MODE_W8A8, I64B_ERR_STATE, "layer was created in bf16 mode");
+    I64B_CHECK(L->cfg.mode == mode, I64B_ERR_STATE, "layer was created in mode %d, these weights are mode %d", L->cfg.mode, mode);
     const i64b_moe_config& c = L->cfg;
     I64B_CHECK(c.num_experts == 0 || (w13_q && w13_s && w2_q && w2_s), I64B_ERR_ARG, "expert weights missing");
     I64B_CHECK(c.shared_inter == 0 || (sh13_q && sh13_s && sh2_q && sh2_s), I64B_ERR_ARG, "shared weights missing");
@@ -375,6 +377,20 @@ int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, c
     L->loaded = true;
     L->cached_ws = nullptr;
     return I64B_OK;
+}
+
+int i64b_moe_load_w8a8(i64b_layer* L, const int8_t* w13_q, const float* w13_s, const int8_t* w2_q, const float* w2_s,
+                       const int8_t* sh13_q, const float* sh13_s, const int8_t* sh2_q, const float* sh2_s, void* packed,
+                       i64b_stream_t stream) {
+    return load_bytes(L, I64B_MODE_W8A8, w13_q, w13_s, w2_q, w2_s, sh13_q, sh13_s, sh2_q, sh2_s, packed, stream);
+}
+
+int i64b_moe_load_fp8(i64b_layer* L, const uint8_t* w13_q, const float* w13_s, const uint8_t* w2_q, const float* w2_s,
+                      const uint8_t* sh13_q, const float* sh13_s, const uint8_t* sh2_q, const float* sh2_s, void* packed,
+                      i64b_stream_t stream) {
+    return load_bytes(L, I64B_MODE_FP8, reinterpret_cast<const int8_t*>(w13_q), w13_s, reinterpret_cast<const int8_t*>(w2_q),
+                      w2_s, reinterpret_cast<const int8_t*>(sh13_q), sh13_s, reinterpret_cast<const int8_t*>(sh2_q), sh2_s,
+                      packed, stream);
 }
 
 int i64b_moe_set_debug(i64b_layer* L, int flags) {
@@ -447,6 +463,7 @@ static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t 
     const int E = c.num_experts;
     if (mode == 0 || !plain_call || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
     if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 256 != 0) return false;
+    if (c.mode == I64B_MODE_FP8) return false;      // FP8 blocks take GEMM2 + combine
     if (c.mode == I64B_MODE_W8A8) {     // int8 rows of 128 elements per k-block, a shared expert, rows the re-quantiser holds in registers
         static const int w8 = getenv("I64B_TRI_W8A8") ? atoi(getenv("I64B_TRI_W8A8")) : 1;
         if (!w8 || c.shared_inter <= 0 || c.expert_inter % 128 != 0 || c.shared_inter % 128 != 0 || c.expert_inter > 1536 ||
@@ -508,6 +525,9 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         c.shared_scale = o.shared_scale;
     }
     const bool q = c.mode == I64B_MODE_W8A8;
+    const bool f8 = c.mode == I64B_MODE_FP8;        // E4M3 activations and weights, fp32 accumulation (core/fp8.py)
+    const bool q8 = q || f8;                        // one-byte operands with per-row / per-channel scales
+    const int gtype = q ? I64B_TYPE_INT8 : (f8 ? I64B_TYPE_FP8 : I64B_TYPE_BF16);
     const bool preq = o.preq_scale != nullptr;
     I64B_CHECK(!preq || q, I64B_ERR_ARG, "pre-quantised activations need a W8A8 layer");
     const int E = c.num_experts, K = c.top_k, H = c.hidden_size, I = c.expert_inter, S = c.shared_inter;
@@ -527,22 +547,22 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
 
     const int64_t cache_key = n * 64 + K * 2 + (S > 0 ? 1 : 0);
     if (L->cached_ws != base || L->cached_n != cache_key) {
-        int rc = i64b_encode_tmap(&L->tm_xs, cv.xs, q, T, H, (int64_t)H * L->elt, 128);
+        int rc = i64b_encode_tmap(&L->tm_xs, cv.xs, q8, T, H, (int64_t)H * L->elt, 128);
         if (rc) return rc;
         if (E > 0) {
-            rc = i64b_encode_tmap(&L->tm_inter_r, cv.inter_r, q, R, I, (int64_t)I * L->elt, 128);
+            rc = i64b_encode_tmap(&L->tm_inter_r, cv.inter_r, q8, R, I, (int64_t)I * L->elt, 128);
             if (rc) return rc;
         } else {
             L->tm_inter_r = L->tm_xs;
         }
         if (S > 0) {
-            rc = i64b_encode_tmap(&L->tm_inter_s, cv.inter_s, q, n, S, (int64_t)S * L->elt, 128);
+            rc = i64b_encode_tmap(&L->tm_inter_s, cv.inter_s, q8, n, S, (int64_t)S * L->elt, 128);
             if (rc) return rc;
         } else {
             L->tm_inter_s = L->tm_inter_r;
         }
         if (E > 0 && K == 2 && (2 * I + S) * L->elt % 16 == 0) {
-            rc = i64b_encode_tmap(&L->tm_cat, cv.inter_r, q, n, 2 * I + S, (int64_t)(2 * I + S) * L->elt, 128);
+            rc = i64b_encode_tmap(&L->tm_cat, cv.inter_r, q8, n, 2 * I + S, (int64_t)(2 * I + S) * L->elt, 128);
             if (rc) return rc;
         }
         L->cached_ws = base;
@@ -553,7 +573,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     cv.tri.ticket = cv.plan.sync + 1;
 
     // decode-sized bf16 batches: the whole layer in ONE persistent launch (csrc/i64b_fused.cu)
-    if (fused_enabled() && !q && !(L->debug & I64B_DEBUG_NO_FUSED) && given_routes == nullptr && o.stage_mask == 0xFFu &&
+    if (fused_enabled() && !q8 && !(L->debug & I64B_DEBUG_NO_FUSED) && given_routes == nullptr && o.stage_mask == 0xFFu &&
         i64b_fused_supported((int)n, H, I, S, E, K)) {
         I64bFusedParams fp = {};
         fp.x = x;
@@ -598,13 +618,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     pa.hidden = H;
     // bf16: the shared expert (and a dense FFN) multiplies the caller's x in place; W8A8 needs the quantised copy unless
     // the caller already brings int8 rows (x_preq)
-    const bool shared_from_x = (!q || preq) && S > 0;
+    const bool shared_from_x = (!q8 || preq) && S > 0;
     pa.shared_from_x = shared_from_x ? 1 : 0;
     pa.ticket = L->sync + 3 * I64B_SYNC_STRIDE;     // free slot of the layer's persistent counter area
     if (shared_from_x && (L->cached_x != x || L->cached_x_n != n)) {
         int rcx = i64b_encode_tmap(&L->tm_x, x, preq, n, H, (int64_t)H * L->elt, 128);
         if (rcx) return rcx;
-        if (!q) {
+        if (!q8) {
             static const int gbox = env_int("I64B_GATHER_BOX", 1);
             rcx = i64b_encode_tmap(&L->tm_xg, x, false, n, H, (int64_t)H * 2, gbox);
             if (rcx) return rcx;
@@ -629,7 +649,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     da.hidden = H;
     da.top_k = K;
     da.num_experts = E;
-    da.quantize = (q && !preq) ? 1 : 0;
+    da.quantize = f8 ? 2 : ((q && !preq) ? 1 : 0);
     da.preq_scale = o.preq_scale;
     da.shared_copy = (S > 0 && !shared_from_x) ? 1 : 0;
     da.xs = cv.xs;
@@ -644,7 +664,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     // 32 four-row requests per k-block feed the SM at well under the rate of one 128-row box, and GEMM1 is bound by exactly
     // that operand ingest.  Opt-in only (I64B_GATHER=1 or I64B_DEBUG_GATHER on the layer).
     static const int gather_mode = env_int("I64B_GATHER", 0);
-    const bool gather = (gather_mode != 0 || (L->debug & I64B_DEBUG_GATHER)) && !q && E > 0 && S > 0 && shared_from_x &&
+    const bool gather = (gather_mode != 0 || (L->debug & I64B_DEBUG_GATHER)) && !q8 && E > 0 && S > 0 && shared_from_x &&
                         o.stage_mask == 0xFFu && use_cta_pairs(256, T, E + 1) && pick_nmma(mt_r_pre(R, E), I, (n + 127) / 128, S, true, "I64B_GEMM1_NMMA") == 256;
     if (gather) {
         da.phase = 1;
@@ -652,7 +672,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     }
     // prefill-sized bf16 blocks with a shared expert: the row copies leave the main stream (see overlap_enabled())
     static const int overlap_min = env_int("I64B_OVERLAP_MIN_TOKENS", 4096);
-    const bool overlap = !gather && L->side != nullptr && !(L->debug & I64B_DEBUG_NO_OVERLAP) && !q && E > 0 && S > 0 && shared_from_x && o.stage_mask == 0xFFu && n >= overlap_min;
+    const bool overlap = !gather && L->side != nullptr && !(L->debug & I64B_DEBUG_NO_OVERLAP) && !q8 && E > 0 && S > 0 && shared_from_x && o.stage_mask == 0xFFu && n >= overlap_min;
     if (overlap) {
         da.phase = 1;
         rc = i64b_run_dispatch(da, cv.plan, s);
@@ -683,8 +703,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.groups = cv.plan.groups1;
         gp.num_groups = E + 1;
         gp.k[0] = gp.k[1] = H;
-        gp.out[0] = q ? (void*)cv.q14_r : (void*)cv.inter_r;
-        gp.out[1] = q ? (void*)cv.q14_s : (void*)cv.inter_s;
+        gp.out[0] = q8 ? (void*)cv.q14_r : (void*)cv.inter_r;      // FP8: bf16 SwiGLU rows, re-quantised below
+        gp.out[1] = q8 ? (void*)cv.q14_s : (void*)cv.inter_s;
         gp.ld_out[0] = I;
         gp.ld_out[1] = S;
         gp.row_scale[0] = cv.xs_scale;
@@ -733,8 +753,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
                                   tiles - tiles_s, s);
             if (rc) return rc;
         } else if (o.stage_mask & I64B_STAGE_GEMM1) {
-            rc = i64b_launch_gemm(q, true, n_mma, pairs ? 2 : 1, gather ? L->tm_xg : L->tm_xs, shared_from_x ? L->tm_x : L->tm_xs,
+            rc = i64b_launch_gemm(gtype, true, n_mma, pairs ? 2 : 1, gather ? L->tm_xg : L->tm_xs, shared_from_x ? L->tm_x : L->tm_xs,
                                   L->tm_w13[wi], L->tm_w13[wi], gp, tiles, s);
+            if (rc) return rc;
+        }
+        if (f8 && (o.stage_mask & I64B_STAGE_REQUANT)) {  // quantize_activations_fp8 of the SwiGLU rows (fp8_linear, core/fp8.py:166)
+            rc = i64b_run_requant_fp8(cv.q14_r, cv.inter_r, cv.inter_scale_r, E > 0 ? R : 0, I, cv.q14_s, cv.inter_s,
+                                      cv.inter_scale_s, S > 0 ? n : 0, S, s);
             if (rc) return rc;
         }
         if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
@@ -785,7 +810,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.out[0] = gp.out[1] = cv.y;
         gp.ld_out[0] = gp.ld_out[1] = H;
         gp.out_dtype = I64B_F32;
-        gp.epi = q ? I64B_EPI_DEQUANT : I64B_EPI_F32;
+        gp.epi = q8 ? I64B_EPI_DEQUANT : I64B_EPI_F32;
         gp.row_scale[0] = cv.inter_scale_r;
         gp.row_scale[1] = cv.inter_scale_s;
         gp.col_scale[0] = L->w2r_scale;
@@ -811,7 +836,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         const int wi = pairs ? 1 : nmma_index(n_mma);       // pairs: each CTA stages a 128-row half of the B tile
         const int64_t tiles = (pairs ? pt_r + pt_s : mt_r + mt_s) * ((H + n_mma - 1) / n_mma);
         if (o.stage_mask & I64B_STAGE_GEMM2) {
-            rc = i64b_launch_gemm(q, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi],
+            rc = i64b_launch_gemm(gtype, false, n_mma, pairs ? 2 : 1, L->tm_inter_r, L->tm_inter_s, L->tm_w2r[wi],
                                   L->tm_w2s[wi], gp, tiles, s);
             if (rc) return rc;
         }

@@ -49,11 +49,15 @@ __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem_ptr)
     return d;
 }
 
-template <bool kInt8, int kNMma, int kCtas>
+// operand kinds of the grouped GEMM
+constexpr int kTypeBf16 = I64B_TYPE_BF16, kTypeInt8 = I64B_TYPE_INT8, kTypeFp8 = I64B_TYPE_FP8;
+
+template <int kType, int kNMma, int kCtas>
 __device__ __forceinline__ constexpr uint32_t make_idesc() {
-    // c_format [4,6): 1=F32, 2=S32; a/b format [7,10)/[10,13): BF16=1 / S8=1; K-major both;
-    // n_dim [17,23) = N>>3; m_dim [24,29) = M>>4
-    return (uint32_t)((kInt8 ? 2u : 1u) << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kNMma >> 3) << 17) |
+    // c_format [4,6): 1=F32, 2=S32; a/b format [7,10)/[10,13): kind::f16 BF16=1 / kind::i8 S8=1 / kind::f8f6f4 E4M3=0;
+    // K-major both; n_dim [17,23) = N>>3; m_dim [24,29) = M>>4
+    constexpr uint32_t ab = kType == kTypeFp8 ? 0u : 1u;
+    return (uint32_t)((kType == kTypeInt8 ? 2u : 1u) << 4) | (ab << 7) | (ab << 10) | ((uint32_t)(kNMma >> 3) << 17) |
            ((uint32_t)((kBlockM * kCtas) >> 4) << 24);
 }
 
@@ -243,18 +247,20 @@ __device__ __forceinline__ void warp_combine_block(uint32_t st_addr, const uint3
     }
 }
 
-template <bool kInt8, bool kDual, int kNMma, int kCtas, bool kGather = false>
+template <int kType, bool kDual, int kNMma, int kCtas, bool kGather = false>
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ I64bGemmParams p) {
+    constexpr bool kInt8 = kType == kTypeInt8;
+    constexpr bool kFp8 = kType == kTypeFp8;      // E4M3 operands, fp32 accumulators, per-row x per-channel scales
     using Cfg = StageCfg<kNMma, kCtas>;
     static_assert(kCtas == 1 || kCtas == 2, "single CTA or a CTA pair");
     static_assert(kCtas == 1 || kNMma == 256, "the pair kernel is built for the widest tile only");
     constexpr int kStages = Cfg::kStages;
     constexpr int kStageB = Cfg::kStageB;
     constexpr int kBnOut = kDual ? kNMma / 2 : kNMma;
-    constexpr int kBlockK = kInt8 ? 128 : 64;          // elements per 128-byte row
+    constexpr int kBlockK = kType != kTypeBf16 ? 128 : 64;   // elements per 128-byte row
     constexpr uint32_t kTmemCols = 2 * kNMma;          // two accumulator stages (power of two ≥ 32)
     static_assert((kDual ? kNMma / 2 : kNMma) >= 32, "a warp drains at least one 32-column TMEM chunk");
     static_assert(kTmemCols >= 32 && kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
@@ -428,7 +434,7 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (one thread)
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc = make_idesc<kInt8, kNMma, kCtas>();
+            constexpr uint32_t idesc = make_idesc<kType, kNMma, kCtas>();
             int stage = 0, g = 0, iter = 0;
             uint32_t phase = 0;
             for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
@@ -456,10 +462,14 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         if constexpr (kCtas == 2) {
                             if constexpr (kInt8)
                                 umma_i8_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                            else if constexpr (kFp8)
+                                umma_f8_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                             else
                                 umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         } else if constexpr (kInt8) {
                             umma_i8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        } else if constexpr (kFp8) {
+                            umma_f8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         } else {
                             umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                         }
@@ -508,8 +518,8 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const int colw0 = tc.n_t * kBnOut + cbase;      // first output column of this warp
 
             // per-column scales of this warp's slice -> smem (before waiting for the accumulator)
-            if constexpr (kInt8 || !kDual) {
-                const bool need = kInt8 ? (kDual || p.epi == I64B_EPI_DEQUANT) : (p.epi == I64B_EPI_DEQUANT);
+            if constexpr (kInt8 || kFp8 || !kDual) {
+                const bool need = (kInt8 || kFp8) ? (kDual || p.epi == I64B_EPI_DEQUANT) : (p.epi == I64B_EPI_DEQUANT);
                 if (active && need) {
                     const float* cs = p.col_scale[w] + grp.w_row_base;
                     __syncwarp();
@@ -613,6 +623,8 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 // token-major layout: this lane's row goes to its token's row of the [N, 2I+S] buffer
                 const bool scatter = p.rowmap[w] != nullptr;
                 int64_t my_off = 0;
+                [[maybe_unused]] float rs8 = 0.0f;          // FP8: this row's activation scale
+                if constexpr (kFp8) rs8 = valid ? p.row_scale[w][a_row] : 0.0f;
                 float mul = 1.0f;           // one-accumulator down projection: w_k * rs (or ss) folded in here, a power of two
                 const bool use_mul = scatter && p.tri_scaled != 0;
                 if (scatter) {
@@ -634,6 +646,21 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         tmem_ld_32x32(taddr + c, gr);
                         tmem_ld_32x32(taddr + kBnOut + c, ur);
                         tmem_ld_wait();
+                        if constexpr (kFp8) {       // _scaled_mm: acc * (x_scale * w_scale), gate and up         core/fp8.py:231-245
+#pragma unroll
+                            for (int j4 = 0; j4 < 8; ++j4) {
+                                const float4 sg4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
+                                const float4 su4 = ld_shared_f4(ws_addr + (kColsW + c + j4 * 4) * 4);
+                                const float sgv[4] = {sg4.x, sg4.y, sg4.z, sg4.w};
+                                const float suv[4] = {su4.x, su4.y, su4.z, su4.w};
+#pragma unroll
+                                for (int jj = 0; jj < 4; ++jj) {
+                                    const int j = j4 * 4 + jj;
+                                    gr[j] = __float_as_uint(__fmul_rn(__uint_as_float(gr[j]), __fmul_rn(rs8, sgv[jj])));
+                                    ur[j] = __float_as_uint(__fmul_rn(__uint_as_float(ur[j]), __fmul_rn(rs8, suv[jj])));
+                                }
+                            }
+                        }
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
                             float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
@@ -1171,10 +1198,10 @@ PFN_tmapEncodeTiled get_encode_fn() {
     return fn;
 }
 
-template <bool kInt8, bool kDual, int kNMma, int kCtas, bool kGather = false>
+template <int kType, bool kDual, int kNMma, int kCtas, bool kGather = false>
 int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b0, const CUtensorMap& b1,
                 const I64bGemmParams& p, int grid, cudaStream_t stream) {
-    auto kern = i64b_gemm_kernel<kInt8, kDual, kNMma, kCtas, kGather>;
+    auto kern = i64b_gemm_kernel<kType, kDual, kNMma, kCtas, kGather>;
     constexpr int smem = StageCfg<kNMma, kCtas>::kSmem;
     static bool configured[I64B_MAX_DEVICES] = {};      // function attributes are per device (one table per instantiation)
     const int dev = i64b_current_device();
@@ -1215,7 +1242,7 @@ int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap&
         if (printed++ < 12) {
             long long g0 = h[0];
             for (int b = 0; b < grid; ++b) if (h[b * 8] && h[b * 8] < g0) g0 = h[b * 8];
-            fprintf(stderr, "[i64b timeline] int8=%d dual=%d nmma=%d grid=%d\n", (int)kInt8, (int)kDual, kNMma, grid);
+            fprintf(stderr, "[i64b timeline] type=%d dual=%d nmma=%d grid=%d\n", kType, (int)kDual, kNMma, grid);
             for (int b = 0; b < grid; b += (grid > 16 ? grid / 8 : 1))
                 fprintf(stderr, "  cta %3d start+%lldns prologue=%lld tma0=%lld full0=%lld lastmma=%lld epi0=%lld epiend=%lld end=%lld (cycles)\n",
                         b, h[b * 8] - g0, h[b * 8 + 1], h[b * 8 + 2], h[b * 8 + 3], h[b * 8 + 4], h[b * 8 + 5], h[b * 8 + 6], h[b * 8 + 7]);
@@ -1272,10 +1299,11 @@ int i64b_set_gemm_cta_limit(int limit) {
     return prev;
 }
 
-int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+int i64b_launch_gemm(int type, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream) {
     if (max_tiles <= 0) return I64B_OK;
+    I64B_CHECK(type == kTypeBf16 || type == kTypeInt8 || type == kTypeFp8, I64B_ERR_ARG, "unknown operand type %d", type);
     I64B_CHECK(ctas == 1 || (ctas == 2 && n_mma == 256), I64B_ERR_ARG, "CTA pairs need the 256-wide tile");
     I64B_CHECK(p.num_groups >= 1 && p.num_groups <= I64B_MAX_GROUPS, I64B_ERR_ARG, "bad group count %d",
                p.num_groups);
@@ -1287,22 +1315,24 @@ int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtenso
         const int pairs = sms / 2;
         const int grid2 = 2 * (int)(max_tiles < pairs ? max_tiles : pairs);
         if (p.gather_idx != nullptr) {
-            I64B_CHECK(!is_int8 && dual, I64B_ERR_ARG, "row gather is built for the bf16 GEMM1 pair kernel");
-            return launch_inst<false, true, 256, 2, true>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+            I64B_CHECK(type == kTypeBf16 && dual, I64B_ERR_ARG, "row gather is built for the bf16 GEMM1 pair kernel");
+            return launch_inst<kTypeBf16, true, 256, 2, true>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
         }
-        if (is_int8 && dual) return launch_inst<true, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
-        if (is_int8) return launch_inst<true, false, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
-        if (dual) return launch_inst<false, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
-        return launch_inst<false, false, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+#define I64B_PAIR(T)                                                                                   \
+        if (type == T && dual) return launch_inst<T, true, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);  \
+        if (type == T) return launch_inst<T, false, 256, 2>(tmA0, tmA1, tmB0, tmB1, p, grid2, stream);
+        I64B_PAIR(kTypeInt8) I64B_PAIR(kTypeFp8) I64B_PAIR(kTypeBf16)
+#undef I64B_PAIR
     }
     const int grid = (int)(max_tiles < sms ? max_tiles : sms);
-#define I64B_DISPATCH(I8, DUAL, N)                                                              \
-    if (is_int8 == I8 && dual == DUAL && n_mma == N)                                            \
-        return launch_inst<I8, DUAL, N, 1>(tmA0, tmA1, tmB0, tmB1, p, grid, stream);
-    I64B_DISPATCH(false, false, 64) I64B_DISPATCH(false, false, 128) I64B_DISPATCH(false, false, 256)
-    I64B_DISPATCH(false, true, 64) I64B_DISPATCH(false, true, 128) I64B_DISPATCH(false, true, 256)
-    I64B_DISPATCH(true, false, 64) I64B_DISPATCH(true, false, 128) I64B_DISPATCH(true, false, 256)
-    I64B_DISPATCH(true, true, 64) I64B_DISPATCH(true, true, 128) I64B_DISPATCH(true, true, 256)
+#define I64B_DISPATCH(T, DUAL, N)                                                               \
+    if (type == T && dual == DUAL && n_mma == N)                                                \
+        return launch_inst<T, DUAL, N, 1>(tmA0, tmA1, tmB0, tmB1, p, grid, stream);
+#define I64B_DISPATCH_T(T)                                                                      \
+    I64B_DISPATCH(T, false, 64) I64B_DISPATCH(T, false, 128) I64B_DISPATCH(T, false, 256)        \
+    I64B_DISPATCH(T, true, 64) I64B_DISPATCH(T, true, 128) I64B_DISPATCH(T, true, 256)
+    I64B_DISPATCH_T(kTypeBf16) I64B_DISPATCH_T(kTypeInt8) I64B_DISPATCH_T(kTypeFp8)
+#undef I64B_DISPATCH_T
 #undef I64B_DISPATCH
     i64b_set_error("unsupported GEMM tile configuration n_mma=%d", n_mma);
     return I64B_ERR_ARG;

@@ -3,6 +3,9 @@
 #include <cuda.h>
 #include "i64b_common.cuh"
 
+// Operand kinds: bf16 x bf16 -> fp32 (kind::f16), int8 x int8 -> int32 (kind::i8), E4M3 x E4M3 -> fp32 (kind::f8f6f4)
+enum { I64B_TYPE_BF16 = 0, I64B_TYPE_INT8 = 1, I64B_TYPE_FP8 = 2 };
+
 // Epilogue selection (runtime, within a template instantiation)
 enum {
     I64B_EPI_F32 = 0,       // plain: out = acc (fp32 or bf16 store)
@@ -66,7 +69,7 @@ int i64b_encode_tmap(CUtensorMap* out, const void* base, bool is_int8, int64_t r
 // ctas = 2 runs CTA pairs (cta_group::2, M = 256 per MMA; n_mma must be 256): the B tensor maps must then have
 // 128-row boxes (each CTA stages half of the B tile) and max_tiles counts (256-row, n) units.
 // p.gather_idx != nullptr (bf16, dual, ctas == 2 only): see I64bGemmParams::gather_idx.
-int i64b_launch_gemm(bool is_int8, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+int i64b_launch_gemm(int type /* I64B_TYPE_* */, bool dual, int n_mma, int ctas, const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                      const CUtensorMap& tmB0, const CUtensorMap& tmB1, const I64bGemmParams& p,
                      int64_t max_tiles, cudaStream_t stream);
 

@@ -63,7 +63,7 @@ struct I64bDispatchArgs {
     int64_t n;
     int hidden;
     int top_k, num_experts;
-    int quantize;               // 1: per-row int8 quantisation fused into the scatter
+    int quantize;               // 1: per-row int8 quantisation fused into the scatter; 2: per-row FP8 E4M3 (scale = absmax / 448)
     const float* preq_scale;    // non-null: x is ALREADY int8 [N, H] with these per-token scales (x_preq from the fused
                                 // RMSNorm+quant): rows and scales are copied, nothing is re-quantised (quantize must be 0)
     int shared_copy;            // 1: also write row N*K + t (token order) for the shared expert
@@ -95,6 +95,11 @@ int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_
 // `scale` as [3, rows_b] by pair-order row; out_b / scale_b are ignored
 // `groups` (device): the first row set is the rows of these GEMM groups instead of rows [0, rows) — `rows` is then only
 // an upper bound used to size the grid
+
+// bf16 SwiGLU rows [rows, cols] -> FP8 E4M3 rows + one fp32 scale per row (quantize_activations_fp8, core/fp8.py:113-129);
+// two row sets per launch (routed assignments, shared expert), either may be empty
+int i64b_run_requant_fp8(const void* h, uint8_t* out, float* scale, int64_t rows, int cols, const void* h_b, uint8_t* out_b,
+                         float* scale_b, int64_t rows_b, int cols_b, cudaStream_t stream);
 
 struct I64bCombineArgs {
     const float* y;             // [N*K + N, H] fp32 per-assignment outputs (shared rows last)

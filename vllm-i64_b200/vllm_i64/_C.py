@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libi64b.so")
 
 BF16, F32, F16 = 0, 1, 2
 STAGE_PLAN, STAGE_DISPATCH, STAGE_GEMM1, STAGE_REQUANT, STAGE_GEMM2, STAGE_COMBINE, STAGE_ALL = 1, 2, 4, 8, 16, 32, 0xFF
-MODE_BF16, MODE_W8A8 = 0, 1
+MODE_BF16, MODE_W8A8, MODE_FP8 = 0, 1, 2
 DEBUG_KEEP_TAPS, DEBUG_FUSE_COMBINE, DEBUG_NO_FUSED, DEBUG_TRI, DEBUG_NO_TRI, DEBUG_TRI_FOLD = 1, 2, 4, 8, 16, 32
 DEBUG_NO_OVERLAP, DEBUG_GATHER = 64, 128
 TRI_MIN_ROWS_ONEACC, TRI_MIN_ROWS_FOLD = 288, 512      # include/i64b.h
@@ -77,6 +77,7 @@ _SIGNATURES = {
     "i64b_moe_packed_bytes": (_Z, [_P]),
     "i64b_moe_load_bf16": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "i64b_moe_load_w8a8": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "i64b_moe_load_fp8": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "i64b_moe_set_table": (_I, [_P, _P]),
     "i64b_moe_workspace_bytes": (_Z, [_P, _L]),
     "i64b_moe_forward": (_I, [_P, _P, _P, _P, _I, _L, _P, _Z, _P]),

@@ -75,6 +75,24 @@ class I64Block:
                                                  _C.stream_ptr(self.device)))
             self._keep = ts
 
+    def load_fp8(self, w13_q, w13_s, w2_q, w2_s, sh13_q=None, sh13_s=None, sh2_q=None, sh2_s=None) -> None:
+        """Materialised ``(out,in)`` E4M3 weights (``torch.float8_e4m3fn`` or their uint8 view) + per-out-row fp32 scales
+        (``quantize_fp8``, core/fp8.py:75-110); same layouts as :meth:`load_w8a8`."""
+        def as_u8(t):
+            if t is None:
+                return None
+            t = t.detach().contiguous()
+            return t.view(torch.uint8) if t.dtype != torch.uint8 else t
+        with torch.cuda.device(self.device):
+            self._alloc_packed()
+            ts = [as_u8(w13_q), None if w13_s is None else w13_s.detach().float().contiguous(),
+                  as_u8(w2_q), None if w2_s is None else w2_s.detach().float().contiguous(),
+                  as_u8(sh13_q), None if sh13_s is None else sh13_s.detach().float().contiguous(),
+                  as_u8(sh2_q), None if sh2_s is None else sh2_s.detach().float().contiguous()]
+            _C.check(_C.lib().i64b_moe_load_fp8(self._h, *[_C.ptr(t) for t in ts], self._packed.data_ptr(),
+                                                _C.stream_ptr(self.device)))
+            self._keep = ts
+
     def set_table(self, table_i64: torch.Tensor) -> None:
         """``topk_token_to_expert [K,V]`` int64 → uint8 device table."""
         t = table_i64.detach().to(self.device, torch.int64).contiguous()
