@@ -628,7 +628,7 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
     single = I64Block(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device)
     single.load_bf16(*ws0)
     single.set_table(table0)
-    single.set_debug(_C.DEBUG_NO_FUSED)
+    single.set_debug(_C.DEBUG_NO_FUSED | _C.DEBUG_TRI_FOLD)     # the forms that sum in the reference's order (EP's own order)
     want = single.forward(x, ids, torch.float32)
     for name, dt in (("f32", torch.float32), ("bf16", torch.bfloat16)):
         b = EPTokenRoutedBlock(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], _C.MODE_BF16, device, ep, transport_dtype=dt)

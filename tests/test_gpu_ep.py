@@ -106,7 +106,7 @@ def _worker(rank, world, port, case, ret):
             single = Hh.build_gpu_block(cfg, w, table, "bf16", device=dev)
             # force the kernel chain: the EP path runs the chain's GEMMs, and the fused decode kernel splits the shared
             # expert's K range differently (same bar against the oracle, different bits)
-            single.set_debug(_C.DEBUG_NO_FUSED)
+            single.set_debug(_C.DEBUG_NO_FUSED | _C.DEBUG_TRI_FOLD)    # the forms that sum in the reference's order
             one = single.forward(xl, il, torch.float32)
             torch.cuda.synchronize(dev)
             res["bit_identical_f32"] = bool(torch.equal(out, one))

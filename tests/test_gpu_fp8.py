@@ -84,7 +84,13 @@ def test_fp8_block_matches_oracle(case):
 def test_fp8_dense_ffn_and_bf16_output():
     """num_experts == 0: the dense FFN of layers/dense_mlp.py:75-83 (dense-306 width), bf16 output, graph replay."""
     n = 513
-    cfg, w, table, ids, x = Hh.make_block(1024, 0, 0, 4096, 1000, 0, n, seed=2)
+    rng = np.random.RandomState(2)
+    u = lambda shape, fan: Hh.bf16_round(rng.uniform(-1, 1, size=shape).astype(np.float32) / np.sqrt(fan))
+    w = O.MoEWeights(np.zeros((0, 1024, 0), np.float32), np.zeros((0, 1024, 0), np.float32), np.zeros((0, 0, 1024), np.float32),
+                     u((4096, 1024), 1024), u((4096, 1024), 1024), u((1024, 4096), 4096))
+    cfg = O.MoEConfig(1024, 0, 0, 1000, top_k=0, shared_inter=4096)
+    table = np.zeros((0, 1000), np.int64)
+    x = Hh.bf16_round(rng.randn(n, 1024).astype(np.float32))
     wq = O.quantize_moe_weights_fp8(w)
     xg = Hh.to_cuda(x, torch.bfloat16)
     blk = build_fp8(cfg, wq, table)

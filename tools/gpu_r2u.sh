@@ -5,6 +5,6 @@ mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_fp8.py -m gpu -q -s --timeout 300 > gpurun_out/r2u_pytest_fp8.log 2>&1
 echo "pytest exit $?" >> gpurun_out/r2u_pytest_fp8.log
 grep -v "^$" gpurun_out/r2u_pytest_fp8.log | tail -40
-timeout 900 python -m pytest tests -m gpu -q -x --timeout 300 --deselect tests/test_gpu_fp8.py > gpurun_out/r2u_pytest_all.log 2>&1
+timeout 900 python -m pytest tests -m gpu -q --timeout 300 --deselect tests/test_gpu_fp8.py > gpurun_out/r2u_pytest_all.log 2>&1
 echo "pytest exit $?" >> gpurun_out/r2u_pytest_all.log
 tail -8 gpurun_out/r2u_pytest_all.log
