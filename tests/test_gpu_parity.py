@@ -274,9 +274,19 @@ def test_block_linearity_full_size():
     xt, it = cu(x, torch.bfloat16), cu(ids)
     full = blk.forward(xt, it, torch.float32)
     sub = torch.arange(0, n, 37, device=DEV)
+    # 16K tokens take the fused down projection (one fp32 sum over K = 2*I_e + S); the 443-token subset would take GEMM2 +
+    # combine (three rounded partial sums): same form first — the rows must not depend on their neighbours at all —
+    # then across the two forms, which differ by fp32 summation order only
+    form = blk.tri_form(n)
+    blk.set_debug(_C.DEBUG_TRI if form else 0)
+    part = blk.forward(xt[sub].contiguous(), it[sub].contiguous(), torch.float32)
+    assert blk.tri_form(sub.numel()) == form
+    mx, mean = O.rel_errors(part.cpu().numpy(), full[sub].cpu().numpy())
+    assert mx < 1e-6 and mean < 1e-7, (mx, mean)
+    blk.set_debug(_C.DEBUG_NO_TRI)
     part = blk.forward(xt[sub].contiguous(), it[sub].contiguous(), torch.float32)
     mx, mean = O.rel_errors(part.cpu().numpy(), full[sub].cpu().numpy())
-    assert mx < 1e-5 and mean < 1e-6, (mx, mean)
+    assert mx < 1e-5 and mean < 1e-5, (mx, mean)
     rows = np.arange(0, n, 997)                                   # oracle on a sample of rows
     ref = O.moe_block_fp32(x[rows], ids[rows], table, w, cfg, inter_bf16=True)
     Hh.assert_close(full[cu(rows)].cpu().numpy(), ref, "full-size sample rows")
