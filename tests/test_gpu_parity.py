@@ -278,7 +278,7 @@ def test_block_linearity_full_size():
     # combine (three rounded partial sums): same form first — the rows must not depend on their neighbours at all —
     # then across the two forms, which differ by fp32 summation order only
     form = blk.tri_form(n)
-    blk.set_debug(_C.DEBUG_TRI if form else 0)
+    blk.set_debug((_C.DEBUG_TRI | _C.DEBUG_NO_FUSED) if form else 0)
     part = blk.forward(xt[sub].contiguous(), it[sub].contiguous(), torch.float32)
     assert blk.tri_form(sub.numel()) == form
     mx, mean = O.rel_errors(part.cpu().numpy(), full[sub].cpu().numpy())
