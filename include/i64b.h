@@ -400,6 +400,17 @@ int i64b_moe_forward_dispatched(i64b_layer* layer, const i64b_ep_ctx* ctx, void*
  * Stand-alone W8A8 / weight-only GEMM ops  (a12, a13)
  * ------------------------------------------------------------------------- */
 
+/* FP8 (f4).  Per-row E4M3 quantisation of [rows, cols] bf16 / fp16 / fp32 rows: scale = max(absmax, 1e-12) / 448,
+ * q = e4m3((x / scale).clamp(+-448)) in IEEE fp32, round to nearest even — quantize_activations_fp8 and
+ * quantize_fp8(per_channel=True), core/fp8.py:75-129; bit-exact with them. */
+int i64b_quantize_rows_fp8(const void* x, int dtype, uint8_t* q, float* scale, int64_t rows, int64_t cols,
+                           i64b_stream_t stream);
+/* out[m,n] = (x_q[m,:] . w_q[n,:]) * (x_scale[m] * w_scale[n]) with E4M3 operands and fp32 accumulation (tcgen05
+ * kind::f8f6f4), fp32 or bf16 output.  Replaces the torch._scaled_mm call sites of fp8_linear / fp8_fused_gate_up
+ * (core/fp8.py:176-182, 236-242). */
+int i64b_fp8_gemm(const uint8_t* x_q, const float* x_scale, const uint8_t* w_q, const float* w_scale, void* out,
+                  int out_dtype, int64_t m, int64_t n, int64_t k, i64b_stream_t stream);
+
 /* out_f32[m,n] = (x_q[m,:] . w_q[n,:]) * (x_scale[m] * w_scale[n])  — tcgen05 kind::i8, exact INT32.
  * Replaces int8_linear_native's torch._int_mm + rescale (core/quantization.py:119-176) and
  * triton_int8_gemm (kernels/triton/I64_int8_gemm.py:30-156).  acc_out (int32 [m,n]) optional. */

@@ -118,3 +118,53 @@ def test_fp8_layer_rejects_other_weights():
     blk = build_fp8(cfg, O.quantize_moe_weights_fp8(w), table)
     with pytest.raises(RuntimeError):
         blk.load_bf16(*[Hh.to_cuda(t) for t in (w.gate, w.up, w.down, w.shared_gate, w.shared_up, w.shared_down)])
+
+
+def test_fp8_host_mirror_ops():
+    """core/fp8.py surface on the kernels: quantisers bit-exact with torch's own E4M3 conversion (= the reference's ops),
+    fp8_linear / fp8_fused_gate_up against the restatement, TokenRoutedMLP.quantize_fp8() and DenseMLP.quantize_fp8()."""
+    from vllm_i64.core import fp8 as F8
+    from vllm_i64.layers.dense_mlp import DenseMLP
+    from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = (torch.randn(77, 256, device="cuda", generator=g) * torch.logspace(-2, 1, 77, device="cuda").unsqueeze(1)).to(torch.bfloat16)
+    xq, xs = F8.quantize_activations_fp8(x)
+    xf = x.float()
+    sc = xf.abs().amax(-1, keepdim=True).clamp(min=1e-12) / 448.0
+    want = (xf / sc).clamp(-448, 448).to(torch.float8_e4m3fn)
+    assert xq.dtype == torch.float8_e4m3fn and xs.shape == (77, 1)
+    assert torch.equal(xs, sc) and torch.equal(xq.view(torch.uint8), want.view(torch.uint8))
+    w = torch.randn(96, 256, device="cuda", generator=g) / 16
+    wq, ws = F8.quantize_fp8(w)
+    qo, so = O.quantize_rows_fp8(w.cpu().numpy())
+    assert np.array_equal(wq.view(torch.uint8).cpu().numpy(), O.e4m3_encode(qo)) and np.array_equal(ws.cpu().numpy(), so[:, 0])
+    y = F8.fp8_linear(x, wq, ws)
+    assert y.dtype == x.dtype
+    aq, as_ = O.quantize_rows_fp8(x.float().cpu().numpy())
+    ref = O.scaled_mm(aq, as_, qo, so[:, 0])
+    mx, mean = O.rel_errors(y.float().cpu().numpy(), ref)
+    assert mx <= 1e-2 and mean <= 2e-3, (mx, mean)            # bf16 output rounding
+    gate, up = F8.fp8_fused_gate_up(x.float(), wq, ws, 48)
+    mx, mean = O.rel_errors(torch.cat([gate, up], -1).cpu().numpy(), ref)
+    assert mx <= 1e-5 and mean <= 1e-6, (mx, mean)            # fp32 in, fp32 out: summation order only
+    # modules
+    cfg, wts, table, ids, xx = Hh.make_block(256, 4, 128, 128, 1000, 2, 300, seed=4)
+    m = TokenRoutedMLP(256, 4 * 128, 4, 1000, shared_expert=True, shared_intermediate_size=128, top_k=2,
+                       top_k_primary_weight=0.5, shared_output_scale=1.0, routed_output_scale=2.0)
+    with torch.no_grad():
+        m.gate_proj_w.copy_(torch.from_numpy(wts.gate)); m.up_proj_w.copy_(torch.from_numpy(wts.up))
+        m.down_proj_w.copy_(torch.from_numpy(wts.down))
+        m.shared_gate.weight.copy_(torch.from_numpy(wts.shared_gate)); m.shared_up.weight.copy_(torch.from_numpy(wts.shared_up))
+        m.shared_down.weight.copy_(torch.from_numpy(wts.shared_down))
+        m.topk_token_to_expert.copy_(torch.from_numpy(table)); m.token_to_expert.copy_(torch.from_numpy(table[0]))
+    m = m.cuda().quantize_fp8()
+    out = m(Hh.to_cuda(xx, torch.bfloat16).float(), Hh.to_cuda(ids))
+    ref = O.moe_block_fp8(xx, ids, table, O.quantize_moe_weights_fp8(wts), cfg)
+    mx, mean = O.rel_errors(out.float().cpu().numpy(), ref)
+    assert mx <= TOL_MAX and mean <= TOL_MEAN, (mx, mean)
+    d = DenseMLP(256, 512).cuda()
+    xd = torch.randn(50, 256, device="cuda", generator=g)
+    want = d(xd)
+    got = d.quantize_fp8()(xd)
+    mx, mean = O.rel_errors(got.cpu().numpy(), want.cpu().numpy())
+    assert mean <= 0.1 and mx <= 0.35, (mx, mean)             # FP8 against the bf16 block: the format's own 6 % noise

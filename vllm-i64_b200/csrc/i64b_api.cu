@@ -1137,6 +1137,34 @@ int i64b_int8_gemm(const int8_t* x_q, const float* x_scale, const int8_t* w_q, c
     return i64b_launch_gemm(true, false, n_mma, 1, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
 }
 
+int i64b_fp8_gemm(const uint8_t* x_q, const float* x_scale, const uint8_t* w_q, const float* w_scale, void* out, int out_dtype,
+                  int64_t m, int64_t n, int64_t k, i64b_stream_t stream) {
+    if (m == 0 || n == 0) return I64B_OK;
+    I64B_CHECK(x_q && w_q && out && x_scale && w_scale, I64B_ERR_ARG, "null pointer");
+    I64B_CHECK(out_dtype == I64B_BF16 || out_dtype == I64B_F32, I64B_ERR_ARG, "unsupported output dtype");
+    I64B_CHECK(k > 0 && k % 16 == 0 && n % 16 == 0, I64B_ERR_ARG, "k (%lld) and n (%lld) must be multiples of 16",
+               (long long)k, (long long)n);
+    I64B_CHECK(m < ((int64_t)1 << 31) && n < ((int64_t)1 << 31), I64B_ERR_ARG, "matrix too large");
+    const int n_mma = pick_nmma_single(m, n);
+    CUtensorMap ta, tb;
+    int rc = i64b_encode_tmap(&ta, x_q, true, m, k, k, 128);
+    if (rc) return rc;
+    rc = i64b_encode_tmap(&tb, w_q, true, n, k, k, n_mma);
+    if (rc) return rc;
+    I64bGemmParams gp = {};
+    gp.inline_group = I64bGroup{0, (int32_t)m, 0, (int32_t)n, 0, 0, 0, 0};
+    gp.num_groups = 1;
+    gp.k[0] = gp.k[1] = (int32_t)k;
+    gp.out[0] = gp.out[1] = out;
+    gp.ld_out[0] = gp.ld_out[1] = n;
+    gp.out_dtype = out_dtype;
+    gp.epi = I64B_EPI_DEQUANT;
+    gp.row_scale[0] = gp.row_scale[1] = x_scale;
+    gp.col_scale[0] = gp.col_scale[1] = w_scale;
+    const int64_t tiles = ((m + 127) / 128) * ((n + n_mma - 1) / n_mma);
+    return i64b_launch_gemm(I64B_TYPE_FP8, false, n_mma, 1, ta, ta, tb, tb, gp, tiles, (cudaStream_t)stream);
+}
+
 int i64b_bf16_gemm(const void* a, const void* b, const float* col_scale, void* out, int out_dtype, int64_t m,
                    int64_t n, int64_t k, i64b_stream_t stream) {
     if (m == 0 || n == 0) return I64B_OK;

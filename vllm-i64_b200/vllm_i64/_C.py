@@ -77,6 +77,8 @@ _SIGNATURES = {
     "i64b_moe_packed_bytes": (_Z, [_P]),
     "i64b_moe_load_bf16": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "i64b_moe_load_w8a8": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "i64b_quantize_rows_fp8": (_I, [_P, _I, _P, _P, _L, _L, _P]),
+    "i64b_fp8_gemm": (_I, [_P, _P, _P, _P, _P, _I, _L, _L, _L, _P]),
     "i64b_moe_load_fp8": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "i64b_moe_set_table": (_I, [_P, _P]),
     "i64b_moe_workspace_bytes": (_Z, [_P, _L]),

@@ -30,16 +30,29 @@ class _DenseBlockMixin(torch_ops.TracedLayer):
     def _ensure_block(self, device: torch.device) -> I64Block:
         gate, up, down = self._weights()
         # identity + storage + in-place version; writes through ``.data`` are invisible to it: see invalidate()
+        ref_fp8 = getattr(self, "gate_fp8", None) is not None      # buffers left by the reference's _quantize_dense_mlp_fp8
+        if ref_fp8:
+            self.quantization = "fp8"
         key = (device, self.quantization, tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in (gate, up, down)),
                tuple(id(p) for p in self.parameters()))
         if self._block is not None and self._block_key == key:
             return self._block
         inter, hidden = gate.shape
-        mode = _C.MODE_W8A8 if self.quantization == "int8" else _C.MODE_BF16
+        mode = {"int8": _C.MODE_W8A8, "fp8": _C.MODE_FP8}.get(self.quantization, _C.MODE_BF16)
         blk = I64Block(hidden, 0, 0, inter, 1, 0, [], 1.0, 1.0, mode, device)
         with torch.no_grad():
             if mode == _C.MODE_BF16:
                 blk.load_bf16(None, None, None, gate, up, down)
+            elif mode == _C.MODE_FP8:
+                if ref_fp8:         # core/loader.py:958-987: the bytes and scales the reference loader made, as they are
+                    q13 = torch.cat([self.gate_fp8.view(torch.uint8), self.up_fp8.view(torch.uint8)], dim=0).to(device)
+                    s13 = torch.cat([self.gate_fp8_scale, self.up_fp8_scale], dim=0).to(device)
+                    q2, s2 = self.down_fp8.view(torch.uint8).to(device), self.down_fp8_scale.to(device)
+                else:
+                    from vllm_i64.core.fp8 import quantize_fp8
+                    q13, s13 = quantize_fp8(torch.cat([gate, up], dim=0).float().contiguous())
+                    q2, s2 = quantize_fp8(down.float().contiguous())
+                blk.load_fp8(None, None, None, None, q13, s13, q2, s2)
             else:
                 from vllm_i64.core.quantization import quantize_int8
                 q13, s13 = quantize_int8(torch.cat([gate, up], dim=0).float().contiguous())
@@ -53,6 +66,13 @@ class _DenseBlockMixin(torch_ops.TracedLayer):
 
     def quantize_w8a8(self):
         self.quantization = "int8"
+        self._block = None
+        return self
+
+    def quantize_fp8(self):
+        """layers/dense_mlp.py:75-83 (``_forward_fp8``) as one FP8 block: fused gate|up GEMM, SiLU·up, per-row re-quantisation,
+        down GEMM on tcgen05 ``kind::f8f6f4``."""
+        self.quantization = "fp8"
         self._block = None
         return self
 

@@ -150,7 +150,7 @@ class TokenRoutedMLP(torch_ops.TracedLayer, nn.Module):
         rs, ss = self._scales()
         if self.tp_size > 1:
             ss = ss / self.tp_size     # the shared expert is replicated: its term is summed tp_size times below
-        mode = _C.MODE_W8A8 if self.quantization == "int8" else _C.MODE_BF16
+        mode = {"int8": _C.MODE_W8A8, "fp8": _C.MODE_FP8}.get(self.quantization, _C.MODE_BF16)
         blk = I64Block(self.hidden_size, self.num_experts, self.expert_inter, self.shared_size, self.vocab_size,
                        self.top_k, self.route_weights(), rs, ss, mode, device)
         gate, up, down = self._expert_tensors()
@@ -159,7 +159,10 @@ class TokenRoutedMLP(torch_ops.TracedLayer, nn.Module):
             if mode == _C.MODE_BF16:
                 blk.load_bf16(gate, up, down, sg, su, sd)
             else:
-                from vllm_i64.core.quantization import quantize_int8
+                if mode == _C.MODE_FP8:
+                    from vllm_i64.core.fp8 import quantize_fp8 as quantize_int8      # same call shape: rows -> (q, scale)
+                else:
+                    from vllm_i64.core.quantization import quantize_int8
                 # materialised (out,in) forms, layers/token_routed_mlp.py:232-242 of the reference
                 w13 = torch.cat([gate.transpose(1, 2), up.transpose(1, 2)], dim=1).float().contiguous()
                 w2 = down.transpose(1, 2).float().contiguous()
@@ -170,10 +173,18 @@ class TokenRoutedMLP(torch_ops.TracedLayer, nn.Module):
                     sh13_q, sh13_s = quantize_int8(torch.cat([sg, su], dim=0).float().contiguous())
                     sh2_q, sh2_s = quantize_int8(sd.float().contiguous())
                     sh = [sh13_q, sh13_s, sh2_q, sh2_s]
-                blk.load_w8a8(w13_q, w13_s, w2_q, w2_s, *sh)
+                (blk.load_fp8 if mode == _C.MODE_FP8 else blk.load_w8a8)(w13_q, w13_s, w2_q, w2_s, *sh)
             blk.set_table(self.topk_token_to_expert)
         self._block, self._block_key = blk, key
         return blk
+
+    def quantize_fp8(self) -> "TokenRoutedMLP":
+        """Switch the block to FP8: E4M3 weights per out-row, activations quantised per token, fp32 accumulation — the recipe
+        of core/fp8.py + layers/dense_mlp.py:75-83 (fused gate|up, SiLU·up, per-row re-quantisation, down) applied to every
+        expert's materialised linears and to the shared expert."""
+        self.quantization = "fp8"
+        self._block = None
+        return self
 
     def quantize_w8a8(self) -> "TokenRoutedMLP":
         """Switch the block to dynamic W8A8 (per-token activation scale × per-out-channel weight scale, INT32
