@@ -49,6 +49,8 @@ WORKLOADS = {
                         mode="bf16", reps=200),
     "prefill_w8a8": dict(desc="tr-hash-moe-500m INT8 W8A8 prefill, 16K-token batch (config 3)", **_M500, L=4, N=16384,
                          mode="int8", reps=40),
+    "prefill_fp8": dict(desc="tr-hash-moe-500m FP8 (E4M3 weights and activations) prefill, 16K-token batch", **_M500, L=4,
+                        N=16384, mode="fp8", reps=40),
     "prefill_bf16": dict(desc="tr-hash-moe-500m bf16 prefill, 16K-token batch", **_M500, L=4, N=16384, mode="bf16", reps=40),
     "decode_w8a8": dict(desc="tr-hash-moe-500m INT8 W8A8 decode, 256 concurrent sequences", **_M500, L=24, N=256,
                         mode="int8", reps=200),
@@ -127,7 +129,7 @@ def cfg_json(wl, world, parallelism=None):
 def stage_bytes(wl, fused_combine=False):
     """ALGORITHMIC HBM bytes per launch of each stage for one layer, and flops of the GEMMs."""
     H, E, I, S, K, N = (wl[k] for k in "HEISKN")
-    a = 1 if wl["mode"] == "int8" else 2               # bytes per operand element fed to the tensor cores
+    a = 1 if wl["mode"] in ("int8", "fp8") else 2      # bytes per operand element fed to the tensor cores
     R = N * K
     has_s = 1 if S else 0
     rows = R + N * has_s
@@ -136,9 +138,10 @@ def stage_bytes(wl, fused_combine=False):
     drows = rows if a == 1 else R          # bf16: the shared expert reads x in place (no token-order copy)
     b["dispatch"] = (N * H * 2 + drows * (H * a + (4 if a == 1 else 0)) + R * 4 * 3) if drows else 0
     w13 = (E * 2 * I + 2 * S) * H * a
-    inter_w = (R * I + N * S) * (4 if a == 1 else 2)   # W8A8: Q14 int32 out; bf16: bf16 out
+    f8 = wl["mode"] == "fp8"
+    inter_w = (R * I + N * S) * (4 if (a == 1 and not f8) else 2)   # W8A8: Q14 int32 out; bf16 and FP8: bf16 out
     b["gemm1"] = w13 + rows * H * a + inter_w
-    b["requant"] = (R * I + N * S) * 5 if a == 1 else 0
+    b["requant"] = (R * I + N * S) * (3 if f8 else 5) if a == 1 else 0
     w2 = (E * H * I + H * S) * a
     if has_s and (E == 0 or fused_combine):
         # fused combine: the shared expert's GEMM2 tiles pull the routed fp32 rows and write the block output
@@ -152,7 +155,7 @@ def stage_bytes(wl, fused_combine=False):
 
 
 def block_min_bytes(wl):
-    a = 1 if wl["mode"] == "int8" else 2
+    a = 1 if wl["mode"] in ("int8", "fp8") else 2
     return ((wl["E"] * 3 * wl["I"] + 3 * wl["S"]) * wl["H"] * a) + wl["N"] * wl["H"] * 2 * 2     # weights once + x in + out
 
 
@@ -234,8 +237,11 @@ def synth_weights(wl, layer, device):
     return gate, up, down, sg, su, sd
 
 
-def quantize_weights(gate, up, down, sg, su, sd):
-    from vllm_i64.core.quantization import quantize_int8
+def quantize_weights(gate, up, down, sg, su, sd, fp8=False):
+    if fp8:
+        from vllm_i64.core.fp8 import quantize_fp8 as quantize_int8      # same call shape: rows -> (q, per-row scale)
+    else:
+        from vllm_i64.core.quantization import quantize_int8
     ex = [None] * 4
     if gate is not None:
         q13, s13 = quantize_int8(torch.cat([gate.transpose(1, 2), up.transpose(1, 2)], 1).contiguous())
@@ -255,13 +261,15 @@ def build_layers(wl, device):
     from vllm_i64.kernels.block import I64Block
     from tools.synth_data import synthetic_hash_table
     H, E, I, S, V, K = (wl[k] for k in "HEISVK")
-    mode = _C.MODE_W8A8 if wl["mode"] == "int8" else _C.MODE_BF16
+    mode = {"int8": _C.MODE_W8A8, "fp8": _C.MODE_FP8}.get(wl["mode"], _C.MODE_BF16)
     layers = []
     for layer in range(wl["L"]):
         blk = I64Block(H, E, I, S, V, K, route_weights(wl), wl["rs"], wl["ss"], mode, device)
         ws = synth_weights(wl, layer, device)
         if mode == _C.MODE_BF16:
             blk.load_bf16(*ws)
+        elif mode == _C.MODE_FP8:
+            blk.load_fp8(*quantize_weights(*ws, fp8=True))
         else:
             blk.load_w8a8(*quantize_weights(*ws))
         if E:
@@ -336,6 +344,30 @@ def measure_int8_peak(device):
         return {"int8_tops": None, "error": f"{type(exc).__name__}: {exc}"[:200]}
 
 
+def measure_fp8_peak(device):
+    """Dense FP8 (E4M3) tensor peak through cuBLASLt (torch._scaled_mm 8192^3, per-tensor scales), best of 10."""
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=device).to(torch.float8_e4m3fn)
+        b = torch.randn(n, n, device=device).to(torch.float8_e4m3fn).t()
+        one = torch.ones((), device=device)
+        for _ in range(3):
+            torch._scaled_mm(a, b, scale_a=one, scale_b=one, out_dtype=torch.bfloat16)
+        torch.cuda.synchronize(device)
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._scaled_mm(a, b, scale_a=one, scale_b=one, out_dtype=torch.bfloat16)
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return {"fp8_tflops": round(2.0 * n ** 3 / (best * 1e-3) / 1e12, 1), "how": "torch._scaled_mm 8192^3 (cuBLASLt), best of 10",
+                "src": "measured in this run"}
+    except Exception as exc:
+        return {"fp8_tflops": None, "error": f"{type(exc).__name__}: {exc}"[:200]}
+
+
 # ------------------------------------------------------------------------------------------------- one workload
 def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, rank=0, barrier=None, sampler=None,
                      with_stages=True):
@@ -386,7 +418,7 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
     ms_host = time_graph(step_host_call, max(3, min(steps, 20)), 3, stream, barrier)
     us_layer = ms * 1e3 / (steps * L)
     res = {"desc": wl["desc"], "value": N * L * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
-           "us_per_layer": round(us_layer, 3), "steps": steps, "dtype": "bf16" if wl["mode"] == "bf16" else "int8",
+           "us_per_layer": round(us_layer, 3), "steps": steps, "dtype": {"bf16": "bf16", "int8": "int8", "fp8": "fp8_e4m3"}[wl["mode"]],
            "gpu_launches_per_step": int(launches_per_step),
            "e2e": {"value": N * L * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / e2e_steps,
                    "h2d_bytes_per_step": N * H * 2 + (N * 8 if wl["E"] else 0), "d2h_bytes_per_step": N * H * 2,
@@ -397,10 +429,16 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
                "value": N * L * max(3, min(steps, 20)) / (ms_host * 1e-3), "unit": UNIT, "copies_per_step": L,
                "h2d_bytes_per_step": L * (N * H * 2 + N * 8), "d2h_bytes_per_step": L * N * H * 2,
                "via": "i64b_moe_forward_host per layer (the plugin call with HOST buffers: H2D + forward + D2H inside the C ABI)"}}
-    i8 = wl["mode"] == "int8"
-    tensor_peak = (int8_peak.get("int8_tops") or 2.0 * pk["tf_burst"]) if i8 else pk["tf_burst"]
-    tensor_src = ("INT8 burst measured in this run (torch._int_mm)" if (i8 and int8_peak.get("int8_tops"))
-                  else ("2x bf16 burst (nominal ratio; int8 peak unmeasured)" if i8 else pk["src"] + " bf16 burst"))
+    i8 = wl["mode"] in ("int8", "fp8")
+    if wl["mode"] == "fp8":
+        f8p = int8_peak.get("fp8") or {}
+        tensor_peak = f8p.get("fp8_tflops") or 2.0 * pk["tf_burst"]
+        tensor_src = ("FP8 burst measured in this run (torch._scaled_mm)" if f8p.get("fp8_tflops")
+                      else "2x bf16 burst (nominal ratio; fp8 peak unmeasured)")
+    else:
+        tensor_peak = (int8_peak.get("int8_tops") or 2.0 * pk["tf_burst"]) if i8 else pk["tf_burst"]
+        tensor_src = ("INT8 burst measured in this run (torch._int_mm)" if (i8 and int8_peak.get("int8_tops"))
+                      else ("2x bf16 burst (nominal ratio; int8 peak unmeasured)" if i8 else pk["src"] + " bf16 burst"))
     fused = layers[0].uses_fused(N)
     mb = block_min_bytes(wl)
     res["block"] = {"min_bytes": mb, "frac_hbm": round(mb / (us_layer * 1e-6) / 1e9 / pk["hbm"], 4),
@@ -434,7 +472,8 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
             st[sname] = ent
         dom = max(st, key=lambda k: st[k]["us_per_launch"])
         d = st[dom]
-        kkey = {"gemm1": "i64b_gemm_kernel<%d, 1" % (1 if i8 else 0), "gemm2": "i64b_gemm_kernel<%d, 0" % (1 if i8 else 0)}.get(dom, dom)
+        kt = {"bf16": 0, "int8": 1, "fp8": 2}[wl["mode"]]
+        kkey = {"gemm1": "i64b_gemm_kernel<%d, 1" % kt, "gemm2": "i64b_gemm_kernel<%d, 0" % kt}.get(dom, dom)
         if d["frac_hbm"] >= d.get("frac_tensor", 0.0):
             res["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": pk["hbm"], "unit": "GB/s",
                                "frac": d["frac_hbm"], "traffic": ncu_traffic(name, kkey), "peak_source": pk["src"] + " (burst copy)"}
@@ -866,6 +905,7 @@ def main():
 
     # ---------------------------------------------------------------- N = 1
     int8_peak = measure_int8_peak(device)
+    int8_peak["fp8"] = measure_fp8_peak(device)
     head = measure_workload(args.workload, wl, device, args.steps, args.warmup, pk, int8_peak, stream, sampler=sampler,
                             with_stages=not args.no_stages)
     workloads = {}

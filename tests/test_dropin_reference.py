@@ -70,3 +70,30 @@ def test_reference_model_logits_match_on_gpu(dtype, tol_max, tol_mean):
             d = (a - b).abs()
             mx, mean = float(d.max() / a.abs().max()), float(d.mean() / a.abs().mean())
             assert mx <= tol_max and mean <= tol_mean, (kind, dtype, mx, mean)
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_engine_wiring_on_gpu():
+    """SURVEY §8 f2 / f3, executed with the reference's own files: its post-load quantisation passes
+    (core/loader.py:627-751, 958-987) switch the new modules to the W8A8 / FP8 kernels (the TokenRoutedMLP pass is dead code
+    in the reference: hooked by patch_reference_models()), its CUDAGraphRunner (core/cuda_graph.py:21-153) captures and
+    replays the block for every common decode batch size, and the per-layer expert histogram is read from the device."""
+    if not torch.cuda.is_available():
+        pytest.skip("CUDA device required")
+    with tempfile.TemporaryDirectory() as wd:
+        _run("ref", wd, "none", "fp32", [REF])          # writes the checkpoints
+        env = dict(os.environ, PYTHONPATH=os.pathsep.join([PKG, REF]), PYTHONDONTWRITEBYTECODE="1")
+        p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "wiring_worker.py"), wd], env=env, capture_output=True,
+                           text=True, timeout=600, cwd=wd)
+        assert p.returncode == 0, p.stderr[-3000:]
+        info = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("WIRING_JSON ")][-1][len("WIRING_JSON "):])
+    assert "vllm_i64.core.loader._quantize_experts" in info["hooked"]
+    assert info["moe_quantization"] == ["int8"] and info["moe_block_modes"] == [1] and info["moe_int8_launches"] > 0
+    assert info["moe_int8_vs_bf16"][1] <= 0.1, info["moe_int8_vs_bf16"]          # int8 noise on a 2-layer model's logits
+    assert info["expert_load_layers"] == 2 and info["expert_load_row_sums"] == [48]   # 2 x 24 tokens on every route
+    for method in ("int8", "fp8"):
+        assert info[f"dense_{method}_modules"] >= 1 and info[f"dense_{method}_quantization"] == [method]
+        assert info[f"dense_{method}_vs_bf16"][1] <= (0.1 if method == "int8" else 0.25), (method, info[f"dense_{method}_vs_bf16"])
+    assert info["graph_sizes"] == [1, 2, 4, 8, 16, 32, 64]
+    assert all(info["graph_replay_equals_eager"]), info["graph_replay_equals_eager"]

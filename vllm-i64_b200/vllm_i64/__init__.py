@@ -13,3 +13,4 @@ from vllm_i64 import _overlay as _ov  # noqa: E402
 
 _ov.extend(__name__, globals())
 patch_reference_models = _ov.patch_reference_models
+collect_expert_load = _ov.collect_expert_load

@@ -121,4 +121,59 @@ def patch_reference_models() -> list:
             done.append("vllm_i64.models.complexity_deep.model.DenseSwiGLUMLP")
     except ImportError:
         pass
+    done += _hook_reference_loader()
     return done
+
+
+def _hook_reference_loader() -> list:
+    """``vllm-i64 serve --quantization int8`` on a GPU (core/loader.py:627-642): the reference's post-load pass
+    ``_quantize_experts`` looks for ``gate_up_proj`` / ``down_proj`` attributes, which ``TokenRoutedMLP`` never had — the
+    routed experts stayed in floating point (dead code).  With this package active the pass also switches every
+    ``TokenRoutedMLP`` to its W8A8 block (``quantize_w8a8()``), so the flag reaches the INT8 kernels; ``fp8`` does the same
+    through ``_quantize_dense_mlp_fp8``.  ``DenseMLP`` needs no hook: the buffers the reference's passes register
+    (``gate_up_int8`` …, ``gate_fp8`` …) are picked up by the module as they are."""
+    import importlib
+    try:
+        loader = importlib.import_module("vllm_i64.core.loader")
+    except ImportError:
+        return []
+    if getattr(loader, "_i64b_hooked", False):
+        return []
+    from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP
+
+    def wrap(name, switch):
+        orig = getattr(loader, name, None)
+        if orig is None:
+            return None
+
+        def hooked(model, *args, **kwargs):
+            out = orig(model, *args, **kwargs)
+            method = args[0] if args else kwargs.get("method", "fp8")
+            for mod in model.modules():
+                if isinstance(mod, TokenRoutedMLP):
+                    switch(mod, method)
+            return out
+        hooked.__wrapped__ = orig
+        setattr(loader, name, hooked)
+        return "vllm_i64.core.loader." + name
+
+    names = [wrap("_quantize_experts", lambda m, method: m.quantize_w8a8() if method == "int8" else None),
+             wrap("_quantize_dense_mlp_fp8", lambda m, method: m.quantize_fp8())]
+    loader._i64b_hooked = True
+    return [n for n in names if n]
+
+
+def collect_expert_load(model) -> dict:
+    """Device-side expert histogram of every token-routed layer's LAST forward, as host lists — what ``/v1/experts`` and
+    the ``vllm_i64_experts_load`` gauge report (api/_admin.py:464-562 derive it from ``token_to_expert`` alone today).
+    ``{module name: [[count of expert e on route k for e in experts] for k in routes]}``; layers that have not run yet are
+    left out.  One small D2H copy per layer: call it from the admin endpoint, not from the step loop."""
+    from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP
+    out = {}
+    for name, mod in model.named_modules():
+        if isinstance(mod, TokenRoutedMLP) and getattr(mod, "_block", None) is not None:
+            try:
+                out[name] = mod.last_expert_counts().cpu().tolist()
+            except RuntimeError:
+                pass
+    return out

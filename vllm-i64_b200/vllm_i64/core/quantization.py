@@ -36,7 +36,11 @@ def _quantize_rows(x2d: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
 
 def quantize_int8(weight: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """Per-channel (per out-row) symmetric INT8: ``(out,in)`` → int8 + ``(out,)`` fp32 scale
-    (core/quantization.py:80-91).  Arithmetic is fp32 whatever the storage dtype."""
+    (core/quantization.py:80-91).  Arithmetic is fp32 whatever the storage dtype.  Weights still on the HOST (the reference's
+    loader quantises before it moves the model, core/loader.py:627-651) go through the reference's own torch ops when this
+    package overlays it — load time only, never the forward path."""
+    if not weight.is_cuda and _REF_MOD is not None:
+        return _REF_MOD.quantize_int8(weight)
     shape = weight.shape
     q, s = _quantize_rows(weight.reshape(-1, shape[-1]))
     return q.view(shape), s.view(shape[:-1])

@@ -31,8 +31,11 @@ class _DenseBlockMixin(torch_ops.TracedLayer):
         gate, up, down = self._weights()
         # identity + storage + in-place version; writes through ``.data`` are invisible to it: see invalidate()
         ref_fp8 = getattr(self, "gate_fp8", None) is not None      # buffers left by the reference's _quantize_dense_mlp_fp8
+        ref_int8 = getattr(self, "gate_up_int8", None) is not None  # ... and by _quantize_dense_mlp(model, "int8")
         if ref_fp8:
             self.quantization = "fp8"
+        elif ref_int8:
+            self.quantization = "int8"
         key = (device, self.quantization, tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in (gate, up, down)),
                tuple(id(p) for p in self.parameters()))
         if self._block is not None and self._block_key == key:
@@ -54,9 +57,13 @@ class _DenseBlockMixin(torch_ops.TracedLayer):
                     q2, s2 = quantize_fp8(down.float().contiguous())
                 blk.load_fp8(None, None, None, None, q13, s13, q2, s2)
             else:
-                from vllm_i64.core.quantization import quantize_int8
-                q13, s13 = quantize_int8(torch.cat([gate, up], dim=0).float().contiguous())
-                q2, s2 = quantize_int8(down.float().contiguous())
+                if ref_int8:        # core/loader.py:670-683: fused gate|up int8 rows + scales, down int8 + scales
+                    q13, s13 = self.gate_up_int8.to(device), self.gate_up_scale.to(device).float()
+                    q2, s2 = self.down_int8.to(device), self.down_scale.to(device).float()
+                else:
+                    from vllm_i64.core.quantization import quantize_int8
+                    q13, s13 = quantize_int8(torch.cat([gate, up], dim=0).float().contiguous())
+                    q2, s2 = quantize_int8(down.float().contiguous())
                 blk.load_w8a8(None, None, None, None, q13, s13, q2, s2)
         self._block, self._block_key = blk, key
         return blk
