@@ -170,3 +170,27 @@ def test_fp8_host_mirror_ops():
     got = d.quantize_fp8()(xd)
     mx, mean = O.rel_errors(got.cpu().numpy(), want.cpu().numpy())
     assert mean <= 0.1 and mx <= 0.35, (mx, mean)             # FP8 against the bf16 block: the format's own 6 % noise
+
+
+@pytest.mark.parametrize("n,shape", [(900, (256, 4, 128, 128, 1000, 2)), (3001, (256, 8, 128, 256, 5000, 2)),
+                                     (16384, (1024, 8, 512, 1280, 32000, 2))], ids=["small", "zipf", "config3-16k"])
+def test_fp8_fused_down_projection_is_bit_identical_to_the_chain(n, shape):
+    """The FP8 form of the token-major fused down projection (three fp32 accumulators, every segment dequantised with its own
+    row and column scales, folded in the reference's order): the same fp32 operations as GEMM2 + combine_kernel."""
+    h, e, ie, s, v, k = shape
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=13, zipf=(n == 3001))
+    wq = O.quantize_moe_weights_fp8(w)
+    xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
+    chain = build_fp8(cfg, wq, table)
+    chain.set_debug(_C.DEBUG_NO_TRI)
+    tri = build_fp8(cfg, wq, table)
+    tri.set_debug(_C.DEBUG_TRI)
+    assert chain.tri_form(n) == 0 and tri.tri_form(n) == 1
+    for odt in (torch.float32, torch.bfloat16):
+        want = chain.forward(xg, ig, odt)
+        got = tri.forward(xg, ig, odt)
+        torch.cuda.synchronize()
+        bad = (got != want).any(dim=1).nonzero().flatten()
+        assert bad.numel() == 0, f"{bad.numel()} of {n} rows differ from the FP8 chain, first {bad[:8].tolist()}"
+    auto = build_fp8(cfg, wq, table)
+    assert auto.tri_form(n) == (1 if n >= (e * (e - 1) // 2) * _C.TRI_MIN_ROWS_FOLD else 0)

@@ -166,7 +166,7 @@ static i64b_layer::Carve carve_ws(const i64b_layer* L, void* base, int64_t n) {
         const bool tri_shape = c.top_k == 2 && c.num_experts >= 1 && c.num_experts * c.num_experts <= I64B_MAX_EXPERTS;
         cv.tri = i64b_tri_ws_carve(p ? p + off : nullptr, tri_shape ? n : 0, c.top_k, tri_shape ? c.num_experts : 1);
         off += align256(cv.tri.bytes);
-        cv.cat_scale = reinterpret_cast<float*>(take(q && tri_shape ? sizeof(float) * 3 * nn : 0));
+        cv.cat_scale = reinterpret_cast<float*>(take(q8 && tri_shape ? sizeof(float) * 3 * nn : 0));
     }
     cv.bytes = off;
     return cv;
@@ -463,8 +463,7 @@ static bool tri_selected(const i64b_layer* L, const i64b_moe_config& c, int64_t 
     const int E = c.num_experts;
     if (mode == 0 || !plain_call || c.top_k != 2 || E < 2 || E * E > I64B_MAX_EXPERTS) return false;
     if (c.expert_inter % 64 != 0 || c.shared_inter % 64 != 0 || c.hidden_size % 256 != 0) return false;
-    if (c.mode == I64B_MODE_FP8) return false;      // FP8 blocks take GEMM2 + combine
-    if (c.mode == I64B_MODE_W8A8) {     // int8 rows of 128 elements per k-block, a shared expert, rows the re-quantiser holds in registers
+    if (c.mode == I64B_MODE_W8A8 || c.mode == I64B_MODE_FP8) {     // int8 rows of 128 elements per k-block, a shared expert, rows the re-quantiser holds in registers
         static const int w8 = getenv("I64B_TRI_W8A8") ? atoi(getenv("I64B_TRI_W8A8")) : 1;
         if (!w8 || c.shared_inter <= 0 || c.expert_inter % 128 != 0 || c.shared_inter % 128 != 0 || c.expert_inter > 1536 ||
             c.shared_inter > 1536)
@@ -715,7 +714,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.amax_ld[0] = cv.amax_ld_r;
         gp.amax_ld[1] = cv.amax_ld_s;
         gp.silu_lut = L->silu_lut;
-        if (tri && !q) {      // SwiGLU rows go straight to their token's row of the [N, 2I+S] buffer
+        if (tri && !q8) {     // SwiGLU rows go straight to their token's row of the [N, 2I+S] buffer
             gp.out[0] = gp.out[1] = cv.inter_r;
             gp.ld_out[0] = gp.ld_out[1] = 2 * I + S;
             gp.rowmap[0] = cv.tri.rowmap;
@@ -758,8 +757,8 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
             if (rc) return rc;
         }
         if (f8 && (o.stage_mask & I64B_STAGE_REQUANT)) {  // quantize_activations_fp8 of the SwiGLU rows (fp8_linear, core/fp8.py:166)
-            rc = i64b_run_requant_fp8(cv.q14_r, cv.inter_r, cv.inter_scale_r, E > 0 ? R : 0, I, cv.q14_s, cv.inter_s,
-                                      cv.inter_scale_s, S > 0 ? n : 0, S, s);
+            rc = i64b_run_requant_fp8(cv.q14_r, cv.inter_r, tri ? cv.cat_scale : cv.inter_scale_r, E > 0 ? R : 0, I, cv.q14_s,
+                                      cv.inter_s, cv.inter_scale_s, S > 0 ? n : 0, S, s, tri ? &cv.tri : nullptr);
             if (rc) return rc;
         }
         if (q && (o.stage_mask & I64B_STAGE_REQUANT)) {   // re-quantise the integer SwiGLU output per row (quantize_activations_int8 of `inter`)
@@ -792,7 +791,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
         gp.col_scale[1] = L->w2s_scale;
         const int64_t units = n / 256 + (int64_t)E * E;
         if (o.stage_mask & I64B_STAGE_GEMM2) {
-            rc = i64b_launch_gemm_tri(q, tri_one_acc(L, c), L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp,
+            rc = i64b_launch_gemm_tri(gtype, tri_one_acc(L, c), L->tm_cat, L->tm_w2r[1], L->tm_w2s[1], gp,
                                       units * ((H + 255) / 256), s);
             if (rc) return rc;
         }

@@ -879,15 +879,18 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 // y = float(acc) * (s_row * s_col) as GEMM2's dequant epilogue does (core/quantization.py:173), then combine in the same
 // order — bit-identical to the W8A8 chain (and through it to the reference arithmetic).  The folded routed sum goes back into acc0 as fp32 bits.
 constexpr int kTriN = 256;
-template <bool kOneAcc, bool kInt8>
+template <bool kOneAcc, int kType>
 __global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
                      const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ I64bGemmParams p) {
     using Cfg = StageCfg<kTriN, 2>;
     constexpr int kStages = Cfg::kStages;
     constexpr int kStageB = Cfg::kStageB;              // this CTA's 128 weight rows
-    constexpr int kBlockK = kInt8 ? 128 : 64;          // elements per 128-byte row
-    static_assert(!(kOneAcc && kInt8), "W8A8 segments carry their own scales: no shared accumulator");
+    constexpr bool kInt8 = kType == kTypeInt8;
+    constexpr bool kFp8 = kType == kTypeFp8;           // E4M3 operands, fp32 accumulators, the same per-segment scales as W8A8
+    constexpr bool kScaled = kInt8 || kFp8;
+    constexpr int kBlockK = kScaled ? 128 : 64;        // elements per 128-byte row
+    static_assert(!(kOneAcc && kScaled), "quantised segments carry their own scales: no shared accumulator");
     constexpr uint32_t kTmemCols = 512;                // acc0 | acc1
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -977,7 +980,7 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc = make_idesc<kInt8, kTriN, 2>();
+            constexpr uint32_t idesc = make_idesc<kType, kTriN, 2>();
             int stage = 0, iter = 0;
             uint32_t phase = 0;
             for (int tile = unit0; tile < total_tiles; tile += unit_step, ++iter) {
@@ -1003,6 +1006,7 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
                             if constexpr (kInt8) umma_i8_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
+                            else if constexpr (kFp8) umma_f8_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
                             else umma_bf16_cta2(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (fresh | k) ? 1u : 0u);
                         }
                         umma_commit_cta2(&empty_bar[stage]);
@@ -1065,14 +1069,14 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 const int rt = __ldg(p.row_tok + grp.row_start + row_in_group);
                 my_off = ((int64_t)(rt & 0x3FFFFFFF) * p.ld_final + colw0) * fsz;
                 if (rt & 0x40000000) { wa = w1; wb = w0; }
-                if constexpr (kInt8) {
+                if constexpr (kScaled) {
                     const float* sc = p.row_scale[0] + grp.row_start + row_in_group;     // [3, n_tokens] by pair-order row
                     rsa = __ldg(sc);
                     rsb = __ldg(sc + p.n_tokens);
                     rsS = __ldg(sc + 2 * (int64_t)p.n_tokens);
                 }
             }
-            if constexpr (kInt8) {
+            if constexpr (kScaled) {
                 // column scales of this warp's 128 columns: segments 0 / 1 into the (idle until epilogue 2) store staging
                 // block, the shared expert's into the scale block
                 __syncwarp();
@@ -1112,7 +1116,7 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 tmem_ld_32x32(t1 + c, a1);
                 tmem_ld_wait();
 #pragma unroll
-                if constexpr (kInt8) {
+                if constexpr (kScaled) {
 #pragma unroll
                     for (int j4 = 0; j4 < 8; ++j4) {
                         const float4 sa4 = ld_shared_f4(st_addr + (c + j4 * 4) * 4);
@@ -1123,8 +1127,10 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         for (int jj = 0; jj < 4; ++jj) {
                             const int j = j4 * 4 + jj;
                             // result_i32.float() * (x_scale * w_scale)                      core/quantization.py:173
-                            a0[j] = __float_as_uint(__fmul_rn((float)(int)a0[j], __fmul_rn(rsa, sav[jj])));
-                            a1[j] = __float_as_uint(__fmul_rn((float)(int)a1[j], __fmul_rn(rsb, sbv[jj])));
+                            const float f0 = kInt8 ? (float)(int)a0[j] : __uint_as_float(a0[j]);
+                            const float f1 = kInt8 ? (float)(int)a1[j] : __uint_as_float(a1[j]);
+                            a0[j] = __float_as_uint(__fmul_rn(f0, __fmul_rn(rsa, sav[jj])));
+                            a1[j] = __float_as_uint(__fmul_rn(f1, __fmul_rn(rsb, sbv[jj])));
                         }
                     }
                 }
@@ -1151,14 +1157,16 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     tmem_ld_32x32(t1 + c, a1);
                     tmem_ld_wait();
 #pragma unroll
-                    if constexpr (kInt8) {
+                    if constexpr (kScaled) {
 #pragma unroll
                         for (int j4 = 0; j4 < 8; ++j4) {
                             const float4 s4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
                             const float sv[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
-                            for (int jj = 0; jj < 4; ++jj)
-                                a1[j4 * 4 + jj] = __float_as_uint(__fmul_rn((float)(int)a1[j4 * 4 + jj], __fmul_rn(rsS, sv[jj])));
+                            for (int jj = 0; jj < 4; ++jj) {
+                                const float f1 = kInt8 ? (float)(int)a1[j4 * 4 + jj] : __uint_as_float(a1[j4 * 4 + jj]);
+                                a1[j4 * 4 + jj] = __float_as_uint(__fmul_rn(f1, __fmul_rn(rsS, sv[jj])));
+                            }
                         }
                     }
 #pragma unroll
@@ -1338,9 +1346,10 @@ int i64b_launch_gemm(int type, bool dual, int n_mma, int ctas, const CUtensorMap
     return I64B_ERR_ARG;
 }
 
-int i64b_launch_gemm_tri(bool is_int8, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
+int i64b_launch_gemm_tri(int type, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
                          const CUtensorMap& tmB1, const I64bGemmParams& p, int64_t max_units, cudaStream_t stream) {
     if (max_units <= 0) return I64B_OK;
+    const bool is_int8 = type != kTypeBf16;         // one-byte operands with per-segment scales (int8 or E4M3)
     I64B_CHECK(!(is_int8 && one_acc), I64B_ERR_ARG, "the single-accumulator form is bf16 only");
     I64B_CHECK(!is_int8 || (p.k[1] > 0 && p.k[0] % 128 == 0 && p.k[1] % 128 == 0 && p.row_scale[0] && p.col_scale[0] &&
                             p.col_scale[1]), I64B_ERR_ARG, "W8A8 fused down projection: shared expert, K %% 128 == 0 and scales");
@@ -1350,11 +1359,12 @@ int i64b_launch_gemm_tri(bool is_int8, bool one_acc, const CUtensorMap& tmA, con
                "K segments must be multiples of 64 (got %d, %d)", p.k[0], p.k[1]);
     I64B_CHECK(p.row_tok && p.final_out, I64B_ERR_ARG, "null pointer");
     constexpr int smem = StageCfg<kTriN, 2>::kSmem;
-    auto kern = is_int8 ? i64b_gemm_tri_kernel<false, true>
-                        : (one_acc ? i64b_gemm_tri_kernel<true, false> : i64b_gemm_tri_kernel<false, false>);
-    static bool configured[3][I64B_MAX_DEVICES] = {};
+    auto kern = type == kTypeInt8 ? i64b_gemm_tri_kernel<false, kTypeInt8>
+                : (type == kTypeFp8 ? i64b_gemm_tri_kernel<false, kTypeFp8>
+                   : (one_acc ? i64b_gemm_tri_kernel<true, kTypeBf16> : i64b_gemm_tri_kernel<false, kTypeBf16>));
+    static bool configured[4][I64B_MAX_DEVICES] = {};
     const int dev = i64b_current_device();
-    const int which = is_int8 ? 2 : (one_acc ? 1 : 0);
+    const int which = type == kTypeInt8 ? 2 : (type == kTypeFp8 ? 3 : (one_acc ? 1 : 0));
     if (!configured[which][dev]) {
         I64B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured[which][dev] = true;

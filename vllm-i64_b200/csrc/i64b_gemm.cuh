@@ -82,7 +82,7 @@ int i64b_launch_gemm(int type /* I64B_TYPE_* */, bool dual, int n_mma, int ctas,
 // 256-row units.
 // one_acc: the scales are already in the rows of A (GEMM1 epilogue, tri_mul — every factor a power of two), the three
 // segments accumulate into ONE TMEM accumulator and the two accumulators alternate between tiles.
-int i64b_launch_gemm_tri(bool is_int8, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
+int i64b_launch_gemm_tri(int type /* I64B_TYPE_* */, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
                          const CUtensorMap& tmB1, const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
 
 int i64b_num_sms();

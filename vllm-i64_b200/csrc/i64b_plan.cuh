@@ -99,7 +99,8 @@ int i64b_run_requant_q14(const int32_t* q14, const int32_t* amax_part, int amax_
 // bf16 SwiGLU rows [rows, cols] -> FP8 E4M3 rows + one fp32 scale per row (quantize_activations_fp8, core/fp8.py:113-129);
 // two row sets per launch (routed assignments, shared expert), either may be empty
 int i64b_run_requant_fp8(const void* h, uint8_t* out, float* scale, int64_t rows, int cols, const void* h_b, uint8_t* out_b,
-                         float* scale_b, int64_t rows_b, int cols_b, cudaStream_t stream);
+                         float* scale_b, int64_t rows_b, int cols_b, cudaStream_t stream,
+                         const struct I64bTriWs* tri = nullptr);      // tri: token-major scatter, as i64b_run_requant_q14
 
 struct I64bCombineArgs {
     const float* y;             // [N*K + N, H] fp32 per-assignment outputs (shared rows last)
