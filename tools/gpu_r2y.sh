@@ -25,5 +25,10 @@ CMD="python bench.py --workload prefill_fp8 --steps 2 --warmup 3 --no-cpu-baseli
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'i64b_gemm|requant|dispatch_kernel' -s 20 -c 10 -f -o gpurun_out/${TAG}_full_prefill_fp8 $CMD > gpurun_out/ncu_f2.log 2>&1; echo "full fp8 rc=$?"
 CMD="python bench.py --workload decode_bf16 --steps 2 --warmup 3 --no-cpu-baseline --no-stages --no-workloads"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'i64b_fused' -s 30 -c 3 -f -o gpurun_out/${TAG}_full_decode_bf16 $CMD > gpurun_out/ncu_f3.log 2>&1; echo "full decode rc=$?"
+# gpurun brings back at most 64 MiB: summarise on the box (profiles/r2y_*, profiles/ncu_traffic.json), keep the summaries
 ls -la gpurun_out/*.ncu-rep | awk '{print $5, $9}'
+python tools/summarize_ncu.py $TAG > gpurun_out/${TAG}_summarize.log 2>&1; echo "summarize rc=$?"
+mkdir -p gpurun_out/${TAG}_profiles && cp profiles/${TAG}_* profiles/ncu_traffic.json gpurun_out/${TAG}_profiles/ 2>/dev/null
+rm -f gpurun_out/*.ncu-rep
+du -sh gpurun_out
 tail -c 600 gpurun_out/r2y_bench_n1.json
