@@ -720,16 +720,8 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                             for (int j = 16; j < 32; ++j) amax = max(amax, abs(o[j]));
                         }
-                        if (p.debug_flags & 64u) {
-                            // bring-up: bit6 = every thread writes its own row's 128 bytes (one full line, four sectors)
-                            // straight from registers instead of going through the staging transpose
-                            if (valid) {
-                                int4* dst = reinterpret_cast<int4*>(obase + (int64_t)lane * pitch + c * 4);
-#pragma unroll
-                                for (int j = 0; j < (second ? 8 : 4); ++j)
-                                    dst[j] = make_int4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
-                            }
-                        } else {
+                        // (every thread writing its own row's 128 bytes straight from registers was measured: GEMM1 82.6 -> 104 us
+                        // at 16K tokens, profiles/r3a_* — the staging transpose stays)
                         uint32_t blk[16];
 #pragma unroll
                         for (int j = 0; j < 16; ++j) blk[j] = (uint32_t)o[j];
@@ -738,7 +730,6 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                             for (int j = 0; j < 16; ++j) blk[j] = (uint32_t)o[16 + j];
                             warp_store_block(st_addr, blk, obase + (c + 16) * 4, pitch, rows_valid, 64, lane);
-                        }
                         }
                     }
                 }
