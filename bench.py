@@ -62,7 +62,8 @@ WORKLOADS = {
                           pw=1.0, rs=1.0, ss=1.0, L=4, N=16384, mode="bf16", reps=40),
 }
 HEADLINE = "ep64k_bf16"
-E2E_CHUNKS = 0              # --e2e-chunks
+E2E_CHUNKS = 0              # --e2e-chunks: a count, or relative micro-batch sizes "1,2,2,2,1"
+E2E_DEFAULT_LARGE = 4       # steps of >= 32K tokens
 METRIC, UNIT = "moe_ffn_tokens_per_s", "tokens/s"
 NVLINK_GBS = 770.0          # measured peer copy per direction per GPU on this pool (B200_PROFILING.md)
 _JSON_FD = None
@@ -391,8 +392,9 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
     # the engine step with HOST buffers: micro-batched so that the PCIe copies run under the kernels (HostStepPipeline);
     # small batches are one micro-batch = copy in, L forwards, copy out
     from vllm_i64.kernels.block import HostStepPipeline
-    e2e_chunks = E2E_CHUNKS or (4 if N >= 32768 else (2 if N >= 8192 else 1))
+    e2e_chunks = E2E_CHUNKS or (E2E_DEFAULT_LARGE if N >= 32768 else (2 if N >= 8192 else 1))
     pipe = HostStepPipeline(layers, N, chunks=e2e_chunks)
+    e2e_chunks = pipe.chunks if not isinstance(e2e_chunks, int) else e2e_chunks
 
     def step_e2e():
         pipe.run(x_host, ids_host if wl["E"] else None, out_host)
@@ -821,7 +823,7 @@ def main():
     ap.add_argument("--no-workloads", action="store_true", help="N = 1: only the line's own workload")
     ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
-    ap.add_argument("--e2e-chunks", type=int, default=0,
+    ap.add_argument("--e2e-chunks", type=lambda v: int(v) if "," not in v else tuple(float(t) for t in v.split(",")), default=0,
                     help="N = 1: micro-batches of the end-to-end step (0 = 4 from 32K tokens, 2 from 8K, else 1)")
     ap.add_argument("--ep-lanes", type=int, default=0,
                     help="N > 1: micro-batch lanes per expert-parallel forward (0 = the library's default)")

@@ -242,23 +242,41 @@ class HostStepPipeline:
     ``layers`` are applied to the SAME input rows, the last layer's output is returned (the shape of bench.py's synthetic
     step); ``chain=True`` feeds every layer the previous layer's output instead (a decoder stack without attention).
     No host synchronisation; capturable in a CUDA graph.
+
+    ``chunks`` is a count (equal micro-batches) or a sequence of relative sizes, e.g. ``(1, 2, 2, 2, 1)``: the first
+    micro-batch's copy-in and the last one's copy-out are the only copies nothing hides, so small micro-batches at both
+    ends and large (more efficient) ones in the middle shorten the step.
     """
 
-    def __init__(self, layers: Sequence["I64Block"], max_tokens: int, chunks: int = 4, out_dtype=torch.bfloat16):
+    def __init__(self, layers: Sequence["I64Block"], max_tokens: int, chunks=4, out_dtype=torch.bfloat16):
         if not layers:
             raise ValueError("no layers")
         self.layers = list(layers)
         self.device = self.layers[0].device
         self.hidden = self.layers[0].cfg.hidden_size
-        self.chunks = max(1, int(chunks))
-        self.per = -(-int(max_tokens) // self.chunks)
-        self.max_tokens = self.per * self.chunks
+        self.weights = [1.0] * max(1, int(chunks)) if isinstance(chunks, int) else [float(w) for w in chunks]
+        if not self.weights or min(self.weights) <= 0:
+            raise ValueError("micro-batch sizes must be positive")
+        self.chunks = len(self.weights)
+        self.max_tokens = int(max_tokens)
+        self.per = max(hi - lo for lo, hi in self._cuts(self.max_tokens)) if self.max_tokens else 1
         dev, h = self.device, self.hidden
         self.x = [torch.empty(self.per, h, dtype=torch.bfloat16, device=dev) for _ in range(2)]
         self.ids = [torch.empty(self.per, dtype=torch.int64, device=dev) for _ in range(2)]
         self.out = [[torch.empty(self.per, h, dtype=out_dtype, device=dev) for _ in range(2)] for _ in range(2)]
         self.h2d = torch.cuda.Stream(dev)
         self.d2h = torch.cuda.Stream(dev)
+
+    def _cuts(self, n: int):
+        """[lo, hi) of every micro-batch of an n-token step: proportional to the weights, inner cuts on multiples of 256."""
+        tot, acc, cuts, lo = sum(self.weights), 0.0, [], 0
+        for i, w in enumerate(self.weights):
+            acc += w
+            hi = n if i == self.chunks - 1 else min(n, int(round(n * acc / tot / 256.0)) * 256)
+            hi = max(hi, lo)
+            cuts.append((lo, hi))
+            lo = hi
+        return cuts
 
     def run(self, x_host: torch.Tensor, ids_host: Optional[torch.Tensor], out_host: torch.Tensor,
             chain: bool = False) -> None:
@@ -267,17 +285,20 @@ class HostStepPipeline:
             raise ValueError(f"{n} tokens exceed the pipeline's capacity of {self.max_tokens}")
         if x_host.dtype != torch.bfloat16 or out_host.dtype != self.out[0][0].dtype:
             raise TypeError("x_host must be bfloat16 and out_host of the pipeline's output dtype")
-        per = -(-n // self.chunks) if n else 0
+        cuts = self._cuts(n)
+        if n and max(hi - lo for lo, hi in cuts) > self.per:
+            raise ValueError("micro-batch larger than the pipeline's buffers")
         with torch.cuda.device(self.device):
             cur = torch.cuda.current_stream(self.device)
             self.h2d.wait_stream(cur)
             self.d2h.wait_stream(cur)
             computed, copied_out = [], []
-            for c in range(self.chunks):
-                lo, hi = min(n, c * per), min(n, (c + 1) * per)
+            c = -1
+            for lo, hi in cuts:
                 m = hi - lo
                 if m == 0:
-                    break
+                    continue
+                c += 1
                 s = c & 1
                 with torch.cuda.stream(self.h2d):
                     if c >= 2:
