@@ -63,7 +63,7 @@ WORKLOADS = {
 }
 HEADLINE = "ep64k_bf16"
 E2E_CHUNKS = 0              # --e2e-chunks: a count, or relative micro-batch sizes "1,2,2,2,1"
-E2E_DEFAULT_LARGE = 4       # steps of >= 32K tokens
+E2E_DEFAULT_LARGE = (1, 2, 3, 4, 3, 2, 1)      # steps of >= 32K tokens: measured 4.77 -> 4.49 ms against 4 equal cuts (profiles/r3b_*)
 METRIC, UNIT = "moe_ffn_tokens_per_s", "tokens/s"
 NVLINK_GBS = 770.0          # measured peer copy per direction per GPU on this pool (B200_PROFILING.md)
 _JSON_FD = None
@@ -824,7 +824,7 @@ def main():
     ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
     ap.add_argument("--e2e-chunks", type=lambda v: int(v) if "," not in v else tuple(float(t) for t in v.split(",")), default=0,
-                    help="N = 1: micro-batches of the end-to-end step (0 = 4 from 32K tokens, 2 from 8K, else 1)")
+                    help="N = 1: micro-batches of the end-to-end step: a count or relative sizes a,b,c (0 = 1,2,3,4,3,2,1 from 32K tokens, 2 from 8K, else 1)")
     ap.add_argument("--ep-lanes", type=int, default=0,
                     help="N > 1: micro-batch lanes per expert-parallel forward (0 = the library's default)")
     ap.add_argument("--ep-plan-ahead", action="store_true",
