@@ -633,9 +633,10 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     }
     int rc = I64B_OK;
     if (o.stage_mask & I64B_STAGE_PLAN) {
-        rc = i64b_run_plan(pa, cv.plan, s);
+        static const int fuse_tri_plan = env_int("I64B_TRI_PLAN_FUSED", 1);     // 0: the pair sort as its own launch (A/B)
+        rc = i64b_run_plan(pa, cv.plan, s, (tri && fuse_tri_plan) ? &cv.tri : nullptr);
         if (rc) return rc;
-        if (tri) {
+        if (tri && !fuse_tri_plan) {
             rc = i64b_run_tri_plan(cv.plan, cv.tri, n, E, H, s);
             if (rc) return rc;
         }

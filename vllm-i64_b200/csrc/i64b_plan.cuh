@@ -35,7 +35,8 @@ struct I64bPlanArgs {
 };
 
 // route + per-tile stable ranks + finalisation (counts, offsets, group tables). 1-2 launches.
-int i64b_run_plan(const I64bPlanArgs& a, const I64bPlanWs& ws, cudaStream_t stream);
+// tri != nullptr (top-2 blocks): the token-major layout's pair ranks and groups (I64bTriWs, below) in the same launch
+int i64b_run_plan(const I64bPlanArgs& a, const I64bPlanWs& ws, cudaStream_t stream, const struct I64bTriWs* tri = nullptr);
 
 // Token-major layout for the fused down projection (top-2 blocks): tokens stably sorted by their ordered expert pair
 // (e0, e1).  All three SwiGLU intermediates of a token (route 0, route 1, shared expert) then sit in ONE row of a
