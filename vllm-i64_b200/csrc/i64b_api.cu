@@ -698,8 +698,7 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     {
         const int n_mma = pick_nmma(mt_r, I, mt_s, S, true, "I64B_GEMM1_NMMA");
         const int bn = n_mma / 2;
-        // |max| partials per GEMM1 tile row: one per epilogue column part (i64b_gemm1_col_parts: 4 in the W8A8 pair kernel)
-        const int nh = i64b_gemm1_col_parts(gtype, n_mma, use_cta_pairs(n_mma, T, E + (S > 0 ? 1 : 0)) ? 2 : 1);
+        const int nh = bn >= 64 ? 2 : 1;       // |max| partials per GEMM1 tile row: one per epilogue column half
         I64bGemmParams gp = {};
         gp.groups = cv.plan.groups1;
         gp.num_groups = E + 1;
@@ -1021,7 +1020,7 @@ int i64b_moe_forward_dispatched(i64b_layer* L, const i64b_ep_ctx* c, void* ep_wo
                               (pairs ? pt : mt) * ((I + bn - 1) / bn), s);
         if (rc) return rc;
         if (q) {
-            const int nh = i64b_gemm1_col_parts(I64B_TYPE_INT8, n_mma, pairs ? 2 : 1);
+            const int nh = bn >= 64 ? 2 : 1;
             rc = i64b_run_requant_q14(w.q14, w.amax, w.amax_ld, ((I + bn - 1) / bn) * nh, reinterpret_cast<int8_t*>(w.inter),
                                       w.inter_scale, cap_rows, I, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, s, g1, ng - 1);
             if (rc) return rc;

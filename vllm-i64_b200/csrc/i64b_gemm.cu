@@ -33,13 +33,12 @@ constexpr int kStageWarpBytes = 32 * kStagePitch;  // per-warp output staging bl
 constexpr int kScaleWarpBytes = 512;               // per-warp column scales of the current tile (<= 128 floats)
 constexpr int kEpiWarpBytes = kStageWarpBytes + kScaleWarpBytes;
 
-template <int kNMma, int kCtas, int kEpi = kEpiWarps> struct StageCfg {
+template <int kNMma, int kCtas> struct StageCfg {
     static constexpr int kStageB = kNMma / kCtas * kRowBytes;     // a CTA pair splits the B tile
-    static constexpr int kFit = (232448 - 1024 - kMiscBytes - kEpi * kEpiWarpBytes) / (kStageA + kStageB);
-    static constexpr int kStagesRaw = 196608 / (kStageA + kStageB) < kFit ? 196608 / (kStageA + kStageB) : kFit;
+    static constexpr int kStagesRaw = 196608 / (kStageA + kStageB);
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-    static constexpr int kSmem = 1024 + kStages * (kStageA + kStageB) + kMiscBytes + kEpi * kEpiWarpBytes;
-    static_assert(kSmem <= 232448 && kStages >= 3, "shared memory budget (227 KB per CTA)");
+    static constexpr int kSmem = 1024 + kStages * (kStageA + kStageB) + kMiscBytes + kEpiWarps * kEpiWarpBytes;
+    static_assert(kSmem <= 232448, "shared memory budget (227 KB per CTA)");
 };
 
 __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem_ptr) {
@@ -52,15 +51,6 @@ __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem_ptr)
 
 // operand kinds of the grouped GEMM
 constexpr int kTypeBf16 = I64B_TYPE_BF16, kTypeInt8 = I64B_TYPE_INT8, kTypeFp8 = I64B_TYPE_FP8;
-
-// Epilogue warps.  The one-byte GEMM1 pair kernels (W8A8, FP8) run their MMAs twice as fast as bf16 over the same number of
-// output elements, and their SwiGLU epilogues (scale products, Q7 LUT or exp, staging) are long dependency chains: with two
-// warps per scheduler the epilogue, not the tensor pipe, set the tile rate (ncu: tensor pipe 43-50 % active, the schedulers
-// issue on ~20 % of the cycles).  They run SIXTEEN epilogue warps (four per scheduler, 16-column TMEM chunks to stay inside
-// 96 registers); every other variant keeps eight.
-template <int kType, bool kDual, int kCtas> __host__ __device__ constexpr int epi_warps() {
-    return (kType != kTypeBf16 && kDual && kCtas == 2) ? 16 : 8;
-}
 
 template <int kType, int kNMma, int kCtas>
 __device__ __forceinline__ constexpr uint32_t make_idesc() {
@@ -258,15 +248,13 @@ __device__ __forceinline__ void warp_combine_block(uint32_t st_addr, const uint3
 }
 
 template <int kType, bool kDual, int kNMma, int kCtas, bool kGather = false>
-__global__ void __launch_bounds__(64 + 32 * epi_warps<kType, kDual, kCtas>(), 1)
+__global__ void __launch_bounds__(kThreads, 1)
 i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmB1,
                  const __grid_constant__ I64bGemmParams p) {
     constexpr bool kInt8 = kType == kTypeInt8;
     constexpr bool kFp8 = kType == kTypeFp8;      // E4M3 operands, fp32 accumulators, per-row x per-channel scales
-    constexpr int kEpiWarps = epi_warps<kType, kDual, kCtas>();       // shadows the file-level default of 8
-    constexpr int kThreads = 64 + 32 * kEpiWarps;                     // warp 0 TMA, warp 1 MMA, the rest epilogue
-    using Cfg = StageCfg<kNMma, kCtas, kEpiWarps>;
+    using Cfg = StageCfg<kNMma, kCtas>;
     static_assert(kCtas == 1 || kCtas == 2, "single CTA or a CTA pair");
     static_assert(kCtas == 1 || kNMma == 256, "the pair kernel is built for the widest tile only");
     constexpr int kStages = Cfg::kStages;
@@ -502,11 +490,10 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         // Every output block goes registers -> per-warp smem staging (row per lane, conflict-free 80-byte pitch) ->
         // coalesced 64-byte row segments in global memory (8 rows per warp instruction) instead of one row per lane.
         const int q = warp & 3;                 // TMEM lane quarter this warp may access (hardware: warp id % 4)
-        const int h = (warp - 2) >> 2;          // column part (half, or quarter with 16 warps) of the tile this warp drains
+        const int h = (warp - 2) >> 2;          // column half of the tile this warp drains
         const int r = q * 32 + lane;            // tile row owned by this thread while reading TMEM
-        constexpr int kColParts = kEpiWarps / 4;
-        constexpr bool kSplit = kBnOut / kColParts >= 32;       // narrow tiles: only the h == 0 warps work
-        constexpr int kColsW = kSplit ? kBnOut / kColParts : kBnOut;    // output columns per warp
+        constexpr bool kSplit = kBnOut >= 64;   // narrow tiles: only the h == 0 warps work
+        constexpr int kColsW = kSplit ? kBnOut / 2 : kBnOut;    // output columns per warp
         const bool active = kSplit || h == 0;
         const int cbase = kSplit ? h * kColsW : 0;
         const uint32_t st_addr = smem_u32(stage_base + (warp - 2) * kEpiWarpBytes);
@@ -650,40 +637,6 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         my_off = ((int64_t)(m & 0x3FFFFFFFu) * p.ld_out[w] + col + colw0) * 2;
                     }
                 }
-                if constexpr (kEpiWarps == 16) {        // FP8 pair kernel: 16-column chunks, 32 bytes of bf16 per row and chunk
-#pragma unroll 1
-                    for (int c = 0; c < kColsW; c += 16) {
-                        if (colw0 + c >= n_out) break;
-                        uint32_t o[16];
-                        {
-                            uint32_t gr[16], ur[16];
-                            tmem_ld_32x16(taddr + c, gr);
-                            tmem_ld_32x16(taddr + kBnOut + c, ur);
-                            tmem_ld_wait();
-#pragma unroll
-                            for (int j4 = 0; j4 < 4; ++j4) {
-                                const float4 sg4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
-                                const float4 su4 = ld_shared_f4(ws_addr + (kColsW + c + j4 * 4) * 4);
-                                const float sgv[4] = {sg4.x, sg4.y, sg4.z, sg4.w};
-                                const float suv[4] = {su4.x, su4.y, su4.z, su4.w};
-#pragma unroll
-                                for (int jj = 0; jj < 4; ++jj) {
-                                    const int j = j4 * 4 + jj;
-                                    gr[j] = __float_as_uint(__fmul_rn(__uint_as_float(gr[j]), __fmul_rn(rs8, sgv[jj])));
-                                    ur[j] = __float_as_uint(__fmul_rn(__uint_as_float(ur[j]), __fmul_rn(rs8, suv[jj])));
-                                }
-                            }
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const float h0 = silu_f32(__uint_as_float(gr[2 * j])) * __uint_as_float(ur[2 * j]);
-                                const float h1 = silu_f32(__uint_as_float(gr[2 * j + 1])) * __uint_as_float(ur[2 * j + 1]);
-                                o[j] = pack_bf16x2(h0, h1);
-                                o[8 + j] = 0;
-                            }
-                        }
-                        warp_store_block(st_addr, o, obase + c * 2, pitch, rows_valid, 32, lane);
-                    }
-                } else {
 #pragma unroll 1
                 for (int c = 0; c < kColsW; c += 32) {
                     if (colw0 + c >= n_out) break;
@@ -724,7 +677,6 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     else
                         warp_store_block(st_addr, o, obase + c * 2, pitch, rows_valid, min(64, (n_out - colw0 - c) * 2), lane);
                 }
-                }
             } else if constexpr (kDual && kInt8) {
                 uint8_t* obase = reinterpret_cast<uint8_t*>(p.out[w]) + (out_row0 * p.ld_out[w] + colw0) * 4;
                 const int64_t pitch = p.ld_out[w] * 4;
@@ -732,36 +684,6 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 // (scaling by 2^7 commutes with round-to-nearest; scales are >= 1e-8/127, nothing denormal)
                 const float rs128 = valid ? __fmul_rn(p.row_scale[w][a_row], 128.0f) : 0.0f;
                 int amax = 0;
-                if constexpr (kEpiWarps == 16) {        // W8A8 pair kernel: 16-column chunks, one 64-byte block of Q14 per row and chunk
-#pragma unroll 1
-                    for (int c = 0; c < kColsW; c += 16) {
-                        if (colw0 + c >= n_out) break;
-                        uint32_t gr[16], ur[16];
-                        tmem_ld_32x16(taddr + c, gr);
-                        tmem_ld_32x16(taddr + kBnOut + c, ur);
-                        tmem_ld_wait();
-                        uint32_t blk[16];
-#pragma unroll
-                        for (int j4 = 0; j4 < 4; ++j4) {
-                            const float4 sg4 = ld_shared_f4(ws_addr + (c + j4 * 4) * 4);
-                            const float4 su4 = ld_shared_f4(ws_addr + (kColsW + c + j4 * 4) * 4);
-                            const float sgv[4] = {sg4.x, sg4.y, sg4.z, sg4.w};
-                            const float suv[4] = {su4.x, su4.y, su4.z, su4.w};
-#pragma unroll
-                            for (int jj = 0; jj < 4; ++jj) {
-                                const int j = j4 * 4 + jj;
-                                const int gq = __float2int_rn(__fmul_rn((float)(int)gr[j], __fmul_rn(rs128, sgv[jj])));
-                                const int uq = __float2int_rn(__fmul_rn((float)(int)ur[j], __fmul_rn(rs128, suv[jj])));
-                                const int idx = min(max(gq, -1024), 1024);
-                                const int sq = ld_shared_s16(lut_addr + (uint32_t)(idx + 1024) * 2) + max(gq - 1024, 0);
-                                const int o = sq * uq;
-                                amax = max(amax, abs(o));
-                                blk[j] = (uint32_t)o;
-                            }
-                        }
-                        warp_store_block(st_addr, blk, obase + c * 4, pitch, rows_valid, 64, lane);
-                    }
-                } else {
 #pragma unroll 1
                 for (int c = 0; c < kColsW; c += 32) {
                     if (colw0 + c >= n_out) break;
@@ -811,9 +733,8 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         }
                     }
                 }
-                }
                 if (valid)
-                    p.amax_part[w][(out_row0 + lane) * p.amax_ld[w] + tc.n_t * (kSplit ? kColParts : 1) + (kSplit ? h : 0)] = amax;
+                    p.amax_part[w][(out_row0 + lane) * p.amax_ld[w] + tc.n_t * (kSplit ? 2 : 1) + (kSplit ? h : 0)] = amax;
             } else {
                 const bool dequant = p.epi == I64B_EPI_DEQUANT;
                 const float rs = (dequant && valid && p.row_scale[w] != nullptr) ? p.row_scale[w][a_row] : 1.0f;
@@ -1291,9 +1212,7 @@ template <int kType, bool kDual, int kNMma, int kCtas, bool kGather = false>
 int launch_inst(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b0, const CUtensorMap& b1,
                 const I64bGemmParams& p, int grid, cudaStream_t stream) {
     auto kern = i64b_gemm_kernel<kType, kDual, kNMma, kCtas, kGather>;
-    constexpr int kEpi = epi_warps<kType, kDual, kCtas>();
-    constexpr int kThreads = 64 + 32 * kEpi;
-    constexpr int smem = StageCfg<kNMma, kCtas, kEpi>::kSmem;
+    constexpr int smem = StageCfg<kNMma, kCtas>::kSmem;
     static bool configured[I64B_MAX_DEVICES] = {};      // function attributes are per device (one table per instantiation)
     const int dev = i64b_current_device();
     if (!configured[dev]) {
@@ -1348,12 +1267,6 @@ int i64b_current_device() {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= I64B_MAX_DEVICES) dev = 0;
     return dev;
-}
-
-int i64b_gemm1_col_parts(int type, int n_mma, int ctas) {
-    const int bn = n_mma / 2;
-    const int parts = (type != kTypeBf16 && ctas == 2) ? 4 : 2;
-    return bn / parts >= 32 ? parts : 1;
 }
 
 int i64b_num_sms() {        // of the CURRENT device (a process may drive several)

@@ -85,9 +85,6 @@ int i64b_launch_gemm(int type /* I64B_TYPE_* */, bool dual, int n_mma, int ctas,
 int i64b_launch_gemm_tri(int type /* I64B_TYPE_* */, bool one_acc, const CUtensorMap& tmA, const CUtensorMap& tmB0,
                          const CUtensorMap& tmB1, const I64bGemmParams& p, int64_t max_units, cudaStream_t stream);
 
-// column parts per GEMM1 (dual) tile, i.e. |max| partials the W8A8 epilogue writes per (row, tile): the epilogue warps split a
-// tile's output columns in halves, or in quarters in the one-byte pair kernels (sixteen epilogue warps)
-int i64b_gemm1_col_parts(int type, int n_mma, int ctas);
 int i64b_num_sms();
 int i64b_set_gemm_cta_limit(int limit);      // thread-local; returns the previous value
 void i64b_count_launch(int n = 1);
