@@ -488,3 +488,24 @@ def test_cuda_graph_capture():
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, eager)
+
+
+def test_dense_w8a8_wide_rows_pair_kernel_bit_exact():
+    """dense-306 width (S = 4096) at a prefill size: GEMM1 runs as CTA pairs and the rows are too wide for the re-quantiser's
+    register path, so the row |max| comes from the epilogue's per-(row, tile, column half) partials.  Whole FFN bit-exact
+    against the oracle."""
+    n, h, s = 2048, 1024, 4096
+    rng = np.random.RandomState(5)
+    u = lambda shape, fan: Hh.bf16_round(rng.uniform(-1, 1, size=shape).astype(np.float32) / np.sqrt(fan))
+    sg, su, sd = u((s, h), h), u((s, h), h), u((h, s), s)
+    x = Hh.bf16_round(rng.randn(n, h).astype(np.float32))
+    w13_q, w13_s = O.quantize_rows_int8(np.concatenate([sg, su], axis=0))
+    w2_q, w2_s = O.quantize_rows_int8(sd)
+    from vllm_i64.kernels.block import I64Block
+    blk = I64Block(h, 0, 0, s, 1, 0, [], 1.0, 1.0, _C.MODE_W8A8, DEV)
+    blk.load_w8a8(None, None, None, None, cu(w13_q), cu(w13_s.reshape(-1)), cu(w2_q), cu(w2_s.reshape(-1)))
+    out = blk.forward(cu(x, torch.bfloat16), None, torch.float32)
+    torch.cuda.synchronize()
+    rows = np.arange(0, n, 7)
+    ref = O.w8a8_swiglu(x[rows], w13_q, w13_s.reshape(-1), w2_q, w2_s.reshape(-1)).y
+    assert np.array_equal(out.cpu().numpy()[rows], ref)
