@@ -406,12 +406,18 @@ i64b_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     if constexpr (kCtas == 2) {
                         // both CTAs load their own A rows and their half of the B tile (dual: leader = gate rows,
                         // peer = up rows); all bytes are credited to the leader's barrier
-                        if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (kStageA + kStageB));
-                        tma_load_2d_cta2(sA + stage * kStageA, ta, &full_bar[stage], kb * kBlockK, a_row,
-                                         I64B_L2_EVICT_NORMAL);
+                        // bring-up (timing only, results are garbage): bit7 / bit8 = no B / no A load on odd k-blocks, i.e.
+                        // what the kernel would do with three quarters of its operand bytes (is it bound by operand ingest?)
+                        const bool skip_b = (p.debug_flags & 128u) && (kb & 1), skip_a = (p.debug_flags & 256u) && (kb & 1);
+                        if (rank == 0)
+                            mbar_arrive_expect_tx(&full_bar[stage], 2 * ((skip_a ? 0 : kStageA) + (skip_b ? 0 : kStageB)));
+                        if (!skip_a)
+                            tma_load_2d_cta2(sA + stage * kStageA, ta, &full_bar[stage], kb * kBlockK, a_row,
+                                             I64B_L2_EVICT_NORMAL);
                         const int bh = kDual ? b_row + rank * grp.n_out : b_row + rank * (kNMma / 2);
-                        tma_load_2d_cta2(sB + stage * kStageB, tb, &full_bar[stage], kb * kBlockK, bh,
-                                         I64B_L2_EVICT_NORMAL);
+                        if (!skip_b)
+                            tma_load_2d_cta2(sB + stage * kStageB, tb, &full_bar[stage], kb * kBlockK, bh,
+                                             I64B_L2_EVICT_NORMAL);
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                         continue;
                     }
