@@ -55,7 +55,8 @@ struct I64bGemmParams {
     const int32_t* gather_idx;
     int32_t gather_rows;
     // bring-up instrumentation (env I64B_DEBUG_FLAGS / I64B_DEBUG_TIMELINE; never set in production)
-    uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores
+    uint32_t debug_flags;      // bit0: skip MMAs (pure TMA streaming), bit1: skip epilogue stores; pair kernels, timing only
+                               // (garbage results): bit7 / bit8 = no B / no A load on odd k-blocks (operand-ingest probe)
     long long* debug_timeline; // [grid, 8] clock64 offsets per CTA
 };
 
