@@ -30,7 +30,7 @@ def _layers(mode, n, count=3):
 
 
 @pytest.mark.parametrize("mode", ["bf16", "int8"])
-@pytest.mark.parametrize("chunks", [1, 2, 3, 5])
+@pytest.mark.parametrize("chunks", [1, 2, 3, 5, (1, 2, 3, 2, 1)], ids=["1", "2", "3", "5", "uneven"])
 @pytest.mark.parametrize("chain", [False, True])
 def test_pipeline_equals_one_shot(mode, chunks, chain):
     n = 1537

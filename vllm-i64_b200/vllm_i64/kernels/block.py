@@ -259,7 +259,8 @@ class HostStepPipeline:
             raise ValueError("micro-batch sizes must be positive")
         self.chunks = len(self.weights)
         self.max_tokens = int(max_tokens)
-        self.per = max(hi - lo for lo, hi in self._cuts(self.max_tokens)) if self.max_tokens else 1
+        # largest micro-batch of a full step, plus one rounding quantum: a shorter step's inner cuts land on other multiples of 256
+        self.per = (max(hi - lo for lo, hi in self._cuts(self.max_tokens)) + 256) if self.max_tokens else 1
         dev, h = self.device, self.hidden
         self.x = [torch.empty(self.per, h, dtype=torch.bfloat16, device=dev) for _ in range(2)]
         self.ids = [torch.empty(self.per, dtype=torch.int64, device=dev) for _ in range(2)]
