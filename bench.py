@@ -447,6 +447,9 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
                     "flops": block_flops(wl),
                     "frac_tensor": round(block_flops(wl) / (us_layer * 1e-6) / 1e12 / tensor_peak, 4),
                     "tensor_peak": tensor_peak, "tensor_peak_source": tensor_src}
+    if wl["mode"] == "bf16":        # a long step runs under the power cap: the sustained peak is its denominator (B200_PROFILING.md)
+        res["block"]["frac_tensor_sustained"] = round(block_flops(wl) / (us_layer * 1e-6) / 1e12 / pk["tf_sust"], 4)
+        res["block"]["tensor_peak_sustained"] = pk["tf_sust"]
     if fused:
         gbs = mb / (us_layer * 1e-6) / 1e9
         res["roofline"] = {"kernel": "i64b_fused_layer_kernel", "bound": "hbm", "achieved": round(gbs, 1), "peak": pk["hbm"],
@@ -497,7 +500,7 @@ def have_ref():
     return os.path.isdir(os.path.join(REF_DIR, "vllm_i64"))
 
 
-def cpu_reference_run(wl, steps, warmup, mode="int8", max_seconds=25.0, sample_tokens=2048, layers_cap=2):
+def cpu_reference_run(wl, steps, warmup, mode="int8", max_seconds=150.0, sample_tokens=8192, layers_cap=4):
     """The reference's CPU recipe on the host cores, on a bounded sample of the workload: `sample_tokens` tokens x
     `layers_cap` layers per step.  kind "reference": the reference's OWN TokenRoutedMLP -> _fuse_cpu_projection_layers ->
     _quantize_cpu_dynamic (core/loader.py:57-94) imported from oracle/_ref (tools/install_ref.py); kind "port": the torch-CPU
@@ -818,6 +821,8 @@ def main():
     ap.add_argument("--workload", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--cpu-mode", default="int8", choices=["int8", "fp32"])
+    ap.add_argument("--cpu-seconds", type=float, default=150.0,
+                    help="--impl reference: stop after this much timed host work even if --steps is not reached")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="N = 1: only the line's own workload")
@@ -843,7 +848,7 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        r = cpu_reference_run(wl, args.steps, args.warmup, args.cpu_mode)
+        r = cpu_reference_run(wl, args.steps, args.warmup, args.cpu_mode, max_seconds=args.cpu_seconds)
         line = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
                 "warmup": min(args.warmup, 2), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "int8" if args.cpu_mode == "int8" else "f32",
@@ -923,7 +928,9 @@ def main():
     cpu = None
     ref_gpu = None
     if not args.no_cpu_baseline:
-        r = run_subprocess_json(["--impl", "reference", "--workload", args.workload, "--steps", "4", "--warmup", "1",
+        # the same arm, for about 12 s of host work (BASELINE: 10-30 s), whatever number of steps that takes
+        r = run_subprocess_json(["--impl", "reference", "--workload", args.workload, "--steps", "100000", "--warmup", "1",
+                                 "--cpu-seconds", "12",
                                  "--cpu-mode", args.cpu_mode])
         cpu = r.get("cpu_baseline") or {"error": r.get("error", "no line")}
         ref_gpu = run_subprocess_json(["--impl", "reference-gpu", "--workload", args.workload, "--steps", "5", "--warmup", "2"])
