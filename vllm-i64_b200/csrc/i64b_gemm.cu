@@ -1116,51 +1116,40 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             mbar_wait(&tfull_bar[0], par);
             mbar_wait(&tfull_bar[1], par);
             tc_fence_after();
-            // epilogue 1: the routed part; with a shared expert it goes back into acc0, else straight out.  Both epilogues sit
-            // on the tile's critical path (the tensor pipe waits for them), so the TMEM loads of chunk i+1 are in flight while
-            // chunk i is folded (two register sets, fully unrolled).
-            constexpr int kChunks = kColsW / 32;
-            {
-                uint32_t b0[2][32], b1[2][32];
-                tmem_ld_32x32(t0, b0[0]);
-                tmem_ld_32x32(t1, b1[0]);
+            // epilogue 1: the routed part; with a shared expert it goes back into acc0, else straight out
+#pragma unroll 1
+            for (int c = 0; c < kColsW; c += 32) {
+                uint32_t a0[32], a1[32];
+                tmem_ld_32x32(t0 + c, a0);
+                tmem_ld_32x32(t1 + c, a1);
+                tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < kChunks; ++i) {
-                    const int c = i * 32;
-                    uint32_t (&a0)[32] = b0[i & 1];
-                    uint32_t (&a1)[32] = b1[i & 1];
-                    tmem_ld_wait();
-                    if (i + 1 < kChunks) {
-                        tmem_ld_32x32(t0 + c + 32, b0[(i + 1) & 1]);
-                        tmem_ld_32x32(t1 + c + 32, b1[(i + 1) & 1]);
-                    }
-                    if constexpr (kScaled) {
+                if constexpr (kScaled) {
 #pragma unroll
-                        for (int j4 = 0; j4 < 8; ++j4) {
-                            const float4 sa4 = ld_shared_f4(st_addr + (c + j4 * 4) * 4);
-                            const float4 sb4 = ld_shared_f4(st_addr + (kColsW + c + j4 * 4) * 4);
-                            const float sav[4] = {sa4.x, sa4.y, sa4.z, sa4.w};
-                            const float sbv[4] = {sb4.x, sb4.y, sb4.z, sb4.w};
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 sa4 = ld_shared_f4(st_addr + (c + j4 * 4) * 4);
+                        const float4 sb4 = ld_shared_f4(st_addr + (kColsW + c + j4 * 4) * 4);
+                        const float sav[4] = {sa4.x, sa4.y, sa4.z, sa4.w};
+                        const float sbv[4] = {sb4.x, sb4.y, sb4.z, sb4.w};
 #pragma unroll
-                            for (int jj = 0; jj < 4; ++jj) {
-                                const int j = j4 * 4 + jj;
-                                // result_i32.float() * (x_scale * w_scale)                      core/quantization.py:173
-                                const float f0 = kInt8 ? (float)(int)a0[j] : __uint_as_float(a0[j]);
-                                const float f1 = kInt8 ? (float)(int)a1[j] : __uint_as_float(a1[j]);
-                                a0[j] = __float_as_uint(__fmul_rn(f0, __fmul_rn(rsa, sav[jj])));
-                                a1[j] = __float_as_uint(__fmul_rn(f1, __fmul_rn(rsb, sbv[jj])));
-                            }
+                        for (int jj = 0; jj < 4; ++jj) {
+                            const int j = j4 * 4 + jj;
+                            // result_i32.float() * (x_scale * w_scale)                      core/quantization.py:173
+                            const float f0 = kInt8 ? (float)(int)a0[j] : __uint_as_float(a0[j]);
+                            const float f1 = kInt8 ? (float)(int)a1[j] : __uint_as_float(a1[j]);
+                            a0[j] = __float_as_uint(__fmul_rn(f0, __fmul_rn(rsa, sav[jj])));
+                            a1[j] = __float_as_uint(__fmul_rn(f1, __fmul_rn(rsb, sbv[jj])));
                         }
                     }
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        float o = __fmul_rn(wa, __uint_as_float(a0[j]));          // a + b == b + a: same bits as w0*y0 + w1*y1
-                        o = __fadd_rn(o, __fmul_rn(wb, __uint_as_float(a1[j])));
-                        a0[j] = __float_as_uint(__fmul_rn(rs, o));
-                    }
-                    if (nseg == 3) tmem_st_32x32(t0 + c, a0);
-                    else store_chunk(a0, c, my_off, rows_valid);
                 }
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    float o = __fmul_rn(wa, __uint_as_float(a0[j]));          // a + b == b + a: same bits as w0*y0 + w1*y1
+                    o = __fadd_rn(o, __fmul_rn(wb, __uint_as_float(a1[j])));
+                    a0[j] = __float_as_uint(__fmul_rn(rs, o));
+                }
+                if (nseg == 3) tmem_st_32x32(t0 + c, a0);
+                else store_chunk(a0, c, my_off, rows_valid);
             }
             if (nseg == 3) {
                 tmem_st_wait();
@@ -1169,19 +1158,13 @@ i64b_gemm_tri_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 if (lane == 0) mbar_arrive_leader(&tempty_bar[0]);       // acc1 may take the shared expert's segment
                 mbar_wait(&tfull_bar[2], par);
                 tc_fence_after();
-                uint32_t b0[2][32], b1[2][32];
-                tmem_ld_32x32(t0, b0[0]);
-                tmem_ld_32x32(t1, b1[0]);
-#pragma unroll
-                for (int i = 0; i < kChunks; ++i) {
-                    const int c = i * 32;
-                    uint32_t (&a0)[32] = b0[i & 1];
-                    uint32_t (&a1)[32] = b1[i & 1];
+#pragma unroll 1
+                for (int c = 0; c < kColsW; c += 32) {
+                    uint32_t a0[32], a1[32];
+                    tmem_ld_32x32(t0 + c, a0);
+                    tmem_ld_32x32(t1 + c, a1);
                     tmem_ld_wait();
-                    if (i + 1 < kChunks) {
-                        tmem_ld_32x32(t0 + c + 32, b0[(i + 1) & 1]);
-                        tmem_ld_32x32(t1 + c + 32, b1[(i + 1) & 1]);
-                    }
+#pragma unroll
                     if constexpr (kScaled) {
 #pragma unroll
                         for (int j4 = 0; j4 < 8; ++j4) {
