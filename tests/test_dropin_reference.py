@@ -97,3 +97,58 @@ def test_engine_wiring_on_gpu():
         assert info[f"dense_{method}_vs_bf16"][1] <= (0.1 if method == "int8" else 0.25), (method, info[f"dense_{method}_vs_bf16"])
     assert info["graph_sizes"] == [1, 2, 4, 8, 16, 32, 64]
     assert all(info["graph_replay_equals_eager"]), info["graph_replay_equals_eager"]
+
+
+@needs_ref
+def test_loader_hooks_switch_the_modules_on_cpu():
+    """CPU, structure only: with the overlay active, the reference loader's post-load passes (its own file) flip the new
+    modules' quantisation mode — `_quantize_experts(model, "int8")` reaches TokenRoutedMLP (dead code in the reference),
+    `_quantize_dense_mlp` / `_quantize_dense_mlp_fp8` leave buffers DenseMLP recognises; host-side weights are quantised by
+    the reference's own torch ops."""
+    code = r'''
+import json, torch, torch.nn as nn, vllm_i64
+hooked = vllm_i64.patch_reference_models()
+from vllm_i64.core import loader
+from vllm_i64.layers.dense_mlp import DenseMLP
+from vllm_i64.layers.token_routed_mlp import TokenRoutedMLP
+class M(nn.Module):
+    def __init__(s):
+        super().__init__()
+        s.a = TokenRoutedMLP(64, 128, 4, 100, shared_expert=True, shared_intermediate_size=32, top_k=2)
+        s.d = DenseMLP(64, 128)
+m = M(); loader._quantize_experts(m, "int8"); loader._quantize_dense_mlp(m, "int8")
+m2 = M(); loader._quantize_dense_mlp_fp8(m2)
+print("HOOKS_JSON " + json.dumps({"hooked": hooked, "moe_int8": m.a.quantization, "dense_int8_buf": str(m.d.gate_up_int8.dtype),
+      "moe_fp8": m2.a.quantization, "dense_fp8_buf": str(m2.d.gate_fp8.dtype), "load": vllm_i64.collect_expert_load(m)}))
+'''
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([PKG, REF]), PYTHONDONTWRITEBYTECODE="1")
+    env.pop("VLLM_I64_REFERENCE", None)
+    p = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-3000:]
+    info = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("HOOKS_JSON ")][-1][len("HOOKS_JSON "):])
+    assert "vllm_i64.core.loader._quantize_experts" in info["hooked"] and "vllm_i64.core.loader._quantize_dense_mlp_fp8" in info["hooked"]
+    assert info["moe_int8"] == "int8" and info["dense_int8_buf"] == "torch.int8"
+    assert info["moe_fp8"] == "fp8" and info["dense_fp8_buf"] == "torch.float8_e4m3fn"
+    assert info["load"] == {}          # no forward has run: nothing to report
+
+
+def test_host_pipeline_cuts_are_a_partition():
+    """HostStepPipeline's micro-batch boundaries (pure host arithmetic): a partition of [0, n), inner cuts on multiples of
+    256, proportional to the weights, never larger than the buffers sized for the full step."""
+    sys.path.insert(0, PKG)
+    from vllm_i64.kernels.block import HostStepPipeline as H
+    for weights in ([1.0] * 4, [1, 2, 3, 4, 3, 2, 1], [1], [5, 1]):
+        p = H.__new__(H)
+        p.weights, p.chunks = [float(w) for w in weights], len(weights)
+        full = p._cuts(65536)
+        per = max(hi - lo for lo, hi in full) + 256
+        for n in (0, 1, 255, 256, 700, 1537, 16384, 40000, 65536):
+            cuts = p._cuts(n)
+            assert len(cuts) == len(weights) and cuts[0][0] == 0 and cuts[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:])) and all(lo <= hi for lo, hi in cuts)
+            assert all(hi % 256 == 0 or hi == n for _, hi in cuts[:-1])
+            assert max(hi - lo for lo, hi in cuts) <= per
+    p = H.__new__(H)
+    p.weights, p.chunks = [1.0, 2.0, 3.0, 4.0, 3.0, 2.0, 1.0], 7
+    sizes = [hi - lo for lo, hi in p._cuts(65536)]
+    assert sizes == sorted(sizes[:4]) + sorted(sizes[4:], reverse=True) and sizes[3] == max(sizes)
