@@ -63,6 +63,7 @@ WORKLOADS = {
 }
 HEADLINE = "ep64k_bf16"
 E2E_CHUNKS = 0              # --e2e-chunks: a count, or relative micro-batch sizes "1,2,2,2,1"
+E2E_STREAM = True           # --e2e-isolated: every step drains its copies before the next one starts (CUDA-graph replay)
 E2E_DEFAULT_LARGE = (1, 2, 3, 4, 3, 2, 1)      # steps of >= 32K tokens: measured 4.77 -> 4.49 ms against 4 equal cuts (profiles/r3b_*)
 METRIC, UNIT = "moe_ffn_tokens_per_s", "tokens/s"
 NVLINK_GBS = 770.0          # measured peer copy per direction per GPU on this pool (B200_PROFILING.md)
@@ -312,6 +313,30 @@ def time_graph(run, steps, warmup, stream, barrier=None, sampler=None):
     return e0.elapsed_time(e1)
 
 
+def time_stream(step, drain, steps, warmup, stream, barrier=None):
+    """Back-to-back eager steps of a streaming pipeline (nothing joins between steps), drained once at the end; CUDA events
+    on the launching stream around the whole run."""
+    with torch.cuda.stream(stream):
+        for _ in range(max(warmup, 3)):
+            step()
+        drain()
+        stream.synchronize()
+        if barrier:
+            barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step()
+        drain()
+        e1.record(stream)
+        e1.synchronize()
+        torch.cuda.synchronize()
+        if barrier:
+            barrier()
+    return e0.elapsed_time(e1)
+
+
 def measure_int8_peak(device):
     """Dense INT8 tensor peak as this pool delivers it through cuBLASLt (torch._int_mm 8192^3): best of 10 (burst) and back
     to back for ~1.5 s (sustained) — the same recipe MEASURED_PEAKS.json uses for bf16 (BASELINE.md §4 asks for it)."""
@@ -416,7 +441,13 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
 
     ms = time_graph(step_device, steps, warmup, stream, barrier, sampler)
     e2e_steps = max(3, min(steps, 50))
-    ms_e2e = time_graph(step_e2e, e2e_steps, 3, stream, barrier)
+    # steps follow one another as in an engine loop: the next step's first copy-in runs under this step's last kernels
+    # (run_stream); every step's H2D and D2H are inside the timed region, which ends when the last copy-out has landed
+    if E2E_STREAM:
+        ms_e2e = time_stream(lambda: pipe.run_stream(x_host, ids_host if wl["E"] else None, out_host), pipe.drain, e2e_steps, 3,
+                             stream, barrier)
+    else:
+        ms_e2e = time_graph(step_e2e, e2e_steps, 3, stream, barrier)
     ms_host = time_graph(step_host_call, max(3, min(steps, 20)), 3, stream, barrier)
     us_layer = ms * 1e3 / (steps * L)
     res = {"desc": wl["desc"], "value": N * L * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
@@ -426,7 +457,10 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
                    "h2d_bytes_per_step": N * H * 2 + (N * 8 if wl["E"] else 0), "d2h_bytes_per_step": N * H * 2,
                    "copies_per_step": e2e_chunks,
                    "via": f"engine step (HostStepPipeline): pinned H2D of x + ids, L block forwards, D2H of the last output, "
-                          f"in {e2e_chunks} micro-batch(es) whose copies run under the kernels of their neighbours"},
+                          f"in {e2e_chunks} micro-batch(es) whose copies run under the kernels of their neighbours"
+                          + ("; steps stream back to back (the next step's copy-in under this step's last kernels), the timed "
+                             "region ends when the last copy-out has landed" if E2E_STREAM else "; every step drains before the next"),
+                   "streaming": bool(E2E_STREAM)},
            "e2e_per_layer_host_call": {
                "value": N * L * max(3, min(steps, 20)) / (ms_host * 1e-3), "unit": UNIT, "copies_per_step": L,
                "h2d_bytes_per_step": L * (N * H * 2 + N * 8), "d2h_bytes_per_step": L * N * H * 2,
@@ -830,6 +864,8 @@ def main():
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
     ap.add_argument("--e2e-chunks", type=lambda v: int(v) if "," not in v else tuple(float(t) for t in v.split(",")), default=0,
                     help="N = 1: micro-batches of the end-to-end step: a count or relative sizes a,b,c (0 = 1,2,3,4,3,2,1 from 32K tokens, 2 from 8K, else 1)")
+    ap.add_argument("--e2e-isolated", action="store_true",
+                    help="N = 1: time the end-to-end step as isolated CUDA-graph replays (no overlap between consecutive steps)")
     ap.add_argument("--ep-lanes", type=int, default=0,
                     help="N > 1: micro-batch lanes per expert-parallel forward (0 = the library's default)")
     ap.add_argument("--ep-plan-ahead", action="store_true",
@@ -838,8 +874,9 @@ def main():
     ap.add_argument("--ep-nccl-baseline", action="store_true", help="also time the all_to_all_single exchange (eager)")
     ap.add_argument("--ep-timeline", action="store_true", help="also report per-stage device times of one EP layer (eager)")
     args = ap.parse_args()
-    global E2E_CHUNKS
+    global E2E_CHUNKS, E2E_STREAM
     E2E_CHUNKS = args.e2e_chunks
+    E2E_STREAM = not args.e2e_isolated
     wl = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

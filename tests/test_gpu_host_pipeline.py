@@ -70,3 +70,39 @@ def test_pipeline_equals_one_shot(mode, chunks, chain):
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out_host[:m], want_m.cpu())
+
+
+@pytest.mark.parametrize("chunks", [3, (1, 2, 3, 2, 1)], ids=["3", "uneven"])
+def test_streaming_steps_equal_one_shot(chunks):
+    """run_stream: consecutive steps with DIFFERENT inputs and output buffers, nothing joined between them (the next step's
+    copy-in overlaps this step's kernels, slot events carry over), one drain at the end: every step's output is the one-shot
+    block's, bit for bit; a second round over the same buffers too."""
+    n = 1537
+    layers, ids, x = _layers("bf16", n)
+    rng = np.random.RandomState(3)
+    steps = []
+    for k in range(4):
+        xk = torch.from_numpy(np.roll(x, k * 37, axis=0)).to(torch.bfloat16).pin_memory()
+        ik = torch.from_numpy(np.roll(ids, k * 37)).pin_memory()
+        m = n - 200 * k                                   # steps of different lengths
+        steps.append((xk[:m], ik[:m], torch.empty(m, 256, dtype=torch.bfloat16).pin_memory()))
+    want = []
+    for xk, ik, _ in steps:
+        w = None
+        for blk in layers:
+            w = blk.forward(xk.cuda(), ik.cuda(), torch.bfloat16)
+        want.append(w.cpu())
+    pipe = HostStepPipeline(layers, n, chunks=chunks)
+    for rnd in range(2):
+        for _, _, ok in steps:
+            ok.zero_()
+        for xk, ik, ok in steps:
+            pipe.run_stream(xk, ik, ok)
+        pipe.drain()
+        torch.cuda.synchronize()
+        for (_, _, ok), w in zip(steps, want):
+            assert torch.equal(ok, w), f"round {rnd}"
+    # and the self-contained form still works after streaming
+    pipe.run(steps[0][0], steps[0][1], steps[0][2])
+    torch.cuda.synchronize()
+    assert torch.equal(steps[0][2], want[0])

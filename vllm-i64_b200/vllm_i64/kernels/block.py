@@ -267,6 +267,7 @@ class HostStepPipeline:
         self.out = [[torch.empty(self.per, h, dtype=out_dtype, device=dev) for _ in range(2)] for _ in range(2)]
         self.h2d = torch.cuda.Stream(dev)
         self.d2h = torch.cuda.Stream(dev)
+        self._computed, self._copied, self._seq = [None, None], [None, None], 0     # slot events (carried across run_stream calls)
 
     def _cuts(self, n: int):
         """[lo, hi) of every micro-batch of an n-token step: proportional to the weights, inner cuts on multiples of 256."""
@@ -281,6 +282,27 @@ class HostStepPipeline:
 
     def run(self, x_host: torch.Tensor, ids_host: Optional[torch.Tensor], out_host: torch.Tensor,
             chain: bool = False) -> None:
+        """One self-contained step: the copy streams first wait for the caller's stream, and the caller's stream waits for
+        the last copy-out before the call returns to it (capturable in a CUDA graph)."""
+        self._step(x_host, ids_host, out_host, chain, streaming=False)
+
+    def run_stream(self, x_host: torch.Tensor, ids_host: Optional[torch.Tensor], out_host: torch.Tensor,
+                   chain: bool = False) -> None:
+        """A step of a STREAM of steps: nothing joins at the step boundary, so the copy-in of the next step's first micro-batch
+        runs under this step's last kernels and this step's last copy-out under the next step's first kernels — the slots'
+        events carry over from call to call.  The host buffers must be ready when the call is made (they are read by the copy
+        engine, not ordered behind work on the caller's stream) and ``out_host`` is complete only after :meth:`drain`.  Not for
+        CUDA-graph capture (use :meth:`run`)."""
+        self._step(x_host, ids_host, out_host, chain, streaming=True)
+
+    def drain(self) -> None:
+        """The caller's stream waits for every copy issued so far."""
+        with torch.cuda.device(self.device):
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_stream(self.h2d)
+            cur.wait_stream(self.d2h)
+
+    def _step(self, x_host, ids_host, out_host, chain, streaming) -> None:
         n = x_host.shape[0]
         if n > self.max_tokens:
             raise ValueError(f"{n} tokens exceed the pipeline's capacity of {self.max_tokens}")
@@ -291,27 +313,27 @@ class HostStepPipeline:
             raise ValueError("micro-batch larger than the pipeline's buffers")
         with torch.cuda.device(self.device):
             cur = torch.cuda.current_stream(self.device)
-            self.h2d.wait_stream(cur)
-            self.d2h.wait_stream(cur)
-            computed, copied_out = [], []
-            c = -1
+            if not streaming:
+                self.h2d.wait_stream(cur)
+                self.d2h.wait_stream(cur)
+                self._computed, self._copied, self._seq = [None, None], [None, None], 0
             for lo, hi in cuts:
                 m = hi - lo
                 if m == 0:
                     continue
-                c += 1
-                s = c & 1
+                s = self._seq & 1
+                self._seq += 1
                 with torch.cuda.stream(self.h2d):
-                    if c >= 2:
-                        self.h2d.wait_event(computed[c - 2])          # the kernels of micro-batch c-2 have read this slot
+                    if self._computed[s] is not None:
+                        self.h2d.wait_event(self._computed[s])        # the kernels that last read this slot are done
                     self.x[s][:m].copy_(x_host[lo:hi], non_blocking=True)
                     if ids_host is not None:
                         self.ids[s][:m].copy_(ids_host[lo:hi], non_blocking=True)
                     arrived = torch.cuda.Event()
                     arrived.record(self.h2d)
                 cur.wait_event(arrived)
-                if c >= 2:
-                    cur.wait_event(copied_out[c - 2])                 # its output buffers have left for the host
+                if self._copied[s] is not None:
+                    cur.wait_event(self._copied[s])                   # this slot's output buffers have left for the host
                 src = self.x[s][:m]
                 ids = self.ids[s][:m] if ids_host is not None else None
                 last = None
@@ -322,12 +344,14 @@ class HostStepPipeline:
                         src = last
                 ev = torch.cuda.Event()
                 ev.record(cur)
-                computed.append(ev)
+                self._computed[s] = ev
                 with torch.cuda.stream(self.d2h):
                     self.d2h.wait_event(ev)
                     out_host[lo:hi].copy_(last, non_blocking=True)
                     ev2 = torch.cuda.Event()
                     ev2.record(self.d2h)
-                    copied_out.append(ev2)
-            cur.wait_stream(self.h2d)
-            cur.wait_stream(self.d2h)
+                    self._copied[s] = ev2
+            if not streaming:
+                cur.wait_stream(self.h2d)
+                cur.wait_stream(self.d2h)
+                self._computed, self._copied, self._seq = [None, None], [None, None], 0
