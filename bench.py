@@ -417,7 +417,10 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
     # the engine step with HOST buffers: micro-batched so that the PCIe copies run under the kernels (HostStepPipeline);
     # small batches are one micro-batch = copy in, L forwards, copy out
     from vllm_i64.kernels.block import HostStepPipeline
-    e2e_chunks = E2E_CHUNKS or (E2E_DEFAULT_LARGE if N >= 32768 else (2 if N >= 8192 else 1))
+    # streamed steps overlap ACROSS steps (the next step's copy-in under this step's kernels), so the whole step per slot is
+    # best: 64K bf16 3.82 / 3.95 / 4.07 ms for 1 / 2 / 3 micro-batches, W8A8 16K 0.95 / 1.22 / 1.36 (profiles/r3l_*);
+    # isolated steps (--e2e-isolated) need micro-batches inside the step to overlap anything
+    e2e_chunks = E2E_CHUNKS or (1 if E2E_STREAM else (E2E_DEFAULT_LARGE if N >= 32768 else (2 if N >= 8192 else 1)))
     pipe = HostStepPipeline(layers, N, chunks=e2e_chunks)
     e2e_chunks = pipe.chunks if not isinstance(e2e_chunks, int) else e2e_chunks
 
@@ -863,7 +866,7 @@ def main():
     ap.add_argument("--ep-transport", default="bf16", choices=["f32", "bf16"],
                     help="dtype the expert outputs travel back in (bf16: the reference's EP semantics; f32: bit-identical to one GPU)")
     ap.add_argument("--e2e-chunks", type=lambda v: int(v) if "," not in v else tuple(float(t) for t in v.split(",")), default=0,
-                    help="N = 1: micro-batches of the end-to-end step: a count or relative sizes a,b,c (0 = 1,2,3,4,3,2,1 from 32K tokens, 2 from 8K, else 1)")
+                    help="N = 1: micro-batches of the end-to-end step: a count or relative sizes a,b,c (0 = 1 when the steps stream; with --e2e-isolated 1,2,3,4,3,2,1 from 32K tokens, 2 from 8K, else 1)")
     ap.add_argument("--e2e-isolated", action="store_true",
                     help="N = 1: time the end-to-end step as isolated CUDA-graph replays (no overlap between consecutive steps)")
     ap.add_argument("--ep-lanes", type=int, default=0,
