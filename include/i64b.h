@@ -81,6 +81,29 @@ int i64b_dispatch_plan(const int32_t* expert_ids, int top_k, int64_t n, int num_
                        int32_t* scatter_indices, int32_t* counts, int32_t* offsets, int32_t* dest_row,
                        int32_t* group_rows, void* workspace, size_t workspace_bytes, i64b_stream_t stream);
 
+/* The same plan, same kernels, same five outputs (each nullable) as i64b_dispatch_plan, for callers that cannot supply a
+ * workspace.  Nothing in the reference corresponds to this entry point; it exists for two kinds of host:
+ *   - a serving process that gave every free byte of HBM to its KV-cache pool at start-up, where a cudaMalloc issued
+ *     while serving fails (or stalls all streams of the device while it is mapped);
+ *   - an FFI host that only receives device pointers from elsewhere and binds no device allocator.
+ * The scratch is an array compiled into the library (device global memory, I64B_DISPATCH_PLAN_STATIC_BYTES per GPU that
+ * loads libi64b.so, held until the process exits).  The call performs no cudaMalloc / cudaFree and uses no allocating
+ * library routine; inputs and outputs remain the caller's.
+ *   Limit: i64b_plan_workspace_bytes(n, top_k, num_experts) <= I64B_DISPATCH_PLAN_STATIC_BYTES (about 250 000
+ *     (token, route) assignments); anything larger returns I64B_ERR_WORKSPACE with the two sizes in i64b_last_error().
+ *   First call on each device: looks the array's device address up (cudaGetSymbolAddress, with the caller's current
+ *     device) and remembers it.  Make that first call during set-up, with the right device current and before any
+ *     stream capture begins on that device; later calls only launch kernels.
+ *   Sharing: there is ONE array per device and every call uses it from offset 0.  Calls on the same stream are ordered
+ *     and safe.  Calls that can overlap on the GPU (different streams without an event between them, or different
+ *     host threads on different streams) race on the scratch and produce garbage plans — serialise them, or use
+ *     i64b_dispatch_plan with one workspace per stream.  The array keeps whatever the last call wrote; the plan never
+ *     reads a word before writing it, so nothing is (or needs to be) cleared between calls. */
+#define I64B_DISPATCH_PLAN_STATIC_BYTES (1 << 20)
+int i64b_dispatch_plan_static(const int32_t* expert_ids, int top_k, int64_t n, int num_experts,
+                              int32_t* scatter_indices, int32_t* counts, int32_t* offsets, int32_t* dest_row,
+                              int32_t* group_rows, i64b_stream_t stream);
+
 /* out[dest[t], :] = x[t, :] for row_bytes-wide rows (row_bytes % 16 == 0).
  * Replaces i64_scatter_kernel (csrc/i64_router.cu:94-134), atomic_scatter / fused_route_scatter row copies. */
 int i64b_scatter_rows(const void* x, const int32_t* dest, void* out, int64_t n, int64_t row_bytes,

@@ -64,6 +64,7 @@ _SIGNATURES = {
     "i64b_route_table": (_I, [_P, _P, _P, _L, _I, _I, _I, _P]),
     "i64b_plan_workspace_bytes": (_Z, [_L, _I, _I]),
     "i64b_dispatch_plan": (_I, [_P, _I, _L, _I, _P, _P, _P, _P, _P, _P, _Z, _P]),
+    "i64b_dispatch_plan_static": (_I, [_P, _I, _L, _I, _P, _P, _P, _P, _P, _P]),     # scratch inside the library
     "i64b_scatter_rows": (_I, [_P, _P, _P, _L, _L, _P]),
     "i64b_gather_rows": (_I, [_P, _P, _P, _L, _L, _P]),
     "i64b_combine": (_I, [_P, _P, _P, _I, C.POINTER(_F), _F, _F, _P, _I, _L, _I, _P]),
