@@ -99,6 +99,21 @@ def _worker(rank, world, port, case, ret):
         out_planned = blk.forward(xl, il, torch.float32)
         torch.cuda.synchronize(dev)
         assert torch.equal(out, out_planned), "plan_ahead changes the result"
+        # a plan whose ids are rewritten in place afterwards (a static ids buffer), or that belongs to another engine step,
+        # must be dropped: the forward then plans for the ids it is given
+        stale = il.clone()
+        side.wait_stream(torch.cuda.current_stream(dev))
+        blk.plan_ahead(stale, side)                                     # also ordered after the previous forward's combine
+        torch.cuda.current_stream(dev).wait_stream(side)
+        stale.copy_(torch.flip(il, [0]))
+        out_flip = blk.forward(torch.flip(xl, [0]).contiguous(), stale, torch.float32)
+        torch.cuda.synchronize(dev)
+        assert torch.equal(out_flip, torch.flip(out, [0])), "a plan made for overwritten token ids was used"
+        side.wait_stream(torch.cuda.current_stream(dev))
+        blk.plan_ahead(il, side, step=7)
+        out_step = blk.forward(xl, il, torch.float32, step=8)
+        torch.cuda.synchronize(dev)
+        assert torch.equal(out, out_step) and blk._planned is None, "a plan of another step was kept"
         if case.get("nccl", False):
             out_nccl = blk.forward(xl, il, torch.float32, exchange="nccl")  # reference-style all_to_all_single exchange
             assert torch.equal(out, out_nccl), "peer-memory and NCCL exchanges disagree"

@@ -128,7 +128,7 @@ def ep_moe_forward(x: torch.Tensor, routes: torch.Tensor, num_experts: int,
 
 class _Lane:
     """One micro-batch pipeline of an EPTokenRoutedBlock: peer-mapped buffers + flags (ctx), workspaces, stream."""
-    __slots__ = ("ctx", "bases", "cap", "ws_plan", "ws_gemm", "shared_out", "stream", "dispatched")
+    __slots__ = ("ctx", "bases", "cap", "ws_plan", "ws_gemm", "shared_out", "stream", "dispatched", "consumed")
 
 
 class EPTokenRoutedBlock:
@@ -310,6 +310,7 @@ class EPTokenRoutedBlock:
                                    if self.shared is not None else None)
                 lane.stream = torch.cuda.Stream(self.device)
                 lane.dispatched = torch.cuda.Event()
+                lane.consumed = None            # recorded after each forward's combine: the last reader of the lane's plan
                 self._lanes.append(lane)
         self._cap_tokens = n_lane * lanes
         l0 = self._lanes[0]
@@ -339,11 +340,23 @@ class EPTokenRoutedBlock:
         self._bases = None
         self._cap_tokens = 0
 
-    def plan_ahead(self, token_ids: torch.Tensor, stream: Optional[torch.cuda.Stream] = None) -> None:
+    def plan_ahead(self, token_ids: torch.Tensor, stream: Optional[torch.cuda.Stream] = None,
+                   step: Optional[int] = None) -> None:
         """Compute this layer's dispatch plan for ``token_ids`` now, on ``stream`` (default: the current one), ahead of
         the ``forward`` that will use it.  Routing depends on the token ids only, so an engine can plan every layer of
         a step on a side stream while earlier layers run (include/i64b.h, i64b_ep_plan); the next ``forward`` with the
-        SAME ``token_ids`` tensor waits for the plan and only moves rows.  Single-lane path only (a no-op otherwise)."""
+        SAME ``token_ids`` tensor waits for the plan and only moves rows.  Single-lane path only (a no-op otherwise).
+
+        Ordering: the plan overwrites the lane's plan workspace, which this layer's PREVIOUS forward reads up to its
+        combine; ``stream`` is therefore made to wait for that combine here (no caller-side wait needed for that).  The
+        ids themselves must be complete on ``stream`` — if another stream writes them, the caller orders that.
+
+        Validity: the plan is used by the next forward only if that forward brings the same memory (this call keeps a
+        reference to ``token_ids``, so the allocator cannot hand the address to another tensor meanwhile), the same
+        count, an unchanged in-place version (``copy_`` / ``fill_`` into a static ids buffer after this call discard the
+        plan) and the same ``step``.  ``step`` is the caller's generation token (engine step number): pass it to both
+        calls when the ids buffer is written by something PyTorch's version counter does not see (a raw kernel, a graph
+        replay, ``.data``).  Any mismatch drops the plan and the forward plans for itself."""
         import ctypes as C
         from vllm_i64 import _C
         n = token_ids.numel()
@@ -359,14 +372,16 @@ class EPTokenRoutedBlock:
         lane.ctx.n_local = n
         with torch.cuda.device(self.device):
             s = stream or torch.cuda.current_stream(self.device)
+            if lane.consumed is not None:
+                s.wait_event(lane.consumed)         # the previous forward of this layer has finished reading its plan
             _C.check(_C.lib().i64b_ep_plan(C.byref(lane.ctx), token_ids.data_ptr(), self._table.data_ptr(),
                                            lane.ws_plan.data_ptr(), lane.ws_plan.numel(), s.cuda_stream))
             ev = torch.cuda.Event()
             ev.record(s)
-        self._planned = (token_ids.data_ptr(), n, ev)
+        self._planned = (token_ids, n, token_ids._version, step, ev)
 
     def forward_peer(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
-                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                     out: Optional[torch.Tensor] = None, step: Optional[int] = None) -> torch.Tensor:
         """One expert-parallel forward over NVLink peer memory: no host synchronisation and no collective call
         (graph-capturable once ``reserve`` has run).  See include/i64b.h (expert parallelism)."""
         import ctypes as C
@@ -412,9 +427,12 @@ class EPTokenRoutedBlock:
             lane.ctx.comm_ctas = self._comm_dispatch
             ids_ptr = token_ids.data_ptr()
             planned, self._planned = self._planned, None
-            if planned is not None and planned[0] == ids_ptr and planned[1] == n and n > 0:
-                cur.wait_event(planned[2])                 # plan_ahead made the plan: rows only
+            if (planned is not None and n > 0 and planned[0].data_ptr() == ids_ptr and planned[1] == n
+                    and planned[2] == token_ids._version and planned[3] == step):
+                cur.wait_event(planned[4])                 # plan_ahead made the plan: rows only
                 ids_ptr = None
+            elif planned is not None:
+                cur.wait_event(planned[4])                 # stale plan: let it finish writing the workspace, then plan afresh
             _C.check(lib.i64b_ep_dispatch(ctx, x.data_ptr(), ids_ptr, self._table.data_ptr(),
                                           lane.ws_plan.data_ptr(), lane.ws_plan.numel(), st))
             mark("plan+dispatch")
@@ -432,6 +450,10 @@ class EPTokenRoutedBlock:
             _C.check(lib.i64b_ep_combine(ctx, lane.ws_plan.data_ptr(), _C.ptr(shared), wts, self.rs, self.ss,
                                          out.data_ptr(), _C.dtype_code(out), st))
             mark("combine (pull)")
+            if not torch.cuda.is_current_stream_capturing():
+                if lane.consumed is None:
+                    lane.consumed = torch.cuda.Event()
+                lane.consumed.record(cur)                  # plan_ahead for this layer's next step waits on this
         return out
 
     def _forward_lanes(self, x, token_ids, out, wts, cur) -> torch.Tensor:
@@ -479,11 +501,11 @@ class EPTokenRoutedBlock:
         return out
 
     def forward(self, x: torch.Tensor, token_ids: torch.Tensor, out_dtype=torch.bfloat16,
-                exchange: str = "peer", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                exchange: str = "peer", out: Optional[torch.Tensor] = None, step: Optional[int] = None) -> torch.Tensor:
         """``exchange="peer"``: NVLink peer-memory path (default).  ``"nccl"``: all_to_all_single exchange with
         host-side split sizes, the reference's scheme — kept as the comparison baseline (bench.py reports both)."""
         if exchange == "peer":
-            return self.forward_peer(x, token_ids, out_dtype, out)
+            return self.forward_peer(x, token_ids, out_dtype, out, step)
         from vllm_i64 import _C
         n = x.shape[0]
         routes = self.route(token_ids)
