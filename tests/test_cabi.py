@@ -109,6 +109,16 @@ def test_host_layer_mirrors_reference_interface():
         ops.route_tokens(torch.arange(8), 4)
 
 
+def test_dense_int4_buffers_raise_instead_of_running_unquantised():
+    """``--quantization int4`` leaves gate_int4 ... buffers on the dense MLP (core/loader.py:685-697).  This build has no INT4
+    kernel: it must say so, not run the float weights as if nothing had been asked."""
+    from vllm_i64.layers.dense_mlp import DenseMLP
+    m = DenseMLP(128, 64)
+    m.register_buffer("gate_int4", torch.zeros(64, 64, dtype=torch.uint8))
+    with pytest.raises(NotImplementedError, match="INT4"):
+        m._ensure_block(torch.device("cpu"))
+
+
 def test_product_never_imports_the_oracle():
     pkg = os.path.join(ROOT, "vllm-i64_b200")
     for dirpath, _, files in os.walk(pkg):

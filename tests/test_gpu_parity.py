@@ -429,6 +429,31 @@ def test_dense_mlp_vs_reference(golden):
     np.testing.assert_array_equal(dm(cu(x16)).cpu().numpy(), O.w8a8_swiglu(x16, w13_q, w13_s, w2_q, w2_s).y)
 
 
+def test_dense_mlp_repacks_when_loader_buffers_change(golden):
+    """The reference loader's int8 buffers (core/loader.py:670-683) are what the W8A8 dense block is packed from: rewriting
+    or re-registering them must repack it."""
+    from vllm_i64.layers.dense_mlp import DenseMLP
+    d = golden("tiny_dense.npz")
+    dm = DenseMLP(128, 192)
+    dm.gate_proj.load_full_weight(torch.from_numpy(d["gate"]))
+    dm.up_proj.load_full_weight(torch.from_numpy(d["up"]))
+    dm.down_proj.load_full_weight(torch.from_numpy(d["down"]))
+    dm = dm.cuda()
+    x16 = Hh.bf16_round(d["x"])
+    w13_q, w13_s = O.quantize_rows_int8(np.concatenate([d["gate"], d["up"]], 0))
+    w2_q, w2_s = O.quantize_rows_int8(d["down"])
+    for name, val in (("gate_up_int8", w13_q), ("gate_up_scale", w13_s), ("down_int8", w2_q), ("down_scale", w2_s)):
+        dm.register_buffer(name, cu(val))
+    want = O.w8a8_swiglu(x16, w13_q, w13_s, w2_q, w2_s).y
+    np.testing.assert_array_equal(dm(cu(x16)).cpu().numpy(), want)
+    blk = dm._block
+    assert dm(cu(x16)) is not None and dm._block is blk                  # unchanged buffers: no repack
+    dm.down_int8.zero_()                                                 # rewritten in place
+    assert dm._block is blk and float(dm(cu(x16)).abs().max()) == 0.0 and dm._block is not blk
+    dm.register_buffer("down_int8", cu(w2_q))                            # re-registered
+    np.testing.assert_array_equal(dm(cu(x16)).cpu().numpy(), want)
+
+
 def test_kernels_package_vs_reference(golden):
     from vllm_i64.kernels import i64_ops, fused_experts
     g = golden("tiny_kernels.npz")
@@ -452,6 +477,28 @@ def test_kernels_package_vs_reference(golden):
     mx, mean = O.rel_errors(o8.cpu().numpy(), g["full_int8"])
     assert mx < 2e-2 and mean < 5e-3
     assert fused_experts.fused_token_routed_forward(x[:0], gu, dn, eid[:0].long(), 4, 32).shape[0] == 0
+
+
+def test_fused_experts_cache_hits_through_views_and_data(golden):
+    """The packed block is keyed on the weights' storage, not on the Python tensor object: ``param.data``, ``.detach()`` and
+    full slices of a live parameter reuse it; an in-place update or a freed storage does not."""
+    from vllm_i64.kernels import fused_experts as FE
+    g = golden("tiny_kernels.npz")
+    x, eid = cu(g["x"]), cu(g["expert_ids"]).long()
+    gu, dn = torch.nn.Parameter(cu(g["gate_up"]), requires_grad=False), torch.nn.Parameter(cu(g["down"]), requires_grad=False)
+    FE.invalidate_cache()
+    base = FE.fused_token_routed_forward(x, gu, dn, eid, 4, 32)
+    blk = FE._cached_block(gu, dn, 4)
+    assert len(FE._CACHE) == 1
+    for a, b in ((gu.data, dn.data), (gu.detach(), dn.detach()), (gu[:], dn[:])):
+        assert FE._cached_block(a, b, 4) is blk, "a view of the same weights repacked the block"
+        assert torch.equal(FE.fused_token_routed_forward(x, a, b, eid, 4, 32), base)
+    assert len(FE._CACHE) == 1
+    with torch.no_grad():
+        gu.mul_(0.5)                                       # version bump -> a new block, different numbers
+    assert FE._cached_block(gu, dn, 4) is not blk
+    assert not torch.equal(FE.fused_token_routed_forward(x, gu, dn, eid, 4, 32), base)
+    FE.invalidate_cache()
 
 
 def test_host_buffer_call_and_launch_count():

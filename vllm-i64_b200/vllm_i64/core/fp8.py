@@ -5,7 +5,8 @@ Semantics of the reference's GPU branch: weights quantised per out-row and activ
 tests/golden/tiny_fp8.npz), every projection ``y = (x_q . w_q^T) * (x_scale[:, None] * w_scale[None, :])`` with exact E4M3
 products and fp32 accumulation — the reference's ``torch._scaled_mm`` call becomes one tcgen05 ``kind::f8f6f4`` GEMM
 (``i64b_fp8_gemm``).  The reference's hardware ladder (``fp8_available()`` → INT8 on SM80 → dequantise + ``F.linear``
-elsewhere) is gone: CUDA tensors run the kernel, CPU tensors raise.
+elsewhere) is gone: CUDA tensors run the kernel; CPU tensors raise, except under the overlay (the reference package importable beside this one), where
+the load-time and host-tensor calls are handed to the reference's own module.
 """
 from __future__ import annotations
 
@@ -85,6 +86,8 @@ def fp8_linear(x: torch.Tensor, weight_fp8: torch.Tensor, weight_scale: torch.Te
                bias: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``y = x @ Wᵀ`` in FP8 (core/fp8.py:137-193): quantise the activations per token, one scaled GEMM, output in the
     dtype of ``x`` (fp16 for non-float inputs, as the reference)."""
+    if not x.is_cuda and _REF_MOD is not None:
+        return _REF_MOD.fp8_linear(x, weight_fp8, weight_scale, bias)      # host tensors: the reference's dequantise + F.linear
     orig = x.shape
     x2 = x.reshape(-1, orig[-1])
     xq, xs = quantize_activations_fp8(x2)
@@ -97,6 +100,8 @@ def fp8_linear(x: torch.Tensor, weight_fp8: torch.Tensor, weight_scale: torch.Te
 def fp8_fused_gate_up(x: torch.Tensor, fused_fp8: torch.Tensor, fused_scale: torch.Tensor, inter_size: int
                       ) -> Tuple[torch.Tensor, torch.Tensor]:
     """One activation quantisation + one FP8 GEMM for ``cat([gate, up])`` (core/fp8.py:196-245)."""
+    if not x.is_cuda and _REF_MOD is not None:
+        return _REF_MOD.fp8_fused_gate_up(x, fused_fp8, fused_scale, inter_size)
     res = fp8_linear(x, fused_fp8, fused_scale)
     gate, up = res.split(inter_size, dim=-1)
     return gate, up

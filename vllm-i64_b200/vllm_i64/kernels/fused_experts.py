@@ -19,17 +19,22 @@ _CACHE_MAX = 64
 
 
 def _key(*tensors: torch.Tensor) -> Tuple:
-    return tuple((t.data_ptr(), t._version, tuple(t.shape), t.dtype) for t in tensors)
+    """What the packed block was made from: the bytes' location (storage address + offset + shape + strides), their type
+    and the in-place version.  Views, slices, ``.detach()`` and ``.data`` of a live parameter describe the same bytes and
+    give the same key, although each access creates a new Python tensor object."""
+    return tuple((t.untyped_storage().data_ptr(), t.storage_offset(), tuple(t.shape), tuple(t.stride()), t.dtype,
+                  t._version) for t in tensors)
 
 
 def _lookup(key: Tuple, tensors) -> "I64Block | None":
-    """A hit needs the SAME tensor objects to be alive: an address alone may have been recycled by the allocator for
-    another tensor after the original was freed (the entry holds weak references to its key tensors)."""
+    """A hit needs the SAME storages to be alive: an address alone may have been recycled by the allocator after the
+    original weights were freed, so the entry holds a weak reference to each storage (the storage object lives as long as
+    any tensor uses it, whichever Python object that is)."""
     ent = _CACHE.get(key)
     if ent is None:
         return None
     blk, refs = ent
-    if all(r() is t for r, t in zip(refs, tensors)):
+    if all(r() is t.untyped_storage() for r, t in zip(refs, tensors)):
         return blk
     del _CACHE[key]
     return None
@@ -39,11 +44,13 @@ def _store(key: Tuple, tensors, blk: I64Block) -> None:
     import weakref
     if len(_CACHE) >= _CACHE_MAX:
         _CACHE.clear()
-    _CACHE[key] = (blk, tuple(weakref.ref(t) for t in tensors))
+    _CACHE[key] = (blk, tuple(weakref.ref(t.untyped_storage()) for t in tensors))
 
 
 def invalidate_cache() -> None:
-    """Drop every packed block (call after rewriting weight tensors through ``.data``, which ``_version`` cannot see)."""
+    """Drop every packed block.  Call it after rewriting weights in a way the key cannot see: writes through ``.data``,
+    and any in-place update of a parameter whose ``.data`` (which has no version counter of its own) is what the caller
+    passes to the functions below.  Slices and ``.detach()`` share the parameter's counter and need nothing."""
     _CACHE.clear()
 
 

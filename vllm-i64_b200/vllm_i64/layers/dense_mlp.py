@@ -36,8 +36,20 @@ class _DenseBlockMixin(torch_ops.TracedLayer):
             self.quantization = "fp8"
         elif ref_int8:
             self.quantization = "int8"
+        if getattr(self, "gate_int4", None) is not None:
+            # buffers of _quantize_dense_mlp(model, "int4") (core/loader.py:685-697): there is no INT4 kernel in this build, and
+            # running the float weights instead would silently ignore the quantisation the user asked for
+            raise NotImplementedError(
+                "vllm_i64 (B200 build): INT4 dense MLP buffers (gate_int4 ...) are present but this build has no INT4 "
+                "kernel; load with --quantization int8 or fp8, or without quantisation")
+        # the packed block is made from the reference loader's quantised buffers when they exist: they are part of the key, so
+        # re-registering or rewriting them repacks
+        qnames = (("gate_fp8", "gate_fp8_scale", "up_fp8", "up_fp8_scale", "down_fp8", "down_fp8_scale") if ref_fp8 else
+                  ("gate_up_int8", "gate_up_scale", "down_int8", "down_scale") if ref_int8 else ())
+        qbufs = tuple(getattr(self, n, None) for n in qnames)
         key = (device, self.quantization, tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in (gate, up, down)),
-               tuple(id(p) for p in self.parameters()))
+               tuple(id(p) for p in self.parameters()),
+               tuple((n, b.data_ptr(), b._version, tuple(b.shape)) for n, b in zip(qnames, qbufs) if b is not None))
         if self._block is not None and self._block_key == key:
             return self._block
         inter, hidden = gate.shape
