@@ -319,7 +319,12 @@ enum {
                                      combine_kernel) even when the scales are powers of two and the single-accumulator
                                      form (scales folded into the SwiGLU rows, one sum over K = 2*I_e + S) would be taken */
 };
-/* auto selection of the fused down projection: at least this many tokens per unordered expert pair, E(E-1)/2 pairs */
+/* auto selection of the fused down projection: at least this many tokens per unordered expert pair, E(E-1)/2 pairs.
+ * Batch invariance: the choice depends on n, and the single-accumulator form sums a token's three contributions in one
+ * fp32 accumulation where every other form rounds three partial sums — so with power-of-two scales the low bf16 bit of a
+ * token's output can differ between a batch below and a batch above I64B_TRI_MIN_ROWS_ONEACC rows per pair (<= 1 bf16 ulp,
+ * <= 2e-5 of max|out| in fp32).  A caller that needs the same bits for a token whatever batch it arrives in sets
+ * I64B_DEBUG_TRI_FOLD (or env I64B_TRI_ONEACC=0): all remaining forms are bit-identical to one another. */
 #define I64B_TRI_MIN_ROWS_ONEACC 288
 #define I64B_TRI_MIN_ROWS_FOLD 512
 int i64b_moe_set_debug(i64b_layer* layer, int flags);

@@ -68,6 +68,8 @@ struct i64b_layer {
     int64_t cached_x_n = -1;
     CUtensorMap tm_x;
     CUtensorMap tm_xg;          // the same x with a one-row box (tile::gather4 source of GEMM1's routed rows)
+    const void* cached_xg = nullptr;   // tm_xg has its own validity: it is encoded only when the opt-in gather path is taken
+    int64_t cached_xg_n = -1;
     // carve of the last forward (debug taps)
     struct Carve {
         I64bPlanWs plan;
@@ -623,11 +625,6 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     if (shared_from_x && (L->cached_x != x || L->cached_x_n != n)) {
         int rcx = i64b_encode_tmap(&L->tm_x, x, preq, n, H, (int64_t)H * L->elt, 128);
         if (rcx) return rcx;
-        if (!q8) {
-            static const int gbox = env_int("I64B_GATHER_BOX", 1);
-            rcx = i64b_encode_tmap(&L->tm_xg, x, false, n, H, (int64_t)H * 2, gbox);
-            if (rcx) return rcx;
-        }
         L->cached_x = x;
         L->cached_x_n = n;
     }
@@ -669,6 +666,13 @@ static int moe_forward_impl(i64b_layer* L, const void* x, const int64_t* token_i
     if (gather) {
         da.phase = 1;
         da.src_tok_out = cv.src_tok;
+        if (L->cached_xg != x || L->cached_xg_n != n) {     // not tied to cached_x: the fused decode branch sets that one too
+            static const int gbox = env_int("I64B_GATHER_BOX", 1);
+            int rcx = i64b_encode_tmap(&L->tm_xg, x, false, n, H, (int64_t)H * 2, gbox);
+            if (rcx) return rcx;
+            L->cached_xg = x;
+            L->cached_xg_n = n;
+        }
     }
     // prefill-sized bf16 blocks with a shared expert: the row copies leave the main stream (see overlap_enabled())
     static const int overlap_min = env_int("I64B_OVERLAP_MIN_TOKENS", 4096);
