@@ -106,3 +106,14 @@ def test_streaming_steps_equal_one_shot(chunks):
     pipe.run(steps[0][0], steps[0][1], steps[0][2])
     torch.cuda.synchronize()
     assert torch.equal(steps[0][2], want[0])
+    # ... also when the streamed steps were NOT drained first: run() orders itself behind their copy-outs, which still read the
+    # slots' output buffers, instead of overwriting them
+    for _ in range(3):
+        for _, _, ok in steps:
+            ok.zero_()
+        for xk, ik, ok in steps[:3]:
+            pipe.run_stream(xk, ik, ok)
+        pipe.run(steps[3][0], steps[3][1], steps[3][2])
+        torch.cuda.synchronize()
+        for (_, _, ok), w in zip(steps, want):
+            assert torch.equal(ok, w), "run() after undrained run_stream()"

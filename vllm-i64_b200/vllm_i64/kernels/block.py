@@ -314,6 +314,11 @@ class HostStepPipeline:
         with torch.cuda.device(self.device):
             cur = torch.cuda.current_stream(self.device)
             if not streaming:
+                # steps streamed before this one and never drained: their last copy-outs may still be reading the slots'
+                # output buffers (and their kernels the input slots) — order this step behind them before forgetting the events
+                for ev in (*self._copied, *self._computed):
+                    if ev is not None:
+                        cur.wait_event(ev)
                 self.h2d.wait_stream(cur)
                 self.d2h.wait_stream(cur)
                 self._computed, self._copied, self._seq = [None, None], [None, None], 0
