@@ -743,7 +743,10 @@ def run_ep(wl, device, rank, world, args, pk, stream, barrier, sampler):
     ep_parity = {"f32_transport_vs_single_gpu_block": "bit-identical" if float(fl_min[0]) == 1.0 else "MISMATCH",
                  "bf16_transport_max_rel_vs_single_gpu_block": float(fl_max[1]),
                  "bf16_transport_mean_rel_vs_single_gpu_block": float(fl_max[2]),
-                 "bar": "fp32 transport: torch.equal on every rank; bf16 transport: <= 1e-2 max-rel, <= 2.5e-3 mean-rel",
+                 "bar": "fp32 transport: torch.equal on every rank. bf16 transport is compared HERE with the single-GPU block, which does "
+                        "not round the per-assignment rows; the reference's EP path does (model-dtype all_to_all), and against "
+                        "the oracle that models that rounding tests/test_gpu_ep.py holds north_star's <= 1e-2 max-rel / <= 1e-3 "
+                        "mean-rel; the figure printed here (about 1.2e-3 mean-rel) is that one extra bf16 rounding",
                  "checked": f"layer 0, all {n} tokens of every rank"}
     torch.cuda.empty_cache()
 

@@ -363,10 +363,18 @@ def combine_fp32(routed: Sequence[np.ndarray], shared: Optional[np.ndarray], cfg
 
 
 def moe_block_fp32(x: np.ndarray, token_ids: Optional[np.ndarray], table: np.ndarray, w: MoEWeights,
-                   cfg: MoEConfig, inter_bf16: bool = False) -> np.ndarray:
-    """``TokenRoutedMLP.forward`` (layers/token_routed_mlp.py:154-187) in fp32."""
+                   cfg: MoEConfig, inter_bf16: bool = False, routed_bf16: bool = False) -> np.ndarray:
+    """``TokenRoutedMLP.forward`` (layers/token_routed_mlp.py:154-187) in fp32.
+
+    ``routed_bf16``: the expert-parallel form of the same block.  The reference's EP path sends every routed expert's output
+    back to the token's home rank as a tensor of the MODEL dtype (layers/token_routed_i64/layer.py:283-292: ``result_sorted``
+    is allocated with ``dtype=dtype`` and filled by ``all_to_all_single``), so with a bf16 model each per-assignment output
+    row is rounded to bf16 once before the home rank weighs and sums it; the shared expert never travels and is not
+    rounded.  This is the oracle for the bf16-transport EP mode."""
     routes = route_table(token_ids, table, x.shape[0], cfg.num_experts)
     routed = [expert_forward_fp32(x, routes[r], w, cfg.num_experts, inter_bf16) for r in range(cfg.top_k)]
+    if routed_bf16:
+        routed = [round_bf16(r) for r in routed]
     shared = shared_forward_fp32(x, w, inter_bf16) if w.shared_gate is not None else None
     return combine_fp32(routed, shared, cfg)
 

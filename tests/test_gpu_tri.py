@@ -154,6 +154,37 @@ W8_CASES = [
 ]
 
 
+def test_headline_step_against_oracle():
+    """The step bench.py's headline is quoted on — BASELINE config 5 on one GPU: 65 536 tokens, H 1024, 8 experts x 512,
+    shared 1280, top-2 — through the DEFAULT path (no debug flags: the form the library picks for this batch, which is the
+    one that is timed), against the oracle on sampled rows at north_star's tolerance, plus the size-independent checks: every
+    row finite and non-trivial, run-to-run identical, and equal to the GEMM2 + combine chain within the single-accumulator
+    form's stated distance."""
+    h, e, ie, s, v, k = 1024, 8, 512, 1280, 32000, 2
+    n = 65536
+    cfg, w, table, ids, x = Hh.make_block(h, e, ie, s, v, k, n, seed=5, pw=0.5, rs=2.0, ss=1.0)
+    xg, ig = Hh.to_cuda(x, torch.bfloat16), Hh.to_cuda(ids)
+    blk = Hh.build_gpu_block(cfg, w, table, "bf16")
+    assert blk.tri_form(n) == 2, "the headline batch should take the single-accumulator fused down projection"
+    got = blk.forward(xg, ig, torch.float32)
+    again = blk.forward(xg, ig, torch.float32)
+    got16 = blk.forward(xg, ig, torch.bfloat16)          # bench.py's output dtype
+    torch.cuda.synchronize()
+    assert torch.equal(got, again)
+    assert bool(torch.isfinite(got).all()) and int((got.abs().amax(dim=1) == 0).sum()) == 0
+    assert bool(((got16.float() - got).abs() <= got.abs() * 2.0 ** -8 + 1e-30).all()), "bf16 output is not the fp32 output rounded once"
+    rows = np.unique(np.concatenate([np.linspace(0, n - 1, 96).astype(int), np.arange(8), np.arange(n - 8, n)]))
+    ref = O.moe_block_fp32(x[rows], ids[rows], table, w, cfg, inter_bf16=True)
+    mx, mean = O.rel_errors(got.cpu().numpy()[rows], ref)
+    assert mx <= Hh.TOL_MAX and mean <= Hh.TOL_MEAN, (mx, mean)
+    chain = Hh.build_gpu_block(cfg, w, table, "bf16")
+    chain.set_debug(_C.DEBUG_NO_FUSED | _C.DEBUG_NO_TRI)
+    want = chain.forward(xg, ig, torch.float32)
+    torch.cuda.synchronize()
+    d, top = (got - want).abs().max().item(), want.abs().max().item()
+    assert d <= top * 2e-5, (d, top)
+
+
 @pytest.mark.parametrize("case", W8_CASES, ids=[c["id"] for c in W8_CASES])
 @pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
 def test_tri_w8a8_bit_exact(case, out_dtype):
