@@ -119,6 +119,26 @@ def test_dense_int4_buffers_raise_instead_of_running_unquantised():
         m._ensure_block(torch.device("cpu"))
 
 
+def test_overlay_int4_functions_refuse_cuda_tensors():
+    """Reference functions taken over by the overlay with ``int4`` in their name run on host tensors (load-time packing) and
+    raise on CUDA tensors: no PyTorch fallback stands in for a kernel this build does not have."""
+    from vllm_i64 import _overlay
+
+    class T:
+        def __init__(self, cuda):
+            self.is_cuda = cuda
+
+    g = _overlay._guard_int4("kernels.fused_experts.fused_token_routed_forward_int4", lambda x, scale=None: "ran")
+    assert g(T(False), scale=T(False)) == "ran"
+    with pytest.raises(NotImplementedError, match="int4"):
+        g(T(True))
+    with pytest.raises(NotImplementedError):
+        g(T(False), scale=T(True))
+    from vllm_i64.kernels import fused_experts
+    if _overlay.load_reference_module("vllm_i64.kernels.fused_experts") is not None:     # overlay active (build container)
+        assert fused_experts.fused_token_routed_forward_int4.__wrapped__ is not None
+
+
 def test_product_never_imports_the_oracle():
     pkg = os.path.join(ROOT, "vllm-i64_b200")
     for dirpath, _, files in os.walk(pkg):

@@ -92,14 +92,35 @@ def load_reference_module(mod_name: str):
     return mod
 
 
+def _guard_int4(name: str, fn):
+    """The reference's INT4 functions (group-128 experts, ``int4_linear`` ...) have no sm_100a kernel in this build.  Taken over
+    as they are they would run the reference's PyTorch code on the GPU — a fallback nobody asked for.  They stay usable on
+    host tensors (load-time packing) and refuse CUDA tensors."""
+    import functools
+
+    @functools.wraps(fn)
+    def guarded(*args, **kwargs):
+        for t in (*args, *kwargs.values()):
+            if getattr(t, "is_cuda", False):
+                raise NotImplementedError(
+                    f"vllm_i64 (B200 build): {name} has no sm_100a kernel; the reference's PyTorch INT4 path is not run in its "
+                    "place on CUDA tensors.  Use --quantization int8 or fp8, or no quantisation")
+        return fn(*args, **kwargs)
+    return guarded
+
+
 def fill(mod_name: str, mod_globals: dict):
-    """Copy the reference module's public names that ``mod_name`` does not define.  Returns the reference module (or None)."""
+    """Copy the reference module's public names that ``mod_name`` does not define.  Returns the reference module (or None).
+    Functions with ``int4`` in their name are wrapped by :func:`_guard_int4`."""
+    import types
     ref = load_reference_module(mod_name)
     if ref is None:
         return None
     for k, v in vars(ref).items():
         if k.startswith("__") or k in mod_globals:
             continue
+        if isinstance(v, types.FunctionType) and "int4" in k.lower():
+            v = _guard_int4(f"{mod_name}.{k}", v)
         mod_globals[k] = v
     return ref
 
