@@ -105,3 +105,14 @@ def fused_token_routed_forward_int8(x: torch.Tensor, gate_up_int8: torch.Tensor,
     out = blk.forward_routed(x, expert_ids.view(1, -1), [1.0], 1.0, 1.0, False,
                              torch.bfloat16 if x.dtype == torch.bfloat16 else torch.float32)
     return out if out.dtype == x.dtype else out.to(x.dtype)
+
+
+def fused_token_routed_forward_int4(x: torch.Tensor, gate_up_int4: torch.Tensor, gate_up_scale: torch.Tensor,
+                                    gate_up_zero: torch.Tensor, down_int4: torch.Tensor, down_scale: torch.Tensor,
+                                    down_zero: torch.Tensor, expert_ids: torch.Tensor, num_experts: int,
+                                    intermediate_per_tp: int, *args, **kwargs) -> torch.Tensor:
+    """Group-128 INT4 experts (kernels/fused_experts.py:294-476 of the reference): NOT built for sm_100a.  The name exists so
+    that a caller gets this message rather than an ImportError or, worse, a silent PyTorch stand-in."""
+    raise NotImplementedError(
+        "vllm_i64 (B200 build): fused_token_routed_forward_int4 has no sm_100a kernel; use the INT8 (weight-only or W8A8) or FP8 "
+        "experts, or no quantisation")
