@@ -313,6 +313,37 @@ def time_graph(run, steps, warmup, stream, barrier=None, sampler=None):
     return e0.elapsed_time(e1)
 
 
+def time_graph_each(run, steps, stream):
+    """Per-step device times (ms) of `steps` single replays of `run`, each bracketed by its own CUDA events on the launching
+    stream: the spread (median, p10, p90) SURVEY 8(d) asks for next to the mean of the back-to-back run."""
+    with torch.cuda.stream(stream):
+        run()
+    stream.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=stream):
+        run()
+    evs = []
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            g.replay()
+        stream.synchronize()
+        for _ in range(steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            g.replay()
+            e1.record(stream)
+            evs.append((e0, e1))
+        stream.synchronize()
+    del g
+    return sorted(a.elapsed_time(b) for a, b in evs)
+
+
+def _spread(ts):
+    pick = lambda q: ts[min(len(ts) - 1, max(0, int(round(q * (len(ts) - 1)))))]
+    return {"median": pick(0.5), "p10": pick(0.1), "p90": pick(0.9), "n": len(ts), "unit": "ms per step",
+            "how": "single graph replays, one CUDA-event pair each (includes the replay's launch gap, unlike ms_per_step)"}
+
+
 def time_stream(step, drain, steps, warmup, stream, barrier=None):
     """Back-to-back eager steps of a streaming pipeline (nothing joins between steps), drained once at the end; CUDA events
     on the launching stream around the whole run."""
@@ -447,6 +478,23 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
     launches_per_step = _C.launch_count()
 
     ms = time_graph(step_device, steps, warmup, stream, barrier, sampler)
+    spread = _spread(time_graph_each(step_device, max(5, min(steps, 30)), stream))
+    zipf = None
+    if wl["E"]:
+        # uniform ids (U, the value above) AND Zipf(1.1) ids (Z): a few very frequent tokens, so the experts their
+        # table entries name get most of the rows (uneven GEMM groups); same step, same weights
+        rs = np.random.RandomState(4321 + rank)
+        ranks_z = rs.zipf(1.1, size=N).astype(np.int64)
+        ids_z = torch.from_numpy(np.random.RandomState(7).permutation(wl["V"])[(ranks_z - 1) % wl["V"]]).to(device)
+
+        def step_device_zipf():
+            for i, blk in enumerate(layers):
+                blk.forward(x_dev, ids_z, torch.bfloat16, out=outs[i & 1])
+        z_steps = max(3, min(steps, 20))
+        ms_z = time_graph(step_device_zipf, z_steps, 3, stream, barrier)
+        top = torch.bincount(ids_z, minlength=1).max().item() / N
+        zipf = {"value": N * L * z_steps / (ms_z * 1e-3), "unit": UNIT, "ms_per_step": ms_z / z_steps, "steps": z_steps,
+                "ids": "Zipf(1.1) ranks over a fixed permutation of the vocabulary", "most_frequent_token_share": round(top, 4)}
     e2e_steps = max(3, min(steps, 50))
     # steps follow one another as in an engine loop: the next step's first copy-in runs under this step's last kernels
     # (run_stream); every step's H2D and D2H are inside the timed region, which ends when the last copy-out has landed
@@ -464,7 +512,7 @@ def measure_workload(name, wl, device, steps, warmup, pk, int8_peak, stream, ran
     us_layer = ms * 1e3 / (steps * L)
     res = {"desc": wl["desc"], "value": N * L * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
            "us_per_layer": round(us_layer, 3), "steps": steps, "dtype": {"bf16": "bf16", "int8": "int8", "fp8": "fp8_e4m3"}[wl["mode"]],
-           "gpu_launches_per_step": int(launches_per_step),
+           "gpu_launches_per_step": int(launches_per_step), "step_ms": spread, "zipf_ids": zipf,
            "e2e": {"value": N * L * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / e2e_steps,
                    "h2d_bytes_per_step": N * H * 2 + (N * 8 if wl["E"] else 0), "d2h_bytes_per_step": N * H * 2,
                    "copies_per_step": e2e_chunks,
@@ -990,6 +1038,7 @@ def main():
             "scaling": "strong", "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic",
             "config": cfg_json(wl, 1),
             "clocks": sampler.summary(), "e2e": head["e2e"], "e2e_per_layer_host_call": head["e2e_per_layer_host_call"],
+            "step_ms": head.get("step_ms"), "zipf_ids": head.get("zipf_ids"),
             "gpu_launches": head["gpu_launches_per_step"] * args.steps, "gpu_launches_per_step": head["gpu_launches_per_step"],
             "roofline": head.get("roofline"), "block": head["block"], "stages": head.get("stages"),
             "measured_int8_peak": int8_peak, "cpu_baseline": cpu, "reference_gpu": ref_gpu, "workloads": workloads}
